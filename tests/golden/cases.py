@@ -1,0 +1,80 @@
+"""Seeded input recipes shared by ``make_golden.py`` (which runs the reference) and the
+parity tests (which run the oracle and the CUDA path).  No reference import here."""
+import torch
+
+from oracle import sd_oracle as O
+
+TIMESTEP_CASES = [0, 1, 7, 49, 500, 999]
+
+STEP_CASES = [0, 1, 49, 500, 999]
+STEP_NOISE_SEED = 1234
+STEP_SCALE = 0.9
+
+
+def _g(seed):
+    return torch.Generator().manual_seed(seed)
+
+
+def step_inputs(step, shape=(2, 4, 16, 16)):
+    g = _g(100 + step)
+    return torch.randn(shape, generator=g), torch.randn(shape, generator=g)
+
+
+def add_noise_inputs(shape=(5, 4, 8, 8)):
+    g = _g(77)
+    x0 = torch.randn(shape, generator=g)
+    nz = torch.randn(shape, generator=g)
+    ts = torch.tensor([0, 1, 49, 500, 999], dtype=torch.long)
+    return x0, nz, ts
+
+
+# name -> (cfg, seed, B, H, W)
+TINY = O.UnetCfg(groups=32, n_heads=4, channels_list=(64, 128), time_emb_dim=128,
+                 n_layers=1, context_dim=64)
+TINY3 = O.UnetCfg(groups=16, n_heads=2, channels_list=(32, 64, 96), time_emb_dim=None,
+                  n_layers=1, context_dim=96, attention_resolutions=(0, 1, 2))
+DEFAULT = O.UnetCfg()
+
+UNET_CASES = {
+    "tiny_8": (TINY, 11, 2, 8, 8),
+    "tiny_16": (TINY, 11, 3, 16, 16),
+    "tiny3_16": (TINY3, 12, 2, 16, 16),
+    "default_8": (DEFAULT, 13, 2, 8, 8),
+    "default_32": (DEFAULT, 13, 2, 32, 32),
+}
+
+
+def unet_inputs(cfg, B, H, W, seed, ctx_len=77):
+    g = _g(1000 + seed)
+    x = torch.randn(B, cfg.latent_channels, H, W, generator=g)
+    t = torch.randint(0, 1000, (B,), generator=g, dtype=torch.long)
+    ctx = torch.randn(B, ctx_len, cfg.context_dim, generator=g)
+    return x, t, ctx
+
+
+# name -> (cfg, seed, B, H, W, steps, guidance)
+SAMPLE_CASES = {
+    "tiny_16": (TINY, 11, 2, 16, 16, 6, 7.5),
+    "default_16": (DEFAULT, 13, 1, 16, 16, 4, 7.5),
+}
+SAMPLE_NOISE_SEED = 4321
+
+
+def sample_inputs(cfg, B, H, W, seed, ctx_len=77):
+    g = _g(2000 + seed)
+    x = torch.rand(B, cfg.latent_channels, H, W, generator=g)  # uniform start, scripts/txt2img.py:33
+    ctx = torch.randn(B, ctx_len, cfg.context_dim, generator=g)
+    uncond = torch.randn(1, ctx_len, cfg.context_dim, generator=g)
+    return x, ctx, uncond
+
+
+VAE_DEFAULT = O.VaeCfg()
+VAE_KL_TINY = O.VaeCfg(autoencoder_channels_list=(32, 64, 64, 64), groups=16)
+VAE_CASES = {
+    "default_16": (VAE_DEFAULT, 21, 2, 16, 16),
+    "kltiny_8": (VAE_KL_TINY, 22, 1, 8, 8),
+}
+
+
+def vae_inputs(cfg, B, H, W, seed):
+    return torch.randn(B, cfg.latent_channels, H, W, generator=_g(3000 + seed))

@@ -1,0 +1,132 @@
+"""Generate golden vectors by running the UNMODIFIED reference on seeded inputs.
+
+Runs only in the build container (needs /root/reference); the GPU box has no
+reference, so the outputs are committed as ``tests/golden/*.npz`` and this script
+is the record of how they were made:
+
+    python tests/golden/make_golden.py
+
+Weights come from ``oracle.sd_oracle.seeded_state_dict`` (every tensor non-zero,
+so zero_module'd layers -- models/utils.py:22-28 -- cannot hide errors) and are
+loaded with ``load_state_dict(strict=True)``, which also proves that the oracle's
+key/shape enumeration equals the reference's module tree.
+"""
+import os
+import sys
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, "/root/reference")
+
+# import order matters: models before modules (circular import in the reference)
+from stable_diffusion.models.unet import UNetModel, UnetConfig  # noqa: E402
+from stable_diffusion.models.autoencoder import AutoEncoderKL, AutoencoderConfig  # noqa: E402
+from stable_diffusion.models.scheduler import DDPMScheduler, DDPMConfig  # noqa: E402
+from stable_diffusion.models.latent_diffusion import LatentDiffusion  # noqa: E402
+from stable_diffusion.modules.timestep_embedding import sinusoidal_time_proj  # noqa: E402
+
+from oracle import sd_oracle as O  # noqa: E402
+from tests.golden import cases  # noqa: E402
+
+
+class StubTextEncoder:
+    """Duck type of models/clip_model.py:72-96 returning a fixed 'empty prompt' embedding."""
+
+    def __init__(self, uncond):
+        self.uncond = uncond  # [1, L, D]
+
+    def tokenize(self, prompts):
+        class _T:
+            pass
+        t = _T()
+        t.input_ids = torch.zeros(len(prompts), self.uncond.shape[1], dtype=torch.long)
+        return t
+
+    def encode_text(self, ids):
+        return (self.uncond.expand(ids.shape[0], -1, -1).clone(),)
+
+
+def ref_unet(ucfg: O.UnetCfg, seed):
+    cfg = UnetConfig(num_res_blocks=ucfg.num_res_blocks, n_heads=ucfg.n_heads,
+                     attention_resolutions=list(ucfg.attention_resolutions),
+                     channels_list=list(ucfg.channels_list), time_emb_dim=ucfg.time_emb_dim,
+                     dropout=0.0, n_layers=ucfg.n_layers, context_dim=ucfg.context_dim)
+    m = UNetModel(ucfg.latent_channels, ucfg.groups, cfg).eval()
+    sd = O.seeded_state_dict(O.unet_param_shapes(ucfg), seed)
+    m.load_state_dict(sd, strict=True)
+    return m
+
+
+def ref_vae(vcfg: O.VaeCfg, seed):
+    cfg = AutoencoderConfig(in_channels=vcfg.in_channels, latent_channels=vcfg.latent_channels,
+                            out_channels=vcfg.out_channels,
+                            autoencoder_channels_list=list(vcfg.autoencoder_channels_list),
+                            autoencoder_num_res_blocks=vcfg.autoencoder_num_res_blocks,
+                            groups=vcfg.groups)
+    m = AutoEncoderKL(cfg).eval()
+    sd = O.seeded_state_dict(O.vae_decoder_param_shapes(vcfg), seed)
+    missing, unexpected = m.load_state_dict(sd, strict=False)
+    assert not unexpected, unexpected
+    assert all(k.startswith(("encoder.", "quant_conv.")) for k in missing), missing
+    return m
+
+
+def main():
+    torch.set_num_threads(8)
+    out = {}
+    with torch.no_grad():
+        # ---- timestep embedding -------------------------------------------------
+        for dim in (64, 160):
+            t = torch.tensor(cases.TIMESTEP_CASES, dtype=torch.long)
+            out[f"temb_{dim}"] = sinusoidal_time_proj(t, dim).numpy()
+
+        # ---- scheduler tables / step / add_noise ---------------------------------
+        sch = DDPMScheduler(DDPMConfig())
+        for name in O.TABLE_NAMES:
+            out[f"table_{name}"] = getattr(sch, name).numpy()
+        out["table_noise_time_steps"] = sch.noise_time_steps.numpy()
+        for step in cases.STEP_CASES:
+            eps, x_t = cases.step_inputs(step)
+            torch.manual_seed(cases.STEP_NOISE_SEED + step)  # reference draws from the global CPU generator
+            x_prev, x0 = sch.step(eps, x_t, step, scale_factor=cases.STEP_SCALE)
+            out[f"step_{step}_xprev"] = x_prev.numpy()
+            out[f"step_{step}_x0"] = x0.numpy()
+        x0s, nz, ts = cases.add_noise_inputs()
+        out["add_noise"] = sch.add_noise(x0s, nz, ts).numpy()
+
+        # ---- UNet forwards -------------------------------------------------------
+        for name, (ucfg, seed, B, H, W) in cases.UNET_CASES.items():
+            m = ref_unet(ucfg, seed)
+            x, t, ctx = cases.unet_inputs(ucfg, B, H, W, seed)
+            out[f"unet_{name}"] = m(x, t, ctx).numpy()
+            print("unet", name, out[f"unet_{name}"].shape, float(np.abs(out[f"unet_{name}"]).mean()))
+
+        # ---- CFG + sampling loop (reference LatentDiffusion with a stub text encoder) --
+        for name, (ucfg, seed, B, H, W, steps, g) in cases.SAMPLE_CASES.items():
+            m = ref_unet(ucfg, seed)
+            x, ctx, uncond = cases.sample_inputs(ucfg, B, H, W, seed)
+            ld = LatentDiffusion(m, None, StubTextEncoder(uncond), sch)
+            t = torch.full((B,), 7, dtype=torch.long)
+            out[f"prednoise_{name}"] = ld.pred_noise(x, t, ctx, guidance_scale=g).numpy()
+            torch.manual_seed(cases.SAMPLE_NOISE_SEED)
+            out[f"sample_{name}"] = ld.sample(x, ctx, guidance_scale=g, time_steps=steps).numpy()
+            print("sample", name, float(np.abs(out[f"sample_{name}"]).mean()))
+
+        # ---- VAE decode ----------------------------------------------------------
+        for name, (vcfg, seed, B, H, W) in cases.VAE_CASES.items():
+            m = ref_vae(vcfg, seed)
+            z = cases.vae_inputs(vcfg, B, H, W, seed)
+            out[f"vae_{name}"] = m.decode(z).numpy()
+            print("vae", name, out[f"vae_{name}"].shape, float(np.abs(out[f"vae_{name}"]).mean()))
+
+    path = os.path.join(HERE, "reference_outputs.npz")
+    np.savez_compressed(path, **out)
+    print("wrote", path, os.path.getsize(path), "bytes,", len(out), "arrays")
+
+
+if __name__ == "__main__":
+    main()

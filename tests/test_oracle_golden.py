@@ -1,0 +1,93 @@
+"""CPU: the oracle restatement vs golden vectors produced by the unmodified reference
+(tests/golden/make_golden.py).  Pins the oracle."""
+import numpy as np
+import pytest
+import torch
+
+from oracle import sd_oracle as O
+from tests.golden import cases
+
+
+def rel_l2(a, b):
+    a = torch.as_tensor(a, dtype=torch.float64)
+    b = torch.as_tensor(b, dtype=torch.float64)
+    return float((a - b).norm() / b.norm().clamp_min(1e-30))
+
+
+def test_tables_bit_exact(golden):
+    tab = O.ddpm_tables(O.DdpmCfg())
+    for name in O.TABLE_NAMES + ("noise_time_steps",):
+        assert np.array_equal(tab[name].numpy(), golden[f"table_{name}"]), name
+
+
+def test_sample_timesteps_ascending():
+    tab = O.ddpm_tables(O.DdpmCfg())
+    assert O.sample_timesteps(tab, 50) == list(range(50))
+    assert O.sample_timesteps(tab, None) == list(range(1000))
+
+
+@pytest.mark.parametrize("dim", [64, 160])
+def test_timestep_embedding_bit_exact(golden, dim):
+    t = torch.tensor(cases.TIMESTEP_CASES, dtype=torch.long)
+    assert np.array_equal(O.sinusoidal_time_proj(t, dim).numpy(), golden[f"temb_{dim}"])
+
+
+@pytest.mark.parametrize("step", cases.STEP_CASES)
+def test_ddpm_step_bit_exact(golden, step):
+    tab = O.ddpm_tables(O.DdpmCfg())
+    eps, x_t = cases.step_inputs(step)
+    torch.manual_seed(cases.STEP_NOISE_SEED + step)
+    noise = None if step == 0 else torch.randn(x_t.shape)
+    x_prev, x0 = O.ddpm_step(tab, eps, x_t, step, noise, cases.STEP_SCALE)
+    assert np.array_equal(x_prev.numpy(), golden[f"step_{step}_xprev"])
+    assert np.array_equal(x0.numpy(), golden[f"step_{step}_x0"])
+
+
+def test_add_noise_bit_exact(golden):
+    tab = O.ddpm_tables(O.DdpmCfg())
+    x0, nz, ts = cases.add_noise_inputs()
+    assert np.array_equal(O.add_noise(tab, x0, nz, ts).numpy(), golden["add_noise"])
+
+
+@pytest.mark.parametrize("name", list(cases.UNET_CASES))
+def test_unet_forward(golden, name):
+    cfg, seed, B, H, W = cases.UNET_CASES[name]
+    sd = O.seeded_state_dict(O.unet_param_shapes(cfg), seed)
+    x, t, ctx = cases.unet_inputs(cfg, B, H, W, seed)
+    with torch.no_grad():
+        y = O.unet_forward(sd, cfg, x, t, ctx)
+    assert rel_l2(y, golden[f"unet_{name}"]) < 1e-5
+
+
+@pytest.mark.parametrize("name", list(cases.SAMPLE_CASES))
+def test_pred_noise_and_sample(golden, name):
+    cfg, seed, B, H, W, steps, g = cases.SAMPLE_CASES[name]
+    sd = O.seeded_state_dict(O.unet_param_shapes(cfg), seed)
+    x, ctx, uncond = cases.sample_inputs(cfg, B, H, W, seed)
+    tab = O.ddpm_tables(O.DdpmCfg())
+    fn = lambda a, b, c: O.unet_forward(sd, cfg, a, b, c)
+    un = uncond.expand(B, -1, -1)
+    with torch.no_grad():
+        t = torch.full((B,), 7, dtype=torch.long)
+        pn = O.pred_noise(fn, x, t, ctx, un, g)
+        assert rel_l2(pn, golden[f"prednoise_{name}"]) < 1e-5
+        torch.manual_seed(cases.SAMPLE_NOISE_SEED)
+        xs = O.sample(fn, tab, x, ctx, un, g, time_steps=steps)
+    assert rel_l2(xs, golden[f"sample_{name}"]) < 1e-4
+
+
+@pytest.mark.parametrize("name", list(cases.VAE_CASES))
+def test_vae_decode(golden, name):
+    cfg, seed, B, H, W = cases.VAE_CASES[name]
+    sd = O.seeded_state_dict(O.vae_decoder_param_shapes(cfg), seed)
+    z = cases.vae_inputs(cfg, B, H, W, seed)
+    with torch.no_grad():
+        y = O.vae_decode(sd, cfg, z)
+    assert rel_l2(y, golden[f"vae_{name}"]) < 1e-5
+
+
+def test_cfg_combine_is_mislabelled_like_reference():
+    # latent_diffusion.py:61-65: first chunk is the UNCOND half
+    e_unc, e_cond = torch.full((1, 1), 1.0), torch.full((1, 1), 3.0)
+    out = O.cfg_combine(torch.cat([e_unc, e_cond]), 2.0)
+    assert out.item() == 1.0 + 2.0 * (1.0 - 3.0)
