@@ -1,0 +1,189 @@
+/* libsdb200 -- C ABI of the B200-native latent-diffusion hot path.
+ *
+ * The reference (lwb2099/stable_diffusion_pytorch) is pure Python: its hot path has no FFI; every
+ * GPU instruction it runs is reached through torch.nn / ATen.  This header is the
+ * boundary a maintainer binds instead of those ATen calls; each entry point names the reference
+ * lines whose arithmetic it replaces (paths relative to the reference repo root).  INTEGRATION.md
+ * shows the ctypes stubs.
+ *
+ * Conventions
+ *  - extern "C", plain pointers and sizes; no torch types.  All pointers are DEVICE pointers
+ *    unless a parameter says "host".  The caller owns every buffer; the library allocates nothing
+ *    on the hot path and never synchronises: all work is enqueued on `stream` (a cudaStream_t).
+ *  - return 0 on success, a negative SDB_E* code otherwise; sdb_last_error() returns a
+ *    thread-local message.  Never throws, never exits.
+ *  - activations are channels-last: images NHWC [B, H, W, C], tokens [B, n, C] (identical memory),
+ *    so `b c h w -> b (h w) c` (modules/transformer.py:378-381) is free.
+ *  - dtype codes: SDB_F32 / SDB_BF16.  bf16 tensors feed the tcgen05 tensor-core kernels; accumu-
+ *    lation, bias, statistics and the sampler arithmetic are fp32.
+ *  - there is NO CPU fallback: every entry point needs an sm_100 device.
+ */
+#ifndef SDB200_H_
+#define SDB200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SDB_OK 0
+#define SDB_EINVAL (-1)  /* bad argument (mirrors the reference's asserts)          */
+#define SDB_ECUDA (-2)   /* a CUDA runtime / driver call failed                      */
+#define SDB_EUNSUPPORTED (-3) /* shape outside what the sm_100a kernels are built for */
+
+#define SDB_F32 0
+#define SDB_BF16 1
+
+#define SDB_ACT_NONE 0
+#define SDB_ACT_SILU 1  /* x*sigmoid(x) on the result                                          */
+#define SDB_ACT_GEGLU 2 /* weight rows interleaved (a0,g0,a1,g1,..): out[:, j] = a_j*gelu_erf(g_j) */
+
+int sdb_version(void);
+const char* sdb_last_error(void);
+/* 1 if any kernel hit its bounded-wait timeout since the last call (debug aid); resets the flag.
+ * Synchronises the device. */
+int sdb_debug_timeout_flag(void);
+/* number of kernel launches enqueued by this library since process start (bench: gpu_launches) */
+int64_t sdb_launch_count(void);
+
+/* ---- K6: timestep embedding ------------------------------------------------------------------
+ * modules/timestep_embedding.py:73-105 (`sinusoidal_time_proj`): out[b] = cat[sin(t_b*freq),
+ * cos(t_b*freq)].  `freq` is the [half] fp32 table the caller builds on the HOST with the
+ * reference's own expression (positive exponent) and uploads once.  Full-range sinf/cosf. */
+int sdb_timestep_embed(const int64_t* t, const float* freq, void* out, int B, int half,
+                       int out_dtype, void* stream);
+
+/* ---- K7: sampler ----------------------------------------------------------------------------
+ * Per-step coefficients live in a device table coef[step_slot][8] (fp32):
+ *   [0] sqrt_recip_alpha_bar  [1] sqrt_recip_m1_alpha_bar  [2] mean_x0_coef  [3] mean_xt_coef
+ *   [4] sigma = exp(0.5*log_var) (0 when the step adds no noise)
+ *   [5] ddim sqrt(abar_prev)  [6] ddim sqrt(1-abar_prev)  [7] unused
+ * all built on the host from models/scheduler.py:52-87 with the reference's torch ops.
+ * `slot_dev` (device int32*, may be NULL) selects the row at run time so one captured CUDA graph
+ * serves every step; when NULL, `slot` is used.
+ *
+ * sdb_cfg_sampler_step fuses models/latent_diffusion.py:62-65 (guidance combine, halves in the
+ * reference's [uncond, cond] order: eps = e0 + g*(e0 - e1); cfg_mode 0 = no guidance, eps = e0
+ * only) with models/scheduler.py:173-213 (DDPM: x0 = c0*x - c1*eps; mean = c2*x0 + c3*x;
+ * x_prev = mean + sigma*(noise*scale_factor)) or the eta=0 DDIM update (kind 1: x_prev =
+ * c5*x0 + c6*eps).  fp32 mode performs each multiply/add with a separate IEEE rounding in the
+ * reference's order, so it is bit-exact against the CPU reference.
+ *   eps   : [2*B or B, n_per] network output (NCHW flattened), dtype `dtype`
+ *   noise : same dtype, [B, n_per] pre-drawn host noise, or NULL -> in-kernel Philox N(0,1)
+ *           keyed by (seed, slot) (statistical parity only), ignored when sigma == 0
+ *   x_prev, x0 (x0 may be NULL): [B, n_per] */
+int sdb_cfg_sampler_step(const void* eps, const void* x_t, const void* noise, const float* coef,
+                         const int32_t* slot_dev, int slot, int kind, int cfg_mode, float guidance,
+                         float scale_factor, uint64_t seed, void* x_prev, void* x0, int B,
+                         int64_t n_per, int dtype, void* stream);
+/* advances the device step slot and refreshes the int64 timestep vector the UNet reads:
+ * t_out[0..nt) = t_table[slot+1] (models/latent_diffusion.py:110). */
+int sdb_sampler_advance(int32_t* slot_dev, const int64_t* t_table, int n_slots, int64_t* t_out,
+                        int nt, void* stream);
+/* models/scheduler.py:95-139 add_noise: out = sqrt(ac[t_b])*x0 + sqrt(1-ac[t_b])*noise with the
+ * table cast to `dtype` first and pow(0.5) taken in that dtype, as the reference does. */
+int sdb_add_noise(const void* x0, const void* noise, const int64_t* t, const float* alphas_cumprod,
+                  int n_steps, void* out, int B, int64_t n_per, int dtype, void* stream);
+
+/* ---- layout helpers --------------------------------------------------------------------------
+ * NCHW (reference layout, any dtype) <-> NHWC bf16/fp32 used inside the path. */
+int sdb_nchw_to_nhwc(const void* src, int src_dtype, void* dst, int dst_dtype, int B, int C, int H,
+                     int W, void* stream);
+int sdb_nhwc_to_nchw(const void* src, int src_dtype, void* dst, int dst_dtype, int B, int C, int H,
+                     int W, void* stream);
+
+/* ---- K2: GroupNorm ---------------------------------------------------------------------------
+ * torch.nn.GroupNorm (modules/resnet2d.py:172,188; transformer.py:329; models/utils.py:195),
+ * eps 1e-5, biased variance.  Two launches: statistics, then normalise(+SiLU).
+ * The input may be a VIRTUAL channel concat of two NHWC tensors (x1: C1 channels, x2: C2
+ * channels, x2 may be NULL) -- replaces torch.cat in models/unet.py:308.
+ *   stats : fp32 [B, groups, 2] (mean, rstd), caller-allocated
+ *   scratch: fp32 [B, chunks, C, 2] partial sums, chunks = sdb_groupnorm_chunks(H*W)          */
+int sdb_groupnorm_chunks(int64_t hw);
+int sdb_groupnorm_stats(const void* x1, int C1, const void* x2, int C2, int dtype, int B,
+                        int64_t hw, int groups, float eps, float* scratch, float* stats,
+                        void* stream);
+/* out[b,p,c] = act((x-mean)*rstd*gamma[c]+beta[c]); act = SDB_ACT_NONE | SDB_ACT_SILU.
+ * out is a dense NHWC tensor with C1+C2 channels, dtype out_dtype. */
+int sdb_groupnorm_apply(const void* x1, int C1, const void* x2, int C2, int dtype,
+                        const float* stats, const float* gamma, const float* beta, int act,
+                        void* out, int out_dtype, int B, int64_t hw, int groups, void* stream);
+
+/* ---- K5: residual add + LayerNorm ------------------------------------------------------------
+ * modules/transformer.py:274-278 post-norm: out = LN(x (+ res)) over the last dim C, eps 1e-5. */
+int sdb_add_layernorm(const void* x, const void* res, const float* gamma, const float* beta,
+                      void* out, int64_t rows, int C, float eps, int dtype, void* stream);
+
+/* ---- K3: GEMM with fused epilogue (tcgen05 + TMEM + TMA) ------------------------------------
+ * out[M, N] = act( A[M, K] . W[N, K]^T + bias[N] ) + residual[M, N]
+ * nn.Linear / 1x1 Conv2d call sites: transformer.py:55-58,151,176,330,347; resnet2d.py:182,202;
+ * unet.py:185-187.  A may be two K segments (a: K1 columns, a2: K2 columns) -- the virtual concat
+ * for the 1x1 skip convolution.  bf16 operands, fp32 accumulate. */
+typedef struct SdbGemmArgs {
+  const void* a;   int64_t lda;  int K1;       /* bf16 [M, K1], row stride lda elements        */
+  const void* a2;  int64_t lda2; int K2;       /* optional second segment, NULL / 0            */
+  const void* w;                               /* bf16 [N, K1+K2] row-major                    */
+  const float* bias;                           /* fp32 [N] or NULL                             */
+  const void* residual; int64_t ldr; int res_dtype; /* [M, Nout] or NULL                      */
+  void* out; int64_t ldo; int out_dtype;       /* [M, Nout]; Nout = N (N/2 for GEGLU)          */
+  int M; int N;
+  int act;                                     /* SDB_ACT_*                                    */
+} SdbGemmArgs;
+int sdb_gemm(const SdbGemmArgs* args, void* stream);
+
+/* ---- K1: 3x3 convolution as implicit GEMM (tcgen05 + TMEM + TMA im2col-by-shifted-box) ------
+ * nn.Conv2d(k=3, padding=1) call sites: resnet2d.py:41,103,174,195; models/utils.py:32,197.
+ * x NHWC bf16 [B,H,W,Cin] (already normalised/activated: padding is applied AFTER GN+SiLU as in
+ * resnet2d.py:171-177, i.e. out-of-image taps contribute exact zeros via TMA OOB fill).
+ * w bf16 [Cout][3][3][Cin].  Epilogue: + bias[Cout] + temb[b, Cout] (resnet2d.py:235) +
+ * residual NHWC (resnet2d.py:238).
+ * down2 = 1: conv followed by nearest x0.5 (resnet2d.py:122-123) == keep even rows/cols.
+ * up2 = 1:   nearest x2 THEN conv (resnet2d.py:61-62); x is the low-res tensor [B,H,W,Cin],
+ *            out is [B,2H,2W,Cout]. */
+typedef struct SdbConvArgs {
+  const void* x; const void* w; const float* bias;
+  const float* temb; int64_t ld_temb;          /* fp32 [B, ld_temb] or NULL                    */
+  const void* residual; int res_dtype;         /* NHWC [B,Ho,Wo,Cout] or NULL                  */
+  void* out; int out_dtype;
+  int B, H, W, Cin, Cout;
+  int down2; int up2;
+} SdbConvArgs;
+int sdb_conv3x3(const SdbConvArgs* args, void* stream);
+
+/* small-channel 3x3 convs on CUDA cores (HBM-bound): conv_in (models/utils.py:31-32, Cin = latent
+ * channels; reads NCHW `src_dtype`, writes NHWC) and the output head conv (models/utils.py:197,
+ * Cout = latent/img channels; reads NHWC, writes NCHW).  fp32 weights OIHW as in the state_dict. */
+int sdb_conv3x3_in(const void* x_nchw, int src_dtype, const float* w, const float* bias, void* out_nhwc,
+                   int out_dtype, int B, int H, int W, int Cin, int Cout, void* stream);
+int sdb_conv3x3_out(const void* x_nhwc, int src_dtype, const float* w, const float* bias,
+                    void* out_nchw, int out_dtype, int B, int H, int W, int Cin, int Cout,
+                    void* stream);
+/* 1x1 conv on a thin NCHW tensor (post_quant_conv, models/autoencoder.py:110,160); C <= 8 */
+int sdb_conv1x1_nchw_small(const void* x, const float* w, const float* bias, void* out, int dtype,
+                           int B, int H, int W, int Cin, int Cout, void* stream);
+/* nearest x2 upsample NHWC (resnet2d.py:61), used ahead of sdb_conv3x3 when up2 is not fused */
+int sdb_upsample2x(const void* x, void* out, int dtype, int B, int H, int W, int C, void* stream);
+
+/* ---- K4: fused attention --------------------------------------------------------------------
+ * modules/transformer.py:93-114: softmax(Q K^T * scale) V per (batch, head) without
+ * materialising `sim`.  q [B, n, *] with head h at columns [h*d, (h+1)*d) and row stride ldq
+ * elements (so a fused QKV GEMM output can be passed as three offset pointers); k, v [B, m, *].
+ * out [B, n, heads*d] row stride ldo.  bf16 in/out, fp32 softmax state.  d <= 128, d % 4 == 0. */
+int sdb_attention(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
+                  int64_t ldv, void* out, int64_t ldo, int B, int heads, int n, int m, int d,
+                  float scale, int dtype, void* stream);
+
+/* ---- elementwise helpers --------------------------------------------------------------------*/
+int sdb_silu(const void* x, void* out, int64_t n, int dtype, int out_dtype, void* stream);
+int sdb_cast(const void* x, int src_dtype, void* out, int dst_dtype, int64_t n, void* stream);
+/* VAE head: img = clip((x+1)/2, 0, 1)*255 -> uint8 (utils/prepare_dataset.py:145-150), NCHW in,
+ * NHWC uint8 out. */
+int sdb_to_uint8_image(const void* x_nchw, int dtype, uint8_t* out_nhwc, int B, int C, int H, int W,
+                       void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SDB200_H_ */

@@ -1,0 +1,416 @@
+// K2 GroupNorm (statistics + normalise/SiLU over a virtual channel concat), K5 residual-add +
+// LayerNorm, and the layout / elementwise helpers.  All HBM-bound: 16-byte vector accesses,
+// channels-last so a warp reads consecutive channels of consecutive pixels.
+#include "common.cuh"
+
+namespace sdb {
+
+// ---- 8-channel vector load/store in fp32 registers --------------------------------------------
+template <typename T> struct Vec8;
+template <> struct Vec8<__nv_bfloat16> {
+  static __device__ __forceinline__ void load(const __nv_bfloat16* p, float (&v)[8]) {
+    uint4 q = __ldg(reinterpret_cast<const uint4*>(p));
+    float2 a = unpack_bf16x2(q.x), b = unpack_bf16x2(q.y), c = unpack_bf16x2(q.z), d = unpack_bf16x2(q.w);
+    v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y; v[4] = c.x; v[5] = c.y; v[6] = d.x; v[7] = d.y;
+  }
+  static __device__ __forceinline__ void store(__nv_bfloat16* p, const float (&v)[8]) {
+    *reinterpret_cast<uint4*>(p) = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]),
+                                              pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+  }
+};
+template <> struct Vec8<float> {
+  static __device__ __forceinline__ void load(const float* p, float (&v)[8]) {
+    float4 a = __ldg(reinterpret_cast<const float4*>(p)), b = __ldg(reinterpret_cast<const float4*>(p) + 1);
+    v[0] = a.x; v[1] = a.y; v[2] = a.z; v[3] = a.w; v[4] = b.x; v[5] = b.y; v[6] = b.z; v[7] = b.w;
+  }
+  static __device__ __forceinline__ void store(float* p, const float (&v)[8]) {
+    reinterpret_cast<float4*>(p)[0] = make_float4(v[0], v[1], v[2], v[3]);
+    reinterpret_cast<float4*>(p)[1] = make_float4(v[4], v[5], v[6], v[7]);
+  }
+};
+
+constexpr int kGnThreads = 256;
+constexpr int kGnMaxChunks = 64;
+
+// ---- GroupNorm statistics, stage 1: per (image, pixel chunk, channel) sum / sum of squares -----
+// grid (chunks, B); thread (r, vec): vec = 8-channel vector of the virtual concat, r = pixel lane.
+template <typename T>
+__global__ void __launch_bounds__(kGnThreads)
+gn_partial_kernel(const T* __restrict__ x1, int C1, const T* __restrict__ x2, int C2, long long hw,
+                  int chunk_px, float* __restrict__ scratch /* [B, chunks, C, 2] */) {
+  extern __shared__ float sm[];  // [R][2*C]
+  const int C = C1 + C2, V = C >> 3;
+  const int R = kGnThreads / V;
+  const int b = blockIdx.y, chunk = blockIdx.x, chunks = gridDim.x;
+  const int vec = threadIdx.x % V, r = threadIdx.x / V;
+  float s[8], ss[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { s[j] = 0.f; ss[j] = 0.f; }
+  const long long p0 = (long long)chunk * chunk_px;
+  const long long p1 = p0 + chunk_px < hw ? p0 + chunk_px : hw;
+  if (r < R) {
+    const int c = vec * 8;
+    const T* base;
+    long long pitch;
+    if (c < C1) { base = x1 + (long long)b * hw * C1 + c; pitch = C1; }
+    else { base = x2 + (long long)b * hw * C2 + (c - C1); pitch = C2; }
+    for (long long px = p0 + r; px < p1; px += R) {
+      float v[8];
+      Vec8<T>::load(base + px * pitch, v);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { s[j] += v[j]; ss[j] = fmaf(v[j], v[j], ss[j]); }
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      sm[(r * C + c + j) * 2] = s[j];
+      sm[(r * C + c + j) * 2 + 1] = ss[j];
+    }
+  }
+  __syncthreads();
+  float* dst = scratch + ((long long)b * chunks + chunk) * C * 2;
+  for (int i = threadIdx.x; i < 2 * C; i += kGnThreads) {
+    float acc = 0.f;
+    for (int rr = 0; rr < R; ++rr) acc += sm[rr * 2 * C + i];  // fixed order: deterministic
+    dst[i] = acc;
+  }
+}
+
+// ---- stage 2: per (image, group) mean / rstd ---------------------------------------------------
+__global__ void __launch_bounds__(128)
+gn_finalize_kernel(const float* __restrict__ scratch, int chunks, int C, int groups, long long hw,
+                   float eps, float* __restrict__ stats /* [B, groups, 2] */) {
+  const int g = blockIdx.x, b = blockIdx.y, cpg = C / groups;
+  float s = 0.f, ss = 0.f;
+  const int n = chunks * cpg;
+  for (int i = threadIdx.x; i < n; i += 128) {
+    const int ch = i / cpg, c = g * cpg + (i - ch * cpg);
+    const float* src = scratch + (((long long)b * chunks + ch) * C + c) * 2;
+    s += src[0];
+    ss += src[1];
+  }
+  __shared__ float red[2][4];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    s += __shfl_xor_sync(0xffffffffu, s, o);
+    ss += __shfl_xor_sync(0xffffffffu, ss, o);
+  }
+  if ((threadIdx.x & 31) == 0) { red[0][threadIdx.x >> 5] = s; red[1][threadIdx.x >> 5] = ss; }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    s = red[0][0] + red[0][1] + red[0][2] + red[0][3];
+    ss = red[1][0] + red[1][1] + red[1][2] + red[1][3];
+    const float inv = 1.0f / ((float)cpg * (float)hw);
+    const float mean = s * inv;
+    float var = ss * inv - mean * mean;
+    var = var > 0.f ? var : 0.f;
+    stats[((long long)b * groups + g) * 2] = mean;
+    stats[((long long)b * groups + g) * 2 + 1] = rsqrtf(var + eps);
+  }
+}
+
+// ---- normalise (+SiLU), writing a dense NHWC tensor with C1+C2 channels -----------------------
+template <typename T, typename OutT>
+__global__ void __launch_bounds__(256)
+gn_apply_kernel(const T* __restrict__ x1, int C1, const T* __restrict__ x2, int C2,
+                const float* __restrict__ stats, const float* __restrict__ gamma,
+                const float* __restrict__ beta, int act, OutT* __restrict__ out, long long hw,
+                int groups) {
+  extern __shared__ float sm[];  // scale[C], shift[C]
+  const int C = C1 + C2, V = C >> 3, cpg = C / groups;
+  const int b = blockIdx.y;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const int g = c / cpg;
+    const float mean = stats[((long long)b * groups + g) * 2];
+    const float rstd = stats[((long long)b * groups + g) * 2 + 1];
+    const float sc = rstd * gamma[c];
+    sm[c] = sc;
+    sm[C + c] = beta[c] - mean * sc;
+  }
+  __syncthreads();
+  const long long total = hw * V;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long px = i / V;
+    const int c = (int)(i - px * V) * 8;
+    float v[8];
+    if (c < C1) Vec8<T>::load(x1 + ((long long)b * hw + px) * C1 + c, v);
+    else Vec8<T>::load(x2 + ((long long)b * hw + px) * C2 + (c - C1), v);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      float y = fmaf(v[j], sm[c + j], sm[C + c + j]);
+      v[j] = act == SDB_ACT_SILU ? silu_f(y) : y;
+    }
+    Vec8<OutT>::store(out + ((long long)b * hw + px) * C + c, v);
+  }
+}
+
+// ---- K5: out = LayerNorm(x (+ res)) over C, one warp per row, two-pass in registers ------------
+template <typename T>
+__global__ void __launch_bounds__(256)
+add_layernorm_kernel(const T* __restrict__ x, const T* __restrict__ res,
+                     const float* __restrict__ gamma, const float* __restrict__ beta,
+                     T* __restrict__ out, long long rows, int C, float eps) {
+  const int lane = threadIdx.x & 31;
+  const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const int V = C >> 3;
+  float v[4][8];
+  float s = 0.f;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int vi = lane + 32 * k;
+    if (vi < V) {
+      Vec8<T>::load(x + row * C + vi * 8, v[k]);
+      if (res) {
+        float r[8];
+        Vec8<T>::load(res + row * C + vi * 8, r);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) v[k][j] += r[j];
+      }
+#pragma unroll
+      for (int j = 0; j < 8; ++j) s += v[k][j];
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  const float mean = s / (float)C;
+  float ss = 0.f;
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    if (lane + 32 * k < V) {
+#pragma unroll
+      for (int j = 0; j < 8; ++j) { const float d = v[k][j] - mean; ss = fmaf(d, d, ss); }
+    }
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+  const float rstd = rsqrtf(ss / (float)C + eps);
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    const int vi = lane + 32 * k;
+    if (vi < V) {
+      float g[8], bt[8], o[8];
+      Vec8<float>::load(gamma + vi * 8, g);
+      Vec8<float>::load(beta + vi * 8, bt);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) o[j] = fmaf((v[k][j] - mean) * rstd, g[j], bt[j]);
+      Vec8<T>::store(out + row * C + vi * 8, o);
+    }
+  }
+}
+
+// ---- batched transpose [B, R, Cc] -> [B, Cc, R] with dtype conversion -------------------------
+template <typename S, typename D>
+__device__ __forceinline__ D cvt(S v);
+template <> __device__ __forceinline__ float cvt<float, float>(float v) { return v; }
+template <> __device__ __forceinline__ __nv_bfloat16 cvt<float, __nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+template <> __device__ __forceinline__ float cvt<__nv_bfloat16, float>(__nv_bfloat16 v) { return __bfloat162float(v); }
+template <> __device__ __forceinline__ __nv_bfloat16 cvt<__nv_bfloat16, __nv_bfloat16>(__nv_bfloat16 v) { return v; }
+
+template <typename S, typename D>
+__global__ void transpose_kernel(const S* __restrict__ src, D* __restrict__ dst, int R, int Cc) {
+  __shared__ float tile[32][33];
+  const long long boff = (long long)blockIdx.z * R * Cc;
+  const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+  for (int i = threadIdx.y; i < 32; i += 8) {
+    const int r = r0 + i, c = c0 + threadIdx.x;
+    if (r < R && c < Cc) tile[i][threadIdx.x] = cvt<S, float>(src[boff + (long long)r * Cc + c]);
+  }
+  __syncthreads();
+  for (int i = threadIdx.y; i < 32; i += 8) {
+    const int c = c0 + i, r = r0 + threadIdx.x;
+    if (r < R && c < Cc) dst[boff + (long long)c * R + r] = cvt<float, D>(tile[threadIdx.x][i]);
+  }
+}
+
+template <typename T>
+__global__ void upsample2x_kernel(const T* __restrict__ x, T* __restrict__ out, int H, int W, int C,
+                                  long long total_vec) {
+  const int V = C >> 3;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total_vec;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int v = (int)(i % V);
+    long long t = i / V;
+    const int wo = (int)(t % (2 * W)); t /= (2 * W);
+    const int ho = (int)(t % (2 * H));
+    const long long b = t / (2 * H);
+    const uint4* s = reinterpret_cast<const uint4*>(x + (((b * H + (ho >> 1)) * W + (wo >> 1)) * C + v * 8));
+    uint4* d = reinterpret_cast<uint4*>(out + (((b * 2 * H + ho) * 2 * W + wo) * C + v * 8));
+    if constexpr (sizeof(T) == 2) { *d = __ldg(s); }
+    else { d[0] = __ldg(s); d[1] = __ldg(s + 1); }
+  }
+}
+
+template <typename S, typename D>
+__global__ void silu_cast_kernel(const S* __restrict__ x, D* __restrict__ out, long long n, int do_silu) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+       i += (long long)gridDim.x * blockDim.x) {
+    float v = cvt<S, float>(x[i]);
+    out[i] = cvt<float, D>(do_silu ? silu_f(v) : v);
+  }
+}
+
+template <typename T>
+__global__ void to_uint8_kernel(const T* __restrict__ x, uint8_t* __restrict__ out, int C, long long hw,
+                                long long total) {
+  // utils/prepare_dataset.py:145-150: (x+1)/2, clip to [0,1], *255, truncate to uint8
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const int c = (int)(i % C);
+    const long long px = (i / C) % hw, b = i / (C * hw);
+    float v = cvt<T, float>(x[(b * C + c) * hw + px]);
+    v = (v + 1.0f) / 2.0f;
+    v = fminf(fmaxf(v, 0.0f), 1.0f);
+    out[i] = (uint8_t)(v * 255.0f);
+  }
+}
+
+static inline int ew_grid(long long n, int threads) {
+  long long want = (n + threads - 1) / threads;
+  long long cap = (long long)sdb_num_sms() * 16;
+  return (int)(want < cap ? (want > 0 ? want : 1) : cap);
+}
+
+}  // namespace sdb
+
+using namespace sdb;
+
+extern "C" int sdb_groupnorm_chunks(int64_t hw) {
+  int64_t c = (hw + 255) / 256;
+  if (c < 1) c = 1;
+  if (c > kGnMaxChunks) c = kGnMaxChunks;
+  return (int)c;
+}
+
+extern "C" int sdb_groupnorm_stats(const void* x1, int C1, const void* x2, int C2, int dtype, int B,
+                                   int64_t hw, int groups, float eps, float* scratch, float* stats,
+                                   void* stream) {
+  if (!x2) C2 = 0;
+  const int C = C1 + C2;
+  SDB_CHECK_ARG(x1 && scratch && stats && B > 0 && hw > 0, "groupnorm_stats: bad args");
+  SDB_CHECK_ARG(C1 % 8 == 0 && C2 % 8 == 0, "groupnorm: C1 (%d), C2 (%d) must be multiples of 8", C1, C2);
+  SDB_CHECK_ARG(groups > 0 && C % groups == 0, "groupnorm: channels (%d) must be divisible by num_groups (%d)", C, groups);
+  const int V = C / 8;
+  SDB_CHECK_ARG(V <= kGnThreads, "groupnorm: C (%d) too large", C);
+  const int chunks = sdb_groupnorm_chunks(hw);
+  const int chunk_px = (int)((hw + chunks - 1) / chunks);
+  const int R = kGnThreads / V;
+  const size_t smem = (size_t)R * 2 * C * sizeof(float);
+  dim3 grid(chunks, B);
+  if (dtype == SDB_BF16)
+    gn_partial_kernel<__nv_bfloat16><<<grid, kGnThreads, smem, sdb_stream(stream)>>>(
+        (const __nv_bfloat16*)x1, C1, (const __nv_bfloat16*)x2, C2, hw, chunk_px, scratch);
+  else
+    gn_partial_kernel<float><<<grid, kGnThreads, smem, sdb_stream(stream)>>>(
+        (const float*)x1, C1, (const float*)x2, C2, hw, chunk_px, scratch);
+  SDB_LAUNCH_OK();
+  gn_finalize_kernel<<<dim3(groups, B), 128, 0, sdb_stream(stream)>>>(scratch, chunks, C, groups, hw, eps, stats);
+  SDB_LAUNCH_OK();
+  return SDB_OK;
+}
+
+extern "C" int sdb_groupnorm_apply(const void* x1, int C1, const void* x2, int C2, int dtype,
+                                   const float* stats, const float* gamma, const float* beta, int act,
+                                   void* out, int out_dtype, int B, int64_t hw, int groups,
+                                   void* stream) {
+  if (!x2) C2 = 0;
+  const int C = C1 + C2;
+  SDB_CHECK_ARG(x1 && stats && gamma && beta && out && B > 0 && hw > 0, "groupnorm_apply: bad args");
+  SDB_CHECK_ARG(C1 % 8 == 0 && C2 % 8 == 0 && groups > 0 && C % groups == 0, "groupnorm_apply: bad channels");
+  const size_t smem = (size_t)2 * C * sizeof(float);
+  long long total = hw * (C / 8);
+  long long want = (total + 255) / 256;
+  long long cap = ((long long)sdb_num_sms() * 8 + B - 1) / B;
+  dim3 grid((unsigned)(want < cap ? want : (cap > 0 ? cap : 1)), B);
+  cudaStream_t st = sdb_stream(stream);
+#define SDB_GN_APPLY(T, O)                                                                       \
+  gn_apply_kernel<T, O><<<grid, 256, smem, st>>>((const T*)x1, C1, (const T*)x2, C2, stats, gamma, \
+                                                 beta, act, (O*)out, hw, groups)
+  if (dtype == SDB_BF16 && out_dtype == SDB_BF16) SDB_GN_APPLY(__nv_bfloat16, __nv_bfloat16);
+  else if (dtype == SDB_BF16) SDB_GN_APPLY(__nv_bfloat16, float);
+  else if (out_dtype == SDB_BF16) SDB_GN_APPLY(float, __nv_bfloat16);
+  else SDB_GN_APPLY(float, float);
+#undef SDB_GN_APPLY
+  SDB_LAUNCH_OK();
+  return SDB_OK;
+}
+
+extern "C" int sdb_add_layernorm(const void* x, const void* res, const float* gamma, const float* beta,
+                                 void* out, int64_t rows, int C, float eps, int dtype, void* stream) {
+  SDB_CHECK_ARG(x && gamma && beta && out && rows > 0, "add_layernorm: bad args");
+  SDB_CHECK_ARG(C % 8 == 0 && C <= 1024, "add_layernorm: C (%d) must be a multiple of 8, <= 1024", C);
+  const int wpb = 8;
+  const unsigned grid = (unsigned)((rows + wpb - 1) / wpb);
+  if (dtype == SDB_BF16)
+    add_layernorm_kernel<__nv_bfloat16><<<grid, wpb * 32, 0, sdb_stream(stream)>>>(
+        (const __nv_bfloat16*)x, (const __nv_bfloat16*)res, gamma, beta, (__nv_bfloat16*)out, rows, C, eps);
+  else
+    add_layernorm_kernel<float><<<grid, wpb * 32, 0, sdb_stream(stream)>>>(
+        (const float*)x, (const float*)res, gamma, beta, (float*)out, rows, C, eps);
+  SDB_LAUNCH_OK();
+  return SDB_OK;
+}
+
+static int launch_transpose(const void* src, int sdt, void* dst, int ddt, int Bn, int R, int Cc, cudaStream_t st) {
+  dim3 grid((Cc + 31) / 32, (R + 31) / 32, Bn), block(32, 8);
+  SDB_CHECK_ARG(grid.y <= 65535 && grid.z <= 65535, "transpose: dims too large");
+  if (sdt == SDB_F32 && ddt == SDB_F32) transpose_kernel<float, float><<<grid, block, 0, st>>>((const float*)src, (float*)dst, R, Cc);
+  else if (sdt == SDB_F32) transpose_kernel<float, __nv_bfloat16><<<grid, block, 0, st>>>((const float*)src, (__nv_bfloat16*)dst, R, Cc);
+  else if (ddt == SDB_F32) transpose_kernel<__nv_bfloat16, float><<<grid, block, 0, st>>>((const __nv_bfloat16*)src, (float*)dst, R, Cc);
+  else transpose_kernel<__nv_bfloat16, __nv_bfloat16><<<grid, block, 0, st>>>((const __nv_bfloat16*)src, (__nv_bfloat16*)dst, R, Cc);
+  SDB_LAUNCH_OK();
+  return SDB_OK;
+}
+
+extern "C" int sdb_nchw_to_nhwc(const void* src, int src_dtype, void* dst, int dst_dtype, int B, int C,
+                                int H, int W, void* stream) {
+  SDB_CHECK_ARG(src && dst && B > 0 && C > 0 && H > 0 && W > 0, "nchw_to_nhwc: bad args");
+  return launch_transpose(src, src_dtype, dst, dst_dtype, B, C, H * W, sdb_stream(stream));
+}
+extern "C" int sdb_nhwc_to_nchw(const void* src, int src_dtype, void* dst, int dst_dtype, int B, int C,
+                                int H, int W, void* stream) {
+  SDB_CHECK_ARG(src && dst && B > 0 && C > 0 && H > 0 && W > 0, "nhwc_to_nchw: bad args");
+  return launch_transpose(src, src_dtype, dst, dst_dtype, B, H * W, C, sdb_stream(stream));
+}
+
+extern "C" int sdb_upsample2x(const void* x, void* out, int dtype, int B, int H, int W, int C, void* stream) {
+  SDB_CHECK_ARG(x && out && B > 0 && H > 0 && W > 0 && C % 8 == 0, "upsample2x: bad args (C %% 8)");
+  long long total = (long long)B * 4 * H * W * (C / 8);
+  if (dtype == SDB_BF16)
+    upsample2x_kernel<__nv_bfloat16><<<ew_grid(total, 256), 256, 0, sdb_stream(stream)>>>(
+        (const __nv_bfloat16*)x, (__nv_bfloat16*)out, H, W, C, total);
+  else
+    upsample2x_kernel<float><<<ew_grid(total, 256), 256, 0, sdb_stream(stream)>>>(
+        (const float*)x, (float*)out, H, W, C, total);
+  SDB_LAUNCH_OK();
+  return SDB_OK;
+}
+
+static int launch_silu_cast(const void* x, int sdt, void* out, int ddt, long long n, int do_silu, cudaStream_t st) {
+  const int g = ew_grid(n, 256);
+  if (sdt == SDB_F32 && ddt == SDB_F32) silu_cast_kernel<float, float><<<g, 256, 0, st>>>((const float*)x, (float*)out, n, do_silu);
+  else if (sdt == SDB_F32) silu_cast_kernel<float, __nv_bfloat16><<<g, 256, 0, st>>>((const float*)x, (__nv_bfloat16*)out, n, do_silu);
+  else if (ddt == SDB_F32) silu_cast_kernel<__nv_bfloat16, float><<<g, 256, 0, st>>>((const __nv_bfloat16*)x, (float*)out, n, do_silu);
+  else silu_cast_kernel<__nv_bfloat16, __nv_bfloat16><<<g, 256, 0, st>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)out, n, do_silu);
+  SDB_LAUNCH_OK();
+  return SDB_OK;
+}
+extern "C" int sdb_silu(const void* x, void* out, int64_t n, int dtype, int out_dtype, void* stream) {
+  SDB_CHECK_ARG(x && out && n > 0, "silu: bad args");
+  return launch_silu_cast(x, dtype, out, out_dtype, n, 1, sdb_stream(stream));
+}
+extern "C" int sdb_cast(const void* x, int src_dtype, void* out, int dst_dtype, int64_t n, void* stream) {
+  SDB_CHECK_ARG(x && out && n > 0, "cast: bad args");
+  return launch_silu_cast(x, src_dtype, out, dst_dtype, n, 0, sdb_stream(stream));
+}
+extern "C" int sdb_to_uint8_image(const void* x_nchw, int dtype, uint8_t* out_nhwc, int B, int C, int H,
+                                  int W, void* stream) {
+  SDB_CHECK_ARG(x_nchw && out_nhwc && B > 0 && C > 0 && H > 0 && W > 0, "to_uint8_image: bad args");
+  long long hw = (long long)H * W, total = hw * C * B;
+  if (dtype == SDB_BF16)
+    to_uint8_kernel<__nv_bfloat16><<<ew_grid(total, 256), 256, 0, sdb_stream(stream)>>>((const __nv_bfloat16*)x_nchw, out_nhwc, C, hw, total);
+  else
+    to_uint8_kernel<float><<<ew_grid(total, 256), 256, 0, sdb_stream(stream)>>>((const float*)x_nchw, out_nhwc, C, hw, total);
+  SDB_LAUNCH_OK();
+  return SDB_OK;
+}

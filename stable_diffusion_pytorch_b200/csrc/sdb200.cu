@@ -1,0 +1,8 @@
+// Unity translation unit of libsdb200.so (one TU keeps the __device__ debug flag and the launch
+// counter shared without relocatable device code).
+#include "runtime.cu"
+#include "sampler.cu"
+#include "norm.cu"
+#include "conv_small.cu"
+#include "attention.cu"
+#include "gemm_umma.cu"

@@ -1,0 +1,286 @@
+"""Thin torch-tensor front end of the C ABI: torch supplies device memory and the current stream,
+every computation happens in ``libsdb200.so``.  All tensors must be CUDA tensors (no CPU path)."""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from . import _lib
+from ._lib import ACT_GEGLU, ACT_NONE, ACT_SILU, SDB_BF16, SDB_F32, SdbConvArgs, SdbGemmArgs, check
+
+Tensor = torch.Tensor
+
+
+def _dt(t_or_dtype) -> int:
+    d = t_or_dtype.dtype if isinstance(t_or_dtype, torch.Tensor) else t_or_dtype
+    if d == torch.float32:
+        return SDB_F32
+    if d == torch.bfloat16:
+        return SDB_BF16
+    raise TypeError(f"unsupported dtype {d}: the B200 path computes in float32 or bfloat16")
+
+
+def _ptr(t: Optional[Tensor]) -> Optional[int]:
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise RuntimeError("stable_diffusion_pytorch_b200 has no CPU fallback: tensor is not on a CUDA device")
+    return t.data_ptr()
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def timestep_embed(t: Tensor, freq: Tensor, out_dtype=torch.float32) -> Tensor:
+    assert t.dtype == torch.int64 and freq.dtype == torch.float32
+    B, half = t.shape[0], freq.shape[0]
+    out = torch.empty(B, 2 * half, device=t.device, dtype=out_dtype)
+    check(_lib.lib().sdb_timestep_embed(_ptr(t), _ptr(freq), _ptr(out), B, half, _dt(out_dtype), _stream()),
+          "timestep_embed")
+    return out
+
+
+def cfg_sampler_step(eps: Tensor, x_t: Tensor, noise: Optional[Tensor], coef: Tensor, slot: int = 0,
+                     slot_dev: Optional[Tensor] = None, kind: int = 0, cfg_mode: int = 1,
+                     guidance: float = 7.5, scale_factor: float = 1.0, seed: int = 0,
+                     x_prev: Optional[Tensor] = None, x0: Optional[Tensor] = None, want_x0: bool = True):
+    B = x_t.shape[0]
+    n_per = x_t.numel() // B
+    assert eps.is_contiguous() and x_t.is_contiguous() and eps.dtype == x_t.dtype
+    assert eps.shape[0] == (2 * B if cfg_mode else B)
+    if noise is not None:
+        assert noise.is_contiguous() and noise.dtype == x_t.dtype and noise.numel() == x_t.numel()
+    if x_prev is None:
+        x_prev = torch.empty_like(x_t)
+    if x0 is None and want_x0:
+        x0 = torch.empty_like(x_t)
+    check(_lib.lib().sdb_cfg_sampler_step(_ptr(eps), _ptr(x_t), _ptr(noise), _ptr(coef), _ptr(slot_dev), slot,
+                                          kind, cfg_mode, guidance, scale_factor, seed, _ptr(x_prev), _ptr(x0),
+                                          B, n_per, _dt(x_t), _stream()), "cfg_sampler_step")
+    return x_prev, x0
+
+
+def sampler_advance(slot_dev: Tensor, t_table: Tensor, t_out: Tensor) -> None:
+    check(_lib.lib().sdb_sampler_advance(_ptr(slot_dev), _ptr(t_table), t_table.numel(), _ptr(t_out),
+                                         t_out.numel(), _stream()), "sampler_advance")
+
+
+def add_noise(x0: Tensor, noise: Tensor, t: Tensor, alphas_cumprod: Tensor) -> Tensor:
+    B = x0.shape[0]
+    out = torch.empty_like(x0)
+    check(_lib.lib().sdb_add_noise(_ptr(x0.contiguous()), _ptr(noise.contiguous()), _ptr(t), _ptr(alphas_cumprod),
+                                   alphas_cumprod.numel(), _ptr(out), B, x0.numel() // B, _dt(x0), _stream()),
+          "add_noise")
+    return out
+
+
+def nchw_to_nhwc(x: Tensor, out_dtype=None) -> Tensor:
+    B, Cc, H, W = x.shape
+    out = torch.empty(B, H, W, Cc, device=x.device, dtype=out_dtype or x.dtype)
+    check(_lib.lib().sdb_nchw_to_nhwc(_ptr(x.contiguous()), _dt(x), _ptr(out), _dt(out), B, Cc, H, W, _stream()),
+          "nchw_to_nhwc")
+    return out
+
+
+def nhwc_to_nchw(x: Tensor, out_dtype=None) -> Tensor:
+    B, H, W, Cc = x.shape
+    out = torch.empty(B, Cc, H, W, device=x.device, dtype=out_dtype or x.dtype)
+    check(_lib.lib().sdb_nhwc_to_nchw(_ptr(x.contiguous()), _dt(x), _ptr(out), _dt(out), B, Cc, H, W, _stream()),
+          "nhwc_to_nchw")
+    return out
+
+
+class GroupNormScratch:
+    """Caller-owned scratch of the two-pass GroupNorm (grown on demand, reused across calls)."""
+
+    def __init__(self):
+        self.partial = None
+        self.stats = None
+
+    def get(self, device, B, hw, Cc, groups):
+        chunks = _lib.lib().sdb_groupnorm_chunks(hw)
+        need_p, need_s = B * chunks * Cc * 2, B * groups * 2
+        if self.partial is None or self.partial.numel() < need_p or self.partial.device != device:
+            self.partial = torch.empty(need_p, device=device, dtype=torch.float32)
+        if self.stats is None or self.stats.numel() < need_s or self.stats.device != device:
+            self.stats = torch.empty(need_s, device=device, dtype=torch.float32)
+        return self.partial, self.stats
+
+
+_default_gn_scratch = GroupNormScratch()
+
+
+def group_norm(x1: Tensor, gamma: Tensor, beta: Tensor, groups: int, act: int = ACT_NONE,
+               x2: Optional[Tensor] = None, out_dtype=None, eps: float = 1e-5,
+               scratch: Optional[GroupNormScratch] = None, out: Optional[Tensor] = None) -> Tensor:
+    """GroupNorm(+SiLU) of the virtual channel concat [x1, x2]; NHWC in, dense NHWC out."""
+    B, H, W, C1 = x1.shape
+    C2 = x2.shape[-1] if x2 is not None else 0
+    assert x1.is_contiguous() and (x2 is None or (x2.is_contiguous() and x2.dtype == x1.dtype))
+    hw = H * W
+    partial, stats = (scratch or _default_gn_scratch).get(x1.device, B, hw, C1 + C2, groups)
+    if out is None:
+        out = torch.empty(B, H, W, C1 + C2, device=x1.device, dtype=out_dtype or x1.dtype)
+    L = _lib.lib()
+    check(L.sdb_groupnorm_stats(_ptr(x1), C1, _ptr(x2), C2, _dt(x1), B, hw, groups, eps, _ptr(partial),
+                                _ptr(stats), _stream()), "groupnorm_stats")
+    check(L.sdb_groupnorm_apply(_ptr(x1), C1, _ptr(x2), C2, _dt(x1), _ptr(stats), _ptr(gamma), _ptr(beta), act,
+                                _ptr(out), _dt(out), B, hw, groups, _stream()), "groupnorm_apply")
+    return out
+
+
+def add_layernorm(x: Tensor, res: Optional[Tensor], gamma: Tensor, beta: Tensor, eps: float = 1e-5,
+                  out: Optional[Tensor] = None) -> Tensor:
+    Cc = x.shape[-1]
+    rows = x.numel() // Cc
+    assert x.is_contiguous() and (res is None or (res.is_contiguous() and res.dtype == x.dtype))
+    if out is None:
+        out = torch.empty_like(x)
+    check(_lib.lib().sdb_add_layernorm(_ptr(x), _ptr(res), _ptr(gamma), _ptr(beta), _ptr(out), rows, Cc, eps,
+                                       _dt(x), _stream()), "add_layernorm")
+    return out
+
+
+def gemm(a: Tensor, w: Tensor, bias: Optional[Tensor] = None, residual: Optional[Tensor] = None,
+         act: int = ACT_NONE, a2: Optional[Tensor] = None, out_dtype=None, out: Optional[Tensor] = None) -> Tensor:
+    """out[M, N] = act(a[M, K] @ w[N, K]^T + bias) + residual; ``a``/``a2`` may be row-strided 2-D views."""
+    assert a.dim() == 2 and w.dim() == 2 and a.dtype == torch.bfloat16 and w.dtype == torch.bfloat16
+    assert a.stride(1) == 1 and w.is_contiguous()
+    M, K1 = a.shape
+    N = w.shape[0]
+    K2 = 0
+    if a2 is not None:
+        assert a2.dim() == 2 and a2.shape[0] == M and a2.stride(1) == 1 and a2.dtype == torch.bfloat16
+        K2 = a2.shape[1]
+    assert w.shape[1] == K1 + K2, f"weight K {w.shape[1]} != {K1}+{K2}"
+    n_out = N // 2 if act == ACT_GEGLU else N
+    if out is None:
+        out = torch.empty(M, n_out, device=a.device, dtype=out_dtype or a.dtype)
+    assert out.stride(1) == 1 and out.shape == (M, n_out)
+    args = SdbGemmArgs()
+    args.a, args.lda, args.K1 = _ptr(a), a.stride(0), K1
+    args.a2, args.lda2, args.K2 = (_ptr(a2), a2.stride(0), K2) if a2 is not None else (None, 0, 0)
+    args.w, args.bias = _ptr(w), _ptr(bias)
+    if residual is not None:
+        assert residual.shape == (M, n_out) and residual.stride(1) == 1
+        args.residual, args.ldr, args.res_dtype = _ptr(residual), residual.stride(0), _dt(residual)
+    else:
+        args.residual, args.ldr, args.res_dtype = None, 0, 0
+    args.out, args.ldo, args.out_dtype = _ptr(out), out.stride(0), _dt(out)
+    args.M, args.N, args.act = M, N, act
+    if bias is not None:
+        assert bias.dtype == torch.float32 and bias.numel() == N
+    check(_lib.lib().sdb_gemm(C.byref(args), _stream()), "gemm")
+    return out
+
+
+def conv3x3(x: Tensor, w: Tensor, bias: Optional[Tensor], temb: Optional[Tensor] = None,
+            residual: Optional[Tensor] = None, down2: bool = False, out_dtype=None,
+            out: Optional[Tensor] = None) -> Tensor:
+    """3x3 / pad 1 convolution, NHWC bf16 ``x`` [B,H,W,Cin], ``w`` bf16 [Cout,3,3,Cin]."""
+    B, H, W, Cin = x.shape
+    Cout = w.shape[0]
+    assert x.is_contiguous() and w.is_contiguous() and x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16
+    assert tuple(w.shape) == (Cout, 3, 3, Cin)
+    Ho, Wo = (H // 2, W // 2) if down2 else (H, W)
+    if out is None:
+        out = torch.empty(B, Ho, Wo, Cout, device=x.device, dtype=out_dtype or x.dtype)
+    a = SdbConvArgs()
+    a.x, a.w, a.bias = _ptr(x), _ptr(w), _ptr(bias)
+    if temb is not None:
+        assert temb.dtype == torch.float32 and temb.stride(1) == 1 and temb.shape[0] == B
+        a.temb, a.ld_temb = _ptr(temb), temb.stride(0)
+    else:
+        a.temb, a.ld_temb = None, 0
+    if residual is not None:
+        assert residual.is_contiguous() and tuple(residual.shape) == (B, Ho, Wo, Cout)
+        a.residual, a.res_dtype = _ptr(residual), _dt(residual)
+    else:
+        a.residual, a.res_dtype = None, 0
+    a.out, a.out_dtype = _ptr(out), _dt(out)
+    a.B, a.H, a.W, a.Cin, a.Cout = B, H, W, Cin, Cout
+    a.down2, a.up2 = int(down2), 0
+    check(_lib.lib().sdb_conv3x3(C.byref(a), _stream()), "conv3x3")
+    return out
+
+
+def conv3x3_in(x_nchw: Tensor, w: Tensor, bias: Tensor, out_dtype=torch.bfloat16) -> Tensor:
+    B, Cin, H, W = x_nchw.shape
+    Cout = w.shape[0]
+    assert w.dtype == torch.float32 and w.is_contiguous() and bias.dtype == torch.float32
+    out = torch.empty(B, H, W, Cout, device=x_nchw.device, dtype=out_dtype)
+    check(_lib.lib().sdb_conv3x3_in(_ptr(x_nchw.contiguous()), _dt(x_nchw), _ptr(w), _ptr(bias), _ptr(out),
+                                    _dt(out), B, H, W, Cin, Cout, _stream()), "conv3x3_in")
+    return out
+
+
+def conv3x3_out(x_nhwc: Tensor, w: Tensor, bias: Tensor, out_dtype=torch.float32) -> Tensor:
+    B, H, W, Cin = x_nhwc.shape
+    Cout = w.shape[0]
+    assert w.dtype == torch.float32 and w.is_contiguous() and x_nhwc.is_contiguous()
+    out = torch.empty(B, Cout, H, W, device=x_nhwc.device, dtype=out_dtype)
+    check(_lib.lib().sdb_conv3x3_out(_ptr(x_nhwc), _dt(x_nhwc), _ptr(w), _ptr(bias), _ptr(out), _dt(out), B, H,
+                                     W, Cin, Cout, _stream()), "conv3x3_out")
+    return out
+
+
+def conv1x1_nchw_small(x: Tensor, w: Tensor, bias: Tensor) -> Tensor:
+    B, Cin, H, W = x.shape
+    Cout = w.shape[0]
+    out = torch.empty(B, Cout, H, W, device=x.device, dtype=x.dtype)
+    check(_lib.lib().sdb_conv1x1_nchw_small(_ptr(x.contiguous()), _ptr(w), _ptr(bias), _ptr(out), _dt(x), B, H, W,
+                                            Cin, Cout, _stream()), "conv1x1_nchw_small")
+    return out
+
+
+def upsample2x(x: Tensor) -> Tensor:
+    B, H, W, Cc = x.shape
+    assert x.is_contiguous()
+    out = torch.empty(B, 2 * H, 2 * W, Cc, device=x.device, dtype=x.dtype)
+    check(_lib.lib().sdb_upsample2x(_ptr(x), _ptr(out), _dt(x), B, H, W, Cc, _stream()), "upsample2x")
+    return out
+
+
+def attention(q: Tensor, k: Tensor, v: Tensor, heads: int, d: int, scale: float,
+              out: Optional[Tensor] = None) -> Tensor:
+    """q [B, n, >=heads*d] (last-dim stride 1, row-strided views allowed), k/v [B, m, ...]."""
+    B, n = q.shape[0], q.shape[1]
+    m = k.shape[1]
+    for t in (q, k, v):
+        assert t.dtype == torch.bfloat16 and t.stride(2) == 1 and t.stride(0) == t.shape[1] * t.stride(1)
+    if out is None:
+        out = torch.empty(B, n, heads * d, device=q.device, dtype=q.dtype)
+    check(_lib.lib().sdb_attention(_ptr(q), q.stride(1), _ptr(k), k.stride(1), _ptr(v), v.stride(1), _ptr(out),
+                                   out.stride(1), B, heads, n, m, d, scale, _dt(q), _stream()), "attention")
+    return out
+
+
+def silu(x: Tensor, out_dtype=None) -> Tensor:
+    out = torch.empty(x.shape, device=x.device, dtype=out_dtype or x.dtype)
+    check(_lib.lib().sdb_silu(_ptr(x.contiguous()), _ptr(out), x.numel(), _dt(x), _dt(out), _stream()), "silu")
+    return out
+
+
+def cast(x: Tensor, dtype) -> Tensor:
+    out = torch.empty(x.shape, device=x.device, dtype=dtype)
+    check(_lib.lib().sdb_cast(_ptr(x.contiguous()), _dt(x), _ptr(out), _dt(out), x.numel(), _stream()), "cast")
+    return out
+
+
+def to_uint8_image(x_nchw: Tensor) -> Tensor:
+    B, Cc, H, W = x_nchw.shape
+    out = torch.empty(B, H, W, Cc, device=x_nchw.device, dtype=torch.uint8)
+    check(_lib.lib().sdb_to_uint8_image(_ptr(x_nchw.contiguous()), _dt(x_nchw), _ptr(out), B, Cc, H, W, _stream()),
+          "to_uint8_image")
+    return out
+
+
+def debug_timeout_flag() -> int:
+    return _lib.lib().sdb_debug_timeout_flag()
+
+
+def launch_count() -> int:
+    return _lib.lib().sdb_launch_count()

@@ -1,0 +1,222 @@
+"""GPU: every libsdb200 kernel through the C ABI against a plain PyTorch fp32 reference of the same
+op on the same (bf16-rounded) inputs."""
+import math
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+ops = None
+
+
+@pytest.fixture(scope="module", autouse=True)
+def _load():
+    global ops
+    if not torch.cuda.is_available():
+        pytest.skip("needs a CUDA device")
+    from stable_diffusion_pytorch_b200 import ops as _ops
+    ops = _ops
+    yield
+    assert ops.debug_timeout_flag() == 0, "a kernel hit its bounded mbarrier wait"
+
+
+def rel_l2(a, b):
+    a, b = a.double(), b.double()
+    return float((a - b).norm() / b.norm().clamp_min(1e-30))
+
+
+def rnd(*shape, seed=0, scale=1.0, dtype=torch.bfloat16):
+    g = torch.Generator(device="cpu").manual_seed(seed)
+    return (torch.randn(*shape, generator=g) * scale).to("cuda", dtype)
+
+
+# ------------------------------------------------------------------ GEMM (tcgen05)
+GEMM_CASES = [
+    # M, N, K, bias, residual, act
+    (128, 64, 64, False, False, 0),      # one tile, SW128, one k-block
+    (128, 160, 160, True, False, 0),     # SW64 path (K % 64 != 0), N = 160
+    (300, 160, 320, True, True, 0),      # M tail, bias + residual
+    (4096, 480, 160, False, False, 0),   # fused QKV shape, many tiles (persistent loop, 2 acc stages)
+    (1024, 1280, 160, True, False, 2),   # GEGLU epilogue
+    (512, 160, 640, True, True, 0),      # FFN out
+    (77 * 3, 320, 768, False, False, 0), # context K/V
+    (32, 512, 160, True, False, 1),      # time MLP with SiLU epilogue, M < 128
+    (2048, 96, 96, True, False, 0),      # small N
+    (1000, 3040, 512, True, False, 0),   # batched temb projections, wide N
+]
+
+
+@pytest.mark.parametrize("M,N,K,has_bias,has_res,act", GEMM_CASES)
+def test_gemm(M, N, K, has_bias, has_res, act):
+    a = rnd(M, K, seed=1)
+    w = rnd(N, K, seed=2, scale=1 / math.sqrt(K))
+    bias = rnd(N, seed=3, dtype=torch.float32) if has_bias else None
+    n_out = N // 2 if act == 2 else N
+    res = rnd(M, n_out, seed=4) if has_res else None
+    out = ops.gemm(a, w, bias, res, act)
+    ref = a.float() @ w.float().t()
+    if has_bias:
+        ref = ref + bias
+    if act == 1:
+        ref = F.silu(ref)
+    if act == 2:
+        ref = ref[:, 0::2] * F.gelu(ref[:, 1::2])
+    if has_res:
+        ref = ref + res.float()
+    assert out.shape == ref.shape
+    assert rel_l2(out.float(), ref) < 6e-3
+
+
+def test_gemm_two_segments_fp32_out():
+    M, K1, K2, N = 640, 320, 160, 320
+    a1, a2 = rnd(M, K1, seed=1), rnd(M, K2, seed=2)
+    w = rnd(N, K1 + K2, seed=3, scale=0.05)
+    bias = rnd(N, seed=4, dtype=torch.float32)
+    out = ops.gemm(a1, w, bias, a2=a2, out_dtype=torch.float32)
+    ref = torch.cat([a1, a2], 1).float() @ w.float().t() + bias
+    assert rel_l2(out, ref) < 1e-5
+
+
+def test_gemm_strided_views():
+    # q/k/v as column slices of a fused projection: lda != K
+    M, K = 256, 160
+    big = rnd(M, 3 * K, seed=5)
+    w = rnd(64, K, seed=6, scale=0.1)
+    out = ops.gemm(big[:, K:2 * K], w, out_dtype=torch.float32)
+    ref = big[:, K:2 * K].float() @ w.float().t()
+    assert rel_l2(out, ref) < 1e-5
+
+
+# ------------------------------------------------------------------ conv3x3 (tcgen05 implicit GEMM)
+CONV_CASES = [
+    # B, H, W, Cin, Cout, temb, residual, down2
+    (1, 16, 16, 64, 64, False, False, False),
+    (2, 32, 32, 160, 160, True, True, False),
+    (3, 8, 8, 64, 128, True, False, False),     # 2 images per tile + batch tail
+    (2, 16, 16, 320, 160, False, True, False),
+    (2, 32, 32, 160, 160, False, False, True),  # DownSample: conv then nearest x0.5
+    (1, 64, 64, 480, 320, True, True, False),   # virtual-concat sized K, 2 N tiles
+    (1, 4, 4, 32, 32, False, False, False),     # tiny map
+    (2, 16, 16, 96, 96, False, False, False),
+    (1, 128, 128, 64, 64, False, False, False), # W = 128: one image row per tile
+]
+
+
+@pytest.mark.parametrize("B,H,W,Cin,Cout,has_temb,has_res,down2", CONV_CASES)
+def test_conv3x3(B, H, W, Cin, Cout, has_temb, has_res, down2):
+    x = rnd(B, H, W, Cin, seed=1)
+    w = rnd(Cout, 3, 3, Cin, seed=2, scale=1 / math.sqrt(9 * Cin))
+    bias = rnd(Cout, seed=3, dtype=torch.float32)
+    temb = rnd(B, Cout, seed=4, dtype=torch.float32) if has_temb else None
+    Ho, Wo = (H // 2, W // 2) if down2 else (H, W)
+    res = rnd(B, Ho, Wo, Cout, seed=5) if has_res else None
+    out = ops.conv3x3(x, w, bias, temb, res, down2=down2, out_dtype=torch.float32)
+    ref = F.conv2d(x.float().permute(0, 3, 1, 2), w.float().permute(0, 3, 1, 2), bias, padding=1)
+    if down2:
+        ref = F.interpolate(ref, scale_factor=0.5, mode="nearest")
+    if has_temb:
+        ref = ref + temb[:, :, None, None]
+    ref = ref.permute(0, 2, 3, 1)
+    if has_res:
+        ref = ref + res.float()
+    assert rel_l2(out, ref) < 1e-5
+
+
+def test_conv_small_in_out():
+    B, H, W = 2, 24, 40
+    x = rnd(B, 4, H, W, seed=1, dtype=torch.float32)
+    w = rnd(160, 4, 3, 3, seed=2, scale=0.2, dtype=torch.float32)
+    b = rnd(160, seed=3, dtype=torch.float32)
+    out = ops.conv3x3_in(x, w, b, out_dtype=torch.float32)
+    ref = F.conv2d(x, w, b, padding=1).permute(0, 2, 3, 1)
+    assert rel_l2(out, ref) < 1e-5
+    xh = rnd(B, H, W, 160, seed=4)
+    for cout in (3, 4, 8):
+        w2 = rnd(cout, 160, 3, 3, seed=5, scale=0.03, dtype=torch.float32)
+        b2 = rnd(cout, seed=6, dtype=torch.float32)
+        out2 = ops.conv3x3_out(xh, w2, b2, out_dtype=torch.float32)
+        ref2 = F.conv2d(xh.float().permute(0, 3, 1, 2), w2, b2, padding=1)
+        assert rel_l2(out2, ref2) < 1e-5
+    w3 = rnd(4, 4, 1, 1, seed=7, dtype=torch.float32)
+    b3 = rnd(4, seed=8, dtype=torch.float32)
+    assert rel_l2(ops.conv1x1_nchw_small(x, w3, b3), F.conv2d(x, w3, b3)) < 1e-6
+
+
+# ------------------------------------------------------------------ norms / layout
+@pytest.mark.parametrize("B,H,W,C1,C2,groups,act", [
+    (2, 16, 16, 160, 0, 32, 1), (2, 32, 32, 320, 160, 32, 1), (3, 8, 8, 320, 0, 2, 1),
+    (1, 64, 64, 160, 0, 32, 0), (2, 16, 16, 64, 32, 16, 1), (1, 128, 128, 64, 0, 32, 1)])
+def test_groupnorm(B, H, W, C1, C2, groups, act):
+    x1 = rnd(B, H, W, C1, seed=1) + 0.3
+    x2 = rnd(B, H, W, C2, seed=2, scale=2.0) if C2 else None
+    C = C1 + C2
+    gamma = 1 + 0.1 * rnd(C, seed=3, dtype=torch.float32)
+    beta = 0.1 * rnd(C, seed=4, dtype=torch.float32)
+    out = ops.group_norm(x1, gamma, beta, groups, act, x2=x2, out_dtype=torch.float32)
+    xc = x1 if x2 is None else torch.cat([x1, x2], -1)
+    ref = F.group_norm(xc.float().permute(0, 3, 1, 2), groups, gamma, beta, 1e-5)
+    if act:
+        ref = F.silu(ref)
+    assert rel_l2(out, ref.permute(0, 2, 3, 1)) < 2e-5
+
+
+@pytest.mark.parametrize("rows,C,dtype", [(1000, 160, torch.bfloat16), (513, 320, torch.float32),
+                                           (64, 64, torch.bfloat16), (100, 1024, torch.float32)])
+def test_add_layernorm(rows, C, dtype):
+    x, r = rnd(rows, C, seed=1, dtype=dtype), rnd(rows, C, seed=2, dtype=dtype)
+    gamma = 1 + 0.1 * rnd(C, seed=3, dtype=torch.float32)
+    beta = 0.1 * rnd(C, seed=4, dtype=torch.float32)
+    out = ops.add_layernorm(x, r, gamma, beta)
+    ref = F.layer_norm(x.float() + r.float(), (C,), gamma, beta, 1e-5)
+    assert rel_l2(out.float(), ref) < (5e-3 if dtype == torch.bfloat16 else 1e-5)
+
+
+def test_layout_and_elementwise():
+    x = rnd(2, 5, 7, 9, seed=1, dtype=torch.float32)
+    y = ops.nchw_to_nhwc(x, torch.bfloat16)
+    assert torch.equal(y, x.permute(0, 2, 3, 1).to(torch.bfloat16))
+    z = ops.nhwc_to_nchw(y, torch.float32)
+    assert torch.equal(z, x.to(torch.bfloat16).float())
+    u = ops.upsample2x(rnd(2, 3, 5, 16, seed=2))
+    assert torch.equal(u, F.interpolate(rnd(2, 3, 5, 16, seed=2).permute(0, 3, 1, 2).float(), scale_factor=2,
+                                        mode="nearest").permute(0, 2, 3, 1).to(torch.bfloat16))
+    s = ops.silu(x)
+    assert rel_l2(s, F.silu(x)) < 1e-6
+    img = ops.to_uint8_image(rnd(2, 3, 8, 8, seed=3, dtype=torch.float32))
+    ref = ((rnd(2, 3, 8, 8, seed=3, dtype=torch.float32) + 1) / 2).clamp(0, 1).mul(255).to(torch.uint8)
+    assert (img.int() - ref.permute(0, 2, 3, 1).int()).abs().max() <= 1
+
+
+# ------------------------------------------------------------------ attention
+@pytest.mark.parametrize("B,heads,n,m,d", [
+    (2, 8, 256, 256, 20), (1, 8, 1024, 1024, 20), (2, 8, 300, 77, 20), (2, 4, 64, 64, 16),
+    (1, 1, 256, 256, 64), (1, 1, 200, 200, 128), (2, 2, 128, 77, 32)])
+def test_attention(B, heads, n, m, d):
+    dm = heads * d
+    qkv = rnd(B, n, 3 * dm, seed=1)
+    q = qkv[:, :, :dm]
+    if m == n:
+        k, v = qkv[:, :, dm:2 * dm], qkv[:, :, 2 * dm:]
+    else:
+        kv = rnd(B, m, 2 * dm, seed=2)
+        k, v = kv[:, :, :dm], kv[:, :, dm:]
+    scale = 1 / math.sqrt(d)
+    out = ops.attention(q, k, v, heads, d, scale)
+    qf = q.float().view(B, n, heads, d).transpose(1, 2)
+    kf = k.float().view(B, m, heads, d).transpose(1, 2)
+    vf = v.float().view(B, m, heads, d).transpose(1, 2)
+    ref = torch.softmax(qf @ kf.transpose(-1, -2) * scale, -1) @ vf
+    ref = ref.transpose(1, 2).reshape(B, n, dm)
+    assert rel_l2(out.float(), ref) < 1e-2
+
+
+# ------------------------------------------------------------------ sampler kernels (bit-exact in fp32)
+def test_timestep_embed():
+    half = 80
+    freq = torch.exp(math.log(10000) / half * torch.arange(0, end=half, dtype=torch.float32))
+    t = torch.tensor([0, 1, 7, 49, 500, 999], dtype=torch.long)
+    ref = torch.cat([torch.sin(t[:, None].float() * freq[None]), torch.cos(t[:, None].float() * freq[None])], -1)
+    out = ops.timestep_embed(t.cuda(), freq.cuda())
+    assert (out.cpu() - ref).abs().max() < 2e-6  # CPU (Sleef) vs CUDA sinf differ by <= 2 ulp of |result| <= 1
