@@ -78,6 +78,8 @@ int sdb_cfg_sampler_step(const void* eps, const void* x_t, const void* noise, co
                          const int32_t* slot_dev, int slot, int kind, int cfg_mode, float guidance,
                          float scale_factor, uint64_t seed, void* x_prev, void* x0, int B,
                          int64_t n_per, int dtype, void* stream);
+/* guidance combine alone: out[i] = e0[i] + g*(e0[i] - e1[i]), eps = [e0 | e1], `total` = |e0| */
+int sdb_cfg_combine(const void* eps, float guidance, void* out, int64_t total, int dtype, void* stream);
 /* advances the device step slot and refreshes the int64 timestep vector the UNet reads:
  * t_out[0..nt) = t_table[slot+1] (models/latent_diffusion.py:110). */
 int sdb_sampler_advance(int32_t* slot_dev, const int64_t* t_table, int n_slots, int64_t* t_out,
@@ -153,10 +155,11 @@ typedef struct SdbConvArgs {
 int sdb_conv3x3(const SdbConvArgs* args, void* stream);
 
 /* small-channel 3x3 convs on CUDA cores (HBM-bound): conv_in (models/utils.py:31-32, Cin = latent
- * channels; reads NCHW `src_dtype`, writes NHWC) and the output head conv (models/utils.py:197,
+ * channels; reads NCHW `src_dtype`, writes NHWC; the input holds src_B images and output image b reads
+ * input image b %% src_B, which is the `torch.cat([x] * 2)` of latent_diffusion.py:53 for free) and the output head conv (models/utils.py:197,
  * Cout = latent/img channels; reads NHWC, writes NCHW).  fp32 weights OIHW as in the state_dict. */
 int sdb_conv3x3_in(const void* x_nchw, int src_dtype, const float* w, const float* bias, void* out_nhwc,
-                   int out_dtype, int B, int H, int W, int Cin, int Cout, void* stream);
+                   int out_dtype, int B, int src_B, int H, int W, int Cin, int Cout, void* stream);
 int sdb_conv3x3_out(const void* x_nhwc, int src_dtype, const float* w, const float* bias,
                     void* out_nchw, int out_dtype, int B, int H, int W, int Cin, int Cout,
                     void* stream);

@@ -53,7 +53,8 @@ SIGNATURES = {
     "sdb_add_layernorm": (_i, [_p, _p, _p, _p, _p, _i64, _i, _f, _i, _p]),
     "sdb_gemm": (_i, [C.POINTER(SdbGemmArgs), _p]),
     "sdb_conv3x3": (_i, [C.POINTER(SdbConvArgs), _p]),
-    "sdb_conv3x3_in": (_i, [_p, _i, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p]),
+    "sdb_conv3x3_in": (_i, [_p, _i, _p, _p, _p, _i, _i, _i, _i, _i, _i, _i, _p]),
+    "sdb_cfg_combine": (_i, [_p, _f, _p, _i64, _i, _p]),
     "sdb_conv3x3_out": (_i, [_p, _i, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p]),
     "sdb_conv1x1_nchw_small": (_i, [_p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p]),
     "sdb_upsample2x": (_i, [_p, _p, _i, _i, _i, _i, _i, _p]),

@@ -1,0 +1,78 @@
+"""Device-side weight packing shared by the modules.
+
+Parameters keep the reference's names, shapes and fp32 OIHW / [out, in] layouts (so a reference
+``state_dict`` loads unchanged); the kernels want bf16, K-major, channels-last operands.  Packed
+copies are built lazily on first use and rebuilt whenever a source parameter changes (version
+counter / storage / device), e.g. after ``load_state_dict`` or an optimizer step.
+"""
+from __future__ import annotations
+
+from typing import Callable, Dict, Sequence, Tuple
+
+import torch
+from torch import nn
+
+Tensor = torch.Tensor
+
+
+class PackCache:
+    def __init__(self):
+        self._store: Dict[str, Tuple[tuple, object]] = {}
+
+    @staticmethod
+    def _sig(params: Sequence[Tensor]) -> tuple:
+        return tuple((p.data_ptr(), p._version, str(p.device), p.dtype) for p in params)
+
+    def get(self, key: str, params: Sequence[Tensor], builder: Callable[[], object]):
+        sig = self._sig(params)
+        hit = self._store.get(key)
+        if hit is not None and hit[0] == sig:
+            return hit[1]
+        with torch.no_grad():
+            val = builder()
+        self._store[key] = (sig, val)
+        return val
+
+    def clear(self):
+        self._store.clear()
+
+
+def f32(p: Tensor) -> Tensor:
+    return p.detach().to(torch.float32).contiguous()
+
+
+def linear_w(p: Tensor) -> Tensor:
+    """[out, in] -> bf16 [N, K] (already K-major)."""
+    return p.detach().to(torch.bfloat16).contiguous()
+
+
+def conv1x1_w(p: Tensor) -> Tensor:
+    """[Cout, Cin, 1, 1] -> bf16 [Cout, Cin]."""
+    return p.detach().reshape(p.shape[0], p.shape[1]).to(torch.bfloat16).contiguous()
+
+
+def conv3x3_w(p: Tensor) -> Tensor:
+    """OIHW [Cout, Cin, 3, 3] -> bf16 [Cout, 3, 3, Cin] (tap-major, channels innermost)."""
+    return p.detach().permute(0, 2, 3, 1).to(torch.bfloat16).contiguous()
+
+
+def geglu_w(w: Tensor, b: Tensor) -> Tuple[Tensor, Tensor]:
+    """GEGLU proj [2*F, C] with halves (a | gate) -> rows interleaved (a0, g0, a1, g1, ...) so one
+    accumulator tile holds both operands of a_j * gelu(g_j)."""
+    F2 = w.shape[0]
+    half = F2 // 2
+    wi = torch.stack([w.detach()[:half], w.detach()[half:]], dim=1).reshape(F2, w.shape[1])
+    bi = torch.stack([b.detach()[:half], b.detach()[half:]], dim=1).reshape(F2)
+    return wi.to(torch.bfloat16).contiguous(), bi.to(torch.float32).contiguous()
+
+
+def require_cuda(x: Tensor, what: str) -> None:
+    if not x.is_cuda:
+        raise RuntimeError(f"{what}: stable_diffusion_pytorch_b200 has no CPU fallback; got a {x.device} tensor")
+
+
+def zero_module(module: nn.Module) -> nn.Module:
+    """Same contract as the reference's models/utils.py:22-28."""
+    for p in module.parameters():
+        p.detach().zero_()
+    return module

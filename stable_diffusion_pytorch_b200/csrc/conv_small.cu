@@ -16,7 +16,7 @@ constexpr int kCinMax = 8, kInPx = 32, kInCo = 64;
 template <typename TI, typename TO>
 __global__ void __launch_bounds__(256)
 conv3x3_in_kernel(const TI* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
-                  TO* __restrict__ out, int H, int W, int Cin, int Cout) {
+                  TO* __restrict__ out, int src_B, int H, int W, int Cin, int Cout) {
   __shared__ float s_in[kCinMax][3][kInPx + 2];
   __shared__ float s_w[kCinMax * 9][kInCo];  // [ci*9 + tap][co]
   const int wt = blockIdx.x % ((W + kInPx - 1) / kInPx);
@@ -27,7 +27,8 @@ conv3x3_in_kernel(const TI* __restrict__ x, const float* __restrict__ w, const f
     const int dy = rem / (kInPx + 2), dx = rem - dy * (kInPx + 2);
     const int hh = h + dy - 1, ww = w0 + dx - 1;
     float v = 0.f;
-    if (hh >= 0 && hh < H && ww >= 0 && ww < W) v = ld_f<TI>(x + (((long long)b * Cin + ci) * H + hh) * W + ww);
+    if (hh >= 0 && hh < H && ww >= 0 && ww < W)
+      v = ld_f<TI>(x + (((long long)(b % src_B) * Cin + ci) * H + hh) * W + ww);
     s_in[ci][dy][dx] = v;
   }
   for (int i = threadIdx.x; i < Cin * 9 * kInCo; i += 256) {
@@ -159,15 +160,16 @@ static int launch_out(const void* x, const float* w, const float* bias, void* ou
 }  // namespace sdb
 
 extern "C" int sdb_conv3x3_in(const void* x_nchw, int src_dtype, const float* w, const float* bias,
-                              void* out_nhwc, int out_dtype, int B, int H, int W, int Cin, int Cout,
-                              void* stream) {
+                              void* out_nhwc, int out_dtype, int B, int src_B, int H, int W, int Cin,
+                              int Cout, void* stream) {
   using namespace sdb;
   SDB_CHECK_ARG(x_nchw && w && bias && out_nhwc && B > 0 && H > 0 && W > 0, "conv3x3_in: bad args");
+  SDB_CHECK_ARG(src_B > 0 && B % src_B == 0, "conv3x3_in: B (%d) must be a multiple of src_B (%d)", B, src_B);
   SDB_CHECK_ARG(Cin >= 1 && Cin <= kCinMax, "conv3x3_in: Cin (%d) must be <= %d", Cin, kCinMax);
   SDB_CHECK_ARG(Cout % 8 == 0, "conv3x3_in: Cout (%d) must be a multiple of 8", Cout);
   dim3 grid(((W + kInPx - 1) / kInPx) * H, (Cout + kInCo - 1) / kInCo, B);
   cudaStream_t st = sdb_stream(stream);
-#define SDB_CIN(TI, TO) conv3x3_in_kernel<TI, TO><<<grid, 256, 0, st>>>((const TI*)x_nchw, w, bias, (TO*)out_nhwc, H, W, Cin, Cout)
+#define SDB_CIN(TI, TO) conv3x3_in_kernel<TI, TO><<<grid, 256, 0, st>>>((const TI*)x_nchw, w, bias, (TO*)out_nhwc, src_B, H, W, Cin, Cout)
   if (src_dtype == SDB_F32 && out_dtype == SDB_F32) SDB_CIN(float, float);
   else if (src_dtype == SDB_F32) SDB_CIN(float, __nv_bfloat16);
   else if (out_dtype == SDB_F32) SDB_CIN(__nv_bfloat16, float);

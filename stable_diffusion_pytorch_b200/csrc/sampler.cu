@@ -116,6 +116,21 @@ cfg_sampler_step_kernel(const T* __restrict__ eps, const T* __restrict__ x_t,
   }
 }
 
+// guidance combine alone (latent_diffusion.py:62-65) for stand-alone pred_noise() calls
+template <typename T>
+__global__ void __launch_bounds__(256)
+cfg_combine_kernel(const T* __restrict__ eps, float g, T* __restrict__ out, int64_t total) {
+  const int64_t stride = (int64_t)gridDim.x * blockDim.x * 4;
+  for (int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4; i < total; i += stride) {
+    float e0[4], e1[4], o[4];
+    Vec4<T>::load(eps + i, e0);
+    Vec4<T>::load(eps + total + i, e1);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) o[j] = __fadd_rn(e0[j], __fmul_rn(g, __fsub_rn(e0[j], e1[j])));
+    Vec4<T>::store(out + i, o);
+  }
+}
+
 __global__ void sampler_advance_kernel(int32_t* slot_dev, const int64_t* __restrict__ t_table,
                                        int n_slots, int64_t* __restrict__ t_out, int nt) {
   int s = *slot_dev + 1;
@@ -192,6 +207,21 @@ extern "C" int sdb_cfg_sampler_step(const void* eps, const void* x_t, const void
         (const __nv_bfloat16*)eps, (const __nv_bfloat16*)x_t, (const __nv_bfloat16*)noise, coef,
         slot_dev, slot, kind, cfg_mode, guidance, scale_factor, seed, (__nv_bfloat16*)x_prev,
         (__nv_bfloat16*)x0, total);
+  SDB_LAUNCH_OK();
+  return SDB_OK;
+}
+
+extern "C" int sdb_cfg_combine(const void* eps, float guidance, void* out, int64_t total, int dtype,
+                               void* stream) {
+  SDB_CHECK_ARG(eps && out && total > 0 && total % 4 == 0, "cfg_combine: bad args (total %% 4)");
+  int th = 256;
+  int64_t want = (total / 4 + th - 1) / th;
+  int grid = (int)(want < (int64_t)sdb_num_sms() * 8 ? want : (int64_t)sdb_num_sms() * 8);
+  if (dtype == SDB_F32)
+    sdb::cfg_combine_kernel<float><<<grid, th, 0, sdb_stream(stream)>>>((const float*)eps, guidance, (float*)out, total);
+  else
+    sdb::cfg_combine_kernel<__nv_bfloat16><<<grid, th, 0, sdb_stream(stream)>>>(
+        (const __nv_bfloat16*)eps, guidance, (__nv_bfloat16*)out, total);
   SDB_LAUNCH_OK();
   return SDB_OK;
 }

@@ -1,0 +1,251 @@
+"""CrossAttention / GEGLU / FeedForward / BasicTransformerBlock / SpatialTransformer with the
+reference's signatures and state_dict keys (stable_diffusion/modules/transformer.py:18-383).
+
+Tokens are [B, n, C] bf16 -- the same memory as the NHWC feature map, so the reference's two
+``rearrange`` calls (:378,:381) vanish.  Kernel plan per BasicTransformerBlock (post-norm, :274-278):
+fused-QKV tcgen05 GEMM -> fused attention -> out-proj GEMM with bias+residual epilogue -> LayerNorm;
+Q GEMM + (precomputed) context K/V -> fused attention -> out-proj(+res) -> LayerNorm;
+GEGLU GEMM (gate applied in the epilogue) -> FFN-out GEMM(+res) -> LayerNorm.
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+from torch import nn
+
+from .. import _pack, ops
+from .._lib import ACT_GEGLU, ACT_NONE
+
+Tensor = torch.Tensor
+
+
+def _tokens_bf16(x: Tensor) -> Tensor:
+    _pack.require_cuda(x, "transformer")
+    x = x.contiguous()
+    return x if x.dtype == torch.bfloat16 else ops.cast(x, torch.bfloat16)
+
+
+class CrossAttention(nn.Module):
+    """softmax(Q K^T / sqrt(d)) V with bias-free q/k/v projections and a biased output projection
+    (transformer.py:18-119).  ``context_emb=None`` => self-attention.  4-D inputs [B, C, H, W] are
+    accepted like the reference's ``convert`` path (used by the VAE bottleneck)."""
+
+    def __init__(self, query_dim: int, context_dim: Optional[int] = None, n_heads: int = 1, d_head: int = 1,
+                 dropout: float = 0.0):
+        super().__init__()
+        if not context_dim:
+            context_dim = query_dim
+        d_model = n_heads * d_head
+        self.n_heads = n_heads
+        self.d_head = d_head
+        self.scale = 1 / (d_head ** 0.5)
+        self.to_q = nn.Linear(query_dim, d_model, bias=False)
+        self.to_k = nn.Linear(context_dim, d_model, bias=False)
+        self.to_v = nn.Linear(context_dim, d_model, bias=False)
+        self.out = nn.Sequential(nn.Linear(d_model, query_dim), nn.Dropout(dropout))
+        self._cache = _pack.PackCache()
+        self._self_qkv_ok = context_dim == query_dim
+
+    def kv_weight(self) -> Tuple[Tensor, Tensor]:
+        return self.to_k.weight, self.to_v.weight
+
+    def _w(self):
+        c = self._cache
+        q, k, v, o = self.to_q.weight, self.to_k.weight, self.to_v.weight, self.out[0]
+        d = {
+            "wq": c.get("wq", [q], lambda: _pack.linear_w(q)),
+            "wkv": c.get("wkv", [k, v], lambda: _pack.linear_w(torch.cat([k.detach(), v.detach()], 0))),
+            "wo": c.get("wo", [o.weight], lambda: _pack.linear_w(o.weight)),
+            "bo": c.get("bo", [o.bias], lambda: _pack.f32(o.bias)),
+        }
+        if self._self_qkv_ok:
+            d["wqkv"] = c.get("wqkv", [q, k, v],
+                              lambda: _pack.linear_w(torch.cat([q.detach(), k.detach(), v.detach()], 0)))
+        return d
+
+    def forward_tokens(self, x: Tensor, ctx: Optional[Tensor] = None, kv: Optional[Tuple[Tensor, Tensor]] = None,
+                       residual: Optional[Tensor] = None) -> Tensor:
+        """x [B, n, C] bf16.  ctx [B, m, Cc] bf16 or ``kv`` = precomputed (K, V) [B, m, d_model] views.
+        Returns out-proj(attn) (+ residual, fused in the GEMM epilogue)."""
+        if self.training and self.out[1].p:
+            raise NotImplementedError("CrossAttention: dropout > 0 in training mode is not built")
+        B, n, C = x.shape
+        dm = self.n_heads * self.d_head
+        w = self._w()
+        x2d = x.view(B * n, C)
+        if ctx is None and kv is None:
+            if "wqkv" not in w:
+                raise ValueError("CrossAttention: context_emb is None but context_dim != query_dim "
+                                 "(the reference fails with a shape mismatch here too)")
+            qkv = ops.gemm(x2d, w["wqkv"]).view(B, n, 3 * dm)
+            q, k, v = qkv[:, :, :dm], qkv[:, :, dm:2 * dm], qkv[:, :, 2 * dm:]
+        else:
+            q = ops.gemm(x2d, w["wq"]).view(B, n, dm)
+            if kv is None:
+                m = ctx.shape[1]
+                kvt = ops.gemm(ctx.view(B * m, ctx.shape[2]), w["wkv"]).view(B, m, 2 * dm)
+                k, v = kvt[:, :, :dm], kvt[:, :, dm:]
+            else:
+                k, v = kv
+        a = ops.attention(q, k, v, self.n_heads, self.d_head, self.scale)
+        res2d = None if residual is None else residual.view(B * n, C)
+        return ops.gemm(a.view(B * n, dm), w["wo"], w["bo"], residual=res2d).view(B, n, C)
+
+    def forward(self, query: Tensor, context_emb: Optional[Tensor] = None, mask: Optional[Tensor] = None):
+        if mask is not None:
+            raise NotImplementedError("CrossAttention: the reference's mask path is dead code (transformer.py:102-107)")
+        in_dtype = query.dtype
+        if query.dim() == 4:
+            B, C, H, W = query.shape
+            t = ops.nchw_to_nhwc(query, torch.bfloat16).view(B, H * W, C)
+            ctx = None if context_emb is None else _tokens_bf16(context_emb)
+            o = self.forward_tokens(t, ctx)
+            return ops.nhwc_to_nchw(o.view(B, H, W, C), in_dtype)
+        t = _tokens_bf16(query)
+        ctx = None if context_emb is None else _tokens_bf16(context_emb)
+        o = self.forward_tokens(t, ctx)
+        return o if in_dtype == torch.bfloat16 else ops.cast(o, in_dtype)
+
+
+class GEGLU(nn.Module):
+    """x, gate = Linear(C -> 2F).chunk(2); x * gelu_erf(gate) (transformer.py:158-192), one GEMM:
+    the weight rows are interleaved at pack time so the gate is applied in the epilogue."""
+
+    def __init__(self, in_features: int, out_features: int):
+        super().__init__()
+        self.proj = nn.Linear(in_features, out_features * 2)
+        self.gelu = nn.GELU()
+        self._cache = _pack.PackCache()
+
+    def forward_tokens(self, x2d: Tensor) -> Tensor:
+        w, b = self._cache.get("wb", [self.proj.weight, self.proj.bias],
+                               lambda: _pack.geglu_w(self.proj.weight, self.proj.bias))
+        return ops.gemm(x2d, w, b, act=ACT_GEGLU)
+
+    def forward(self, x: Tensor) -> Tensor:
+        t = _tokens_bf16(x)
+        o = self.forward_tokens(t.view(-1, t.shape[-1])).view(*x.shape[:-1], -1)
+        return o if x.dtype == torch.bfloat16 else ops.cast(o, x.dtype)
+
+
+class FeedForward(nn.Module):
+    """GEGLU -> Dropout -> Linear(4C -> C) (transformer.py:122-155)."""
+
+    def __init__(self, d_model: int, dim_mult: int = 4, dropout: float = 0.0):
+        super().__init__()
+        self.net = nn.Sequential(GEGLU(d_model, dim_mult * d_model), nn.Dropout(p=dropout),
+                                 nn.Linear(d_model * dim_mult, d_model))
+        self._cache = _pack.PackCache()
+
+    def forward_tokens(self, x2d: Tensor, residual: Optional[Tensor] = None) -> Tensor:
+        if self.training and self.net[1].p:
+            raise NotImplementedError("FeedForward: dropout > 0 in training mode is not built")
+        lin = self.net[2]
+        w = self._cache.get("w", [lin.weight], lambda: _pack.linear_w(lin.weight))
+        b = self._cache.get("b", [lin.bias], lambda: _pack.f32(lin.bias))
+        return ops.gemm(self.net[0].forward_tokens(x2d), w, b, residual=residual)
+
+    def forward(self, x: Tensor) -> Tensor:
+        t = _tokens_bf16(x)
+        o = self.forward_tokens(t.view(-1, t.shape[-1])).view(x.shape)
+        return o if x.dtype == torch.bfloat16 else ops.cast(o, x.dtype)
+
+
+class BasicTransformerBlock(nn.Module):
+    """Post-norm block: x = LN1(x + SA(x)); x = LN2(x + CA(x, ctx)); x = LN3(x + FFN(x))
+    (transformer.py:195-279)."""
+
+    def __init__(self, d_model: int, n_heads: int, d_head: int, dropout: float = 0.0, context_dim: int = 768):
+        super().__init__()
+        self.d_model = d_model
+        self.context_dim = context_dim
+        self.self_attn = CrossAttention(d_model, context_dim=d_model, n_heads=n_heads, d_head=d_head, dropout=dropout)
+        self.norm1 = nn.LayerNorm(d_model)
+        self.cross_attn = CrossAttention(d_model, context_dim=context_dim, n_heads=n_heads, d_head=d_head,
+                                         dropout=dropout)
+        self.norm2 = nn.LayerNorm(d_model)
+        self.ffn = FeedForward(d_model, dropout=dropout)
+        self.norm3 = nn.LayerNorm(d_model)
+        self._cache = _pack.PackCache()
+
+    def _ln(self, i: int):
+        ln = getattr(self, f"norm{i}")
+        return (self._cache.get(f"g{i}", [ln.weight], lambda: _pack.f32(ln.weight)),
+                self._cache.get(f"b{i}", [ln.bias], lambda: _pack.f32(ln.bias)))
+
+    def forward_tokens(self, x: Tensor, ctx: Optional[Tensor] = None,
+                       kv: Optional[Tuple[Tensor, Tensor]] = None) -> Tensor:
+        B, n, C = x.shape
+        h = self.self_attn.forward_tokens(x, None, None, residual=x)            # x + SA(x)
+        x = ops.add_layernorm(h, None, *self._ln(1))
+        if ctx is None and kv is None:
+            h = self.cross_attn.forward_tokens(x, None, None, residual=x)        # reference: ctx None => self-attn
+        else:
+            h = self.cross_attn.forward_tokens(x, ctx, kv, residual=x)
+        x = ops.add_layernorm(h, None, *self._ln(2))
+        h = self.ffn.forward_tokens(x.view(B * n, C), residual=x.view(B * n, C)).view(B, n, C)
+        return ops.add_layernorm(h, None, *self._ln(3))
+
+    def forward(self, x: Tensor, context_emb: Optional[Tensor] = None) -> Tensor:
+        assert x.shape[-1] == self.d_model, f"input dim {x.shape[-1]} should be equal to d_model {self.d_model}"
+        if context_emb is not None:
+            assert context_emb.shape[-1] == self.context_dim, (
+                f"context dim {context_emb.shape[-1]} should be equal to context_dim {self.context_dim}")
+        t = _tokens_bf16(x)
+        ctx = None if context_emb is None else _tokens_bf16(context_emb)
+        o = self.forward_tokens(t, ctx)
+        return o if x.dtype == torch.bfloat16 else ops.cast(o, x.dtype)
+
+
+class SpatialTransformer(nn.Module):
+    """GN (no SiLU) -> 1x1 conv -> n_layers blocks -> 1x1 conv (zero-init) -> + x_in
+    (transformer.py:282-383)."""
+
+    act_dtype = torch.bfloat16
+
+    def __init__(self, in_channels: int, n_heads: int, d_head: int, n_layers: int = 1, dropout: float = 0.0,
+                 context_dim: int = None, groups: int = 2):
+        super().__init__()
+        assert n_heads > 0, f"n_heads({n_heads}) should be greater than 0 for SpatialTransformer"
+        assert in_channels % groups == 0, (
+            f"in_channels({in_channels}) should be divisible by num_groups({groups}) for GroupNorm")
+        self.in_channels = in_channels
+        self.context_dim = context_dim
+        self.groups = groups
+        self.norm = nn.GroupNorm(groups, in_channels)
+        self.proj_in = nn.Conv2d(in_channels, in_channels, kernel_size=1, padding=0)
+        self.transformer_blocks = nn.ModuleList(
+            [BasicTransformerBlock(in_channels, n_heads, d_head, dropout=dropout, context_dim=context_dim)
+             for _ in range(n_layers)])
+        self.proj_out = _pack.zero_module(nn.Conv2d(in_channels, in_channels, kernel_size=1, padding=0))
+        self._cache = _pack.PackCache()
+
+    def forward_nhwc(self, x: Tensor, ctx: Optional[Tensor] = None, kvs=None) -> Tensor:
+        """x NHWC bf16; ctx [B, m, Cc] bf16; kvs = optional per-layer precomputed (K, V)."""
+        B, H, W, C = x.shape
+        assert C == self.in_channels, f"input channels {C} should be equal to in_channels {self.in_channels}"
+        c = self._cache
+        g = c.get("g", [self.norm.weight], lambda: _pack.f32(self.norm.weight))
+        b = c.get("b", [self.norm.bias], lambda: _pack.f32(self.norm.bias))
+        wi = c.get("wi", [self.proj_in.weight], lambda: _pack.conv1x1_w(self.proj_in.weight))
+        bi = c.get("bi", [self.proj_in.bias], lambda: _pack.f32(self.proj_in.bias))
+        wo = c.get("wo", [self.proj_out.weight], lambda: _pack.conv1x1_w(self.proj_out.weight))
+        bo = c.get("bo", [self.proj_out.bias], lambda: _pack.f32(self.proj_out.bias))
+        h = ops.group_norm(x, g, b, self.groups, ACT_NONE)
+        t = ops.gemm(h.view(B * H * W, C), wi, bi).view(B, H * W, C)
+        for i, blk in enumerate(self.transformer_blocks):
+            t = blk.forward_tokens(t, ctx, None if kvs is None else kvs[i])
+        o = ops.gemm(t.view(B * H * W, C), wo, bo, residual=x.view(B * H * W, C))
+        return o.view(B, H, W, C)
+
+    def forward(self, x: Tensor, context_emb: Tensor = None) -> Tensor:
+        assert x.shape[1] == self.in_channels, (
+            f"input channels {x.shape[1]} should be equal to in_channels {self.in_channels}")
+        if context_emb is not None:
+            assert context_emb.shape[-1] == self.context_dim, (
+                f"context dim {context_emb.shape[-1]} should be equal to context_dim {self.context_dim}")
+        _pack.require_cuda(x, "SpatialTransformer")
+        ctx = None if context_emb is None else _tokens_bf16(context_emb)
+        o = self.forward_nhwc(ops.nchw_to_nhwc(x, self.act_dtype), ctx)
+        return ops.nhwc_to_nchw(o, x.dtype)

@@ -207,13 +207,24 @@ def conv3x3(x: Tensor, w: Tensor, bias: Optional[Tensor], temb: Optional[Tensor]
     return out
 
 
-def conv3x3_in(x_nchw: Tensor, w: Tensor, bias: Tensor, out_dtype=torch.bfloat16) -> Tensor:
-    B, Cin, H, W = x_nchw.shape
+def conv3x3_in(x_nchw: Tensor, w: Tensor, bias: Tensor, out_dtype=torch.bfloat16, repeat: int = 1) -> Tensor:
+    """``repeat`` > 1: output batch = repeat * input batch, image b reads input b % B_in (virtual cat)."""
+    Bs, Cin, H, W = x_nchw.shape
+    B = Bs * repeat
     Cout = w.shape[0]
     assert w.dtype == torch.float32 and w.is_contiguous() and bias.dtype == torch.float32
     out = torch.empty(B, H, W, Cout, device=x_nchw.device, dtype=out_dtype)
     check(_lib.lib().sdb_conv3x3_in(_ptr(x_nchw.contiguous()), _dt(x_nchw), _ptr(w), _ptr(bias), _ptr(out),
-                                    _dt(out), B, H, W, Cin, Cout, _stream()), "conv3x3_in")
+                                    _dt(out), B, Bs, H, W, Cin, Cout, _stream()), "conv3x3_in")
+    return out
+
+
+def cfg_combine(eps2: Tensor, guidance: float) -> Tensor:
+    """first + g * (first - second) over the two batch halves (latent_diffusion.py:62-65)."""
+    assert eps2.is_contiguous() and eps2.shape[0] % 2 == 0
+    out = torch.empty((eps2.shape[0] // 2, *eps2.shape[1:]), device=eps2.device, dtype=eps2.dtype)
+    check(_lib.lib().sdb_cfg_combine(_ptr(eps2), guidance, _ptr(out), out.numel(), _dt(eps2), _stream()),
+          "cfg_combine")
     return out
 
 

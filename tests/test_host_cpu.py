@@ -1,0 +1,82 @@
+"""CPU: host-side logic of the drop-in modules -- state_dict compatibility, scheduler tables,
+timestep order, error behaviour.  No kernel is launched."""
+import os
+import sys
+
+import pytest
+import torch
+
+from oracle import sd_oracle as O
+from stable_diffusion_pytorch_b200.models import (AutoEncoderKL, AutoencoderConfig, DDPMConfig, DDPMScheduler,
+                                                  UNetModel, UnetConfig)
+from tests.golden import cases
+
+
+def _ucfg(c: O.UnetCfg) -> UnetConfig:
+    return UnetConfig(num_res_blocks=c.num_res_blocks, n_heads=c.n_heads,
+                      attention_resolutions=list(c.attention_resolutions), channels_list=list(c.channels_list),
+                      time_emb_dim=c.time_emb_dim, dropout=0.0, n_layers=c.n_layers, context_dim=c.context_dim)
+
+
+@pytest.mark.parametrize("cfg", [cases.DEFAULT, cases.TINY, cases.TINY3])
+def test_unet_state_dict_keys_match_reference_layout(cfg):
+    m = UNetModel(cfg.latent_channels, cfg.groups, _ucfg(cfg))
+    shapes = O.unet_param_shapes(cfg)   # pinned to the reference by make_golden.py (strict load)
+    sd = m.state_dict()
+    assert set(sd) == set(shapes)
+    assert all(tuple(sd[k].shape) == shapes[k] for k in sd)
+    m.load_state_dict(O.seeded_state_dict(shapes, 3), strict=True)
+
+
+def test_reference_zero_init_is_kept():
+    m = UNetModel(4, 32, UnetConfig())
+    assert float(m.input_blocks[0][0].out_layers[3].weight.abs().sum()) == 0.0   # resnet2d.py:194-198
+    assert float(m.input_blocks[0][1].proj_out.weight.abs().sum()) == 0.0        # transformer.py:346-348
+    assert m.middle_block[0].groups == 2 and m.middle_block[2].groups == 32      # models/utils.py:112
+    assert m.middle_block[1].transformer_blocks[0].self_attn.d_head == 20        # d_head leak, unet.py:198
+
+
+@pytest.mark.parametrize("cfg", [cases.VAE_DEFAULT, cases.VAE_KL_TINY])
+def test_vae_state_dict(cfg):
+    m = AutoEncoderKL(AutoencoderConfig(autoencoder_channels_list=list(cfg.autoencoder_channels_list),
+                                        groups=cfg.groups))
+    shapes = O.vae_decoder_param_shapes(cfg)
+    sd = m.state_dict()
+    assert all(k in sd and tuple(sd[k].shape) == shapes[k] for k in shapes)
+    assert all(k.startswith(("encoder.", "decoder.", "quant_conv.", "post_quant_conv.")) for k in sd)
+
+
+@pytest.mark.skipif(not os.path.isdir("/root/reference"), reason="reference tree only exists in the build container")
+def test_state_dict_keys_equal_the_live_reference():
+    sys.path.insert(0, "/root/reference")
+    from stable_diffusion.models.unet import UNetModel as RefUNet, UnetConfig as RefCfg
+    from stable_diffusion.models.autoencoder import AutoEncoderKL as RefVae, AutoencoderConfig as RefVaeCfg
+    ref, mine = RefUNet(4, 32, RefCfg()).state_dict(), UNetModel(4, 32, UnetConfig()).state_dict()
+    assert list(ref) == list(mine)          # same keys in the same order
+    assert all(ref[k].shape == mine[k].shape for k in ref)
+    rv, mv = RefVae(RefVaeCfg()).state_dict(), AutoEncoderKL(AutoencoderConfig()).state_dict()
+    assert list(rv) == list(mv) and all(rv[k].shape == mv[k].shape for k in rv)
+
+
+def test_scheduler_tables_bit_exact(golden):
+    s = DDPMScheduler(DDPMConfig())
+    for name in O.TABLE_NAMES:
+        assert (getattr(s, name).numpy() == golden[f"table_{name}"]).all(), name
+    assert (s.noise_time_steps.numpy() == golden["table_noise_time_steps"]).all()
+    rows = s.coef_rows([0, 49])
+    assert rows[0, 4] == 0.0 and rows[1, 4] == (0.5 * s.log_var[49]).exp()
+    assert rows[0, 5] == 1.0 and rows[0, 6] == 0.0
+
+
+def test_errors_mirror_reference_asserts():
+    m = UNetModel(4, 32, UnetConfig())
+    with pytest.raises(AssertionError, match="context dim"):
+        m(torch.zeros(1, 4, 8, 8), torch.zeros(1, dtype=torch.long), torch.zeros(1, 77, 64))
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        m(torch.zeros(1, 4, 8, 8), torch.zeros(1, dtype=torch.long), torch.zeros(1, 77, 768))
+    s = DDPMScheduler(DDPMConfig())
+    with pytest.raises(AssertionError, match="should be less than"):
+        s.step(torch.zeros(1, 4, 8, 8), torch.zeros(1, 4, 8, 8), 1000)
+    v = AutoEncoderKL(AutoencoderConfig())
+    with pytest.raises(AssertionError, match="Expected latent"):
+        v.decode(torch.zeros(1, 3, 8, 8))

@@ -18,6 +18,9 @@ def _load():
         pytest.skip("needs a CUDA device")
     from stable_diffusion_pytorch_b200 import ops as _ops
     ops = _ops
+    # the torch references must be true fp32 (cuDNN / cuBLAS default to TF32 for fp32 inputs)
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
     yield
     assert ops.debug_timeout_flag() == 0, "a kernel hit its bounded mbarrier wait"
 
