@@ -1,0 +1,355 @@
+#!/usr/bin/env python
+"""Benchmark of the latent-diffusion hot path (BASELINE.json config 2 at N = 1).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl reference]
+
+A "step" is one latent-step of the workload batch: the CFG pair of UNet evaluations (UNet batch
+2*B), the guidance combine and the sampler update, i.e. one iteration of the reference's sampling
+loop (models/latent_diffusion.py:109-123).  Metric: latent-steps/s = B * n_gpus * K / time.
+Prints ONE JSON line on rank 0 (see the contract in the task statement / DESIGN.md section 6).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+WORKLOAD = "unet-default bs16 64x64x4 latents, CFG g=7.5 (UNet batch 32), DDIM eta=0, bf16"
+GF_PER_LATENT_STEP = 453.46  # 2 UNet evals @64x64, reference formulation
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--batch", type=int, default=16, help="latents per GPU (weak scaling)")
+    ap.add_argument("--size", type=int, default=64, help="latent height = width")
+    ap.add_argument("--sampler", default="ddim", choices=["ddim", "ddpm"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-graph", action="store_true")
+    return ap.parse_args()
+
+
+def peaks():
+    p = {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        try:
+            d = json.load(open(path))
+            p.update({k: d[k] for k in ("hbm_gbs", "bf16_tflops", "bf16_tflops_sustained") if k in d})
+            p["source"] = "measured"
+        except Exception:
+            pass
+    return p
+
+
+class ClockSampler:
+    """Samples nvidia-smi clocks / throttle reasons DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index: int):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append([c.strip() for c in line.split(",")])
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        sm, mx, reasons = [], None, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            try:
+                sm.append(float(r[0])); mx = float(r[1])
+            except Exception:
+                continue
+            for n, v in zip(names, r[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx, "samples": len(sm),
+                "reasons": sorted(reasons)}
+
+
+# ----------------------------------------------------------------------------------------------
+# CPU legs: the oracle port of the reference's algorithm, timed on the host cores (the only place
+# bench.py executes oracle/).
+# ----------------------------------------------------------------------------------------------
+def cpu_latent_steps(size: int, steps: int, warmup: int, budget_s: float = 25.0):
+    import torch
+    from oracle import sd_oracle as O
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    cfg = O.UnetCfg()
+    sd = O.seeded_state_dict(O.unet_param_shapes(cfg), 13)
+    tab = O.ddpm_tables(O.DdpmCfg())
+    g = torch.Generator().manual_seed(0)
+    x = torch.rand(1, 4, size, size, generator=g)
+    ctx = torch.randn(1, 77, 768, generator=g)
+    unc = torch.randn(1, 77, 768, generator=g)
+    fn = lambda a, b, c: O.unet_forward(sd, cfg, a, b, c)  # noqa: E731
+    times = []
+    with torch.no_grad():
+        for i in range(warmup + steps):
+            t0 = time.perf_counter()
+            t = torch.full((1,), i, dtype=torch.long)
+            eps = O.pred_noise(fn, x, t, ctx, unc, 7.5)
+            x, _ = O.ddim_step(tab, eps, x, i)
+            dt = time.perf_counter() - t0
+            if i >= warmup:
+                times.append(dt)
+            if i >= warmup and sum(times) > budget_s:
+                break
+    n = len(times)
+    total = sum(times)
+    return {"value": n / total, "unit": "latent-steps/s", "cores": cores, "kind": "port",
+            "sample": f"{n} CFG latent-steps of ONE {size}x{size} latent (UNet batch 2, fp32, torch CPU "
+                      f"{torch.get_num_threads()} threads) = 1/16 of the workload batch",
+            "ms_per_step": 1e3 * total / n, "steps": n}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    res = cpu_latent_steps(args.size, max(1, args.steps), max(0, min(args.warmup, 1)))
+    line = {"impl": "reference", "metric": "latent_steps_per_sec", "value": res["value"],
+            "unit": "latent-steps/s", "n_gpus": args.gpus, "steps": res["steps"], "warmup": min(args.warmup, 1),
+            "ms_per_step": res["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "note": "oracle port of the reference's CPU path; each step is a "
+                                                      "bounded sample (1 latent) of the workload batch"},
+            "cpu_baseline": {k: res[k] for k in ("value", "unit", "cores", "kind", "sample")},
+            "e2e": {"value": res["value"], "unit": "latent-steps/s", "h2d_bytes_per_step": 0,
+                    "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+
+
+# ----------------------------------------------------------------------------------------------
+# B200 arm
+# ----------------------------------------------------------------------------------------------
+def build_unet(device):
+    """Repo-default UNet, random init (reference init + every all-zero tensor re-randomised so the
+    zero_module'd convs do real work; weights differ from any checkpoint: data = synthetic)."""
+    import torch
+    from stable_diffusion_pytorch_b200.models import UNetModel, UnetConfig
+    torch.manual_seed(0)
+    m = UNetModel(4, 32, UnetConfig(dropout=0.0)).eval()
+    g = torch.Generator().manual_seed(1)
+    with torch.no_grad():
+        for p in m.parameters():
+            if float(p.abs().sum()) == 0.0:
+                p.copy_(torch.randn(p.shape, generator=g) * 0.02)
+    return m.to(device)
+
+
+def time_kernel(fn, iters=10, warm=3):
+    import torch
+    for _ in range(warm):
+        fn()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters  # ms
+
+
+def kernel_rooflines(B2, size, pk):
+    """Isolated timings (CUDA events, current stream) of the three dominant kernel families at the
+    workload's shapes; algorithmic flops in the reference's formulation."""
+    import math
+    import torch
+    from stable_diffusion_pytorch_b200 import ops
+    dev = "cuda"
+    n = size * size
+    out = []
+    # K4 self-attention, level 0: [B2*8 heads, n, n, d=20]
+    qkv = torch.randn(B2, n, 480, device=dev).to(torch.bfloat16)
+    q, k, v = qkv[:, :, :160], qkv[:, :, 160:320], qkv[:, :, 320:]
+    ms = time_kernel(lambda: ops.attention(q, k, v, 8, 20, 1 / math.sqrt(20)))
+    fl = 4.0 * B2 * 8 * n * n * 20
+    out.append({"kernel": "attention_kernel<32> self-attn d=20", "ms": ms, "flops": fl})
+    # K1 conv3x3 160->160 @ size^2
+    x = torch.randn(B2, size, size, 160, device=dev).to(torch.bfloat16)
+    w = (torch.randn(160, 3, 3, 160, device=dev) * 0.03).to(torch.bfloat16)
+    b = torch.zeros(160, device=dev)
+    ms = time_kernel(lambda: ops.conv3x3(x, w, b))
+    out.append({"kernel": "umma_gemm_kernel conv3x3 160->160", "ms": ms, "flops": 2.0 * B2 * n * 9 * 160 * 160})
+    # K1 conv3x3 320->320 @ (size/2)^2
+    x2 = torch.randn(B2, size // 2, size // 2, 320, device=dev).to(torch.bfloat16)
+    w2 = (torch.randn(320, 3, 3, 320, device=dev) * 0.02).to(torch.bfloat16)
+    b2 = torch.zeros(320, device=dev)
+    ms = time_kernel(lambda: ops.conv3x3(x2, w2, b2))
+    out.append({"kernel": "umma_gemm_kernel conv3x3 320->320", "ms": ms, "flops": 2.0 * B2 * (n // 4) * 9 * 320 * 320})
+    # K3 GEGLU GEMM [B2*n,160]x[160,1280]
+    a = torch.randn(B2 * n, 160, device=dev).to(torch.bfloat16)
+    wg = (torch.randn(1280, 160, device=dev) * 0.05).to(torch.bfloat16)
+    bg = torch.zeros(1280, device=dev)
+    ms = time_kernel(lambda: ops.gemm(a, wg, bg, act=2))
+    out.append({"kernel": "umma_gemm_kernel GEGLU 160->1280", "ms": ms, "flops": 2.0 * B2 * n * 160 * 1280,
+                "bytes": B2 * n * (160 + 640) * 2.0})
+    for o in out:
+        o["tflops"] = o["flops"] / (o["ms"] * 1e-3) / 1e12
+        o["frac_of_bf16_peak"] = o["tflops"] / pk["bf16_tflops"]
+        if "bytes" in o:
+            o["gbs"] = o["bytes"] / (o["ms"] * 1e-3) / 1e9
+            o["frac_of_hbm_peak"] = o["gbs"] / pk["hbm_gbs"]
+    return out
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the B200 path has no CPU fallback "
+                         "(use --impl reference for the CPU baseline)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    from stable_diffusion_pytorch_b200 import ops
+    from stable_diffusion_pytorch_b200.graph_sampler import GraphedLatentStep
+    from stable_diffusion_pytorch_b200.models import DDPMConfig, DDPMScheduler
+    pk = peaks()
+    B, S = args.batch, args.size
+    unet = build_unet(dev)
+    sch = DDPMScheduler(DDPMConfig())
+    gs = GraphedLatentStep(unet, sch, B, S, S, time_steps=50, guidance_scale=7.5, sampler=args.sampler,
+                           dtype=torch.bfloat16, device=dev, seed=1234 + rank)
+    g = torch.Generator().manual_seed(100 + rank)   # each rank owns its shard of the latent batch
+    x_host = torch.rand(B, 4, S, S, generator=g).to(torch.bfloat16).pin_memory()
+    ctx_host = torch.randn(B, 77, 768, generator=g).to(torch.bfloat16).pin_memory()
+    unc = torch.randn(1, 77, 768, generator=torch.Generator().manual_seed(7)).to(torch.bfloat16)
+    out_host = torch.empty_like(x_host).pin_memory()
+    gs.reset(x_host, ctx_host, unc)
+    if not args.no_graph:
+        gs.capture()
+    gs.reset(x_host, ctx_host, unc)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    # ---- device-resident timing --------------------------------------------------------------
+    for _ in range(max(args.warmup, 3)):
+        gs.step()
+    barrier()
+    clk = ClockSampler(local)
+    if rank == 0:
+        clk.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    launches0 = ops.launch_count()
+    e0.record()
+    for _ in range(args.steps):
+        gs.step()
+    e1.record()
+    barrier()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    clocks = clk.stop() if rank == 0 else None
+    eager_launches = ops.launch_count() - launches0
+    # ---- end-to-end timing: host buffers in, host result out, every step ------------------------
+    gs.reset(x_host, ctx_host, unc)
+    for _ in range(3):
+        gs.step_host(x_host, ctx_host, out_host)
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        gs.step_host(x_host, ctx_host, out_host)
+    e1.record()
+    barrier()
+    ms_e2e = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        dist.all_reduce(ms_e2e, op=dist.ReduceOp.MAX)
+    ms, ms_e2e = float(ms), float(ms_e2e)
+    finite = bool(torch.isfinite(gs.x.float()).all())
+    flag = ops.debug_timeout_flag()
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+    n_lat = B * world
+    value = n_lat * args.steps / (ms * 1e-3)
+    e2e = n_lat * args.steps / (ms_e2e * 1e-3)
+    kr = kernel_rooflines(2 * B, S, pk)
+    dom = kr[0]
+    traffic = None
+    tpath = os.path.join(ROOT, "profiles", "roofline_traffic.json")
+    if os.path.exists(tpath):
+        try:
+            traffic = json.load(open(tpath)).get("attention_dram_bytes_per_launch")
+        except Exception:
+            traffic = None
+    step_tf = GF_PER_LATENT_STEP * 1e9 * B * (S * S / 4096.0) / (ms / args.steps * 1e-3) / 1e12
+    line = {
+        "metric": "latent_steps_per_sec", "value": value, "unit": "latent-steps/s", "n_gpus": world,
+        "steps": args.steps, "warmup": max(args.warmup, 3), "ms_per_step": ms / args.steps,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+        "config": {"workload": WORKLOAD if (B, S) == (16, 64) else f"unet-default bs{B} {S}x{S}x4, CFG, {args.sampler}",
+                   "batch_per_gpu": B, "latent": [4, S, S], "sampler": args.sampler, "guidance_scale": 7.5,
+                   "parallelism": f"latent-batch sharded x{world}, no collective in the step",
+                   "cuda_graph": not args.no_graph,
+                   "l2": "no flush: per-step activation working set (~3 GB) is far larger than the 126 MB L2"},
+        "e2e": {"value": e2e, "unit": "latent-steps/s", "ms_per_step": ms_e2e / args.steps,
+                "h2d_bytes_per_step": x_host.numel() * 2 + ctx_host.numel() * 2,
+                "d2h_bytes_per_step": out_host.numel() * 2},
+        "gpu_launches": (gs.launches_per_step * args.steps) if gs.graph is not None else eager_launches,
+        "launches_per_step": gs.launches_per_step if gs.graph is not None else eager_launches // max(args.steps, 1),
+        "clocks": clocks,
+        "roofline": {"bound": "tensor", "kernel": dom["kernel"], "achieved": dom["tflops"], "peak": pk["bf16_tflops"],
+                     "unit": "TFLOP/s", "frac": dom["tflops"] / pk["bf16_tflops"], "traffic": traffic,
+                     "peak_source": pk["source"] + " (burst: kernel timed alone)", "ms_per_launch": dom["ms"],
+                     "note": "d_head=20 attention is MUFU-exp/softmax bound, not tensor bound (DESIGN.md 4)"},
+        "kernels": kr,
+        "step_roofline": {"algorithmic_tflops": step_tf, "peak_sustained": pk["bf16_tflops_sustained"],
+                          "frac": step_tf / pk["bf16_tflops_sustained"]},
+        "finite": finite, "timeout_flag": flag,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        try:
+            cb = cpu_latent_steps(S, 3, 1)
+            line["cpu_baseline"] = {k: cb[k] for k in ("value", "unit", "cores", "kind", "sample")}
+        except Exception as ex:  # pragma: no cover
+            line["cpu_baseline"] = {"error": repr(ex)}
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_b200(a)

@@ -71,8 +71,9 @@ int sdb_timestep_embed(const int64_t* t, const float* freq, void* out, int B, in
  * c5*x0 + c6*eps).  fp32 mode performs each multiply/add with a separate IEEE rounding in the
  * reference's order, so it is bit-exact against the CPU reference.
  *   eps   : [2*B or B, n_per] network output (NCHW flattened), dtype `dtype`
- *   noise : same dtype, [B, n_per] pre-drawn host noise, or NULL -> in-kernel Philox N(0,1)
- *           keyed by (seed, slot) (statistical parity only), ignored when sigma == 0
+ *   noise : same dtype, [B, n_per] pre-drawn host noise ([n_slots, B, n_per], indexed by the device
+ *           slot, when slot_dev is given), or NULL -> in-kernel Philox N(0,1) keyed by
+ *           (seed, slot) (statistical parity only); ignored when sigma == 0
  *   x_prev, x0 (x0 may be NULL): [B, n_per] */
 int sdb_cfg_sampler_step(const void* eps, const void* x_t, const void* noise, const float* coef,
                          const int32_t* slot_dev, int slot, int kind, int cfg_mode, float guidance,

@@ -85,7 +85,10 @@ cfg_sampler_step_kernel(const T* __restrict__ eps, const T* __restrict__ x_t,
                         const int32_t* __restrict__ slot_dev, int slot, int kind, int cfg_mode,
                         float g, float scale_factor, uint64_t seed, T* __restrict__ x_prev,
                         T* __restrict__ x0_out, int64_t total /* B*n_per, multiple of 4 */) {
-  if (slot_dev) slot = *slot_dev;
+  if (slot_dev) {
+    slot = *slot_dev;
+    if (noise) noise += (size_t)slot * (size_t)total;  // device-slot mode: noise is a per-slot table
+  }
   const float* c = coef + 8 * (size_t)slot;
   const float c0 = c[0], c1 = c[1], c2 = c[2], c3 = c[3], sigma = c[4], d0 = c[5], d1 = c[6];
   const int64_t stride = (int64_t)gridDim.x * blockDim.x * 4;

@@ -52,7 +52,9 @@ def cfg_sampler_step(eps: Tensor, x_t: Tensor, noise: Optional[Tensor], coef: Te
     assert eps.is_contiguous() and x_t.is_contiguous() and eps.dtype == x_t.dtype
     assert eps.shape[0] == (2 * B if cfg_mode else B)
     if noise is not None:
-        assert noise.is_contiguous() and noise.dtype == x_t.dtype and noise.numel() == x_t.numel()
+        assert noise.is_contiguous() and noise.dtype == x_t.dtype
+        # device-slot mode: noise is the per-slot table [n_slots, B, ...]
+        assert noise.numel() == x_t.numel() or (slot_dev is not None and noise.numel() % x_t.numel() == 0)
     if x_prev is None:
         x_prev = torch.empty_like(x_t)
     if x0 is None and want_x0:
@@ -121,7 +123,12 @@ def group_norm(x1: Tensor, gamma: Tensor, beta: Tensor, groups: int, act: int = 
     C2 = x2.shape[-1] if x2 is not None else 0
     assert x1.is_contiguous() and (x2 is None or (x2.is_contiguous() and x2.dtype == x1.dtype))
     hw = H * W
-    partial, stats = (scratch or _default_gn_scratch).get(x1.device, B, hw, C1 + C2, groups)
+    if scratch is not None:
+        partial, stats = scratch.get(x1.device, B, hw, C1 + C2, groups)
+    else:  # per-call scratch from torch's caching allocator: safe under CUDA-graph capture
+        chunks = _lib.lib().sdb_groupnorm_chunks(hw)
+        partial = torch.empty(B * chunks * (C1 + C2) * 2, device=x1.device, dtype=torch.float32)
+        stats = torch.empty(B * groups * 2, device=x1.device, dtype=torch.float32)
     if out is None:
         out = torch.empty(B, H, W, C1 + C2, device=x1.device, dtype=out_dtype or x1.dtype)
     L = _lib.lib()
