@@ -179,6 +179,16 @@ int sdb_attention(const void* q, int64_t ldq, const void* k, int64_t ldk, const 
                   int64_t ldv, void* out, int64_t ldo, int B, int heads, int n, int m, int d,
                   float scale, int dtype, void* stream);
 
+/* Tensor-core (tcgen05 + TMEM + TMA) variant for small head dims, d <= 20 (the UNet's d_head = 20).
+ * Operands are HEAD-PADDED to 32 columns by the projection GEMM (weights packed once at load):
+ * head h of q / k / v occupies columns [32h, 32h+32) of rows with stride ldq / ldk / ldv;
+ * q and k are zero in columns d..31, v holds 1.0 in column d (so P.V also yields the softmax
+ * denominator) and anything finite beyond.  out stays dense: [B, n, heads*d], row stride ldo.
+ * bf16 in/out, fp32 softmax state; any n, m (ragged tails are masked). */
+int sdb_attention_p32(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
+                      int64_t ldv, void* out, int64_t ldo, int B, int heads, int n, int m, int d,
+                      float scale, void* stream);
+
 /* ---- elementwise helpers --------------------------------------------------------------------*/
 int sdb_silu(const void* x, void* out, int64_t n, int dtype, int out_dtype, void* stream);
 int sdb_cast(const void* x, int src_dtype, void* out, int dst_dtype, int64_t n, void* stream);

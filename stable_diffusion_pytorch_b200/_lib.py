@@ -59,6 +59,7 @@ SIGNATURES = {
     "sdb_conv1x1_nchw_small": (_i, [_p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p]),
     "sdb_upsample2x": (_i, [_p, _p, _i, _i, _i, _i, _i, _p]),
     "sdb_attention": (_i, [_p, _i64, _p, _i64, _p, _i64, _p, _i64, _i, _i, _i, _i, _i, _f, _i, _p]),
+    "sdb_attention_p32": (_i, [_p, _i64, _p, _i64, _p, _i64, _p, _i64, _i, _i, _i, _i, _i, _f, _p]),
     "sdb_silu": (_i, [_p, _p, _i64, _i, _i, _p]),
     "sdb_cast": (_i, [_p, _i, _p, _i, _i64, _p]),
     "sdb_to_uint8_image": (_i, [_p, _i, _p, _i, _i, _i, _i, _p]),

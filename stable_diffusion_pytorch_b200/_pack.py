@@ -66,6 +66,26 @@ def geglu_w(w: Tensor, b: Tensor) -> Tuple[Tensor, Tensor]:
     return wi.to(torch.bfloat16).contiguous(), bi.to(torch.float32).contiguous()
 
 
+HEAD_PAD = 32  # padded head width of the tcgen05 attention operands (sdb_attention_p32)
+
+
+def head_pad_w(w: Tensor, heads: int, d: int) -> Tensor:
+    """Projection weight [heads*d, K] -> [heads*32, K]: head h's rows move to [32h, 32h+d), the rest are
+    zero, so the GEMM writes zero-padded 64-byte head rows (what the attention TMA boxes load)."""
+    K = w.shape[1]
+    out = torch.zeros(heads, HEAD_PAD, K, dtype=w.dtype, device=w.device)
+    out[:, :d] = w.detach().reshape(heads, d, K)
+    return out.reshape(heads * HEAD_PAD, K)
+
+
+def head_pad_ones_bias(heads: int, d: int, device) -> Tensor:
+    """fp32 bias [heads*32], 1.0 at column d of every head: the V projection then carries the
+    column of ones that makes P.V also produce the softmax denominator."""
+    b = torch.zeros(heads, HEAD_PAD, dtype=torch.float32, device=device)
+    b[:, d] = 1.0
+    return b.reshape(heads * HEAD_PAD)
+
+
 def require_cuda(x: Tensor, what: str) -> None:
     if not x.is_cuda:
         raise RuntimeError(f"{what}: stable_diffusion_pytorch_b200 has no CPU fallback; got a {x.device} tensor")

@@ -1,0 +1,461 @@
+// K4 (tensor-core path): flash-style attention for small head dims on tcgen05 / TMEM / TMA.
+// (reference: modules/transformer.py:93-114 -- softmax(Q K^T * scale) V per (batch, head))
+//
+// The UNet's head dim is 20 (SURVEY top item 7): per (query, key) pair there are 80 useful flops
+// and one exp, so the kernel is bound by the MUFU ex2 pipe (16/clk/SM measured) and the issue
+// slots of the softmax warps, never by the tensor pipe.  Design:
+//   * operands arrive HEAD-PADDED from the projection GEMM: head h of Q / K / V lives at columns
+//     [32h, 32h+32) with zeros beyond d for Q and K, and V carries a column of ones at index d
+//     so that the P.V product also yields the softmax denominator (no per-element adds);
+//   * one CTA = 256 queries of one (batch, head): two softmax warpgroups (128 rows each, ONE ROW
+//     PER THREAD -> no shuffles), one TMA warp, one MMA-issuing warp;
+//   * S = Q K^T (128 x 128 fp32) is produced in TMEM by two K=16 tcgen05.mma, read back with
+//     tcgen05.ld, exponentiated, written back to TMEM as packed bf16 P and consumed directly as
+//     the A operand of the P.V tcgen05.mma (B = V tile, MN-major straight from the TMA box);
+//   * ~3/8 of the exponentials are evaluated on the FMA pipe (Cody-Waite split + degree-3
+//     polynomial in packed f32x2 arithmetic) so MUFU and FMA pipes finish together;
+//   * O (128 x 32 fp32) is read back per key tile and folded into registers with the usual
+//     online-softmax rescale (cheap: 21 live columns).
+#include <stdlib.h>
+
+#include "common.cuh"
+
+namespace sdb {
+
+constexpr int kFaThreads = 384;  // warps 0-3: TMA / MMA / TMEM alloc / idle; 4-7, 8-11: softmax
+constexpr int kFaStages = 4;
+constexpr int kFaBM = 128;       // query rows per softmax warpgroup
+constexpr int kFaBN = 128;       // keys per tile
+constexpr int kFaDP = 32;        // padded head dim (64-byte rows, SWIZZLE_64B)
+constexpr int kFaQBytes = kFaBM * kFaDP * 2;       // 8 KB
+constexpr int kFaKVBytes = kFaBN * kFaDP * 2;      // 8 KB each for K and V
+constexpr int kFaStageBytes = 2 * kFaKVBytes;
+constexpr int kFaSmem = 2 * kFaQBytes + kFaStages * kFaStageBytes + 1024 /*align*/ + 256 /*barriers*/;
+
+struct FaParams {
+  CUtensorMap tmQ, tmK, tmV;
+  __nv_bfloat16* out;
+  long long ldo;
+  int n, m, d, heads;
+  float scale_log2;
+};
+
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const void* tmap, uint32_t bar, int c0, int c1,
+                                            int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5}], [%2];"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+// D[tmem] (+)= A[tmem] * B[smem desc]
+__device__ __forceinline__ void umma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc,
+                                            uint32_t accumulate) {
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t"
+      "}\n"
+      ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_32x16(uint32_t taddr, const uint32_t (&v)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0],"
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+      ::"r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
+      "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
+      : "memory");
+}
+template <int OFF>
+__device__ __forceinline__ void tmem_ld_32x32_at(uint32_t taddr, uint32_t (&v)[128]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32"
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15,"
+      " %16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(v[OFF + 0]), "=r"(v[OFF + 1]), "=r"(v[OFF + 2]), "=r"(v[OFF + 3]), "=r"(v[OFF + 4]), "=r"(v[OFF + 5]),
+        "=r"(v[OFF + 6]), "=r"(v[OFF + 7]), "=r"(v[OFF + 8]), "=r"(v[OFF + 9]), "=r"(v[OFF + 10]), "=r"(v[OFF + 11]),
+        "=r"(v[OFF + 12]), "=r"(v[OFF + 13]), "=r"(v[OFF + 14]), "=r"(v[OFF + 15]), "=r"(v[OFF + 16]), "=r"(v[OFF + 17]),
+        "=r"(v[OFF + 18]), "=r"(v[OFF + 19]), "=r"(v[OFF + 20]), "=r"(v[OFF + 21]), "=r"(v[OFF + 22]), "=r"(v[OFF + 23]),
+        "=r"(v[OFF + 24]), "=r"(v[OFF + 25]), "=r"(v[OFF + 26]), "=r"(v[OFF + 27]), "=r"(v[OFF + 28]), "=r"(v[OFF + 29]),
+        "=r"(v[OFF + 30]), "=r"(v[OFF + 31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+// MN-major B operand (the V tile exactly as the TMA box lands: [keys][32] bf16, 64-byte rows,
+// SWIZZLE_64B): 8-key groups are 512 B apart (SBO); one swizzle atom wide in N so LBO is unused.
+__device__ __forceinline__ uint64_t umma_smem_desc_mn64(uint32_t saddr) {
+  uint64_t d = 0;
+  d |= static_cast<uint64_t>((saddr & 0x3ffff) >> 4);
+  d |= 1ull << 16;
+  d |= static_cast<uint64_t>(512 >> 4) << 32;
+  d |= 1ull << 46;
+  d |= 4ull << 61;  // SWIZZLE_64B
+  return d;
+}
+
+__device__ __forceinline__ float ex2_mufu(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float max3(float a, float b, float c) {
+  float d;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+  return d;
+}
+// (d0, d1) = (a0, a1) * (b0, b1) + (c0, c1) in one FFMA2
+__device__ __forceinline__ void ffma2(float& d0, float& d1, float a0, float a1, float b0, float b1, float c0,
+                                      float c1) {
+  asm("{\n\t.reg .b64 ra, rb, rc, rd;\n\t"
+      "mov.b64 ra, {%2, %3};\n\tmov.b64 rb, {%4, %5};\n\tmov.b64 rc, {%6, %7};\n\t"
+      "fma.rn.f32x2 rd, ra, rb, rc;\n\t"
+      "mov.b64 {%0, %1}, rd;\n\t}"
+      : "=f"(d0), "=f"(d1)
+      : "f"(a0), "f"(a1), "f"(b0), "f"(b1), "f"(c0), "f"(c1));
+}
+__device__ __forceinline__ void fadd2(float& d0, float& d1, float a0, float a1, float b0, float b1) {
+  asm("{\n\t.reg .b64 ra, rb, rd;\n\t"
+      "mov.b64 ra, {%2, %3};\n\tmov.b64 rb, {%4, %5};\n\t"
+      "add.rn.f32x2 rd, ra, rb;\n\t"
+      "mov.b64 {%0, %1}, rd;\n\t}"
+      : "=f"(d0), "=f"(d1)
+      : "f"(a0), "f"(a1), "f"(b0), "f"(b1));
+}
+// exp2 of two non-positive arguments on the FMA pipe: x = floor(x) + f, 2^f by a degree-3 minimax
+// polynomial on [0, 1), exponent patched in with an integer add.  Relative error ~1e-4, well
+// inside the bf16 rounding of P.
+__device__ __forceinline__ void ex2_poly2(float& x0, float& x1) {
+  const float kMagic = 12582912.0f;  // 2^23 + 2^22: floor(x) lands in the low mantissa bits
+  x0 = fmaxf(x0, -125.0f);
+  x1 = fmaxf(x1, -125.0f);
+  float r0, r1, f0, f1, p0, p1;
+  asm("{\n\t.reg .b64 ra, rb, rd;\n\t"
+      "mov.b64 ra, {%2, %3};\n\tmov.b64 rb, {%4, %4};\n\t"
+      "add.rm.ftz.f32x2 rd, ra, rb;\n\t"
+      "mov.b64 {%0, %1}, rd;\n\t}"
+      : "=f"(r0), "=f"(r1)
+      : "f"(x0), "f"(x1), "f"(kMagic));
+  // f = x - (r - magic)  (both subtractions exact)
+  ffma2(f0, f1, r0, r1, -1.0f, -1.0f, kMagic, kMagic);  // magic - r = -floor(x)
+  fadd2(f0, f1, f0, f1, x0, x1);
+  ffma2(p0, p1, f0, f1, 0.077119089663028717041015625f, 0.077119089663028717041015625f,
+        0.227564394474029541015625f, 0.227564394474029541015625f);
+  ffma2(p0, p1, p0, p1, f0, f1, 0.695146143436431884765625f, 0.695146143436431884765625f);
+  ffma2(p0, p1, p0, p1, f0, f1, 1.0f, 1.0f);
+  x0 = __int_as_float(__float_as_int(p0) + (__float_as_int(r0) << 23));
+  x1 = __int_as_float(__float_as_int(p1) + (__float_as_int(r1) << 23));
+}
+
+template <int REGS>
+__device__ __forceinline__ void setmaxnreg_inc() {
+  asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(REGS));
+}
+template <int REGS>
+__device__ __forceinline__ void setmaxnreg_dec() {
+  asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(REGS));
+}
+
+// kPoly = number of element PAIRS out of every 8 pairs exponentiated on the FMA pipe
+template <int kPoly>
+__global__ void __launch_bounds__(kFaThreads, 1)
+attention_umma_kernel(const __grid_constant__ FaParams p) {
+  extern __shared__ __align__(1024) uint8_t fa_smem[];
+  const uint32_t base = (smem_u32(fa_smem) + 1023u) & ~1023u;
+  const uint32_t sQ = base;                                  // 2 x 8 KB
+  const uint32_t sKV = base + 2 * kFaQBytes;                 // stages x (K 8 KB | V 8 KB)
+  const uint32_t bars = sKV + kFaStages * kFaStageBytes;
+  const uint32_t bar_q = bars;
+  auto bar_kv_full = [&](int s) { return bars + 8u * (1 + s); };
+  auto bar_kv_empty = [&](int s) { return bars + 8u * (1 + kFaStages + s); };
+  auto bar_s_full = [&](int w) { return bars + 8u * (1 + 2 * kFaStages + w); };
+  auto bar_s_free = [&](int w) { return bars + 8u * (3 + 2 * kFaStages + w); };
+  auto bar_p_full = [&](int w) { return bars + 8u * (5 + 2 * kFaStages + w); };
+  auto bar_o_full = [&](int w) { return bars + 8u * (7 + 2 * kFaStages + w); };
+  const uint32_t tmem_slot = bars + 8u * (9 + 2 * kFaStages);
+  volatile uint32_t* tmem_slot_ptr =
+      reinterpret_cast<volatile uint32_t*>(fa_smem + (tmem_slot - smem_u32(fa_smem)));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int b = blockIdx.z, h = blockIdx.y, q0 = blockIdx.x * (2 * kFaBM);
+  const int T = (p.m + kFaBN - 1) / kFaBN;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&p.tmQ);
+    prefetch_tmap(&p.tmK);
+    prefetch_tmap(&p.tmV);
+    mbar_init(bar_q, 1);
+    for (int s = 0; s < kFaStages; ++s) {
+      mbar_init(bar_kv_full(s), 1);
+      mbar_init(bar_kv_empty(s), 1);
+    }
+    for (int w = 0; w < 2; ++w) {
+      mbar_init(bar_s_full(w), 1);
+      mbar_init(bar_s_free(w), 4);
+      mbar_init(bar_p_full(w), 4);
+      mbar_init(bar_o_full(w), 1);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_slot, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+  // TMEM columns per warpgroup w: S at 256w + [0,128), P at 256w + [128,192), O at 256w + [192,224)
+
+  if (warp < 4) {
+    setmaxnreg_dec<56>();
+    if (warp == 0 && lane == 0) {
+      // ===================== TMA producer =====================
+      mbar_arrive_expect_tx(bar_q, 2 * kFaQBytes);
+      tma_load_3d(sQ, &p.tmQ, bar_q, h * kFaDP, q0, b);
+      tma_load_3d(sQ + kFaQBytes, &p.tmQ, bar_q, h * kFaDP, q0 + kFaBM, b);
+      bool ok = true;
+      for (int j = 0; j < T && ok; ++j) {
+        const int s = j % kFaStages;
+        ok = mbar_wait(bar_kv_empty(s), (((uint32_t)(j / kFaStages)) & 1u) ^ 1u);
+        if (!ok) break;
+        const uint32_t sk = sKV + (uint32_t)s * kFaStageBytes;
+        mbar_arrive_expect_tx(bar_kv_full(s), kFaStageBytes);
+        tma_load_3d(sk, &p.tmK, bar_kv_full(s), h * kFaDP, j * kFaBN, b);
+        tma_load_3d(sk + kFaKVBytes, &p.tmV, bar_kv_full(s), h * kFaDP, j * kFaBN, b);
+      }
+    } else if (warp == 1 && lane == 0) {
+      // ===================== MMA issuer =====================
+      const uint32_t idesc_s = umma_idesc_bf16(kFaBM, kFaBN);
+      const uint32_t idesc_o = umma_idesc_bf16(kFaBM, kFaDP) | (1u << 16);  // B (= V) is MN-major
+      auto issue_s = [&](int w, int stage) {
+        const uint64_t adesc = umma_smem_desc(sQ + (uint32_t)w * kFaQBytes, 64);
+        const uint64_t bdesc = umma_smem_desc(sKV + (uint32_t)stage * kFaStageBytes, 64);
+        const uint32_t d = tmem_base + (uint32_t)w * 256u;
+        umma_f16(d, adesc, bdesc, idesc_s, 0u);
+        umma_f16(d, adesc + 2, bdesc + 2, idesc_s, 1u);
+        umma_commit(bar_s_full(w));
+      };
+      bool ok = mbar_wait(bar_q, 0) && mbar_wait(bar_kv_full(0), 0);
+      if (ok) {
+        tc_fence_after();
+        issue_s(0, 0);
+        issue_s(1, 0);
+      }
+      for (int j = 0; j < T && ok; ++j) {
+        const int s = j % kFaStages, sn = (j + 1) % kFaStages;
+        const uint32_t par = (uint32_t)j & 1u;
+        if (j + 1 < T) ok = mbar_wait(bar_kv_full(sn), ((uint32_t)((j + 1) / kFaStages)) & 1u);
+        for (int w = 0; w < 2 && ok; ++w) {
+          if (j + 1 < T) {
+            ok = mbar_wait(bar_s_free(w), par);
+            if (!ok) break;
+            tc_fence_after();
+            issue_s(w, sn);
+          }
+          ok = mbar_wait(bar_p_full(w), par);
+          if (!ok) break;
+          tc_fence_after();
+          const uint64_t vdesc = umma_smem_desc_mn64(sKV + (uint32_t)s * kFaStageBytes + kFaKVBytes);
+          const uint32_t d = tmem_base + (uint32_t)w * 256u + 192u;
+          const uint32_t a = tmem_base + (uint32_t)w * 256u + 128u;
+#pragma unroll
+          for (int kk = 0; kk < kFaBN / 16; ++kk)
+            umma_f16_ts(d, a + (uint32_t)kk * 8u, vdesc + (uint64_t)(kk * 64), idesc_o, kk ? 1u : 0u);
+          umma_commit(bar_o_full(w));
+        }
+        if (ok) umma_commit(bar_kv_empty(s));
+      }
+    }
+  } else {
+    // ===================== softmax warpgroups: one query row per thread =====================
+    setmaxnreg_inc<224>();
+    const int w = (warp - 4) >> 2, quarter = warp & 3;
+    const uint32_t tw = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)w * 256u;
+    const float c = p.scale_log2;
+    float acc[kFaDP];
+#pragma unroll
+    for (int i = 0; i < kFaDP; ++i) acc[i] = 0.f;
+    float m_run = -INFINITY;
+    bool ok = true;
+    for (int j = 0; j < T; ++j) {
+      const uint32_t par = (uint32_t)j & 1u;
+      if (ok) ok = mbar_wait(bar_s_full(w), par);
+      tc_fence_after();
+      uint32_t su[128];
+      tmem_ld_32x32_at<0>(tw + 0, su);
+      tmem_ld_32x32_at<32>(tw + 32, su);
+      tmem_ld_32x32_at<64>(tw + 64, su);
+      tmem_ld_32x32_at<96>(tw + 96, su);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_s_free(w));
+      // fold the previous tile's P.V (relative to m_run) into the register accumulator
+      if (j > 0) {
+        if (ok) ok = mbar_wait(bar_o_full(w), par ^ 1u);
+        tc_fence_after();
+        uint32_t o[32];
+        tmem_ld_32x32(tw + 192, o);
+        tmem_ld_wait();
+#pragma unroll
+        for (int i = 0; i < 24; ++i) acc[i] += __uint_as_float(o[i]);
+      }
+      // ragged key tail: keys >= m contribute exp2(-inf) = 0
+      if (j == T - 1 && (p.m & (kFaBN - 1)) != 0) {
+        const int valid = p.m - j * kFaBN;
+#pragma unroll
+        for (int i = 0; i < 128; ++i)
+          if (i >= valid) su[i] = 0xff800000u;
+      }
+      // row max (3-input max, 4 independent chains)
+      float mx[4] = {m_run, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+      for (int i = 0; i < 128; i += 8) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          mx[k] = max3(mx[k], __uint_as_float(su[i + 2 * k]), __uint_as_float(su[i + 2 * k + 1]));
+      }
+      const float m_new = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+      const float alpha = ex2_mufu((m_run - m_new) * c);  // first tile: exp2(-inf) = 0
+      m_run = m_new;
+      const float negm = -m_new * c;
+#pragma unroll
+      for (int i = 0; i < 24; ++i) acc[i] *= alpha;
+      // P = exp2(s*c - m*c) -> packed bf16 -> TMEM (A operand of P.V)
+#pragma unroll
+      for (int ch = 0; ch < 4; ++ch) {
+        uint32_t pk[16];
+#pragma unroll
+        for (int g = 0; g < 2; ++g) {        // 8 pairs per group
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const int i = ch * 32 + g * 16 + 2 * k;
+            float x0, x1;
+            ffma2(x0, x1, __uint_as_float(su[i]), __uint_as_float(su[i + 1]), c, c, negm, negm);
+            if (k < kPoly) {
+              ex2_poly2(x0, x1);
+            } else {
+              x0 = ex2_mufu(x0);
+              x1 = ex2_mufu(x1);
+            }
+            pk[g * 8 + k] = pack_bf16x2(x0, x1);
+          }
+        }
+        tmem_st_32x16(tw + 128 + ch * 16, pk);
+      }
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_p_full(w));
+    }
+    // ---- last tile's P.V, normalise, store ---------------------------------------------------
+    if (ok) ok = mbar_wait(bar_o_full(w), ((uint32_t)(T - 1)) & 1u);
+    tc_fence_after();
+    {
+      uint32_t o[32];
+      tmem_ld_32x32(tw + 192, o);
+      tmem_ld_wait();
+#pragma unroll
+      for (int i = 0; i < 24; ++i) acc[i] += __uint_as_float(o[i]);
+    }
+    const int row = q0 + w * kFaBM + quarter * 32 + lane;
+    if (row < p.n && ok) {
+      float den = acc[0];
+#pragma unroll
+      for (int i = 1; i < 24; ++i)
+        if (i == p.d) den = acc[i];
+      const float inv = 1.0f / den;
+      __nv_bfloat16* og = p.out + ((long long)b * p.n + row) * p.ldo + h * p.d;
+#pragma unroll
+      for (int i = 0; i < 24; i += 4) {
+        if (i < p.d) {
+          uint2 v = make_uint2(pack_bf16x2(acc[i] * inv, acc[i + 1] * inv),
+                               pack_bf16x2(acc[i + 2] * inv, acc[i + 3] * inv));
+          *reinterpret_cast<uint2*>(og + i) = v;
+        }
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+}  // namespace sdb
+
+extern "C" int sdb_attention_p32(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
+                                 int64_t ldv, void* out, int64_t ldo, int B, int heads, int n, int m, int d,
+                                 float scale, void* stream) {
+  using namespace sdb;
+  SDB_CHECK_ARG(q && k && v && out && B > 0 && heads > 0 && n > 0 && m > 0, "attention_p32: bad args");
+  SDB_CHECK_ARG(d > 0 && d <= 20 && d % 4 == 0, "attention_p32: head dim (%d) must be a multiple of 4, <= 20", d);
+  SDB_CHECK_ARG(ldq % 8 == 0 && ldk % 8 == 0 && ldv % 8 == 0 && ldo % 4 == 0,
+                "attention_p32: ldq/ldk/ldv must be multiples of 8 (16-byte TMA rows), ldo of 4");
+  SDB_CHECK_ARG(ldq >= heads * 32 && ldk >= heads * 32 && ldv >= heads * 32,
+                "attention_p32: row strides must cover heads*32 padded columns");
+  SDB_CHECK_ARG(((uintptr_t)q & 15) == 0 && ((uintptr_t)k & 15) == 0 && ((uintptr_t)v & 15) == 0 &&
+                    ((uintptr_t)out & 7) == 0,
+                "attention_p32: q/k/v must be 16-byte aligned, out 8-byte aligned");
+  SDB_CHECK_ARG(heads <= 65535 && B <= 65535, "attention_p32: grid too large");
+  FaParams p;
+  memset(&p, 0, sizeof(p));
+  const uint32_t box[3] = {32, 128, 1};
+  {
+    uint64_t dims[3] = {(uint64_t)heads * 32, (uint64_t)n, (uint64_t)B};
+    uint64_t st[3] = {0, (uint64_t)ldq * 2, (uint64_t)n * ldq * 2};
+    int rc = sdb_make_tensor_map(&p.tmQ, q, 2, 3, dims, st, box, 64);
+    if (rc) return rc;
+  }
+  {
+    uint64_t dims[3] = {(uint64_t)heads * 32, (uint64_t)m, (uint64_t)B};
+    uint64_t st[3] = {0, (uint64_t)ldk * 2, (uint64_t)m * ldk * 2};
+    int rc = sdb_make_tensor_map(&p.tmK, k, 2, 3, dims, st, box, 64);
+    if (rc) return rc;
+    st[1] = (uint64_t)ldv * 2;
+    st[2] = (uint64_t)m * ldv * 2;
+    rc = sdb_make_tensor_map(&p.tmV, v, 2, 3, dims, st, box, 64);
+    if (rc) return rc;
+  }
+  p.out = (__nv_bfloat16*)out;
+  p.ldo = ldo;
+  p.n = n; p.m = m; p.d = d; p.heads = heads;
+  p.scale_log2 = scale * 1.4426950408889634f;
+  // share of exponentials evaluated on the FMA pipe: kPoly pairs out of 8 (tuning aid: SDB_FA_POLY)
+  static int poly = -1;
+  if (poly < 0) {
+    const char* e = getenv("SDB_FA_POLY");
+    poly = e ? atoi(e) : 3;
+    if (poly < 0 || poly > 5) poly = 3;
+  }
+  dim3 grid((n + 2 * kFaBM - 1) / (2 * kFaBM), heads, B);
+#define SDB_FA_LAUNCH(P)                                                                                   \
+  case P: {                                                                                                \
+    static bool attr_set[64] = {false};                                                                    \
+    int dev = 0;                                                                                           \
+    SDB_CUDA_OK(cudaGetDevice(&dev));                                                                      \
+    if (dev < 0 || dev >= 64 || !attr_set[dev]) {                                                          \
+      SDB_CUDA_OK(cudaFuncSetAttribute(attention_umma_kernel<P>, cudaFuncAttributeMaxDynamicSharedMemorySize, \
+                                       kFaSmem));                                                          \
+      if (dev >= 0 && dev < 64) attr_set[dev] = true;                                                      \
+    }                                                                                                      \
+    attention_umma_kernel<P><<<grid, kFaThreads, kFaSmem, sdb_stream(stream)>>>(p);                        \
+  } break;
+  switch (poly) {
+    SDB_FA_LAUNCH(0)
+    SDB_FA_LAUNCH(1)
+    SDB_FA_LAUNCH(2)
+    SDB_FA_LAUNCH(3)
+    SDB_FA_LAUNCH(4)
+    SDB_FA_LAUNCH(5)
+  }
+#undef SDB_FA_LAUNCH
+  SDB_LAUNCH_OK();
+  return SDB_OK;
+}

@@ -5,4 +5,5 @@
 #include "norm.cu"
 #include "conv_small.cu"
 #include "attention.cu"
+#include "attention_umma.cu"
 #include "gemm_umma.cu"

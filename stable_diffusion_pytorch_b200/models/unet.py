@@ -110,18 +110,19 @@ class UNetModel(nn.Module):
             o += rb.out_channels
         d["temb_offsets"] = offs
         # context K/V weights of every cross-attention layer, concatenated along N
-        kvw, kv_offs, o = [], {}, 0
+        kvw, packed, kv_offs, o = [], [], {}, 0
         for st in self._transformers():
             lay = []
             for blk in st.transformer_blocks:
-                wk, wv = blk.cross_attn.kv_weight()
-                kvw += [wk, wv]
-                dm = wk.shape[0]
-                lay.append((o, dm))
-                o += 2 * dm
+                ca = blk.cross_attn
+                kvw += list(ca.kv_weight())
+                packed.append(ca.kv_packed)
+                lay.append((o, ca.kv_width))
+                o += 2 * ca.kv_width
             kv_offs[id(st)] = lay
         d["kv_offsets"] = kv_offs
-        d["wkv"] = c.get("wkv", kvw, lambda: _pack.linear_w(torch.cat([w.detach() for w in kvw], 0))) if kvw else None
+        d["wkv"] = c.get("wkv", kvw, lambda: torch.cat([f()[0] for f in packed], 0)) if kvw else None
+        d["bkv"] = c.get("bkv", kvw, lambda: torch.cat([f()[1] for f in packed], 0)) if kvw else None
         return d
 
     def _context_kv(self, p, ctx: Tensor) -> Dict[int, list]:
@@ -132,7 +133,7 @@ class UNetModel(nn.Module):
             return self._ctx_cache[1]
         B, m, cd = ctx.shape
         c16 = ctx.contiguous() if ctx.dtype == torch.bfloat16 else ops.cast(ctx.contiguous(), torch.bfloat16)
-        kv = ops.gemm(c16.view(B * m, cd), p["wkv"]).view(B, m, -1)
+        kv = ops.gemm(c16.view(B * m, cd), p["wkv"], p["bkv"]).view(B, m, -1)
         views = {sid: [(kv[:, :, o:o + dm], kv[:, :, o + dm:o + 2 * dm]) for (o, dm) in lay]
                  for sid, lay in p["kv_offsets"].items()}
         if not torch.cuda.is_current_stream_capturing():

@@ -47,48 +47,87 @@ class CrossAttention(nn.Module):
         self._cache = _pack.PackCache()
         self._self_qkv_ok = context_dim == query_dim
 
+    @property
+    def use_p32(self) -> bool:
+        """Small head dims run on the tcgen05 attention kernel over head-padded operands."""
+        return self.d_head <= 20 and self.d_head % 4 == 0
+
+    @property
+    def kv_width(self) -> int:
+        """Columns of one of K / V as produced by the packed context projection."""
+        return self.n_heads * (_pack.HEAD_PAD if self.use_p32 else self.d_head)
+
     def kv_weight(self) -> Tuple[Tensor, Tensor]:
         return self.to_k.weight, self.to_v.weight
+
+    def kv_packed(self) -> Tuple[Tensor, Tensor]:
+        """(weight bf16 [2*kv_width, Cc], bias fp32 [2*kv_width]) of the fused K|V projection."""
+        c = self._cache
+        k, v = self.to_k.weight, self.to_v.weight
+        H, d = self.n_heads, self.d_head
+
+        def build_w():
+            if self.use_p32:
+                return _pack.linear_w(torch.cat([_pack.head_pad_w(k, H, d), _pack.head_pad_w(v, H, d)], 0))
+            return _pack.linear_w(torch.cat([k.detach(), v.detach()], 0))
+
+        def build_b():
+            kw = self.kv_width
+            b = torch.zeros(2 * kw, dtype=torch.float32, device=k.device)
+            if self.use_p32:
+                b[kw:] = _pack.head_pad_ones_bias(H, d, k.device)
+            return b
+
+        return c.get("wkv", [k, v], build_w), c.get("bkv", [k, v], build_b)
 
     def _w(self):
         c = self._cache
         q, k, v, o = self.to_q.weight, self.to_k.weight, self.to_v.weight, self.out[0]
+        H, dh = self.n_heads, self.d_head
+        pad = (lambda w: _pack.head_pad_w(w, H, dh)) if self.use_p32 else (lambda w: w.detach())
         d = {
-            "wq": c.get("wq", [q], lambda: _pack.linear_w(q)),
-            "wkv": c.get("wkv", [k, v], lambda: _pack.linear_w(torch.cat([k.detach(), v.detach()], 0))),
+            "wq": c.get("wq", [q], lambda: _pack.linear_w(pad(q))),
             "wo": c.get("wo", [o.weight], lambda: _pack.linear_w(o.weight)),
             "bo": c.get("bo", [o.bias], lambda: _pack.f32(o.bias)),
         }
+        d["wkv"], d["bkv"] = self.kv_packed()
         if self._self_qkv_ok:
-            d["wqkv"] = c.get("wqkv", [q, k, v],
-                              lambda: _pack.linear_w(torch.cat([q.detach(), k.detach(), v.detach()], 0)))
+            d["wqkv"] = c.get("wqkv", [q, k, v], lambda: _pack.linear_w(torch.cat([pad(q), pad(k), pad(v)], 0)))
+            kw = self.kv_width
+            d["bqkv"] = c.get("bqkv", [q, k, v],
+                              lambda: torch.cat([torch.zeros(kw, dtype=torch.float32, device=q.device), d["bkv"]]))
         return d
 
     def forward_tokens(self, x: Tensor, ctx: Optional[Tensor] = None, kv: Optional[Tuple[Tensor, Tensor]] = None,
                        residual: Optional[Tensor] = None) -> Tensor:
-        """x [B, n, C] bf16.  ctx [B, m, Cc] bf16 or ``kv`` = precomputed (K, V) [B, m, d_model] views.
-        Returns out-proj(attn) (+ residual, fused in the GEMM epilogue)."""
+        """x [B, n, C] bf16.  ctx [B, m, Cc] bf16 or ``kv`` = precomputed (K, V) [B, m, kv_width] views (the
+        output layout of ``kv_packed``).  Returns out-proj(attn) (+ residual, fused in the GEMM epilogue)."""
         if self.training and self.out[1].p:
             raise NotImplementedError("CrossAttention: dropout > 0 in training mode is not built")
         B, n, C = x.shape
         dm = self.n_heads * self.d_head
+        kw = self.kv_width
         w = self._w()
         x2d = x.view(B * n, C)
         if ctx is None and kv is None:
             if "wqkv" not in w:
                 raise ValueError("CrossAttention: context_emb is None but context_dim != query_dim "
                                  "(the reference fails with a shape mismatch here too)")
-            qkv = ops.gemm(x2d, w["wqkv"]).view(B, n, 3 * dm)
-            q, k, v = qkv[:, :, :dm], qkv[:, :, dm:2 * dm], qkv[:, :, 2 * dm:]
+            qkv = ops.gemm(x2d, w["wqkv"], w["bqkv"] if self.use_p32 else None).view(B, n, 3 * kw)
+            q, k, v = qkv[:, :, :kw], qkv[:, :, kw:2 * kw], qkv[:, :, 2 * kw:]
         else:
-            q = ops.gemm(x2d, w["wq"]).view(B, n, dm)
+            q = ops.gemm(x2d, w["wq"]).view(B, n, kw)
             if kv is None:
                 m = ctx.shape[1]
-                kvt = ops.gemm(ctx.view(B * m, ctx.shape[2]), w["wkv"]).view(B, m, 2 * dm)
-                k, v = kvt[:, :, :dm], kvt[:, :, dm:]
+                kvt = ops.gemm(ctx.view(B * m, ctx.shape[2]), w["wkv"],
+                               w["bkv"] if self.use_p32 else None).view(B, m, 2 * kw)
+                k, v = kvt[:, :, :kw], kvt[:, :, kw:]
             else:
                 k, v = kv
-        a = ops.attention(q, k, v, self.n_heads, self.d_head, self.scale)
+        if self.use_p32:
+            a = ops.attention_p32(q, k, v, self.n_heads, self.d_head, self.scale)
+        else:
+            a = ops.attention(q, k, v, self.n_heads, self.d_head, self.scale)
         res2d = None if residual is None else residual.view(B * n, C)
         return ops.gemm(a.view(B * n, dm), w["wo"], w["bo"], residual=res2d).view(B, n, C)
 

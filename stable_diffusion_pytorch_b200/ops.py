@@ -276,6 +276,21 @@ def attention(q: Tensor, k: Tensor, v: Tensor, heads: int, d: int, scale: float,
     return out
 
 
+def attention_p32(q: Tensor, k: Tensor, v: Tensor, heads: int, d: int, scale: float,
+                  out: Optional[Tensor] = None) -> Tensor:
+    """tcgen05 attention over head-padded operands: q [B, n, >=heads*32], k/v [B, m, >=heads*32] (row-strided
+    views allowed); head h at columns [32h, 32h+32), q/k zero beyond d, v[..., 32h+d] == 1."""
+    B, n = q.shape[0], q.shape[1]
+    m = k.shape[1]
+    for t in (q, k, v):
+        assert t.dtype == torch.bfloat16 and t.stride(2) == 1 and t.stride(0) == t.shape[1] * t.stride(1)
+    if out is None:
+        out = torch.empty(B, n, heads * d, device=q.device, dtype=q.dtype)
+    check(_lib.lib().sdb_attention_p32(_ptr(q), q.stride(1), _ptr(k), k.stride(1), _ptr(v), v.stride(1), _ptr(out),
+                                       out.stride(1), B, heads, n, m, d, scale, _stream()), "attention_p32")
+    return out
+
+
 def silu(x: Tensor, out_dtype=None) -> Tensor:
     out = torch.empty(x.shape, device=x.device, dtype=out_dtype or x.dtype)
     check(_lib.lib().sdb_silu(_ptr(x.contiguous()), _ptr(out), x.numel(), _dt(x), _dt(out), _stream()), "silu")

@@ -215,6 +215,33 @@ def test_attention(B, heads, n, m, d):
     assert rel_l2(out.float(), ref) < 1e-2
 
 
+@pytest.mark.parametrize("B,heads,n,m,d", [
+    (1, 1, 256, 128, 20), (1, 2, 256, 256, 20), (2, 8, 1024, 1024, 20), (2, 8, 300, 77, 20),
+    (1, 8, 4096, 4096, 20), (1, 3, 128, 640, 16), (2, 4, 1000, 333, 8)])
+def test_attention_p32(B, heads, n, m, d):
+    """tcgen05 attention on head-padded operands vs fp32 softmax attention of the same bf16 inputs."""
+    g = torch.Generator(device="cpu").manual_seed(n + m)
+
+    def padded(rows, ones_col):
+        t = torch.zeros(B, rows, heads, 32)
+        t[..., :d] = torch.randn(B, rows, heads, d, generator=g)
+        if ones_col:
+            t[..., d] = 1.0
+            t[..., d + 1:] = 3.0      # finite garbage beyond the ones column must not matter
+        return t.reshape(B, rows, heads * 32).to("cuda", torch.bfloat16)
+
+    q, k, v = padded(n, False), padded(m, False), padded(m, True)
+    scale = 1 / math.sqrt(d)
+    out = ops.attention_p32(q, k, v, heads, d, scale)
+    qf = q.float().view(B, n, heads, 32)[..., :d].transpose(1, 2)
+    kf = k.float().view(B, m, heads, 32)[..., :d].transpose(1, 2)
+    vf = v.float().view(B, m, heads, 32)[..., :d].transpose(1, 2)
+    ref = torch.softmax(qf @ kf.transpose(-1, -2) * scale, -1) @ vf
+    ref = ref.transpose(1, 2).reshape(B, n, heads * d)
+    assert out.shape == ref.shape
+    assert rel_l2(out.float(), ref) < 1e-2
+
+
 # ------------------------------------------------------------------ sampler kernels (bit-exact in fp32)
 def test_timestep_embed():
     half = 80

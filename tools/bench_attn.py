@@ -1,0 +1,27 @@
+"""Times the self-attention kernels at the config-2 shape (UNet batch 32, 8 heads, 4096 tokens, d=20)."""
+import math, os, sys, torch
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from stable_diffusion_pytorch_b200 import ops
+
+def timeit(fn, it=10, warm=3):
+    for _ in range(warm): fn()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize(); e0.record()
+    for _ in range(it): fn()
+    e1.record(); torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / it
+
+B, H, n, d = int(os.environ.get("B", 32)), 8, int(os.environ.get("N", 4096)), 20
+qkv = torch.randn(B, n, 3 * H * 32, device="cuda").to(torch.bfloat16)
+qkv.view(B, n, 3, H, 32)[..., d:] = 0
+qkv.view(B, n, 3, H, 32)[:, :, 2, :, d] = 1
+q, k, v = qkv[:, :, :256], qkv[:, :, 256:512], qkv[:, :, 512:]
+ms = timeit(lambda: ops.attention_p32(q, k, v, H, d, 1 / math.sqrt(d)))
+pairs = B * H * n * n
+print(f"attention_p32 poly={os.environ.get('SDB_FA_POLY','3')}: {ms:.3f} ms  {pairs/ms/1e9:.2f} Gpairs/ms... "
+      f"{pairs/(ms*1e-3)/148/1.965e9:.2f} pairs/clk/SM  {4*pairs*d/(ms*1e-3)/1e12:.1f} TFLOP/s(alg)")
+if os.environ.get("OLD"):
+    qkv2 = torch.randn(B, n, 480, device="cuda").to(torch.bfloat16)
+    ms = timeit(lambda: ops.attention(qkv2[:, :, :160], qkv2[:, :, 160:320], qkv2[:, :, 320:], H, d, 1 / math.sqrt(d)))
+    print(f"attention (mma.sync): {ms:.3f} ms")
+print("timeout flag", ops.debug_timeout_flag())
