@@ -22,7 +22,7 @@
 
 namespace sdb {
 
-constexpr int kFaThreads = 384;  // warps 0-3: TMA / MMA / TMEM alloc / idle; 4-7, 8-11: softmax
+constexpr int kFaThreads = 384;  // warp 0: TMA, 1-2: MMA issue (one per warpgroup), 3: TMEM alloc; 4-7, 8-11: softmax
 constexpr int kFaStages = 4;
 constexpr int kFaBM = 128;       // query rows per softmax warpgroup
 constexpr int kFaBN = 128;       // keys per tile
@@ -190,7 +190,7 @@ attention_umma_kernel(const __grid_constant__ FaParams p) {
     mbar_init(bar_q, 1);
     for (int s = 0; s < kFaStages; ++s) {
       mbar_init(bar_kv_full(s), 1);
-      mbar_init(bar_kv_empty(s), 1);
+      mbar_init(bar_kv_empty(s), 2);
     }
     for (int w = 0; w < 2; ++w) {
       mbar_init(bar_s_full(w), 1);
@@ -200,7 +200,7 @@ attention_umma_kernel(const __grid_constant__ FaParams p) {
     }
     fence_barrier_init();
   }
-  if (warp == 2) {
+  if (warp == 3) {
     tmem_alloc(tmem_slot, 512);
     tmem_relinquish();
   }
@@ -227,47 +227,52 @@ attention_umma_kernel(const __grid_constant__ FaParams p) {
         tma_load_3d(sk, &p.tmK, bar_kv_full(s), h * kFaDP, j * kFaBN, b);
         tma_load_3d(sk + kFaKVBytes, &p.tmV, bar_kv_full(s), h * kFaDP, j * kFaBN, b);
       }
-    } else if (warp == 1 && lane == 0) {
-      // ===================== MMA issuer =====================
+    } else if (warp == 1 || warp == 2) {
+      // ===================== MMA issuers: one warp per softmax warpgroup =====================
+      // The whole warp runs the loop (warp-uniform control flow keeps descriptors and addresses in
+      // uniform registers; measured 2x faster issue than a divergent lane-0 path, and one thread
+      // serving both warpgroups was a bottleneck); tcgen05 instructions go out from one elected lane.
+      const int w = warp - 1;
       const uint32_t idesc_s = umma_idesc_bf16(kFaBM, kFaBN);
       const uint32_t idesc_o = umma_idesc_bf16(kFaBM, kFaDP) | (1u << 16);  // B (= V) is MN-major
-      auto issue_s = [&](int w, int stage) {
-        const uint64_t adesc = umma_smem_desc(sQ + (uint32_t)w * kFaQBytes, 64);
+      const uint64_t qdesc = umma_smem_desc(sQ + (uint32_t)w * kFaQBytes, 64);
+      const uint32_t tcol = tmem_base + (uint32_t)w * 256u;
+      auto issue_s = [&](int stage) {
         const uint64_t bdesc = umma_smem_desc(sKV + (uint32_t)stage * kFaStageBytes, 64);
-        const uint32_t d = tmem_base + (uint32_t)w * 256u;
-        umma_f16(d, adesc, bdesc, idesc_s, 0u);
-        umma_f16(d, adesc + 2, bdesc + 2, idesc_s, 1u);
-        umma_commit(bar_s_full(w));
+        if (elect_one()) {
+          umma_f16(tcol, qdesc, bdesc, idesc_s, 0u);
+          umma_f16(tcol, qdesc + 2, bdesc + 2, idesc_s, 1u);
+          umma_commit(bar_s_full(w));
+        }
+        __syncwarp();
       };
       bool ok = mbar_wait(bar_q, 0) && mbar_wait(bar_kv_full(0), 0);
       if (ok) {
         tc_fence_after();
-        issue_s(0, 0);
-        issue_s(1, 0);
+        issue_s(0);
       }
       for (int j = 0; j < T && ok; ++j) {
         const int s = j % kFaStages, sn = (j + 1) % kFaStages;
         const uint32_t par = (uint32_t)j & 1u;
-        if (j + 1 < T) ok = mbar_wait(bar_kv_full(sn), ((uint32_t)((j + 1) / kFaStages)) & 1u);
-        for (int w = 0; w < 2 && ok; ++w) {
-          if (j + 1 < T) {
-            ok = mbar_wait(bar_s_free(w), par);
-            if (!ok) break;
-            tc_fence_after();
-            issue_s(w, sn);
-          }
-          ok = mbar_wait(bar_p_full(w), par);
+        if (j + 1 < T) {
+          ok = mbar_wait(bar_kv_full(sn), ((uint32_t)((j + 1) / kFaStages)) & 1u) && mbar_wait(bar_s_free(w), par);
           if (!ok) break;
           tc_fence_after();
-          const uint64_t vdesc = umma_smem_desc_mn64(sKV + (uint32_t)s * kFaStageBytes + kFaKVBytes);
-          const uint32_t d = tmem_base + (uint32_t)w * 256u + 192u;
-          const uint32_t a = tmem_base + (uint32_t)w * 256u + 128u;
+          issue_s(sn);
+        }
+        ok = mbar_wait(bar_p_full(w), par);
+        if (!ok) break;
+        tc_fence_after();
+        const uint64_t vdesc = umma_smem_desc_mn64(sKV + (uint32_t)s * kFaStageBytes + kFaKVBytes);
+        if (elect_one()) {
 #pragma unroll
           for (int kk = 0; kk < kFaBN / 16; ++kk)
-            umma_f16_ts(d, a + (uint32_t)kk * 8u, vdesc + (uint64_t)(kk * 64), idesc_o, kk ? 1u : 0u);
+            umma_f16_ts(tcol + 192u, tcol + 128u + (uint32_t)kk * 8u, vdesc + (uint64_t)(kk * 64), idesc_o,
+                        kk ? 1u : 0u);
           umma_commit(bar_o_full(w));
+          umma_commit(bar_kv_empty(s));   // one arrival per warpgroup
         }
-        if (ok) umma_commit(bar_kv_empty(s));
+        __syncwarp();
       }
     }
   } else {
@@ -382,7 +387,7 @@ attention_umma_kernel(const __grid_constant__ FaParams p) {
   }
   tc_fence_before();
   __syncthreads();
-  if (warp == 2) {
+  if (warp == 3) {
     tc_fence_after();
     tmem_dealloc(tmem_base, 512);
   }

@@ -242,6 +242,32 @@ def test_attention_p32(B, heads, n, m, d):
     assert rel_l2(out.float(), ref) < 1e-2
 
 
+@pytest.mark.parametrize("growth", [0.3, 2.0, 12.0])
+def test_attention_p32_growing_scores(growth):
+    """Scores that keep growing along the keys: exercises the lazy rescale of the TMEM accumulator
+    (reference maximum lagging by > 2^8) and, for the largest growth, the redo path (> 2^60 per tile)."""
+    B, heads, n, m, d = 1, 2, 384, 512, 20
+    g = torch.Generator(device="cpu").manual_seed(7)
+    q = torch.zeros(B, n, heads, 32)
+    k = torch.zeros(B, m, heads, 32)
+    v = torch.zeros(B, m, heads, 32)
+    q[..., :d] = 0.05 * torch.randn(B, n, heads, d, generator=g)
+    k[..., :d] = 0.05 * torch.randn(B, m, heads, d, generator=g)
+    q[..., 0] = 4.0
+    k[..., 0] = growth * torch.arange(m).float()[None, :, None] / 4.0   # log2-score slope ~ 0.32 * growth per key
+    v[..., :d] = torch.randn(B, m, heads, d, generator=g)
+    v[..., d] = 1.0
+    q, k, v = (t.reshape(B, -1, heads * 32).to("cuda", torch.bfloat16) for t in (q, k, v))
+    scale = 1 / math.sqrt(d)
+    out = ops.attention_p32(q, k, v, heads, d, scale)
+    qf = q.float().view(B, n, heads, 32)[..., :d].transpose(1, 2)
+    kf = k.float().view(B, m, heads, 32)[..., :d].transpose(1, 2)
+    vf = v.float().view(B, m, heads, 32)[..., :d].transpose(1, 2)
+    ref = (torch.softmax(qf @ kf.transpose(-1, -2) * scale, -1) @ vf).transpose(1, 2).reshape(B, n, heads * d)
+    assert torch.isfinite(out.float()).all()
+    assert rel_l2(out.float(), ref) < 1e-2
+
+
 # ------------------------------------------------------------------ sampler kernels (bit-exact in fp32)
 def test_timestep_embed():
     half = 80
