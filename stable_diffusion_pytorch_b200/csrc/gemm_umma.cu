@@ -3,16 +3,18 @@
 //   * GEMM  out[M,N] = A[M,K] W[N,K]^T           (A = one or two K segments, 2-D tensor maps)
 //   * 3x3 convolution as implicit GEMM over NHWC  (A = 9 shifted 4-D boxes per channel chunk;
 //     out-of-image taps are zero-filled by the TMA unit, which is exactly Conv2d(padding=1))
-// Roles: warp 0 = TMA producer, warp 1 = MMA issuer (owns TMEM), warps 2..5 = epilogue
+// Roles: warp 0 = TMA producer, warp 1 = MMA issuer (owns TMEM), warps 2..9 = epilogue
 // (TMEM -> registers -> fused bias/temb/residual/activation -> global).  Two TMEM accumulator
 // stages let the epilogue of tile i overlap the main loop of tile i+1.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 namespace sdb {
 
 constexpr int kTileM = 128;
 constexpr int kMaxBN = 256;
-constexpr int kGemmThreads = 192;
+constexpr int kGemmThreads = 320;  // warp 0 TMA, warp 1 MMA, warps 2..9 epilogue
 constexpr int kMaxStages = 12;
 constexpr int kSmemBudget = 200 * 1024;  // operand ring; + 1 KB barriers / alignment slack
 
@@ -45,9 +47,28 @@ struct UmmaParams {
   int act;
 };
 
+// exact-erf GELU (transformer.py:177 uses nn.GELU()) with erf from Abramowitz-Stegun 7.1.26
+// (|error| <= 1.5e-7, far inside the bf16 rounding of the result): 2 MUFU + ~10 FMA-pipe ops
+// instead of the ~30-instruction branchy erff -- the GEGLU epilogue is issue-bound.
+__device__ __forceinline__ float gelu_erf_fast(float x) {
+  const float z = fabsf(x) * 0.70710678118654752440f;
+  const float t = __fdividef(1.0f, fmaf(0.3275911f, z, 1.0f));
+  float poly = fmaf(1.061405429f, t, -1.453152027f);
+  poly = fmaf(poly, t, 1.421413741f);
+  poly = fmaf(poly, t, -0.284496736f);
+  poly = fmaf(poly, t, 0.254829592f);
+  const float e = exp2f(-z * z * 1.4426950408889634f);
+  const float erf_abs = fmaf(-poly * t, e, 1.0f);          // erf(|x|/sqrt2)
+  const float erf_v = copysignf(erf_abs, x);
+  return 0.5f * x * (1.0f + erf_v);
+}
+
 // ---- epilogue for 16 consecutive accumulator columns of one row -------------------------------
+// `res` holds the row's 16 residual values (bf16, prefetched before the accumulator was ready)
+// when kResPre, else the residual is read here (fp32 residual: rare, un-prefetched path).
+template <bool kResPre>
 __device__ __forceinline__ void epilogue16(const UmmaParams& p, const uint32_t (&acc)[16],
-                                           long long out_row, int img, int col) {
+                                           long long out_row, int img, int col, const uint4 (&res)[2]) {
   float v[16];
 #pragma unroll
   for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(acc[j]);
@@ -70,7 +91,7 @@ __device__ __forceinline__ void epilogue16(const UmmaParams& p, const uint32_t (
     // interleaved columns (a_j, g_j): 16 accumulator columns -> 8 outputs
     float o[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) o[j] = v[2 * j] * gelu_erf_f(v[2 * j + 1]);
+    for (int j = 0; j < 8; ++j) o[j] = v[2 * j] * gelu_erf_fast(v[2 * j + 1]);
     const long long off = out_row * p.ldo + (col >> 1);
     if (p.out_dtype == SDB_BF16) {
       uint4 w = make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]),
@@ -88,21 +109,18 @@ __device__ __forceinline__ void epilogue16(const UmmaParams& p, const uint32_t (
     for (int j = 0; j < 16; ++j) v[j] = silu_f(v[j]);
   }
   if (p.residual) {
-    const long long roff = out_row * p.ldr + col;
-    if (p.res_dtype == SDB_BF16) {
-      const uint4* r = reinterpret_cast<const uint4*>(
-          reinterpret_cast<const __nv_bfloat16*>(p.residual) + roff);
+    if (kResPre) {
 #pragma unroll
       for (int h = 0; h < 2; ++h) {
-        uint4 q = __ldg(r + h);
+        const uint4 q = res[h];
         float2 a = unpack_bf16x2(q.x), b = unpack_bf16x2(q.y), c = unpack_bf16x2(q.z),
                d = unpack_bf16x2(q.w);
         v[8 * h + 0] += a.x; v[8 * h + 1] += a.y; v[8 * h + 2] += b.x; v[8 * h + 3] += b.y;
         v[8 * h + 4] += c.x; v[8 * h + 5] += c.y; v[8 * h + 6] += d.x; v[8 * h + 7] += d.y;
       }
     } else {
-      const float4* r =
-          reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.residual) + roff);
+      const float4* r = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.residual) +
+                                                        out_row * p.ldr + col);
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
         float4 q = __ldg(r + j);
@@ -151,7 +169,7 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(tfull_bar(a), 1);
-      mbar_init(tempty_bar(a), 128);
+      mbar_init(tempty_bar(a), 256);
     }
     fence_barrier_init();
   }
@@ -168,7 +186,9 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
 
   if (warp == 0) {
     // ===================== TMA producer =====================
-    if (lane == 0) {
+    // (whole warp runs the loop -- warp-uniform control flow keeps coordinates and descriptors in
+    // uniform registers; one elected lane issues the TMA / tcgen05 instructions)
+    {
       int stage = 0;
       uint32_t phase = 0;
       bool ok = true;
@@ -186,6 +206,7 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
           if (!ok) break;
           const uint32_t sa = smem_base + (uint32_t)stage * p.stage_bytes;
           const uint32_t sb = sa + p.a_bytes;
+          if (elect_one()) {
           mbar_arrive_expect_tx(full_bar(stage), (uint32_t)(p.a_bytes + p.b_bytes));
           if (p.mode == 0) {
             if (kb < p.kb1) {
@@ -202,13 +223,15 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
                         h0 + p.tap_dh[tap], i0);
             tma_load_2d(sb, &p.tmB, full_bar(stage), tap * p.Cin + c0, n0);
           }
+          }
+          __syncwarp();
           if (++stage == p.num_stages) { stage = 0; phase ^= 1u; }
         }
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    if (lane == 0) {
+    {
       const uint32_t idesc = umma_idesc_bf16(kTileM, (uint32_t)p.BN);
       const int k_sub = p.BK / 16;
       int stage = 0;
@@ -230,21 +253,30 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
           const uint32_t sb = sa + p.a_bytes;
           const uint64_t adesc = umma_smem_desc(sa, (uint32_t)p.swz);
           const uint64_t bdesc = umma_smem_desc(sb, (uint32_t)p.swz);
-          for (int k = 0; k < k_sub; ++k) {
-            // advance 16 bf16 = 32 B along K inside the swizzle atom: +2 in the (addr >> 4) field
-            umma_f16(tmem_d, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc,
-                     (kb | k) != 0 ? 1u : 0u);
+          if (elect_one()) {
+            for (int k = 0; k < k_sub; ++k) {
+              // advance 16 bf16 = 32 B along K inside the swizzle atom: +2 in the (addr >> 4) field
+              umma_f16(tmem_d, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc,
+                       (kb | k) != 0 ? 1u : 0u);
+            }
+            umma_commit(empty_bar(stage));
           }
-          umma_commit(empty_bar(stage));
+          __syncwarp();
           if (++stage == p.num_stages) { stage = 0; phase ^= 1u; }
         }
-        umma_commit(tfull_bar(acc));
+        if (elect_one()) umma_commit(tfull_bar(acc));
+        __syncwarp();
       }
     }
   } else {
-    // ===================== epilogue (warps 2..5) =====================
-    const int q = warp & 3;  // TMEM lane quarter this warp may access
+    // ===================== epilogue (warps 2..9) =====================
+    // Two warps per TMEM lane quarter; each thread owns one output row and every other 32-column
+    // pair of the tile.  The row's bf16 residual is fetched BEFORE the accumulator is waited for,
+    // so its latency hides behind the main loop instead of serialising 32 bytes at a time.
+    const int q = warp & 3;            // TMEM lane quarter this warp may access
+    const int hf = (warp - 2) >> 2;    // which 32-column pairs: hf, hf + 2, ...
     const int r = q * 32 + lane;
+    const bool res_pre = p.residual != nullptr && p.res_dtype == SDB_BF16;
     int it = 0;
     bool ok = true;
     for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
@@ -268,18 +300,41 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
             out_row = ((long long)img * (p.H >> 1) + (h >> 1)) * (p.W >> 1) + (w >> 1);
         }
       }
+      uint4 res[4][4];   // up to 4 pairs x 32 columns of bf16 residual
+      if (res_pre && out_row >= 0) {
+        const __nv_bfloat16* rrow = reinterpret_cast<const __nv_bfloat16*>(p.residual) + out_row * p.ldr + n0;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int c0 = (hf + 2 * i) * 32;
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            if (c0 + 8 * j < p.BN && n0 + c0 + 8 * j < p.N)
+              res[i][j] = __ldg(reinterpret_cast<const uint4*>(rrow + c0 + 8 * j));
+        }
+      }
       if (ok) ok = mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)acc * kMaxBN;
-      for (int c0 = 0; c0 < p.BN; c0 += 32) {
-        uint32_t v0[16], v1[16];
-        const bool two = (c0 + 16 < p.BN);
-        tmem_ld_32x16(taddr + c0, v0);
-        if (two) tmem_ld_32x16(taddr + c0 + 16, v1);
-        tmem_ld_wait();
-        if (out_row >= 0 && ok) {
-          if (n0 + c0 < p.N) epilogue16(p, v0, out_row, img, n0 + c0);
-          if (two && n0 + c0 + 16 < p.N) epilogue16(p, v1, out_row, img, n0 + c0 + 16);
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int c0 = (hf + 2 * i) * 32;
+        if (c0 < p.BN) {
+          uint32_t v0[16], v1[16];
+          const bool two = (c0 + 16 < p.BN);
+          tmem_ld_32x16(taddr + c0, v0);
+          if (two) tmem_ld_32x16(taddr + c0 + 16, v1);
+          tmem_ld_wait();
+          if (out_row >= 0 && ok) {
+            const uint4(&r0)[2] = *reinterpret_cast<const uint4(*)[2]>(&res[i][0]);
+            const uint4(&r1)[2] = *reinterpret_cast<const uint4(*)[2]>(&res[i][2]);
+            if (res_pre) {
+              if (n0 + c0 < p.N) epilogue16<true>(p, v0, out_row, img, n0 + c0, r0);
+              if (two && n0 + c0 + 16 < p.N) epilogue16<true>(p, v1, out_row, img, n0 + c0 + 16, r1);
+            } else {
+              if (n0 + c0 < p.N) epilogue16<false>(p, v0, out_row, img, n0 + c0, r0);
+              if (two && n0 + c0 + 16 < p.N) epilogue16<false>(p, v1, out_row, img, n0 + c0 + 16, r1);
+            }
+          }
         }
       }
       tc_fence_before();
@@ -308,9 +363,14 @@ static int pick_bn(int N) {
 }
 
 static void pick_bk(int K, int K2, int* BK, int* swz) {
+  // 128-byte rows (BK = 64, SWIZZLE_128B) even when K is not a multiple of 64: the K tail of the last
+  // block is zero-filled by the TMA unit (operands AND weights), which costs a few idle MMA columns
+  // but halves the number of TMA row requests per byte compared with 64-byte rows.
+  static int force32 = -1;
+  if (force32 < 0) { const char* e = getenv("SDB_GEMM_BK32"); force32 = e ? atoi(e) : 0; }
   const bool d64 = (K % 64 == 0) && (K2 % 64 == 0);
   const bool d32 = (K % 32 == 0) && (K2 % 32 == 0);
-  if (d64 || !d32) { *BK = 64; *swz = 128; }
+  if (d64 || !d32 || !force32) { *BK = 64; *swz = 128; }
   else { *BK = 32; *swz = 64; }
 }
 
