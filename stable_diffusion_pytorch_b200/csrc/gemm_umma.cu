@@ -16,11 +16,13 @@ constexpr int kTileM = 128;
 constexpr int kMaxBN = 256;
 constexpr int kGemmThreads = 320;  // warp 0 TMA, warp 1 MMA, warps 2..9 epilogue
 constexpr int kMaxStages = 12;
-constexpr int kSmemBudget = 200 * 1024;  // operand ring; + 1 KB barriers / alignment slack
+constexpr int kSmemBudget = 224 * 1024;  // operand ring + epilogue staging; + barriers / alignment slack
 
 struct UmmaParams {
-  CUtensorMap tmA[4];
+  CUtensorMap tmA[2];
   CUtensorMap tmB;
+  CUtensorMap tmO, tmOt;   // output: 64-column slabs (SWIZZLE_128B) and the narrower tail slab
+  CUtensorMap tmR, tmRt;   // bf16 residual, same boxes
   // main loop
   int mode;  // 0 = GEMM, 1 = conv3x3
   int num_kb, kb1, K1;
@@ -45,6 +47,12 @@ struct UmmaParams {
   long long ldo;
   int out_dtype;
   int act;
+  // staged epilogue (bf16 output through swizzled smem slabs + TMA store): 0 = direct stores
+  int staged;
+  int bno;          // output columns per tile (BN, or BN/2 for GEGLU)
+  int nslab;        // full 64-column slabs per tile
+  int tail_cols;    // columns of the last, narrower slab (0, 16 or 32)
+  int staging_bytes;
 };
 
 // exact-erf GELU (transformer.py:177 uses nn.GELU()) with erf from Abramowitz-Stegun 7.1.26
@@ -142,18 +150,104 @@ __device__ __forceinline__ void epilogue16(const UmmaParams& p, const uint32_t (
   }
 }
 
+__device__ __forceinline__ void tma_store_2d(const void* tmap, uint32_t src, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(tmap)), "r"(src), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tma_store_4d(const void* tmap, uint32_t src, int c0, int c1, int c2, int c3) {
+  asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];"
+               ::"l"(reinterpret_cast<uint64_t>(tmap)), "r"(src), "r"(c0), "r"(c1), "r"(c2), "r"(c3) : "memory");
+}
+__device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ uint4 lds128(uint32_t a) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ void sts128(uint32_t a, uint4 v) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+// Shared-memory address of the 16-byte chunk holding output columns [oc, oc+8) of tile row r.  The tile is
+// staged as 64-column slabs of 128 rows x 128 B (SWIZZLE_128B: chunk ^= r & 7) followed by one narrower tail
+// slab (64-byte rows: chunk ^= (r >> 1) & 3; 32-byte rows: chunk ^= (r >> 2) & 1) -- exactly the layouts
+// the TMA store / residual-load boxes use, and conflict-free for row-per-thread 16-byte accesses.
+__device__ __forceinline__ uint32_t stage_addr(const UmmaParams& p, uint32_t stg, int r, int oc) {
+  const int slab = oc >> 6;
+  if (slab < p.nslab) {
+    const int chunk = (oc & 63) >> 3;
+    return stg + (uint32_t)slab * 16384u + (uint32_t)r * 128u + (uint32_t)((chunk ^ (r & 7)) << 4);
+  }
+  const int chunk = (oc - 64 * p.nslab) >> 3;
+  const uint32_t base = stg + (uint32_t)p.nslab * 16384u;
+  if (p.tail_cols == 32) return base + (uint32_t)r * 64u + (uint32_t)((chunk ^ ((r >> 1) & 3)) << 4);
+  return base + (uint32_t)r * 32u + (uint32_t)((chunk ^ ((r >> 2) & 1)) << 4);
+}
+
+// epilogue of 16 accumulator columns into the staged tile: bias / temb / activation, residual read from
+// (and result written back to) the swizzled slab the TMA unit loaded / will store.
+__device__ __forceinline__ void epilogue16_staged(const UmmaParams& p, const uint32_t (&acc)[16], uint32_t stg,
+                                                  int r, int img, int col, int col_in_tile) {
+  float v[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(acc[j]);
+  if (p.bias) {
+#pragma unroll
+    for (int j = 0; j < 16; j += 4) {
+      float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col + j));
+      v[j] += b.x; v[j + 1] += b.y; v[j + 2] += b.z; v[j + 3] += b.w;
+    }
+  }
+  if (p.temb) {
+    const float* t = p.temb + (long long)img * p.ld_temb + col;
+#pragma unroll
+    for (int j = 0; j < 16; j += 4) {
+      float4 b = __ldg(reinterpret_cast<const float4*>(t + j));
+      v[j] += b.x; v[j + 1] += b.y; v[j + 2] += b.z; v[j + 3] += b.w;
+    }
+  }
+  if (p.act == SDB_ACT_GEGLU) {
+    float o[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o[j] = v[2 * j] * gelu_erf_fast(v[2 * j + 1]);
+    sts128(stage_addr(p, stg, r, col_in_tile >> 1),
+           make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]),
+                      pack_bf16x2(o[6], o[7])));
+    return;
+  }
+  if (p.act == SDB_ACT_SILU) {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) v[j] = silu_f(v[j]);
+  }
+#pragma unroll
+  for (int h = 0; h < 2; ++h) {
+    const uint32_t a = stage_addr(p, stg, r, col_in_tile + 8 * h);
+    if (p.residual) {
+      const uint4 q = lds128(a);
+      float2 x = unpack_bf16x2(q.x), y = unpack_bf16x2(q.y), z = unpack_bf16x2(q.z), w = unpack_bf16x2(q.w);
+      v[8 * h + 0] += x.x; v[8 * h + 1] += x.y; v[8 * h + 2] += y.x; v[8 * h + 3] += y.y;
+      v[8 * h + 4] += z.x; v[8 * h + 5] += z.y; v[8 * h + 6] += w.x; v[8 * h + 7] += w.y;
+    }
+    sts128(a, make_uint4(pack_bf16x2(v[8 * h], v[8 * h + 1]), pack_bf16x2(v[8 * h + 2], v[8 * h + 3]),
+                         pack_bf16x2(v[8 * h + 4], v[8 * h + 5]), pack_bf16x2(v[8 * h + 6], v[8 * h + 7])));
+  }
+}
+
 __global__ void __launch_bounds__(kGemmThreads, 1)
 umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   // 1024-B aligned operand ring (SWIZZLE_128B atoms), then the barriers
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t ring_bytes = (uint32_t)p.num_stages * (uint32_t)p.stage_bytes;
-  const uint32_t bar_base = smem_base + ring_bytes;
+  const uint32_t stg_base = smem_base + ring_bytes;                 // epilogue staging (1024-B aligned)
+  const uint32_t bar_base = stg_base + (uint32_t)p.staging_bytes;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (kMaxStages + s); };
   auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * kMaxStages + a); };
   auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * kMaxStages + 2 + a); };
-  const uint32_t tmem_slot = bar_base + 8u * (2 * kMaxStages + 4);
+  const uint32_t res_bar = bar_base + 8u * (2 * kMaxStages + 4);
+  const uint32_t tmem_slot = bar_base + 8u * (2 * kMaxStages + 5);
   volatile uint32_t* tmem_slot_ptr =
       reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
@@ -171,6 +265,7 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
       mbar_init(tfull_bar(a), 1);
       mbar_init(tempty_bar(a), 256);
     }
+    mbar_init(res_bar, 1);
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -276,6 +371,87 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
     const int q = warp & 3;            // TMEM lane quarter this warp may access
     const int hf = (warp - 2) >> 2;    // which 32-column pairs: hf, hf + 2, ...
     const int r = q * 32 + lane;
+    if (p.staged) {
+      // ---- staged epilogue: TMEM -> registers -> swizzled smem slabs -> TMA store ----------------
+      // Row-per-thread global stores touch 32 lines per warp instruction; staging the tile and letting
+      // the TMA unit write full lines (and fetch the bf16 residual the same way) removes that bound.
+      int it = 0;
+      bool ok = true;
+      const bool leader = (warp == 2);
+      const uint32_t res_bytes = 128u * (uint32_t)p.bno * 2u;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
+        const int n_tile = tile % p.tiles_n, m_tile = tile / p.tiles_n;
+        const int n0 = n_tile * p.BN;
+        const int o0 = (p.act == SDB_ACT_GEGLU) ? (n0 >> 1) : n0;   // first output column of the tile
+        const int acc = it & 1;
+        const uint32_t acc_phase = (uint32_t)(it >> 1) & 1u;
+        int img = 0, w0 = 0, h0 = 0, i0 = 0;
+        if (p.mode == 1) {
+          w0 = (m_tile % p.tiles_w) * p.TW;
+          h0 = ((m_tile / p.tiles_w) % p.tiles_h) * p.TH;
+          i0 = (m_tile / (p.tiles_w * p.tiles_h)) * p.TN;
+          img = i0 + r / (p.TW * p.TH);
+          if (img >= p.B) img = p.B - 1;   // clipped rows: any valid temb row will do
+        }
+        if (leader) {
+          if (elect_one()) {
+            tma_store_wait_read();          // the previous tile's stores have drained the staging slabs
+            if (p.residual) {
+              mbar_arrive_expect_tx(res_bar, res_bytes);
+              for (int sl = 0; sl <= p.nslab; ++sl) {
+                if (sl == p.nslab && p.tail_cols == 0) break;
+                const void* tm = sl < p.nslab ? (const void*)&p.tmR : (const void*)&p.tmRt;
+                const uint32_t dst = stg_base + (uint32_t)sl * 16384u;
+                if (p.mode == 0) tma_load_2d(dst, tm, res_bar, o0 + sl * 64, m_tile * kTileM);
+                else tma_load_4d(dst, tm, res_bar, o0 + sl * 64, w0, h0, i0);
+              }
+            }
+          }
+          __syncwarp();
+        }
+        asm volatile("bar.sync 1, 256;" ::: "memory");   // staging is free (and the residual is on its way)
+        if (ok) ok = mbar_wait(tfull_bar(acc), acc_phase);
+        if (p.residual && ok) ok = mbar_wait(res_bar, (uint32_t)it & 1u);
+        tc_fence_after();
+        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)acc * kMaxBN;
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const int c0 = (hf + 2 * i) * 32;
+          if (c0 < p.BN) {
+            uint32_t v0[16], v1[16];
+            const bool two = (c0 + 16 < p.BN);
+            tmem_ld_32x16(taddr + c0, v0);
+            if (two) tmem_ld_32x16(taddr + c0 + 16, v1);
+            tmem_ld_wait();
+            // columns beyond N carry zero-filled weights; they are clipped by the TMA store
+            const int cb = (n0 + c0 < p.N) ? n0 + c0 : 0, cb1 = (n0 + c0 + 16 < p.N) ? n0 + c0 + 16 : 0;
+            epilogue16_staged(p, v0, stg_base, r, img, cb, c0);
+            if (two) epilogue16_staged(p, v1, stg_base, r, img, cb1, c0 + 16);
+          }
+        }
+        tc_fence_before();
+        mbar_arrive(tempty_bar(acc));
+        fence_proxy_async();                               // generic-proxy smem writes -> async proxy
+        asm volatile("bar.sync 1, 256;" ::: "memory");
+        if (leader) {
+          if (elect_one() && ok) {
+            for (int sl = 0; sl <= p.nslab; ++sl) {
+              if (sl == p.nslab && p.tail_cols == 0) break;
+              const void* tm = sl < p.nslab ? (const void*)&p.tmO : (const void*)&p.tmOt;
+              const uint32_t src = stg_base + (uint32_t)sl * 16384u;
+              if (p.mode == 0) tma_store_2d(tm, src, o0 + sl * 64, m_tile * kTileM);
+              else tma_store_4d(tm, src, o0 + sl * 64, w0, h0, i0);
+            }
+            tma_store_commit();
+          }
+          __syncwarp();
+        }
+      }
+      if (leader) {
+        if (elect_one()) tma_store_wait_read();            // smem must outlive the last store's reads
+        __syncwarp();
+      }
+    } else {
     const bool res_pre = p.residual != nullptr && p.res_dtype == SDB_BF16;
     int it = 0;
     bool ok = true;
@@ -340,6 +516,7 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
       tc_fence_before();
       mbar_arrive(tempty_bar(acc));
     }
+      }
   }
   tc_fence_before();
   __syncthreads();
@@ -352,13 +529,13 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
 // ---------------------------------------------------------------------------------------------
 // host side
 // ---------------------------------------------------------------------------------------------
-static int pick_bn(int N) {
+static int pick_bn(int N, int cap = kMaxBN) {
   // largest multiple of 16 (<= 256) that divides N; if only a narrow one exists, take a wide tile
   // and let the last N tile be partial (TMA zero-fills the missing weight rows, stores are masked)
   int best = 16;
-  for (int bn = 16; bn <= kMaxBN; bn += 16)
+  for (int bn = 16; bn <= cap; bn += 16)
     if (N % bn == 0) best = bn;
-  if (best < 96 && N > best) best = N >= kMaxBN ? kMaxBN : ((N + 15) / 16) * 16;
+  if (best < 96 && N > best) best = N >= cap ? cap : ((N + 15) / 16) * 16;
   return best;
 }
 
@@ -374,12 +551,45 @@ static void pick_bk(int K, int K2, int* BK, int* swz) {
   else { *BK = 32; *swz = 64; }
 }
 
+// Decides whether the epilogue can be staged through smem + TMA stores (bf16 output at the tile's own
+// resolution, bf16 or no residual, a tail slab the swizzle modes can express) and sizes the staging area.
+static void plan_staging(UmmaParams& p, bool bf16_out, bool res_ok, bool same_res) {
+  static int off = -1;
+  if (off < 0) { const char* e = getenv("SDB_GEMM_DIRECT"); off = e ? atoi(e) : 0; }
+  p.bno = p.act == SDB_ACT_GEGLU ? p.BN / 2 : p.BN;
+  p.nslab = p.bno / 64;
+  p.tail_cols = p.bno % 64;
+  p.staged = (!off && bf16_out && res_ok && same_res &&
+              (p.tail_cols == 0 || p.tail_cols == 16 || p.tail_cols == 32)) ? 1 : 0;
+  p.staging_bytes = p.staged ? ((kTileM * p.bno * 2 + 1023) & ~1023) : 0;
+}
+
 static void finish_stages(UmmaParams& p) {
   p.a_bytes = kTileM * p.BK * 2;
   p.b_bytes = p.BN * p.BK * 2;
   p.stage_bytes = (p.a_bytes + p.b_bytes + 1023) & ~1023;
-  int s = kSmemBudget / p.stage_bytes;
+  int s = (kSmemBudget - p.staging_bytes) / p.stage_bytes;
   p.num_stages = s > kMaxStages ? kMaxStages : s;
+}
+
+// output / residual tensor maps of the staged epilogue: `rank` 2 (GEMM rows) or 4 (conv pixel boxes)
+static int make_slab_maps(UmmaParams& p, const void* out, const void* res, int rank, const uint64_t* dims,
+                          const uint64_t* so, const uint64_t* sr, const uint32_t* box_rows) {
+  uint32_t box[4] = {64, box_rows[0], box_rows[1], box_rows[2]};
+  int rc = 0;
+  if (p.nslab > 0) {
+    rc = sdb_make_tensor_map(&p.tmO, out, 2, rank, dims, so, box, 128);
+    if (rc) return rc;
+    if (res) rc = sdb_make_tensor_map(&p.tmR, res, 2, rank, dims, sr, box, 128);
+    if (rc) return rc;
+  }
+  if (p.tail_cols > 0) {
+    box[0] = (uint32_t)p.tail_cols;
+    rc = sdb_make_tensor_map(&p.tmOt, out, 2, rank, dims, so, box, p.tail_cols * 2);
+    if (rc) return rc;
+    if (res) rc = sdb_make_tensor_map(&p.tmRt, res, 2, rank, dims, sr, box, p.tail_cols * 2);
+  }
+  return rc;
 }
 
 static int launch_umma(const UmmaParams& p, cudaStream_t st) {
@@ -422,7 +632,11 @@ extern "C" int sdb_gemm(const SdbGemmArgs* a, void* stream) {
   memset(&p, 0, sizeof(p));
   p.mode = 0;
   pick_bk(a->K1, K2, &p.BK, &p.swz);
-  p.BN = pick_bn(a->N);
+  // short-K GEMMs are bound by the output stream, not the tensor pipe: 128-wide tiles keep the
+  // staging area small (deeper operand ring) at no cost
+  p.BN = pick_bn(a->N, (K <= 320 && a->N > 256) ? 128 : kMaxBN);
+  p.act = a->act;
+  plan_staging(p, a->out_dtype == SDB_BF16, !a->residual || a->res_dtype == SDB_BF16, true);
   finish_stages(p);
   p.kb1 = (a->K1 + p.BK - 1) / p.BK;
   p.K1 = a->K1;
@@ -457,6 +671,14 @@ extern "C" int sdb_gemm(const SdbGemmArgs* a, void* stream) {
   box[0] = (uint32_t)p.BK; box[1] = (uint32_t)p.BN;
   rc = sdb_make_tensor_map(&p.tmB, a->w, 2, 2, dims, strides, box, p.swz);
   if (rc) return rc;
+  if (p.staged) {
+    const int n_out = a->act == SDB_ACT_GEGLU ? a->N / 2 : a->N;
+    uint64_t od[2] = {(uint64_t)n_out, (uint64_t)a->M};
+    uint64_t so[2] = {0, (uint64_t)a->ldo * 2}, sr[2] = {0, (uint64_t)a->ldr * 2};
+    uint32_t rows[3] = {kTileM, 1, 1};
+    rc = make_slab_maps(p, a->out, a->residual, 2, od, so, sr, rows);
+    if (rc) return rc;
+  }
   return launch_umma(p, sdb_stream(stream));
 }
 
@@ -478,6 +700,8 @@ extern "C" int sdb_conv3x3(const SdbConvArgs* a, void* stream) {
   p.mode = 1;
   pick_bk(a->Cin, 0, &p.BK, &p.swz);
   p.BN = pick_bn(a->Cout);
+  p.act = SDB_ACT_NONE;
+  plan_staging(p, a->out_dtype == SDB_BF16, !a->residual || a->res_dtype == SDB_BF16, !a->down2);
   finish_stages(p);
   p.Cin = a->Cin;
   p.kb_per_tap = (a->Cin + p.BK - 1) / p.BK;
@@ -530,5 +754,12 @@ extern "C" int sdb_conv3x3(const SdbConvArgs* a, void* stream) {
   uint32_t wb[2] = {(uint32_t)p.BK, (uint32_t)p.BN};
   rc = sdb_make_tensor_map(&p.tmB, a->w, 2, 2, wd, ws, wb, p.swz);
   if (rc) return rc;
+  if (p.staged) {
+    uint64_t od[4] = {(uint64_t)a->Cout, (uint64_t)a->W, (uint64_t)a->H, (uint64_t)a->B};
+    uint64_t so[4] = {0, (uint64_t)a->Cout * 2, (uint64_t)a->W * a->Cout * 2, (uint64_t)a->H * a->W * a->Cout * 2};
+    uint32_t rows[3] = {(uint32_t)tw, (uint32_t)th, (uint32_t)tn};
+    rc = make_slab_maps(p, a->out, a->residual, 4, od, so, so, rows);
+    if (rc) return rc;
+  }
   return launch_umma(p, sdb_stream(stream));
 }
