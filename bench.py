@@ -35,6 +35,9 @@ def parse():
     ap.add_argument("--sampler", default="ddim", choices=["ddim", "ddpm"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--profile-step", action="store_true",
+                    help="after warm-up run ONE eager step between cudaProfilerStart/Stop and exit "
+                         "(for `ncu --profile-from-start off`; prints no bench line)")
     return ap.parse_args()
 
 
@@ -189,12 +192,20 @@ def kernel_rooflines(B2, size, pk):
     dev = "cuda"
     n = size * size
     out = []
-    # K4 self-attention, level 0: [B2*8 heads, n, n, d=20]
-    qkv = torch.randn(B2, n, 480, device=dev).to(torch.bfloat16)
-    q, k, v = qkv[:, :, :160], qkv[:, :, 160:320], qkv[:, :, 320:]
-    ms = time_kernel(lambda: ops.attention(q, k, v, 8, 20, 1 / math.sqrt(20)))
+    # K4 self-attention, level 0: [B2*8 heads, n, n, d=20] on head-padded operands (32 columns per head:
+    # q/k zero beyond d, v carries the ones column that yields the softmax denominator)
+    def padded(ones):
+        t = torch.zeros(B2, n, 8, 32, device=dev)
+        t[..., :20] = torch.randn(B2, n, 8, 20, device=dev)
+        if ones:
+            t[..., 20] = 1.0
+        return t.reshape(B2, n, 256).to(torch.bfloat16)
+    q, k, v = padded(False), padded(False), padded(True)
+    ms = time_kernel(lambda: ops.attention_p32(q, k, v, 8, 20, 1 / math.sqrt(20)))
     fl = 4.0 * B2 * 8 * n * n * 20
-    out.append({"kernel": "attention_kernel<32> self-attn d=20", "ms": ms, "flops": fl})
+    out.append({"kernel": "attention_umma_kernel<3> self-attn d=20 (tcgen05, head-padded)", "ms": ms, "flops": fl,
+                "exp_pairs_per_clk_per_sm": B2 * 8.0 * n * n / (ms * 1e-3) / 148 / 1.965e9})
+    del q, k, v
     # K1 conv3x3 160->160 @ size^2
     x = torch.randn(B2, size, size, 160, device=dev).to(torch.bfloat16)
     w = (torch.randn(160, 3, 3, 160, device=dev) * 0.03).to(torch.bfloat16)
@@ -264,6 +275,12 @@ def run_b200(args):
     for _ in range(max(args.warmup, 3)):
         gs.step()
     barrier()
+    if args.profile_step:
+        torch.cuda.profiler.start()
+        gs.step()
+        torch.cuda.synchronize()
+        torch.cuda.profiler.stop()
+        return
     clk = ClockSampler(local)
     if rank == 0:
         clk.start()
@@ -308,7 +325,7 @@ def run_b200(args):
     tpath = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     if os.path.exists(tpath):
         try:
-            traffic = json.load(open(tpath)).get("attention_dram_bytes_per_launch")
+            traffic = json.load(open(tpath)).get("attention_umma_dram_bytes_per_launch")
         except Exception:
             traffic = None
     step_tf = GF_PER_LATENT_STEP * 1e9 * B * (S * S / 4096.0) / (ms / args.steps * 1e-3) / 1e12
