@@ -3,9 +3,16 @@
 //   * GEMM  out[M,N] = A[M,K] W[N,K]^T           (A = one or two K segments, 2-D tensor maps)
 //   * 3x3 convolution as implicit GEMM over NHWC  (A = 9 shifted 4-D boxes per channel chunk;
 //     out-of-image taps are zero-filled by the TMA unit, which is exactly Conv2d(padding=1))
-// Roles: warp 0 = TMA producer, warp 1 = MMA issuer (owns TMEM), warps 2..9 = epilogue
-// (TMEM -> registers -> fused bias/temb/residual/activation -> global).  Two TMEM accumulator
-// stages let the epilogue of tile i overlap the main loop of tile i+1.
+// Roles (384 threads):
+//   warp 0      TMA producer (operand ring; in "resident-B" mode the weight tile is loaded once)
+//   warp 1      MMA issuer (owns TMEM: two accumulator stages of up to 256 columns)
+//   warp 2      epilogue DMA: bias (+temb) rows and the bf16 residual tile into the staging buffers
+//               (TMA loads), finished tiles out of them (TMA stores)
+//   warp 3      idle (keeps the epilogue warps on warpgroup boundaries)
+//   warps 4-7   epilogue warpgroup 0: tiles 0, 2, 4, ... of this CTA (accumulator stage 0)
+//   warps 8-11  epilogue warpgroup 1: tiles 1, 3, 5, ... (accumulator stage 1)
+// Every hand-off is an mbarrier; the two epilogue warpgroups ping-pong so that the epilogue of
+// tile i, the main loop of tile i+1 and the store / residual fetch of tiles i-1 / i+1 overlap.
 #include <stdlib.h>
 
 #include "common.cuh"
@@ -14,9 +21,10 @@ namespace sdb {
 
 constexpr int kTileM = 128;
 constexpr int kMaxBN = 256;
-constexpr int kGemmThreads = 320;  // warp 0 TMA, warp 1 MMA, warps 2..9 epilogue
+constexpr int kGemmThreads = 384;
 constexpr int kMaxStages = 12;
-constexpr int kSmemBudget = 224 * 1024;  // operand ring + epilogue staging; + barriers / alignment slack
+constexpr int kSmemBudget = 222 * 1024;  // resident B + operand ring + epilogue staging
+constexpr int kBiasBytes = 2 * kMaxBN * 4;
 
 struct UmmaParams {
   CUtensorMap tmA[2];
@@ -29,6 +37,9 @@ struct UmmaParams {
   int BK, swz, BN;
   int num_stages, stage_bytes, a_bytes, b_bytes;
   int tiles_m, tiles_n;
+  // resident-B scheduling (GEMM with a short K): each CTA keeps one n-tile of the weights in smem for
+  // its whole life and streams only A; CTA c owns n-tile c % tiles_n and m-tiles c / tiles_n + j * m_groups
+  int resB, bres_bytes, m_groups;
   // conv geometry (GEMM-M space = input-resolution pixels)
   int kb_per_tap, Cin;
   int TW, TH, TN, tiles_w, tiles_h;
@@ -40,6 +51,7 @@ struct UmmaParams {
   const float* bias;
   const float* temb;
   long long ld_temb;
+  int temb_in_bias;  // tile lies inside one image: temb row folded into the staged bias row
   const void* residual;
   long long ldr;
   int res_dtype;
@@ -49,105 +61,46 @@ struct UmmaParams {
   int act;
   // staged epilogue (bf16 output through swizzled smem slabs + TMA store): 0 = direct stores
   int staged;
+  int nbuf;         // staging buffers (2 = one per epilogue warpgroup, 1 = shared)
   int bno;          // output columns per tile (BN, or BN/2 for GEGLU)
   int nslab;        // full 64-column slabs per tile
   int tail_cols;    // columns of the last, narrower slab (0, 16 or 32)
-  int staging_bytes;
+  int stg_bytes;    // bytes of one staging buffer
 };
 
-// exact-erf GELU (transformer.py:177 uses nn.GELU()) with erf from Abramowitz-Stegun 7.1.26
-// (|error| <= 1.5e-7, far inside the bf16 rounding of the result): 2 MUFU + ~10 FMA-pipe ops
-// instead of the ~30-instruction branchy erff -- the GEGLU epilogue is issue-bound.
-__device__ __forceinline__ float gelu_erf_fast(float x) {
-  const float z = fabsf(x) * 0.70710678118654752440f;
-  const float t = __fdividef(1.0f, fmaf(0.3275911f, z, 1.0f));
-  float poly = fmaf(1.061405429f, t, -1.453152027f);
-  poly = fmaf(poly, t, 1.421413741f);
-  poly = fmaf(poly, t, -0.284496736f);
-  poly = fmaf(poly, t, 0.254829592f);
-  const float e = exp2f(-z * z * 1.4426950408889634f);
-  const float erf_abs = fmaf(-poly * t, e, 1.0f);          // erf(|x|/sqrt2)
-  const float erf_v = copysignf(erf_abs, x);
-  return 0.5f * x * (1.0f + erf_v);
+// ---- packed fp32 pair helpers (one issue slot for two elements) ---------------------------------
+__device__ __forceinline__ void fmul2(float& d0, float& d1, float a0, float a1, float b0, float b1) {
+  asm("{\n\t.reg .b64 ra, rb, rd;\n\t"
+      "mov.b64 ra, {%2, %3};\n\tmov.b64 rb, {%4, %5};\n\t"
+      "mul.rn.f32x2 rd, ra, rb;\n\t"
+      "mov.b64 {%0, %1}, rd;\n\t}"
+      : "=f"(d0), "=f"(d1)
+      : "f"(a0), "f"(a1), "f"(b0), "f"(b1));
 }
 
-// ---- epilogue for 16 consecutive accumulator columns of one row -------------------------------
-// `res` holds the row's 16 residual values (bf16, prefetched before the accumulator was ready)
-// when kResPre, else the residual is read here (fp32 residual: rare, un-prefetched path).
-template <bool kResPre>
-__device__ __forceinline__ void epilogue16(const UmmaParams& p, const uint32_t (&acc)[16],
-                                           long long out_row, int img, int col, const uint4 (&res)[2]) {
-  float v[16];
-#pragma unroll
-  for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(acc[j]);
-  if (p.bias) {
-#pragma unroll
-    for (int j = 0; j < 16; j += 4) {
-      float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col + j));
-      v[j] += b.x; v[j + 1] += b.y; v[j + 2] += b.z; v[j + 3] += b.w;
-    }
-  }
-  if (p.temb) {
-    const float* t = p.temb + (long long)img * p.ld_temb + col;
-#pragma unroll
-    for (int j = 0; j < 16; j += 4) {
-      float4 b = __ldg(reinterpret_cast<const float4*>(t + j));
-      v[j] += b.x; v[j + 1] += b.y; v[j + 2] += b.z; v[j + 3] += b.w;
-    }
-  }
-  if (p.act == SDB_ACT_GEGLU) {
-    // interleaved columns (a_j, g_j): 16 accumulator columns -> 8 outputs
-    float o[8];
-#pragma unroll
-    for (int j = 0; j < 8; ++j) o[j] = v[2 * j] * gelu_erf_fast(v[2 * j + 1]);
-    const long long off = out_row * p.ldo + (col >> 1);
-    if (p.out_dtype == SDB_BF16) {
-      uint4 w = make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]),
-                           pack_bf16x2(o[4], o[5]), pack_bf16x2(o[6], o[7]));
-      *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + off) = w;
-    } else {
-      float4* d = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + off);
-      d[0] = make_float4(o[0], o[1], o[2], o[3]);
-      d[1] = make_float4(o[4], o[5], o[6], o[7]);
-    }
-    return;
-  }
-  if (p.act == SDB_ACT_SILU) {
-#pragma unroll
-    for (int j = 0; j < 16; ++j) v[j] = silu_f(v[j]);
-  }
-  if (p.residual) {
-    if (kResPre) {
-#pragma unroll
-      for (int h = 0; h < 2; ++h) {
-        const uint4 q = res[h];
-        float2 a = unpack_bf16x2(q.x), b = unpack_bf16x2(q.y), c = unpack_bf16x2(q.z),
-               d = unpack_bf16x2(q.w);
-        v[8 * h + 0] += a.x; v[8 * h + 1] += a.y; v[8 * h + 2] += b.x; v[8 * h + 3] += b.y;
-        v[8 * h + 4] += c.x; v[8 * h + 5] += c.y; v[8 * h + 6] += d.x; v[8 * h + 7] += d.y;
-      }
-    } else {
-      const float4* r = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.residual) +
-                                                        out_row * p.ldr + col);
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        float4 q = __ldg(r + j);
-        v[4 * j] += q.x; v[4 * j + 1] += q.y; v[4 * j + 2] += q.z; v[4 * j + 3] += q.w;
-      }
-    }
-  }
-  const long long off = out_row * p.ldo + col;
-  if (p.out_dtype == SDB_BF16) {
-    uint4* d = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + off);
-    d[0] = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
-                      pack_bf16x2(v[6], v[7]));
-    d[1] = make_uint4(pack_bf16x2(v[8], v[9]), pack_bf16x2(v[10], v[11]),
-                      pack_bf16x2(v[12], v[13]), pack_bf16x2(v[14], v[15]));
-  } else {
-    float4* d = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + off);
-#pragma unroll
-    for (int j = 0; j < 4; ++j) d[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-  }
+// a * gelu(g) for two (a, g) pairs, exact-erf GELU (transformer.py:177 uses nn.GELU()).
+//   erf(|g|/sqrt2) = 1 - 2^(-|g| P(|g|)),  P = degree-7 fit of -log2(erfc(u/sqrt2))/u on [0, 6]
+// (|error| <= 1.6e-6 in erf, i.e. <= 5e-6 in the GELU value -- three orders below the bf16 rounding
+// of the result).  One MUFU (ex2) per element and packed FMAs: the GEGLU epilogue is issue-bound.
+__device__ __forceinline__ void geglu2(float a0, float a1, float g0, float g1, float& o0, float& o1) {
+  const float u0 = fminf(fabsf(g0), 6.0f), u1 = fminf(fabsf(g1), 6.0f);
+  float p0, p1;
+  ffma2(p0, p1, u0, u1, 2.566215187016496e-07f, 2.566215187016496e-07f, -4.049981271236902e-06f,
+        -4.049981271236902e-06f);
+  ffma2(p0, p1, p0, p1, u0, u1, -7.237450518005062e-06f, -7.237450518005062e-06f);
+  ffma2(p0, p1, p0, p1, u0, u1, 0.000671996793244034f, 0.000671996793244034f);
+  ffma2(p0, p1, p0, p1, u0, u1, -0.007837459444999695f, -0.007837459444999695f);
+  ffma2(p0, p1, p0, p1, u0, u1, 0.05303756147623062f, 0.05303756147623062f);
+  ffma2(p0, p1, p0, p1, u0, u1, 0.4590655267238617f, 0.4590655267238617f);
+  ffma2(p0, p1, p0, p1, u0, u1, 1.1511108875274658f, 1.1511108875274658f);
+  fmul2(p0, p1, p0, p1, -u0, -u1);
+  const float e0 = ex2_mufu(p0), e1 = ex2_mufu(p1);
+  // 0.5 g (1 + erf(g/sqrt2)) = h + h * copysign(1 - e, g),  h = g / 2
+  const float s0 = copysignf(1.0f - e0, g0), s1 = copysignf(1.0f - e1, g1);
+  float h0, h1;
+  fmul2(h0, h1, g0, g1, 0.5f, 0.5f);
+  ffma2(h0, h1, h0, h1, s0, s1, h0, h1);
+  fmul2(o0, o1, h0, h1, a0, a1);
 }
 
 __device__ __forceinline__ void tma_store_2d(const void* tmap, uint32_t src, int c0, int c1) {
@@ -165,8 +118,16 @@ __device__ __forceinline__ uint4 lds128(uint32_t a) {
   asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
   return v;
 }
+__device__ __forceinline__ float4 lds128f(uint32_t a) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(a));
+  return v;
+}
 __device__ __forceinline__ void sts128(uint32_t a, uint4 v) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ void sts32f(uint32_t a, float v) {
+  asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(v) : "memory");
 }
 
 // Shared-memory address of the 16-byte chunk holding output columns [oc, oc+8) of tile row r.  The tile is
@@ -185,35 +146,50 @@ __device__ __forceinline__ uint32_t stage_addr(const UmmaParams& p, uint32_t stg
   return base + (uint32_t)r * 32u + (uint32_t)((chunk ^ ((r >> 2) & 1)) << 4);
 }
 
-// epilogue of 16 accumulator columns into the staged tile: bias / temb / activation, residual read from
-// (and result written back to) the swizzled slab the TMA unit loaded / will store.
+// acc[0..16) += bias row (fp32 in shared memory; every lane reads the same address: one wavefront)
+__device__ __forceinline__ void add_bias16(float (&v)[16], const uint32_t (&acc)[16], uint32_t bias_s) {
+#pragma unroll
+  for (int j = 0; j < 16; j += 4) {
+    const float4 b = lds128f(bias_s + 4u * j);
+    fadd2(v[j], v[j + 1], __uint_as_float(acc[j]), __uint_as_float(acc[j + 1]), b.x, b.y);
+    fadd2(v[j + 2], v[j + 3], __uint_as_float(acc[j + 2]), __uint_as_float(acc[j + 3]), b.z, b.w);
+  }
+}
+
+__device__ __forceinline__ void add_bf16x8(float* v, uint4 q) {
+  const float2 x = unpack_bf16x2(q.x), y = unpack_bf16x2(q.y), z = unpack_bf16x2(q.z), w = unpack_bf16x2(q.w);
+  fadd2(v[0], v[1], v[0], v[1], x.x, x.y);
+  fadd2(v[2], v[3], v[2], v[3], y.x, y.y);
+  fadd2(v[4], v[5], v[4], v[5], z.x, z.y);
+  fadd2(v[6], v[7], v[6], v[7], w.x, w.y);
+}
+__device__ __forceinline__ uint4 pack_bf16x8(const float* v) {
+  return make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
+                    pack_bf16x2(v[6], v[7]));
+}
+
+// ---- 16 accumulator columns of one row -> staged tile ------------------------------------------
+// `tcol` = accumulator column inside the tile, `temb_row` = per-element temb (only when it could not be
+// folded into the staged bias row).  The residual is read from (and the result written back to) the
+// swizzled slab the TMA unit loaded / will store.
+template <bool kGeglu>
 __device__ __forceinline__ void epilogue16_staged(const UmmaParams& p, const uint32_t (&acc)[16], uint32_t stg,
-                                                  int r, int img, int col, int col_in_tile) {
+                                                  uint32_t bias_s, const float* temb_row, int r, int tcol) {
   float v[16];
-#pragma unroll
-  for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(acc[j]);
-  if (p.bias) {
+  add_bias16(v, acc, bias_s + 4u * tcol);
+  if (temb_row) {
 #pragma unroll
     for (int j = 0; j < 16; j += 4) {
-      float4 b = __ldg(reinterpret_cast<const float4*>(p.bias + col + j));
+      const float4 b = __ldg(reinterpret_cast<const float4*>(temb_row + tcol + j));
       v[j] += b.x; v[j + 1] += b.y; v[j + 2] += b.z; v[j + 3] += b.w;
     }
   }
-  if (p.temb) {
-    const float* t = p.temb + (long long)img * p.ld_temb + col;
-#pragma unroll
-    for (int j = 0; j < 16; j += 4) {
-      float4 b = __ldg(reinterpret_cast<const float4*>(t + j));
-      v[j] += b.x; v[j + 1] += b.y; v[j + 2] += b.z; v[j + 3] += b.w;
-    }
-  }
-  if (p.act == SDB_ACT_GEGLU) {
+  if (kGeglu) {
+    // interleaved columns (a_j, g_j): 16 accumulator columns -> 8 outputs
     float o[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) o[j] = v[2 * j] * gelu_erf_fast(v[2 * j + 1]);
-    sts128(stage_addr(p, stg, r, col_in_tile >> 1),
-           make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]),
-                      pack_bf16x2(o[6], o[7])));
+    for (int j = 0; j < 8; j += 2) geglu2(v[2 * j], v[2 * j + 2], v[2 * j + 1], v[2 * j + 3], o[j], o[j + 1]);
+    sts128(stage_addr(p, stg, r, tcol >> 1), pack_bf16x8(o));
     return;
   }
   if (p.act == SDB_ACT_SILU) {
@@ -222,32 +198,101 @@ __device__ __forceinline__ void epilogue16_staged(const UmmaParams& p, const uin
   }
 #pragma unroll
   for (int h = 0; h < 2; ++h) {
-    const uint32_t a = stage_addr(p, stg, r, col_in_tile + 8 * h);
-    if (p.residual) {
-      const uint4 q = lds128(a);
-      float2 x = unpack_bf16x2(q.x), y = unpack_bf16x2(q.y), z = unpack_bf16x2(q.z), w = unpack_bf16x2(q.w);
-      v[8 * h + 0] += x.x; v[8 * h + 1] += x.y; v[8 * h + 2] += y.x; v[8 * h + 3] += y.y;
-      v[8 * h + 4] += z.x; v[8 * h + 5] += z.y; v[8 * h + 6] += w.x; v[8 * h + 7] += w.y;
-    }
-    sts128(a, make_uint4(pack_bf16x2(v[8 * h], v[8 * h + 1]), pack_bf16x2(v[8 * h + 2], v[8 * h + 3]),
-                         pack_bf16x2(v[8 * h + 4], v[8 * h + 5]), pack_bf16x2(v[8 * h + 6], v[8 * h + 7])));
+    const uint32_t a = stage_addr(p, stg, r, tcol + 8 * h);
+    if (p.residual) add_bf16x8(v + 8 * h, lds128(a));
+    sts128(a, pack_bf16x8(v + 8 * h));
   }
+}
+
+// ---- 16 accumulator columns of one row -> global memory (fp32 output / fp32 residual / strided rows) ----
+__device__ __forceinline__ void epilogue16_direct(const UmmaParams& p, const uint32_t (&acc)[16], uint32_t bias_s,
+                                                  const float* temb_row, long long out_row, int n0, int tcol) {
+  float v[16];
+  add_bias16(v, acc, bias_s + 4u * tcol);
+  const int col = n0 + tcol;
+  if (temb_row) {
+#pragma unroll
+    for (int j = 0; j < 16; j += 4) {
+      const float4 b = __ldg(reinterpret_cast<const float4*>(temb_row + tcol + j));
+      v[j] += b.x; v[j + 1] += b.y; v[j + 2] += b.z; v[j + 3] += b.w;
+    }
+  }
+  if (p.act == SDB_ACT_GEGLU) {
+    float o[8];
+#pragma unroll
+    for (int j = 0; j < 8; j += 2) geglu2(v[2 * j], v[2 * j + 2], v[2 * j + 1], v[2 * j + 3], o[j], o[j + 1]);
+    const long long off = out_row * p.ldo + (col >> 1);
+    if (p.out_dtype == SDB_BF16) {
+      *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + off) = pack_bf16x8(o);
+    } else {
+      float4* d = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + off);
+      d[0] = make_float4(o[0], o[1], o[2], o[3]);
+      d[1] = make_float4(o[4], o[5], o[6], o[7]);
+    }
+    return;
+  }
+  if (p.act == SDB_ACT_SILU) {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) v[j] = silu_f(v[j]);
+  }
+  if (p.residual) {
+    if (p.res_dtype == SDB_BF16) {
+      const uint4* rr = reinterpret_cast<const uint4*>(reinterpret_cast<const __nv_bfloat16*>(p.residual) +
+                                                       out_row * p.ldr + col);
+      add_bf16x8(v, __ldg(rr));
+      add_bf16x8(v + 8, __ldg(rr + 1));
+    } else {
+      const float4* rr = reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.residual) +
+                                                         out_row * p.ldr + col);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float4 q = __ldg(rr + j);
+        v[4 * j] += q.x; v[4 * j + 1] += q.y; v[4 * j + 2] += q.z; v[4 * j + 3] += q.w;
+      }
+    }
+  }
+  const long long off = out_row * p.ldo + col;
+  if (p.out_dtype == SDB_BF16) {
+    uint4* d = reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + off);
+    d[0] = pack_bf16x8(v);
+    d[1] = pack_bf16x8(v + 8);
+  } else {
+    float4* d = reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + off);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) d[j] = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+  }
+}
+
+// j-th tile of this CTA (see UmmaParams::resB); false once the CTA has run out of tiles
+__device__ __forceinline__ bool cta_tile(const UmmaParams& p, int j, int& m_tile, int& n_tile) {
+  if (p.resB) {
+    n_tile = (int)blockIdx.x % p.tiles_n;
+    m_tile = (int)blockIdx.x / p.tiles_n + j * p.m_groups;
+    return m_tile < p.tiles_m;
+  }
+  const int t = (int)blockIdx.x + j * (int)gridDim.x;
+  n_tile = t % p.tiles_n;
+  m_tile = t / p.tiles_n;
+  return t < p.tiles_m * p.tiles_n;
 }
 
 __global__ void __launch_bounds__(kGemmThreads, 1)
 umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  // 1024-B aligned operand ring (SWIZZLE_128B atoms), then the barriers
+  // 1024-B aligned: [resident B][operand ring][staging buffers][bias rows][barriers]
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t ring_bytes = (uint32_t)p.num_stages * (uint32_t)p.stage_bytes;
-  const uint32_t stg_base = smem_base + ring_bytes;                 // epilogue staging (1024-B aligned)
-  const uint32_t bar_base = stg_base + (uint32_t)p.staging_bytes;
+  const uint32_t ring_base = smem_base + (uint32_t)p.bres_bytes;
+  const uint32_t stg_base = ring_base + (uint32_t)p.num_stages * (uint32_t)p.stage_bytes;
+  const uint32_t bias_base = stg_base + (uint32_t)p.nbuf * (uint32_t)p.stg_bytes;
+  const uint32_t bar_base = bias_base + (uint32_t)kBiasBytes;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
   auto empty_bar = [&](int s) { return bar_base + 8u * (kMaxStages + s); };
   auto tfull_bar = [&](int a) { return bar_base + 8u * (2 * kMaxStages + a); };
   auto tempty_bar = [&](int a) { return bar_base + 8u * (2 * kMaxStages + 2 + a); };
-  const uint32_t res_bar = bar_base + 8u * (2 * kMaxStages + 4);
-  const uint32_t tmem_slot = bar_base + 8u * (2 * kMaxStages + 5);
+  auto res_full_bar = [&](int b) { return bar_base + 8u * (2 * kMaxStages + 4 + b); };   // bias row (+ residual) landed
+  auto stg_full_bar = [&](int b) { return bar_base + 8u * (2 * kMaxStages + 6 + b); };   // tile staged / bias row consumed
+  const uint32_t bfull_bar = bar_base + 8u * (2 * kMaxStages + 8);
+  const uint32_t tmem_slot = bar_base + 8u * (2 * kMaxStages + 9);
   volatile uint32_t* tmem_slot_ptr =
       reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
 
@@ -263,9 +308,11 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(tfull_bar(a), 1);
-      mbar_init(tempty_bar(a), 256);
+      mbar_init(tempty_bar(a), 128);
+      mbar_init(res_full_bar(a), 1);
+      mbar_init(stg_full_bar(a), 128);
     }
-    mbar_init(res_bar, 1);
+    mbar_init(bfull_bar, 1);
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -277,39 +324,47 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
 
-  const int total_tiles = p.tiles_m * p.tiles_n;
-
   if (warp == 0) {
     // ===================== TMA producer =====================
     // (whole warp runs the loop -- warp-uniform control flow keeps coordinates and descriptors in
-    // uniform registers; one elected lane issues the TMA / tcgen05 instructions)
-    {
-      int stage = 0;
-      uint32_t phase = 0;
-      bool ok = true;
-      for (int tile = blockIdx.x; tile < total_tiles && ok; tile += gridDim.x) {
-        const int n_tile = tile % p.tiles_n, m_tile = tile / p.tiles_n;
-        const int n0 = n_tile * p.BN;
-        int w0 = 0, h0 = 0, i0 = 0;
-        if (p.mode == 1) {
-          w0 = (m_tile % p.tiles_w) * p.TW;
-          h0 = ((m_tile / p.tiles_w) % p.tiles_h) * p.TH;
-          i0 = (m_tile / (p.tiles_w * p.tiles_h)) * p.TN;
-        }
+    // uniform registers; one elected lane issues the TMA instructions)
+    int stage = 0;
+    uint32_t phase = 0;
+    bool ok = true;
+    int m_tile, n_tile;
+    if (p.resB && cta_tile(p, 0, m_tile, n_tile)) {
+      if (elect_one()) {
+        mbar_arrive_expect_tx(bfull_bar, (uint32_t)p.bres_bytes);
         for (int kb = 0; kb < p.num_kb; ++kb) {
-          ok = mbar_wait(empty_bar(stage), phase ^ 1u);
-          if (!ok) break;
-          const uint32_t sa = smem_base + (uint32_t)stage * p.stage_bytes;
-          const uint32_t sb = sa + p.a_bytes;
-          if (elect_one()) {
-          mbar_arrive_expect_tx(full_bar(stage), (uint32_t)(p.a_bytes + p.b_bytes));
+          const int kc = kb < p.kb1 ? kb * p.BK : p.K1 + (kb - p.kb1) * p.BK;
+          tma_load_2d(smem_base + (uint32_t)kb * p.b_bytes, &p.tmB, bfull_bar, kc, n_tile * p.BN);
+        }
+      }
+      __syncwarp();
+    }
+    const uint32_t tx = (uint32_t)(p.resB ? p.a_bytes : p.a_bytes + p.b_bytes);
+    for (int j = 0; cta_tile(p, j, m_tile, n_tile) && ok; ++j) {
+      const int n0 = n_tile * p.BN;
+      int w0 = 0, h0 = 0, i0 = 0;
+      if (p.mode == 1) {
+        w0 = (m_tile % p.tiles_w) * p.TW;
+        h0 = ((m_tile / p.tiles_w) % p.tiles_h) * p.TH;
+        i0 = (m_tile / (p.tiles_w * p.tiles_h)) * p.TN;
+      }
+      for (int kb = 0; kb < p.num_kb; ++kb) {
+        ok = mbar_wait(empty_bar(stage), phase ^ 1u);
+        if (!ok) break;
+        const uint32_t sa = ring_base + (uint32_t)stage * p.stage_bytes;
+        const uint32_t sb = sa + p.a_bytes;
+        if (elect_one()) {
+          mbar_arrive_expect_tx(full_bar(stage), tx);
           if (p.mode == 0) {
             if (kb < p.kb1) {
               tma_load_2d(sa, &p.tmA[0], full_bar(stage), kb * p.BK, m_tile * kTileM);
-              tma_load_2d(sb, &p.tmB, full_bar(stage), kb * p.BK, n0);
+              if (!p.resB) tma_load_2d(sb, &p.tmB, full_bar(stage), kb * p.BK, n0);
             } else {
               tma_load_2d(sa, &p.tmA[1], full_bar(stage), (kb - p.kb1) * p.BK, m_tile * kTileM);
-              tma_load_2d(sb, &p.tmB, full_bar(stage), p.K1 + (kb - p.kb1) * p.BK, n0);
+              if (!p.resB) tma_load_2d(sb, &p.tmB, full_bar(stage), p.K1 + (kb - p.kb1) * p.BK, n0);
             }
           } else {
             const int tap = kb / p.kb_per_tap;
@@ -318,148 +373,152 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
                         h0 + p.tap_dh[tap], i0);
             tma_load_2d(sb, &p.tmB, full_bar(stage), tap * p.Cin + c0, n0);
           }
-          }
-          __syncwarp();
-          if (++stage == p.num_stages) { stage = 0; phase ^= 1u; }
         }
+        __syncwarp();
+        if (++stage == p.num_stages) { stage = 0; phase ^= 1u; }
       }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
-    {
-      const uint32_t idesc = umma_idesc_bf16(kTileM, (uint32_t)p.BN);
-      const int k_sub = p.BK / 16;
-      int stage = 0;
-      uint32_t phase = 0;
-      int it = 0;
-      bool ok = true;
-      for (int tile = blockIdx.x; tile < total_tiles && ok; tile += gridDim.x, ++it) {
-        const int acc = it & 1;
-        const uint32_t acc_phase = (uint32_t)(it >> 1) & 1u;
-        ok = mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
+    const uint32_t idesc = umma_idesc_bf16(kTileM, (uint32_t)p.BN);
+    const int k_sub = p.BK / 16;
+    int stage = 0;
+    uint32_t phase = 0;
+    bool ok = true;
+    int m_tile, n_tile;
+    if (p.resB && cta_tile(p, 0, m_tile, n_tile)) ok = mbar_wait(bfull_bar, 0);
+    for (int j = 0; cta_tile(p, j, m_tile, n_tile) && ok; ++j) {
+      const int acc = j & 1;
+      const uint32_t acc_phase = (uint32_t)(j >> 1) & 1u;
+      ok = mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
+      if (!ok) break;
+      tc_fence_after();
+      const uint32_t tmem_d = tmem_base + (uint32_t)acc * kMaxBN;
+      for (int kb = 0; kb < p.num_kb; ++kb) {
+        ok = mbar_wait(full_bar(stage), phase);
         if (!ok) break;
         tc_fence_after();
-        const uint32_t tmem_d = tmem_base + (uint32_t)acc * kMaxBN;
-        for (int kb = 0; kb < p.num_kb; ++kb) {
-          ok = mbar_wait(full_bar(stage), phase);
-          if (!ok) break;
-          tc_fence_after();
-          const uint32_t sa = smem_base + (uint32_t)stage * p.stage_bytes;
-          const uint32_t sb = sa + p.a_bytes;
-          const uint64_t adesc = umma_smem_desc(sa, (uint32_t)p.swz);
-          const uint64_t bdesc = umma_smem_desc(sb, (uint32_t)p.swz);
-          if (elect_one()) {
-            for (int k = 0; k < k_sub; ++k) {
-              // advance 16 bf16 = 32 B along K inside the swizzle atom: +2 in the (addr >> 4) field
-              umma_f16(tmem_d, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc,
-                       (kb | k) != 0 ? 1u : 0u);
-            }
-            umma_commit(empty_bar(stage));
+        const uint32_t sa = ring_base + (uint32_t)stage * p.stage_bytes;
+        const uint32_t sb = p.resB ? smem_base + (uint32_t)kb * p.b_bytes : sa + p.a_bytes;
+        const uint64_t adesc = umma_smem_desc(sa, (uint32_t)p.swz);
+        const uint64_t bdesc = umma_smem_desc(sb, (uint32_t)p.swz);
+        if (elect_one()) {
+          for (int k = 0; k < k_sub; ++k) {
+            // advance 16 bf16 = 32 B along K inside the swizzle atom: +2 in the (addr >> 4) field
+            umma_f16(tmem_d, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc,
+                     (kb | k) != 0 ? 1u : 0u);
           }
-          __syncwarp();
-          if (++stage == p.num_stages) { stage = 0; phase ^= 1u; }
+          umma_commit(empty_bar(stage));
         }
-        if (elect_one()) umma_commit(tfull_bar(acc));
         __syncwarp();
+        if (++stage == p.num_stages) { stage = 0; phase ^= 1u; }
+      }
+      if (elect_one()) umma_commit(tfull_bar(acc));
+      __syncwarp();
+    }
+  } else if (warp == 2) {
+    // ===================== epilogue DMA =====================
+    // For every tile: stage its bias (+temb) row as fp32, fetch the bf16 residual tile into the staging
+    // buffer (TMA), and -- once the owning warpgroup has overwritten it with the result -- store it (TMA).
+    auto tile_coords = [&](int m_tile, int n_tile, int& o0, int& w0, int& h0, int& i0) {
+      const int n0 = n_tile * p.BN;
+      o0 = (p.act == SDB_ACT_GEGLU) ? (n0 >> 1) : n0;   // first output column of the tile
+      w0 = h0 = i0 = 0;
+      if (p.mode == 1) {
+        w0 = (m_tile % p.tiles_w) * p.TW;
+        h0 = ((m_tile / p.tiles_w) % p.tiles_h) * p.TH;
+        i0 = (m_tile / (p.tiles_w * p.tiles_h)) * p.TN;
+      }
+    };
+    auto prep = [&](int j, int m_tile, int n_tile) {   // buffer j % nbuf is free
+      const int buf = p.nbuf == 2 ? (j & 1) : 0;
+      const uint32_t bias_s = bias_base + (uint32_t)buf * (kMaxBN * 4);
+      int o0, w0, h0, i0;
+      tile_coords(m_tile, n_tile, o0, w0, h0, i0);
+      const int n0 = n_tile * p.BN;
+      const int img = i0 < p.B ? i0 : 0;
+      for (int i = lane; i < p.BN; i += 32) {
+        float b = 0.f;
+        if (n0 + i < p.N) {
+          if (p.bias) b = __ldg(p.bias + n0 + i);
+          if (p.temb_in_bias) b += __ldg(p.temb + (long long)img * p.ld_temb + n0 + i);
+        }
+        sts32f(bias_s + 4u * i, b);
+      }
+      __syncwarp();
+      if (elect_one()) {
+        if (p.staged && p.residual) {
+          mbar_arrive_expect_tx(res_full_bar(j & 1), 128u * (uint32_t)p.bno * 2u);
+          const uint32_t stg = stg_base + (uint32_t)buf * (uint32_t)p.stg_bytes;
+          for (int sl = 0; sl <= p.nslab; ++sl) {
+            if (sl == p.nslab && p.tail_cols == 0) break;
+            const void* tm = sl < p.nslab ? (const void*)&p.tmR : (const void*)&p.tmRt;
+            const uint32_t dst = stg + (uint32_t)sl * 16384u;
+            if (p.mode == 0) tma_load_2d(dst, tm, res_full_bar(j & 1), o0 + sl * 64, m_tile * kTileM);
+            else tma_load_4d(dst, tm, res_full_bar(j & 1), o0 + sl * 64, w0, h0, i0);
+          }
+        } else {
+          mbar_arrive(res_full_bar(j & 1));
+        }
+      }
+      __syncwarp();
+    };
+    bool ok = true;
+    int m_tile, n_tile, m2, n2;
+    if (cta_tile(p, 0, m_tile, n_tile)) prep(0, m_tile, n_tile);
+    for (int j = 0; cta_tile(p, j, m_tile, n_tile); ++j) {
+      const int buf = p.nbuf == 2 ? (j & 1) : 0;
+      const uint32_t use_phase = (uint32_t)(j >> 1) & 1u;   // barriers are per warpgroup even when the buffer is shared
+      const bool more = cta_tile(p, j + 1, m2, n2);
+      if (p.nbuf == 2 && more) {
+        if (p.staged) {
+          if (elect_one()) tma_store_wait_read();   // tile j-1's store has drained the other buffer
+          __syncwarp();
+        }
+        prep(j + 1, m2, n2);
+      }
+      if (ok) ok = mbar_wait(stg_full_bar(j & 1), use_phase);
+      if (p.staged) {
+        if (elect_one() && ok) {
+          int o0, w0, h0, i0;
+          tile_coords(m_tile, n_tile, o0, w0, h0, i0);
+          const uint32_t stg = stg_base + (uint32_t)buf * (uint32_t)p.stg_bytes;
+          for (int sl = 0; sl <= p.nslab; ++sl) {
+            if (sl == p.nslab && p.tail_cols == 0) break;
+            const void* tm = sl < p.nslab ? (const void*)&p.tmO : (const void*)&p.tmOt;
+            const uint32_t src = stg + (uint32_t)sl * 16384u;
+            if (p.mode == 0) tma_store_2d(tm, src, o0 + sl * 64, m_tile * kTileM);
+            else tma_store_4d(tm, src, o0 + sl * 64, w0, h0, i0);
+          }
+          tma_store_commit();
+        }
+        __syncwarp();
+      }
+      if (p.nbuf == 1 && more) {
+        if (p.staged) {
+          if (elect_one()) tma_store_wait_read();
+          __syncwarp();
+        }
+        prep(j + 1, m2, n2);
       }
     }
-  } else {
-    // ===================== epilogue (warps 2..9) =====================
-    // Two warps per TMEM lane quarter; each thread owns one output row and every other 32-column
-    // pair of the tile.  The row's bf16 residual is fetched BEFORE the accumulator is waited for,
-    // so its latency hides behind the main loop instead of serialising 32 bytes at a time.
-    const int q = warp & 3;            // TMEM lane quarter this warp may access
-    const int hf = (warp - 2) >> 2;    // which 32-column pairs: hf, hf + 2, ...
-    const int r = q * 32 + lane;
     if (p.staged) {
-      // ---- staged epilogue: TMEM -> registers -> swizzled smem slabs -> TMA store ----------------
-      // Row-per-thread global stores touch 32 lines per warp instruction; staging the tile and letting
-      // the TMA unit write full lines (and fetch the bf16 residual the same way) removes that bound.
-      int it = 0;
-      bool ok = true;
-      const bool leader = (warp == 2);
-      const uint32_t res_bytes = 128u * (uint32_t)p.bno * 2u;
-      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-        const int n_tile = tile % p.tiles_n, m_tile = tile / p.tiles_n;
-        const int n0 = n_tile * p.BN;
-        const int o0 = (p.act == SDB_ACT_GEGLU) ? (n0 >> 1) : n0;   // first output column of the tile
-        const int acc = it & 1;
-        const uint32_t acc_phase = (uint32_t)(it >> 1) & 1u;
-        int img = 0, w0 = 0, h0 = 0, i0 = 0;
-        if (p.mode == 1) {
-          w0 = (m_tile % p.tiles_w) * p.TW;
-          h0 = ((m_tile / p.tiles_w) % p.tiles_h) * p.TH;
-          i0 = (m_tile / (p.tiles_w * p.tiles_h)) * p.TN;
-          img = i0 + r / (p.TW * p.TH);
-          if (img >= p.B) img = p.B - 1;   // clipped rows: any valid temb row will do
-        }
-        if (leader) {
-          if (elect_one()) {
-            tma_store_wait_read();          // the previous tile's stores have drained the staging slabs
-            if (p.residual) {
-              mbar_arrive_expect_tx(res_bar, res_bytes);
-              for (int sl = 0; sl <= p.nslab; ++sl) {
-                if (sl == p.nslab && p.tail_cols == 0) break;
-                const void* tm = sl < p.nslab ? (const void*)&p.tmR : (const void*)&p.tmRt;
-                const uint32_t dst = stg_base + (uint32_t)sl * 16384u;
-                if (p.mode == 0) tma_load_2d(dst, tm, res_bar, o0 + sl * 64, m_tile * kTileM);
-                else tma_load_4d(dst, tm, res_bar, o0 + sl * 64, w0, h0, i0);
-              }
-            }
-          }
-          __syncwarp();
-        }
-        asm volatile("bar.sync 1, 256;" ::: "memory");   // staging is free (and the residual is on its way)
-        if (ok) ok = mbar_wait(tfull_bar(acc), acc_phase);
-        if (p.residual && ok) ok = mbar_wait(res_bar, (uint32_t)it & 1u);
-        tc_fence_after();
-        const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)acc * kMaxBN;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const int c0 = (hf + 2 * i) * 32;
-          if (c0 < p.BN) {
-            uint32_t v0[16], v1[16];
-            const bool two = (c0 + 16 < p.BN);
-            tmem_ld_32x16(taddr + c0, v0);
-            if (two) tmem_ld_32x16(taddr + c0 + 16, v1);
-            tmem_ld_wait();
-            // columns beyond N carry zero-filled weights; they are clipped by the TMA store
-            const int cb = (n0 + c0 < p.N) ? n0 + c0 : 0, cb1 = (n0 + c0 + 16 < p.N) ? n0 + c0 + 16 : 0;
-            epilogue16_staged(p, v0, stg_base, r, img, cb, c0);
-            if (two) epilogue16_staged(p, v1, stg_base, r, img, cb1, c0 + 16);
-          }
-        }
-        tc_fence_before();
-        mbar_arrive(tempty_bar(acc));
-        fence_proxy_async();                               // generic-proxy smem writes -> async proxy
-        asm volatile("bar.sync 1, 256;" ::: "memory");
-        if (leader) {
-          if (elect_one() && ok) {
-            for (int sl = 0; sl <= p.nslab; ++sl) {
-              if (sl == p.nslab && p.tail_cols == 0) break;
-              const void* tm = sl < p.nslab ? (const void*)&p.tmO : (const void*)&p.tmOt;
-              const uint32_t src = stg_base + (uint32_t)sl * 16384u;
-              if (p.mode == 0) tma_store_2d(tm, src, o0 + sl * 64, m_tile * kTileM);
-              else tma_store_4d(tm, src, o0 + sl * 64, w0, h0, i0);
-            }
-            tma_store_commit();
-          }
-          __syncwarp();
-        }
-      }
-      if (leader) {
-        if (elect_one()) tma_store_wait_read();            // smem must outlive the last store's reads
-        __syncwarp();
-      }
-    } else {
-    const bool res_pre = p.residual != nullptr && p.res_dtype == SDB_BF16;
-    int it = 0;
+      if (elect_one()) tma_store_wait_read();            // smem must outlive the last store's reads
+      __syncwarp();
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue warpgroups =====================
+    // Warpgroup wg owns accumulator stage wg and every second tile; thread = one output row.
+    const int wg = (warp - 4) >> 2;
+    const int q = warp & 3;            // TMEM lane quarter this warp may access
+    const int r = q * 32 + lane;
+    const int nchunk = (p.BN + 31) >> 5;
     bool ok = true;
-    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x, ++it) {
-      const int n_tile = tile % p.tiles_n, m_tile = tile / p.tiles_n;
+    int m_tile, n_tile;
+    for (int j = wg; cta_tile(p, j, m_tile, n_tile); j += 2) {
       const int n0 = n_tile * p.BN;
-      const int acc = it & 1;
-      const uint32_t acc_phase = (uint32_t)(it >> 1) & 1u;
+      const int buf = p.nbuf == 2 ? wg : 0;
+      const uint32_t acc_phase = (uint32_t)(j >> 1) & 1u;
       long long out_row = -1;
       int img = 0;
       if (p.mode == 0) {
@@ -475,48 +534,52 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
           else if (((h | w) & 1) == 0)
             out_row = ((long long)img * (p.H >> 1) + (h >> 1)) * (p.W >> 1) + (w >> 1);
         }
+        if (img >= p.B) img = p.B - 1;   // clipped rows: any valid temb row will do
       }
-      uint4 res[4][4];   // up to 4 pairs x 32 columns of bf16 residual
-      if (res_pre && out_row >= 0) {
-        const __nv_bfloat16* rrow = reinterpret_cast<const __nv_bfloat16*>(p.residual) + out_row * p.ldr + n0;
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          const int c0 = (hf + 2 * i) * 32;
-#pragma unroll
-          for (int j = 0; j < 4; ++j)
-            if (c0 + 8 * j < p.BN && n0 + c0 + 8 * j < p.N)
-              res[i][j] = __ldg(reinterpret_cast<const uint4*>(rrow + c0 + 8 * j));
-        }
-      }
-      if (ok) ok = mbar_wait(tfull_bar(acc), acc_phase);
+      const float* temb_row =
+          (p.temb && !p.temb_in_bias) ? p.temb + (long long)img * p.ld_temb + n0 : nullptr;
+      const uint32_t stg = stg_base + (uint32_t)buf * (uint32_t)p.stg_bytes;
+      const uint32_t bias_s = bias_base + (uint32_t)buf * (kMaxBN * 4);
+      if (ok) ok = mbar_wait(res_full_bar(wg), acc_phase);
+      if (ok) ok = mbar_wait(tfull_bar(wg), acc_phase);
       tc_fence_after();
-      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)acc * kMaxBN;
-#pragma unroll
-      for (int i = 0; i < 4; ++i) {
-        const int c0 = (hf + 2 * i) * 32;
-        if (c0 < p.BN) {
-          uint32_t v0[16], v1[16];
-          const bool two = (c0 + 16 < p.BN);
-          tmem_ld_32x16(taddr + c0, v0);
-          if (two) tmem_ld_32x16(taddr + c0 + 16, v1);
-          tmem_ld_wait();
-          if (out_row >= 0 && ok) {
-            const uint4(&r0)[2] = *reinterpret_cast<const uint4(*)[2]>(&res[i][0]);
-            const uint4(&r1)[2] = *reinterpret_cast<const uint4(*)[2]>(&res[i][2]);
-            if (res_pre) {
-              if (n0 + c0 < p.N) epilogue16<true>(p, v0, out_row, img, n0 + c0, r0);
-              if (two && n0 + c0 + 16 < p.N) epilogue16<true>(p, v1, out_row, img, n0 + c0 + 16, r1);
-            } else {
-              if (n0 + c0 < p.N) epilogue16<false>(p, v0, out_row, img, n0 + c0, r0);
-              if (two && n0 + c0 + 16 < p.N) epilogue16<false>(p, v1, out_row, img, n0 + c0 + 16, r1);
-            }
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)wg * kMaxBN;
+      auto process = [&](const uint32_t (&v)[32], int tcol) {
+        const uint32_t(&lo)[16] = *reinterpret_cast<const uint32_t(*)[16]>(&v[0]);
+        const uint32_t(&hi)[16] = *reinterpret_cast<const uint32_t(*)[16]>(&v[16]);
+        const bool two = tcol + 16 < p.BN;
+        if (p.staged) {
+          if (p.act == SDB_ACT_GEGLU) {
+            epilogue16_staged<true>(p, lo, stg, bias_s, temb_row, r, tcol);
+            if (two) epilogue16_staged<true>(p, hi, stg, bias_s, temb_row, r, tcol + 16);
+          } else {
+            epilogue16_staged<false>(p, lo, stg, bias_s, temb_row, r, tcol);
+            if (two) epilogue16_staged<false>(p, hi, stg, bias_s, temb_row, r, tcol + 16);
           }
+        } else if (out_row >= 0 && ok) {
+          if (n0 + tcol < p.N) epilogue16_direct(p, lo, bias_s, temb_row, out_row, n0, tcol);
+          if (two && n0 + tcol + 16 < p.N) epilogue16_direct(p, hi, bias_s, temb_row, out_row, n0, tcol + 16);
+        }
+      };
+      // 32-column chunks, the TMEM load of chunk c+1 in flight while chunk c is processed
+      uint32_t va[32], vb[32];
+      tmem_ld_32x32(taddr, va);
+#pragma unroll 1
+      for (int c = 0; c < nchunk; c += 2) {
+        tmem_ld_wait();
+        if (c + 1 < nchunk) tmem_ld_32x32(taddr + (uint32_t)(c + 1) * 32u, vb);
+        process(va, c * 32);
+        if (c + 1 < nchunk) {
+          tmem_ld_wait();
+          if (c + 2 < nchunk) tmem_ld_32x32(taddr + (uint32_t)(c + 2) * 32u, va);
+          process(vb, (c + 1) * 32);
         }
       }
       tc_fence_before();
-      mbar_arrive(tempty_bar(acc));
+      mbar_arrive(tempty_bar(wg));
+      if (p.staged) fence_proxy_async();                   // generic-proxy smem writes -> async proxy
+      mbar_arrive(stg_full_bar(wg));
     }
-      }
   }
   tc_fence_before();
   __syncthreads();
@@ -552,7 +615,7 @@ static void pick_bk(int K, int K2, int* BK, int* swz) {
 }
 
 // Decides whether the epilogue can be staged through smem + TMA stores (bf16 output at the tile's own
-// resolution, bf16 or no residual, a tail slab the swizzle modes can express) and sizes the staging area.
+// resolution, bf16 or no residual, a tail slab the swizzle modes can express) and sizes one staging buffer.
 static void plan_staging(UmmaParams& p, bool bf16_out, bool res_ok, bool same_res) {
   static int off = -1;
   if (off < 0) { const char* e = getenv("SDB_GEMM_DIRECT"); off = e ? atoi(e) : 0; }
@@ -561,14 +624,39 @@ static void plan_staging(UmmaParams& p, bool bf16_out, bool res_ok, bool same_re
   p.tail_cols = p.bno % 64;
   p.staged = (!off && bf16_out && res_ok && same_res &&
               (p.tail_cols == 0 || p.tail_cols == 16 || p.tail_cols == 32)) ? 1 : 0;
-  p.staging_bytes = p.staged ? ((kTileM * p.bno * 2 + 1023) & ~1023) : 0;
+  p.stg_bytes = p.staged ? ((kTileM * p.bno * 2 + 1023) & ~1023) : 0;
 }
 
+// Splits the shared-memory budget between the resident weight tile (short-K GEMMs), the operand ring and
+// the staging buffers.  Needs mode, BK, BN, num_kb, tiles_m, tiles_n and plan_staging() done.
 static void finish_stages(UmmaParams& p) {
+  static int no_resb = -1;
+  if (no_resb < 0) { const char* e = getenv("SDB_GEMM_NO_RESB"); no_resb = e ? atoi(e) : 0; }
+  const int sms = sdb_num_sms();
   p.a_bytes = kTileM * p.BK * 2;
   p.b_bytes = p.BN * p.BK * 2;
-  p.stage_bytes = (p.a_bytes + p.b_bytes + 1023) & ~1023;
-  int s = (kSmemBudget - p.staging_bytes) / p.stage_bytes;
+  p.resB = 0;
+  p.bres_bytes = 0;
+  p.m_groups = 1;
+  if (p.mode == 0 && !no_resb && p.tiles_n <= sms) {
+    // weights stay resident when they leave room for two staging buffers and a >= 4-deep A ring, and
+    // every CTA gets enough m-tiles to amortise loading them
+    const int bres = p.num_kb * p.b_bytes;
+    const int groups = sms / p.tiles_n;
+    if (bres + 2 * p.stg_bytes + 4 * p.a_bytes <= kSmemBudget && p.tiles_m >= 2 * groups) {
+      p.resB = 1;
+      p.bres_bytes = bres;
+      p.m_groups = groups;
+    }
+  }
+  p.stage_bytes = p.resB ? p.a_bytes : ((p.a_bytes + p.b_bytes + 1023) & ~1023);
+  // one staging buffer per epilogue warpgroup when the tile is epilogue-heavy (few k-blocks) and the ring
+  // stays >= 4 deep; long main loops hide a shared buffer's hand-off
+  p.nbuf = 2;
+  if (p.staged && !p.resB &&
+      (p.num_kb > 12 || (kSmemBudget - 2 * p.stg_bytes) / p.stage_bytes < 4))
+    p.nbuf = 1;
+  int s = (kSmemBudget - p.bres_bytes - p.nbuf * p.stg_bytes) / p.stage_bytes;
   p.num_stages = s > kMaxStages ? kMaxStages : s;
 }
 
@@ -594,7 +682,7 @@ static int make_slab_maps(UmmaParams& p, const void* out, const void* res, int r
 
 static int launch_umma(const UmmaParams& p, cudaStream_t st) {
   static bool attr_set[64] = {false};
-  const int smem = kSmemBudget + 2048;
+  const int smem = kSmemBudget + kBiasBytes + 1024 /* alignment */ + 512 /* barriers */;
   int dev = 0;
   SDB_CUDA_OK(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64 || !attr_set[dev]) {
@@ -602,9 +690,13 @@ static int launch_umma(const UmmaParams& p, cudaStream_t st) {
                                      smem));
     if (dev >= 0 && dev < 64) attr_set[dev] = true;
   }
+  if (p.num_stages < 2) {
+    sdb_set_error("umma: tile %dx%d (BK %d) leaves no room for a 2-stage operand ring", kTileM, p.BN, p.BK);
+    return SDB_EUNSUPPORTED;
+  }
   const int total = p.tiles_m * p.tiles_n;
   const int sms = sdb_num_sms();
-  const int grid = total < sms ? total : sms;
+  const int grid = p.resB ? p.m_groups * p.tiles_n : (total < sms ? total : sms);
   umma_gemm_kernel<<<grid, kGemmThreads, smem, st>>>(p);
   SDB_LAUNCH_OK();
   return SDB_OK;
@@ -632,17 +724,21 @@ extern "C" int sdb_gemm(const SdbGemmArgs* a, void* stream) {
   memset(&p, 0, sizeof(p));
   p.mode = 0;
   pick_bk(a->K1, K2, &p.BK, &p.swz);
-  // short-K GEMMs are bound by the output stream, not the tensor pipe: 128-wide tiles keep the
-  // staging area small (deeper operand ring) at no cost
-  p.BN = pick_bn(a->N, (K <= 320 && a->N > 256) ? 128 : kMaxBN);
+  // short-K GEMMs are bound by the output stream, not the tensor pipe: tiles of <= 128 output columns keep
+  // two staging buffers and the resident weight tile inside shared memory
   p.act = a->act;
-  plan_staging(p, a->out_dtype == SDB_BF16, !a->residual || a->res_dtype == SDB_BF16, true);
-  finish_stages(p);
   p.kb1 = (a->K1 + p.BK - 1) / p.BK;
   p.K1 = a->K1;
   p.num_kb = p.kb1 + (K2 + p.BK - 1) / p.BK;
   p.tiles_m = (a->M + kTileM - 1) / kTileM;
-  p.tiles_n = (a->N + p.BN - 1) / p.BN;
+  for (int cap = (K <= 320 && a->act != SDB_ACT_GEGLU) ? 128 : kMaxBN;; cap = 128) {
+    p.BN = pick_bn(a->N, cap);
+    if (K <= 320 && a->N <= 192) p.BN = a->N;   // one n-tile: the whole weight matrix stays resident
+    plan_staging(p, a->out_dtype == SDB_BF16, !a->residual || a->res_dtype == SDB_BF16, true);
+    p.tiles_n = (a->N + p.BN - 1) / p.BN;
+    finish_stages(p);
+    if (p.resB || cap == 128 || K > 320) break;   // a narrower tile may make the weights fit
+  }
   p.M = a->M;
   p.N = a->N;
   p.bias = a->bias;
@@ -702,7 +798,6 @@ extern "C" int sdb_conv3x3(const SdbConvArgs* a, void* stream) {
   p.BN = pick_bn(a->Cout);
   p.act = SDB_ACT_NONE;
   plan_staging(p, a->out_dtype == SDB_BF16, !a->residual || a->res_dtype == SDB_BF16, !a->down2);
-  finish_stages(p);
   p.Cin = a->Cin;
   p.kb_per_tap = (a->Cin + p.BK - 1) / p.BK;
   p.num_kb = 9 * p.kb_per_tap;
@@ -723,6 +818,8 @@ extern "C" int sdb_conv3x3(const SdbConvArgs* a, void* stream) {
   const int tiles_b = (a->B + tn - 1) / tn;
   p.tiles_m = p.tiles_w * p.tiles_h * tiles_b;
   p.tiles_n = (a->Cout + p.BN - 1) / p.BN;
+  finish_stages(p);
+  p.temb_in_bias = (a->temb && tn == 1) ? 1 : 0;
   p.B = a->B; p.H = a->H; p.W = a->W;
   p.out_mode = a->down2 ? 1 : 0;
   for (int t = 0; t < 9; ++t) {

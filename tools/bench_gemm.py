@@ -15,8 +15,10 @@ B = 32
 dev = "cuda"
 tot = 0.0
 print(f"{'op':34s} {'ms':>8s} {'TFLOP/s':>8s} {'GB/s':>8s}  count  total_ms")
+ONLY = os.environ.get("ONLY")   # substring filter, e.g. ONLY=geglu for an ncu capture of one shape
 def conv(name, H, cin, cout, count, down=False, temb=False, res=False):
     global tot
+    if ONLY and ONLY not in name: return
     x = torch.randn(B, H, H, cin, device=dev).to(torch.bfloat16)
     w = (torch.randn(cout, 3, 3, cin, device=dev) * 0.02).to(torch.bfloat16)
     b = torch.zeros(cout, device=dev)
@@ -30,6 +32,7 @@ def conv(name, H, cin, cout, count, down=False, temb=False, res=False):
     tot += ms * count
 def gemm(name, M, K, N, count, act=0, res=False, bias=True):
     global tot
+    if ONLY and ONLY not in name: return
     a = torch.randn(M, K, device=dev).to(torch.bfloat16)
     w = (torch.randn(N, K, device=dev) * 0.05).to(torch.bfloat16)
     b = torch.zeros(N, device=dev) if bias else None
