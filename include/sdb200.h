@@ -38,7 +38,7 @@ extern "C" {
 
 #define SDB_ACT_NONE 0
 #define SDB_ACT_SILU 1  /* x*sigmoid(x) on the result                                          */
-#define SDB_ACT_GEGLU 2 /* weight rows interleaved (a0,g0,a1,g1,..): out[:, j] = a_j*gelu_erf(g_j) */
+#define SDB_ACT_GEGLU 2 /* weight rows interleaved in pairs (a0,a1,g0,g1,a2,a3,g2,g3,..): out[:, j] = a_j*gelu_erf(g_j) */
 
 int sdb_version(void);
 const char* sdb_last_error(void);

@@ -57,13 +57,16 @@ def conv3x3_w(p: Tensor) -> Tensor:
 
 
 def geglu_w(w: Tensor, b: Tensor) -> Tuple[Tensor, Tensor]:
-    """GEGLU proj [2*F, C] with halves (a | gate) -> rows interleaved (a0, g0, a1, g1, ...) so one
-    accumulator tile holds both operands of a_j * gelu(g_j)."""
+    """GEGLU proj [2*F, C] with halves (a | gate) -> rows interleaved in pairs (a0, a1, g0, g1, a2, a3, g2, g3,
+    ...) so one accumulator tile holds both operands of a_j * gelu(g_j) and the epilogue's packed fp32x2
+    arithmetic works on adjacent registers."""
     F2 = w.shape[0]
     half = F2 // 2
-    wi = torch.stack([w.detach()[:half], w.detach()[half:]], dim=1).reshape(F2, w.shape[1])
-    bi = torch.stack([b.detach()[:half], b.detach()[half:]], dim=1).reshape(F2)
-    return wi.to(torch.bfloat16).contiguous(), bi.to(torch.float32).contiguous()
+    assert half % 2 == 0
+    wd, bd = w.detach(), b.detach()
+    wi = torch.stack([wd[:half].reshape(half // 2, 2, -1), wd[half:].reshape(half // 2, 2, -1)], dim=1)
+    bi = torch.stack([bd[:half].reshape(half // 2, 2), bd[half:].reshape(half // 2, 2)], dim=1)
+    return wi.reshape(F2, w.shape[1]).to(torch.bfloat16).contiguous(), bi.reshape(F2).to(torch.float32).contiguous()
 
 
 HEAD_PAD = 32  # padded head width of the tcgen05 attention operands (sdb_attention_p32)

@@ -168,40 +168,49 @@ __device__ __forceinline__ uint4 pack_bf16x8(const float* v) {
                     pack_bf16x2(v[6], v[7]));
 }
 
+// Epilogue flavours the kernel is instantiated for: the common ones are straight-line code (two warps
+// per scheduler cannot hide fetch bubbles of a branchy epilogue), the generic one branches at run time.
+enum { kEpiPlain = 0, kEpiRes = 1, kEpiGeglu = 2, kEpiGeneric = 3 };
+
 // ---- 16 accumulator columns of one row -> staged tile ------------------------------------------
-// `tcol` = accumulator column inside the tile, `temb_row` = per-element temb (only when it could not be
-// folded into the staged bias row).  The residual is read from (and the result written back to) the
-// swizzled slab the TMA unit loaded / will store.
-template <bool kGeglu>
+// `tcol` = accumulator column inside the tile, `temb_row` = per-element temb (generic flavour only, when
+// it could not be folded into the staged bias row).  The residual is read from (and the result written
+// back to) the swizzled slab the TMA unit loaded / will store.
+template <int kEpi>
 __device__ __forceinline__ void epilogue16_staged(const UmmaParams& p, const uint32_t (&acc)[16], uint32_t stg,
                                                   uint32_t bias_s, const float* temb_row, int r, int tcol) {
   float v[16];
   add_bias16(v, acc, bias_s + 4u * tcol);
-  if (temb_row) {
-#pragma unroll
-    for (int j = 0; j < 16; j += 4) {
-      const float4 b = __ldg(reinterpret_cast<const float4*>(temb_row + tcol + j));
-      v[j] += b.x; v[j + 1] += b.y; v[j + 2] += b.z; v[j + 3] += b.w;
-    }
-  }
-  if (kGeglu) {
-    // interleaved columns (a_j, g_j): 16 accumulator columns -> 8 outputs
+  if (kEpi == kEpiGeglu) {
+    // pair-interleaved columns (a0, a1, g0, g1, ...): 16 accumulator columns -> 8 outputs, and every
+    // operand of the packed arithmetic is an adjacent register pair
     float o[8];
 #pragma unroll
-    for (int j = 0; j < 8; j += 2) geglu2(v[2 * j], v[2 * j + 2], v[2 * j + 1], v[2 * j + 3], o[j], o[j + 1]);
+    for (int k = 0; k < 4; ++k) geglu2(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3], o[2 * k], o[2 * k + 1]);
     sts128(stage_addr(p, stg, r, tcol >> 1), pack_bf16x8(o));
     return;
   }
-  if (p.act == SDB_ACT_SILU) {
+  if (kEpi == kEpiGeneric) {
+    if (temb_row) {
 #pragma unroll
-    for (int j = 0; j < 16; ++j) v[j] = silu_f(v[j]);
-  }
+      for (int j = 0; j < 16; j += 4) {
+        const float4 b = __ldg(reinterpret_cast<const float4*>(temb_row + tcol + j));
+        v[j] += b.x; v[j + 1] += b.y; v[j + 2] += b.z; v[j + 3] += b.w;
+      }
+    }
+    if (p.act == SDB_ACT_SILU) {
 #pragma unroll
-  for (int h = 0; h < 2; ++h) {
-    const uint32_t a = stage_addr(p, stg, r, tcol + 8 * h);
-    if (p.residual) add_bf16x8(v + 8 * h, lds128(a));
-    sts128(a, pack_bf16x8(v + 8 * h));
+      for (int j = 0; j < 16; ++j) v[j] = silu_f(v[j]);
+    }
   }
+  const uint32_t a = stage_addr(p, stg, r, tcol);   // 16 columns never straddle a slab: chunks c, c ^ 1
+  const uint32_t a1 = a ^ 16u;
+  if (kEpi == kEpiRes || (kEpi == kEpiGeneric && p.residual)) {
+    add_bf16x8(v, lds128(a));
+    add_bf16x8(v + 8, lds128(a1));
+  }
+  sts128(a, pack_bf16x8(v));
+  sts128(a1, pack_bf16x8(v + 8));
 }
 
 // ---- 16 accumulator columns of one row -> global memory (fp32 output / fp32 residual / strided rows) ----
@@ -220,7 +229,7 @@ __device__ __forceinline__ void epilogue16_direct(const UmmaParams& p, const uin
   if (p.act == SDB_ACT_GEGLU) {
     float o[8];
 #pragma unroll
-    for (int j = 0; j < 8; j += 2) geglu2(v[2 * j], v[2 * j + 2], v[2 * j + 1], v[2 * j + 3], o[j], o[j + 1]);
+    for (int k = 0; k < 4; ++k) geglu2(v[4 * k], v[4 * k + 1], v[4 * k + 2], v[4 * k + 3], o[2 * k], o[2 * k + 1]);
     const long long off = out_row * p.ldo + (col >> 1);
     if (p.out_dtype == SDB_BF16) {
       *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(p.out) + off) = pack_bf16x8(o);
@@ -276,6 +285,7 @@ __device__ __forceinline__ bool cta_tile(const UmmaParams& p, int j, int& m_tile
   return t < p.tiles_m * p.tiles_n;
 }
 
+template <int kEpi>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -512,7 +522,7 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
     const int wg = (warp - 4) >> 2;
     const int q = warp & 3;            // TMEM lane quarter this warp may access
     const int r = q * 32 + lane;
-    const int nchunk = (p.BN + 31) >> 5;
+    const int nchunk = p.BN >> 4;
     bool ok = true;
     int m_tile, n_tile;
     for (int j = wg; cta_tile(p, j, m_tile, n_tile); j += 2) {
@@ -536,43 +546,33 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
         }
         if (img >= p.B) img = p.B - 1;   // clipped rows: any valid temb row will do
       }
-      const float* temb_row =
-          (p.temb && !p.temb_in_bias) ? p.temb + (long long)img * p.ld_temb + n0 : nullptr;
+      const float* temb_row = (kEpi == kEpiGeneric && p.temb && !p.temb_in_bias)
+                                  ? p.temb + (long long)img * p.ld_temb + n0 : nullptr;
       const uint32_t stg = stg_base + (uint32_t)buf * (uint32_t)p.stg_bytes;
       const uint32_t bias_s = bias_base + (uint32_t)buf * (kMaxBN * 4);
       if (ok) ok = mbar_wait(res_full_bar(wg), acc_phase);
       if (ok) ok = mbar_wait(tfull_bar(wg), acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)wg * kMaxBN;
-      auto process = [&](const uint32_t (&v)[32], int tcol) {
-        const uint32_t(&lo)[16] = *reinterpret_cast<const uint32_t(*)[16]>(&v[0]);
-        const uint32_t(&hi)[16] = *reinterpret_cast<const uint32_t(*)[16]>(&v[16]);
-        const bool two = tcol + 16 < p.BN;
-        if (p.staged) {
-          if (p.act == SDB_ACT_GEGLU) {
-            epilogue16_staged<true>(p, lo, stg, bias_s, temb_row, r, tcol);
-            if (two) epilogue16_staged<true>(p, hi, stg, bias_s, temb_row, r, tcol + 16);
-          } else {
-            epilogue16_staged<false>(p, lo, stg, bias_s, temb_row, r, tcol);
-            if (two) epilogue16_staged<false>(p, hi, stg, bias_s, temb_row, r, tcol + 16);
-          }
-        } else if (out_row >= 0 && ok) {
-          if (n0 + tcol < p.N) epilogue16_direct(p, lo, bias_s, temb_row, out_row, n0, tcol);
-          if (two && n0 + tcol + 16 < p.N) epilogue16_direct(p, hi, bias_s, temb_row, out_row, n0, tcol + 16);
+      auto process = [&](const uint32_t (&v)[16], int tcol) {
+        if (kEpi != kEpiGeneric || p.staged) {
+          epilogue16_staged<kEpi>(p, v, stg, bias_s, temb_row, r, tcol);
+        } else if (out_row >= 0 && ok && n0 + tcol < p.N) {
+          epilogue16_direct(p, v, bias_s, temb_row, out_row, n0, tcol);
         }
       };
-      // 32-column chunks, the TMEM load of chunk c+1 in flight while chunk c is processed
-      uint32_t va[32], vb[32];
-      tmem_ld_32x32(taddr, va);
+      // 16-column chunks, the TMEM load of chunk c+1 in flight while chunk c is processed
+      uint32_t va[16], vb[16];
+      tmem_ld_32x16(taddr, va);
 #pragma unroll 1
       for (int c = 0; c < nchunk; c += 2) {
         tmem_ld_wait();
-        if (c + 1 < nchunk) tmem_ld_32x32(taddr + (uint32_t)(c + 1) * 32u, vb);
-        process(va, c * 32);
+        if (c + 1 < nchunk) tmem_ld_32x16(taddr + (uint32_t)(c + 1) * 16u, vb);
+        process(va, c * 16);
         if (c + 1 < nchunk) {
           tmem_ld_wait();
-          if (c + 2 < nchunk) tmem_ld_32x32(taddr + (uint32_t)(c + 2) * 32u, va);
-          process(vb, (c + 1) * 32);
+          if (c + 2 < nchunk) tmem_ld_32x16(taddr + (uint32_t)(c + 2) * 16u, va);
+          process(vb, (c + 1) * 16);
         }
       }
       tc_fence_before();
@@ -680,16 +680,22 @@ static int make_slab_maps(UmmaParams& p, const void* out, const void* res, int r
   return rc;
 }
 
-static int launch_umma(const UmmaParams& p, cudaStream_t st) {
+template <int kEpi>
+static int launch_umma_epi(const UmmaParams& p, int grid, int smem, cudaStream_t st) {
   static bool attr_set[64] = {false};
-  const int smem = kSmemBudget + kBiasBytes + 1024 /* alignment */ + 512 /* barriers */;
   int dev = 0;
   SDB_CUDA_OK(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-    SDB_CUDA_OK(cudaFuncSetAttribute(umma_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     smem));
+    SDB_CUDA_OK(cudaFuncSetAttribute(umma_gemm_kernel<kEpi>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     if (dev >= 0 && dev < 64) attr_set[dev] = true;
   }
+  umma_gemm_kernel<kEpi><<<grid, kGemmThreads, smem, st>>>(p);
+  SDB_LAUNCH_OK();
+  return SDB_OK;
+}
+
+static int launch_umma(const UmmaParams& p, cudaStream_t st) {
+  const int smem = kSmemBudget + kBiasBytes + 1024 /* alignment */ + 512 /* barriers */;
   if (p.num_stages < 2) {
     sdb_set_error("umma: tile %dx%d (BK %d) leaves no room for a 2-stage operand ring", kTileM, p.BN, p.BK);
     return SDB_EUNSUPPORTED;
@@ -697,9 +703,11 @@ static int launch_umma(const UmmaParams& p, cudaStream_t st) {
   const int total = p.tiles_m * p.tiles_n;
   const int sms = sdb_num_sms();
   const int grid = p.resB ? p.m_groups * p.tiles_n : (total < sms ? total : sms);
-  umma_gemm_kernel<<<grid, kGemmThreads, smem, st>>>(p);
-  SDB_LAUNCH_OK();
-  return SDB_OK;
+  const bool slow_temb = p.temb && !p.temb_in_bias;
+  if (p.staged && p.act == SDB_ACT_GEGLU) return launch_umma_epi<kEpiGeglu>(p, grid, smem, st);
+  if (p.staged && p.act == SDB_ACT_NONE && !slow_temb)
+    return p.residual ? launch_umma_epi<kEpiRes>(p, grid, smem, st) : launch_umma_epi<kEpiPlain>(p, grid, smem, st);
+  return launch_umma_epi<kEpiGeneric>(p, grid, smem, st);
 }
 
 }  // namespace sdb
