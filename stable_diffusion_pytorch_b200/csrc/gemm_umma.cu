@@ -40,6 +40,7 @@ struct UmmaParams {
   // resident-B scheduling (GEMM with a short K): each CTA keeps one n-tile of the weights in smem for
   // its whole life and streams only A; CTA c owns n-tile c % tiles_n and m-tiles c / tiles_n + j * m_groups
   int resB, bres_bytes, m_groups;
+  int walk_dm, walk_dn;   // TileWalk increments (host-computed from the grid size)
   // conv geometry (GEMM-M space = input-resolution pixels)
   int kb_per_tap, Cin;
   int TW, TH, TN, tiles_w, tiles_h;
@@ -272,18 +273,25 @@ __device__ __forceinline__ void epilogue16_direct(const UmmaParams& p, const uin
   }
 }
 
-// j-th tile of this CTA (see UmmaParams::resB); false once the CTA has run out of tiles
-__device__ __forceinline__ bool cta_tile(const UmmaParams& p, int j, int& m_tile, int& n_tile) {
-  if (p.resB) {
-    n_tile = (int)blockIdx.x % p.tiles_n;
-    m_tile = (int)blockIdx.x / p.tiles_n + j * p.m_groups;
-    return m_tile < p.tiles_m;
+// The tiles of this CTA, in order, without per-tile divisions.  Resident-B: fixed n-tile, m-tiles m_groups
+// apart; otherwise tile t = blockIdx.x + j * gridDim.x of the row-major (m, n) enumeration.
+struct TileWalk {
+  int m, n, dm, dn, tiles_m, tiles_n;
+  __device__ __forceinline__ explicit TileWalk(const UmmaParams& p) {
+    tiles_m = p.tiles_m;
+    tiles_n = p.tiles_n;
+    n = (int)blockIdx.x % tiles_n;
+    m = (int)blockIdx.x / tiles_n;
+    dm = p.walk_dm;
+    dn = p.walk_dn;
   }
-  const int t = (int)blockIdx.x + j * (int)gridDim.x;
-  n_tile = t % p.tiles_n;
-  m_tile = t / p.tiles_n;
-  return t < p.tiles_m * p.tiles_n;
-}
+  __device__ __forceinline__ bool valid() const { return m < tiles_m; }
+  __device__ __forceinline__ void next() {
+    m += dm;
+    n += dn;
+    if (n >= tiles_n) { n -= tiles_n; ++m; }
+  }
+};
 
 template <int kEpi>
 __global__ void __launch_bounds__(kGemmThreads, 1)
@@ -341,20 +349,21 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
     int stage = 0;
     uint32_t phase = 0;
     bool ok = true;
-    int m_tile, n_tile;
-    if (p.resB && cta_tile(p, 0, m_tile, n_tile)) {
+    TileWalk tw(p);
+    if (p.resB && tw.valid()) {
       if (elect_one()) {
         mbar_arrive_expect_tx(bfull_bar, (uint32_t)p.bres_bytes);
         for (int kb = 0; kb < p.num_kb; ++kb) {
           const int kc = kb < p.kb1 ? kb * p.BK : p.K1 + (kb - p.kb1) * p.BK;
-          tma_load_2d(smem_base + (uint32_t)kb * p.b_bytes, &p.tmB, bfull_bar, kc, n_tile * p.BN);
+          tma_load_2d(smem_base + (uint32_t)kb * p.b_bytes, &p.tmB, bfull_bar, kc, tw.n * p.BN);
         }
       }
       __syncwarp();
     }
     const uint32_t tx = (uint32_t)(p.resB ? p.a_bytes : p.a_bytes + p.b_bytes);
-    for (int j = 0; cta_tile(p, j, m_tile, n_tile) && ok; ++j) {
-      const int n0 = n_tile * p.BN;
+    for (; tw.valid() && ok; tw.next()) {
+      const int m_tile = tw.m;
+      const int n0 = tw.n * p.BN;
       int w0 = 0, h0 = 0, i0 = 0;
       if (p.mode == 1) {
         w0 = (m_tile % p.tiles_w) * p.TW;
@@ -390,38 +399,49 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
+    // Descriptors are kept as (constant high word | 14-bit address field) and advanced by adds: the loop
+    // body is a barrier wait, four MMAs and a commit.
     const uint32_t idesc = umma_idesc_bf16(kTileM, (uint32_t)p.BN);
-    const int k_sub = p.BK / 16;
+    const uint64_t desc_hi = umma_smem_desc(0u, (uint32_t)p.swz);
+    const uint32_t a_step = (uint32_t)p.stage_bytes >> 4;
+    const uint32_t a_lo0 = (ring_base & 0x3ffffu) >> 4;
+    const uint32_t b_step = p.resB ? ((uint32_t)p.b_bytes >> 4) : 0u;
+    const uint32_t b_lo0 = p.resB ? ((smem_base & 0x3ffffu) >> 4) : a_lo0 + ((uint32_t)p.a_bytes >> 4);
+    const bool bk64 = p.BK == 64;
     int stage = 0;
     uint32_t phase = 0;
+    uint32_t a_lo = a_lo0;
     bool ok = true;
-    int m_tile, n_tile;
-    if (p.resB && cta_tile(p, 0, m_tile, n_tile)) ok = mbar_wait(bfull_bar, 0);
-    for (int j = 0; cta_tile(p, j, m_tile, n_tile) && ok; ++j) {
+    TileWalk tw(p);
+    if (p.resB && tw.valid()) ok = mbar_wait(bfull_bar, 0);
+    for (int j = 0; tw.valid() && ok; tw.next(), ++j) {
       const int acc = j & 1;
       const uint32_t acc_phase = (uint32_t)(j >> 1) & 1u;
       ok = mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
       if (!ok) break;
       tc_fence_after();
       const uint32_t tmem_d = tmem_base + (uint32_t)acc * kMaxBN;
+      uint32_t b_lo = b_lo0;
       for (int kb = 0; kb < p.num_kb; ++kb) {
         ok = mbar_wait(full_bar(stage), phase);
         if (!ok) break;
         tc_fence_after();
-        const uint32_t sa = ring_base + (uint32_t)stage * p.stage_bytes;
-        const uint32_t sb = p.resB ? smem_base + (uint32_t)kb * p.b_bytes : sa + p.a_bytes;
-        const uint64_t adesc = umma_smem_desc(sa, (uint32_t)p.swz);
-        const uint64_t bdesc = umma_smem_desc(sb, (uint32_t)p.swz);
+        const uint64_t adesc = desc_hi | (uint64_t)a_lo;
+        const uint64_t bdesc = desc_hi | (uint64_t)(p.resB ? b_lo : a_lo + ((uint32_t)p.a_bytes >> 4));
         if (elect_one()) {
-          for (int k = 0; k < k_sub; ++k) {
-            // advance 16 bf16 = 32 B along K inside the swizzle atom: +2 in the (addr >> 4) field
-            umma_f16(tmem_d, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc,
-                     (kb | k) != 0 ? 1u : 0u);
+          // advance 16 bf16 = 32 B along K inside the swizzle atom: +2 in the (addr >> 4) field
+          umma_f16(tmem_d, adesc, bdesc, idesc, kb != 0 ? 1u : 0u);
+          umma_f16(tmem_d, adesc + 2, bdesc + 2, idesc, 1u);
+          if (bk64) {
+            umma_f16(tmem_d, adesc + 4, bdesc + 4, idesc, 1u);
+            umma_f16(tmem_d, adesc + 6, bdesc + 6, idesc, 1u);
           }
           umma_commit(empty_bar(stage));
         }
         __syncwarp();
-        if (++stage == p.num_stages) { stage = 0; phase ^= 1u; }
+        b_lo += b_step;
+        a_lo += a_step;
+        if (++stage == p.num_stages) { stage = 0; phase ^= 1u; a_lo = a_lo0; }
       }
       if (elect_one()) umma_commit(tfull_bar(acc));
       __syncwarp();
@@ -474,12 +494,14 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
       __syncwarp();
     };
     bool ok = true;
-    int m_tile, n_tile, m2, n2;
-    if (cta_tile(p, 0, m_tile, n_tile)) prep(0, m_tile, n_tile);
-    for (int j = 0; cta_tile(p, j, m_tile, n_tile); ++j) {
+    TileWalk tw(p), nx(p);
+    if (tw.valid()) prep(0, tw.m, tw.n);
+    nx.next();
+    for (int j = 0; tw.valid(); tw.next(), nx.next(), ++j) {
+      const int m_tile = tw.m, n_tile = tw.n, m2 = nx.m, n2 = nx.n;
       const int buf = p.nbuf == 2 ? (j & 1) : 0;
       const uint32_t use_phase = (uint32_t)(j >> 1) & 1u;   // barriers are per warpgroup even when the buffer is shared
-      const bool more = cta_tile(p, j + 1, m2, n2);
+      const bool more = nx.valid();
       if (p.nbuf == 2 && more) {
         if (p.staged) {
           if (elect_one()) tma_store_wait_read();   // tile j-1's store has drained the other buffer
@@ -524,8 +546,10 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
     const int r = q * 32 + lane;
     const int nchunk = p.BN >> 4;
     bool ok = true;
-    int m_tile, n_tile;
-    for (int j = wg; cta_tile(p, j, m_tile, n_tile); j += 2) {
+    TileWalk tw(p);
+    if (wg) tw.next();
+    for (int j = wg; tw.valid(); tw.next(), tw.next(), j += 2) {
+      const int m_tile = tw.m, n_tile = tw.n;
       const int n0 = n_tile * p.BN;
       const int buf = p.nbuf == 2 ? wg : 0;
       const uint32_t acc_phase = (uint32_t)(j >> 1) & 1u;
@@ -694,7 +718,7 @@ static int launch_umma_epi(const UmmaParams& p, int grid, int smem, cudaStream_t
   return SDB_OK;
 }
 
-static int launch_umma(const UmmaParams& p, cudaStream_t st) {
+static int launch_umma(UmmaParams& p, cudaStream_t st) {
   const int smem = kSmemBudget + kBiasBytes + 1024 /* alignment */ + 512 /* barriers */;
   if (p.num_stages < 2) {
     sdb_set_error("umma: tile %dx%d (BK %d) leaves no room for a 2-stage operand ring", kTileM, p.BN, p.BK);
@@ -703,6 +727,8 @@ static int launch_umma(const UmmaParams& p, cudaStream_t st) {
   const int total = p.tiles_m * p.tiles_n;
   const int sms = sdb_num_sms();
   const int grid = p.resB ? p.m_groups * p.tiles_n : (total < sms ? total : sms);
+  p.walk_dm = p.resB ? p.m_groups : grid / p.tiles_n;
+  p.walk_dn = p.resB ? 0 : grid % p.tiles_n;
   const bool slow_temb = p.temb && !p.temb_in_bias;
   if (p.staged && p.act == SDB_ACT_GEGLU) return launch_umma_epi<kEpiGeglu>(p, grid, smem, st);
   if (p.staged && p.act == SDB_ACT_NONE && !slow_temb)
