@@ -24,7 +24,8 @@ constexpr int kMaxBN = 256;
 constexpr int kGemmThreads = 384;
 constexpr int kMaxStages = 12;
 constexpr int kSmemBudget = 222 * 1024;  // resident B + operand ring + epilogue staging
-constexpr int kBiasBytes = 2 * kMaxBN * 4;
+constexpr int kMaxBuf = 3;
+constexpr int kBiasBytes = kMaxBuf * kMaxBN * 4;
 
 struct UmmaParams {
   CUtensorMap tmA[2];
@@ -62,7 +63,8 @@ struct UmmaParams {
   int act;
   // staged epilogue (bf16 output through swizzled smem slabs + TMA store): 0 = direct stores
   int staged;
-  int nbuf;         // staging buffers (2 = one per epilogue warpgroup, 1 = shared)
+  int nbuf;         // staging buffers, tile j uses buffer j % nbuf (3 = a store never delays the next tile,
+                    // 2 = one per epilogue warpgroup, 1 = shared)
   int bno;          // output columns per tile (BN, or BN/2 for GEGLU)
   int nslab;        // full 64-column slabs per tile
   int tail_cols;    // columns of the last, narrower slab (0, 16 or 32)
@@ -80,21 +82,20 @@ __device__ __forceinline__ void fmul2(float& d0, float& d1, float a0, float a1, 
 }
 
 // a * gelu(g) for two (a, g) pairs, exact-erf GELU (transformer.py:177 uses nn.GELU()).
-//   erf(|g|/sqrt2) = 1 - 2^(-|g| P(|g|)),  P = degree-7 fit of -log2(erfc(u/sqrt2))/u on [0, 6]
-// (|error| <= 1.6e-6 in erf, i.e. <= 5e-6 in the GELU value -- three orders below the bf16 rounding
-// of the result).  One MUFU (ex2) per element and packed FMAs: the GEGLU epilogue is issue-bound.
+//   erfc(u/sqrt2) = 2^(-u P(u)),  u = min(|g|, 6),  P = degree-5 fit of -log2(erfc(u/sqrt2))/u on [0, 6]
+// Absolute error of Phi(g) <= 3e-6 and -- because the error sits in the exponent -- relative error of the
+// negative-side tail <= 1.5e-4, an order below the bf16 rounding of the result.  One MUFU (ex2) per element;
+// the polynomial runs in nu = -u (odd coefficients negated) so no negation is needed.
 __device__ __forceinline__ void geglu2(float a0, float a1, float g0, float g1, float& o0, float& o1) {
-  const float u0 = fminf(fabsf(g0), 6.0f), u1 = fminf(fabsf(g1), 6.0f);
+  const float n0 = fmaxf(-fabsf(g0), -6.0f), n1 = fmaxf(-fabsf(g1), -6.0f);
   float p0, p1;
-  ffma2(p0, p1, u0, u1, 2.566215187016496e-07f, 2.566215187016496e-07f, -4.049981271236902e-06f,
-        -4.049981271236902e-06f);
-  ffma2(p0, p1, p0, p1, u0, u1, -7.237450518005062e-06f, -7.237450518005062e-06f);
-  ffma2(p0, p1, p0, p1, u0, u1, 0.000671996793244034f, 0.000671996793244034f);
-  ffma2(p0, p1, p0, p1, u0, u1, -0.007837459444999695f, -0.007837459444999695f);
-  ffma2(p0, p1, p0, p1, u0, u1, 0.05303756147623062f, 0.05303756147623062f);
-  ffma2(p0, p1, p0, p1, u0, u1, 0.4590655267238617f, 0.4590655267238617f);
-  ffma2(p0, p1, p0, p1, u0, u1, 1.1511108875274658f, 1.1511108875274658f);
-  fmul2(p0, p1, p0, p1, -u0, -u1);
+  ffma2(p0, p1, n0, n1, 2.7593860068009235e-05f, 2.7593860068009235e-05f, 0.0006911802338436246f,
+        0.0006911802338436246f);
+  ffma2(p0, p1, p0, p1, n0, n1, 0.00771324010565877f, 0.00771324010565877f);
+  ffma2(p0, p1, p0, p1, n0, n1, 0.05270770937204361f, 0.05270770937204361f);
+  ffma2(p0, p1, p0, p1, n0, n1, -0.4592883586883545f, -0.4592883586883545f);
+  ffma2(p0, p1, p0, p1, n0, n1, 1.1510891914367676f, 1.1510891914367676f);
+  fmul2(p0, p1, p0, p1, n0, n1);
   const float e0 = ex2_mufu(p0), e1 = ex2_mufu(p1);
   // 0.5 g (1 + erf(g/sqrt2)) = h + h * copysign(1 - e, g),  h = g / 2
   const float s0 = copysignf(1.0f - e0, g0), s1 = copysignf(1.0f - e1, g1);
@@ -114,6 +115,8 @@ __device__ __forceinline__ void tma_store_4d(const void* tmap, uint32_t src, int
 }
 __device__ __forceinline__ void tma_store_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
 __device__ __forceinline__ void tma_store_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+// all but the most recent committed store have finished reading shared memory
+__device__ __forceinline__ void tma_store_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;" ::: "memory"); }
 __device__ __forceinline__ uint4 lds128(uint32_t a) {
   uint4 v;
   asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
@@ -273,6 +276,20 @@ __device__ __forceinline__ void epilogue16_direct(const UmmaParams& p, const uin
   }
 }
 
+// Optional pipeline trace (tools/trace_gemm.py builds a private copy of the library with -DSDB_GEMM_TRACE):
+// clock64 stamps of CTA 0's roles for its first 16 tiles.
+#ifdef SDB_GEMM_TRACE
+__device__ long long g_gemm_trace[5 * 16 * 8];
+__device__ long long g_gemm_cta_ns[160 * 4];   // per CTA: globaltimer at start / end, clock64 at start / end
+#define GEMM_TRACE(role, j, ev)                                                                   \
+  do {                                                                                            \
+    if (blockIdx.x == 0 && (j) < 16 && (threadIdx.x & 31) == 0 && ((role) < 3 || (threadIdx.x & 127) == 0)) \
+      g_gemm_trace[(((role) * 16 + (j)) * 8) + (ev)] = clock64();                                 \
+  } while (0)
+#else
+#define GEMM_TRACE(role, j, ev) do { } while (0)
+#endif
+
 // The tiles of this CTA, in order, without per-tile divisions.  Resident-B: fixed n-tile, m-tiles m_groups
 // apart; otherwise tile t = blockIdx.x + j * gridDim.x of the row-major (m, n) enumeration.
 struct TileWalk {
@@ -316,6 +333,12 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
+#ifdef SDB_GEMM_TRACE
+  if (threadIdx.x == 0 && blockIdx.x < 160) {
+    g_gemm_cta_ns[blockIdx.x * 4] = (long long)globaltimer_ns();
+    g_gemm_cta_ns[blockIdx.x * 4 + 2] = clock64();
+  }
+#endif
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&p.tmA[0]);
@@ -361,7 +384,8 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
       __syncwarp();
     }
     const uint32_t tx = (uint32_t)(p.resB ? p.a_bytes : p.a_bytes + p.b_bytes);
-    for (; tw.valid() && ok; tw.next()) {
+    for (int j = 0; tw.valid() && ok; tw.next(), ++j) {
+      GEMM_TRACE(0, j, 0);
       const int m_tile = tw.m;
       const int n0 = tw.n * p.BN;
       int w0 = 0, h0 = 0, i0 = 0;
@@ -396,6 +420,7 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
         __syncwarp();
         if (++stage == p.num_stages) { stage = 0; phase ^= 1u; }
       }
+      GEMM_TRACE(0, j, 1);
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
@@ -417,8 +442,10 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
     for (int j = 0; tw.valid() && ok; tw.next(), ++j) {
       const int acc = j & 1;
       const uint32_t acc_phase = (uint32_t)(j >> 1) & 1u;
+      GEMM_TRACE(1, j, 0);
       ok = mbar_wait(tempty_bar(acc), acc_phase ^ 1u);
       if (!ok) break;
+      GEMM_TRACE(1, j, 1);
       tc_fence_after();
       const uint32_t tmem_d = tmem_base + (uint32_t)acc * kMaxBN;
       uint32_t b_lo = b_lo0;
@@ -445,6 +472,7 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
       }
       if (elect_one()) umma_commit(tfull_bar(acc));
       __syncwarp();
+      GEMM_TRACE(1, j, 2);
     }
   } else if (warp == 2) {
     // ===================== epilogue DMA =====================
@@ -460,24 +488,38 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
         i0 = (m_tile / (p.tiles_w * p.tiles_h)) * p.TN;
       }
     };
-    auto prep = [&](int j, int m_tile, int n_tile) {   // buffer j % nbuf is free
-      const int buf = p.nbuf == 2 ? (j & 1) : 0;
-      const uint32_t bias_s = bias_base + (uint32_t)buf * (kMaxBN * 4);
-      int o0, w0, h0, i0;
-      tile_coords(m_tile, n_tile, o0, w0, h0, i0);
+    // bias (+temb) row of a tile: 8 values per lane, fetched early so the latency overlaps the store drain
+    auto load_bias = [&](int m_tile, int n_tile, float (&bv)[8]) {
       const int n0 = n_tile * p.BN;
-      const int img = i0 < p.B ? i0 : 0;
-      for (int i = lane; i < p.BN; i += 32) {
-        float b = 0.f;
-        if (n0 + i < p.N) {
-          if (p.bias) b = __ldg(p.bias + n0 + i);
-          if (p.temb_in_bias) b += __ldg(p.temb + (long long)img * p.ld_temb + n0 + i);
-        }
-        sts32f(bias_s + 4u * i, b);
+      int img = 0;
+      if (p.temb_in_bias) {
+        img = (m_tile / (p.tiles_w * p.tiles_h)) * p.TN;
+        if (img >= p.B) img = 0;
       }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int c = lane + 32 * i;
+        float b = 0.f;
+        if (c < p.BN && n0 + c < p.N) {
+          if (p.bias) b = __ldg(p.bias + n0 + c);
+          if (p.temb_in_bias) b += __ldg(p.temb + (long long)img * p.ld_temb + n0 + c);
+        }
+        bv[i] = b;
+      }
+    };
+    auto store_bias = [&](int buf, const float (&bv)[8]) {
+      const uint32_t bias_s = bias_base + (uint32_t)buf * (kMaxBN * 4);
+#pragma unroll
+      for (int i = 0; i < 8; ++i)
+        if (lane + 32 * i < p.BN) sts32f(bias_s + 4u * (lane + 32 * i), bv[i]);
+    };
+    // hand buffer `buf` to the warpgroup of tile j: residual tile on its way (or nothing to wait for)
+    auto release = [&](int j, int buf, int m_tile, int n_tile) {
       __syncwarp();
       if (elect_one()) {
         if (p.staged && p.residual) {
+          int o0, w0, h0, i0;
+          tile_coords(m_tile, n_tile, o0, w0, h0, i0);
           mbar_arrive_expect_tx(res_full_bar(j & 1), 128u * (uint32_t)p.bno * 2u);
           const uint32_t stg = stg_base + (uint32_t)buf * (uint32_t)p.stg_bytes;
           for (int sl = 0; sl <= p.nslab; ++sl) {
@@ -495,21 +537,35 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
     };
     bool ok = true;
     TileWalk tw(p), nx(p);
-    if (tw.valid()) prep(0, tw.m, tw.n);
+    const bool bias_static = p.resB != 0;   // fixed n-tile: the bias rows are written once
+    float bv[8];
+    if (tw.valid()) {
+      load_bias(tw.m, tw.n, bv);
+      for (int b = 0; b < (bias_static ? p.nbuf : 1); ++b) store_bias(b, bv);
+      release(0, 0, tw.m, tw.n);
+    }
     nx.next();
+    int buf = 0, nbuf_next = p.nbuf > 1 ? 1 : 0;
     for (int j = 0; tw.valid(); tw.next(), nx.next(), ++j) {
       const int m_tile = tw.m, n_tile = tw.n, m2 = nx.m, n2 = nx.n;
-      const int buf = p.nbuf == 2 ? (j & 1) : 0;
-      const uint32_t use_phase = (uint32_t)(j >> 1) & 1u;   // barriers are per warpgroup even when the buffer is shared
+      const uint32_t use_phase = (uint32_t)(j >> 1) & 1u;   // barriers are per warpgroup, whatever the buffer
       const bool more = nx.valid();
-      if (p.nbuf == 2 && more) {
+      GEMM_TRACE(2, j, 0);
+      if (more && !bias_static) load_bias(m2, n2, bv);
+      if (p.nbuf >= 2 && more) {
+        // buffer (j+1) % nbuf was last used by tile j+1-nbuf: its store must have been read out
         if (p.staged) {
-          if (elect_one()) tma_store_wait_read();   // tile j-1's store has drained the other buffer
+          if (elect_one()) {
+            if (p.nbuf == 2) tma_store_wait_read(); else tma_store_wait_read1();
+          }
           __syncwarp();
         }
-        prep(j + 1, m2, n2);
+        if (!bias_static) store_bias(nbuf_next, bv);
+        release(j + 1, nbuf_next, m2, n2);
       }
+      GEMM_TRACE(2, j, 1);
       if (ok) ok = mbar_wait(stg_full_bar(j & 1), use_phase);
+      GEMM_TRACE(2, j, 2);
       if (p.staged) {
         if (elect_one() && ok) {
           int o0, w0, h0, i0;
@@ -526,13 +582,17 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
         }
         __syncwarp();
       }
+      GEMM_TRACE(2, j, 3);
       if (p.nbuf == 1 && more) {
         if (p.staged) {
           if (elect_one()) tma_store_wait_read();
           __syncwarp();
         }
-        prep(j + 1, m2, n2);
+        if (!bias_static) store_bias(0, bv);
+        release(j + 1, 0, m2, n2);
       }
+      buf = nbuf_next;
+      if (++nbuf_next >= p.nbuf) nbuf_next = 0;
     }
     if (p.staged) {
       if (elect_one()) tma_store_wait_read();            // smem must outlive the last store's reads
@@ -544,14 +604,14 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
     const int wg = (warp - 4) >> 2;
     const int q = warp & 3;            // TMEM lane quarter this warp may access
     const int r = q * 32 + lane;
-    const int nchunk = p.BN >> 4;
+    const int nchunk = (p.BN + 31) >> 5;
     bool ok = true;
     TileWalk tw(p);
     if (wg) tw.next();
+    int buf = wg < p.nbuf ? wg : 0;                       // j % nbuf
     for (int j = wg; tw.valid(); tw.next(), tw.next(), j += 2) {
       const int m_tile = tw.m, n_tile = tw.n;
       const int n0 = n_tile * p.BN;
-      const int buf = p.nbuf == 2 ? wg : 0;
       const uint32_t acc_phase = (uint32_t)(j >> 1) & 1u;
       long long out_row = -1;
       int img = 0;
@@ -574,39 +634,62 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
                                   ? p.temb + (long long)img * p.ld_temb + n0 : nullptr;
       const uint32_t stg = stg_base + (uint32_t)buf * (uint32_t)p.stg_bytes;
       const uint32_t bias_s = bias_base + (uint32_t)buf * (kMaxBN * 4);
+      GEMM_TRACE(3 + wg, j >> 1, 0);
       if (ok) ok = mbar_wait(res_full_bar(wg), acc_phase);
+      GEMM_TRACE(3 + wg, j >> 1, 1);
       if (ok) ok = mbar_wait(tfull_bar(wg), acc_phase);
+      GEMM_TRACE(3 + wg, j >> 1, 2);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)wg * kMaxBN;
-      auto process = [&](const uint32_t (&v)[16], int tcol) {
+      auto process16 = [&](const uint32_t (&v)[16], int tcol) {
         if (kEpi != kEpiGeneric || p.staged) {
           epilogue16_staged<kEpi>(p, v, stg, bias_s, temb_row, r, tcol);
         } else if (out_row >= 0 && ok && n0 + tcol < p.N) {
           epilogue16_direct(p, v, bias_s, temb_row, out_row, n0, tcol);
         }
       };
-      // 16-column chunks, the TMEM load of chunk c+1 in flight while chunk c is processed
-      uint32_t va[16], vb[16];
-      tmem_ld_32x16(taddr, va);
+      // both 16-column halves in one basic block: their dependency chains interleave
+      auto process = [&](const uint32_t (&v)[32], int tcol) {
+        const uint32_t(&lo)[16] = *reinterpret_cast<const uint32_t(*)[16]>(&v[0]);
+        const uint32_t(&hi)[16] = *reinterpret_cast<const uint32_t(*)[16]>(&v[16]);
+        if (tcol + 16 < p.BN) {
+          process16(lo, tcol);
+          process16(hi, tcol + 16);
+        } else {
+          process16(lo, tcol);
+        }
+      };
+      // 32-column chunks, the TMEM load of chunk c+1 in flight while chunk c is processed
+      uint32_t va[32], vb[32];
+      tmem_ld_32x32(taddr, va);
 #pragma unroll 1
       for (int c = 0; c < nchunk; c += 2) {
         tmem_ld_wait();
-        if (c + 1 < nchunk) tmem_ld_32x16(taddr + (uint32_t)(c + 1) * 16u, vb);
-        process(va, c * 16);
+        if (c + 1 < nchunk) tmem_ld_32x32(taddr + (uint32_t)(c + 1) * 32u, vb);
+        process(va, c * 32);
         if (c + 1 < nchunk) {
           tmem_ld_wait();
-          if (c + 2 < nchunk) tmem_ld_32x16(taddr + (uint32_t)(c + 2) * 16u, va);
-          process(vb, (c + 1) * 16);
+          if (c + 2 < nchunk) tmem_ld_32x32(taddr + (uint32_t)(c + 2) * 32u, va);
+          process(vb, (c + 1) * 32);
         }
       }
       tc_fence_before();
       mbar_arrive(tempty_bar(wg));
       if (p.staged) fence_proxy_async();                   // generic-proxy smem writes -> async proxy
       mbar_arrive(stg_full_bar(wg));
+      GEMM_TRACE(3 + wg, j >> 1, 3);
+      buf += 2;
+      while (buf >= p.nbuf) buf -= p.nbuf;
     }
   }
   tc_fence_before();
   __syncthreads();
+#ifdef SDB_GEMM_TRACE
+  if (threadIdx.x == 0 && blockIdx.x < 160) {
+    g_gemm_cta_ns[blockIdx.x * 4 + 1] = (long long)globaltimer_ns();
+    g_gemm_cta_ns[blockIdx.x * 4 + 3] = clock64();
+  }
+#endif
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, 512);
@@ -662,21 +745,30 @@ static void finish_stages(UmmaParams& p) {
   p.resB = 0;
   p.bres_bytes = 0;
   p.m_groups = 1;
+  static int force_nbuf = -1;
+  if (force_nbuf < 0) { const char* e = getenv("SDB_GEMM_NBUF"); force_nbuf = e ? atoi(e) : 0; }
+  p.nbuf = 2;
   if (p.mode == 0 && !no_resb && p.tiles_n <= sms) {
-    // weights stay resident when they leave room for two staging buffers and a >= 4-deep A ring, and
-    // every CTA gets enough m-tiles to amortise loading them
+    // weights stay resident when they leave room for the staging buffers and a >= 3-deep A ring, and
+    // every CTA gets enough m-tiles to amortise loading them.  Three staging buffers (the store of tile j
+    // then never delays the same warpgroup's tile j+2) only if the A ring stays >= 6 deep: measured, ring
+    // depth matters more than the third buffer.
     const int bres = p.num_kb * p.b_bytes;
     const int groups = sms / p.tiles_n;
-    if (bres + 2 * p.stg_bytes + 4 * p.a_bytes <= kSmemBudget && p.tiles_m >= 2 * groups) {
-      p.resB = 1;
-      p.bres_bytes = bres;
-      p.m_groups = groups;
+    for (int nb = (p.staged ? 3 : 2); nb >= 2 && p.tiles_m >= 2 * groups; --nb) {
+      if (force_nbuf && nb != force_nbuf && force_nbuf >= 2) continue;
+      if (bres + nb * p.stg_bytes + (nb == 3 ? 6 : 3) * p.a_bytes <= kSmemBudget) {
+        p.resB = 1;
+        p.bres_bytes = bres;
+        p.m_groups = groups;
+        p.nbuf = nb;
+        break;
+      }
     }
   }
   p.stage_bytes = p.resB ? p.a_bytes : ((p.a_bytes + p.b_bytes + 1023) & ~1023);
-  // one staging buffer per epilogue warpgroup when the tile is epilogue-heavy (few k-blocks) and the ring
-  // stays >= 4 deep; long main loops hide a shared buffer's hand-off
-  p.nbuf = 2;
+  // without resident weights: one staging buffer per epilogue warpgroup when the tile is epilogue-heavy
+  // (few k-blocks) and the ring stays >= 4 deep; long main loops hide a shared buffer's hand-off
   if (p.staged && !p.resB &&
       (p.num_kb > 12 || (kSmemBudget - 2 * p.stg_bytes) / p.stage_bytes < 4))
     p.nbuf = 1;
@@ -738,6 +830,17 @@ static int launch_umma(UmmaParams& p, cudaStream_t st) {
 
 }  // namespace sdb
 
+#ifdef SDB_GEMM_TRACE
+extern "C" int sdb_debug_gemm_trace(long long* host_dst) {
+  if (cudaDeviceSynchronize() != cudaSuccess) return -1;
+  return cudaMemcpyFromSymbol(host_dst, sdb::g_gemm_trace, sizeof(long long) * 5 * 16 * 8) == cudaSuccess ? 0 : -1;
+}
+extern "C" int sdb_debug_gemm_cta_ns(long long* host_dst) {
+  if (cudaDeviceSynchronize() != cudaSuccess) return -1;
+  return cudaMemcpyFromSymbol(host_dst, sdb::g_gemm_cta_ns, sizeof(long long) * 160 * 4) == cudaSuccess ? 0 : -1;
+}
+#endif
+
 extern "C" int sdb_gemm(const SdbGemmArgs* a, void* stream) {
   using namespace sdb;
   SDB_CHECK_ARG(a && a->a && a->w && a->out, "gemm: null pointer");
@@ -765,13 +868,17 @@ extern "C" int sdb_gemm(const SdbGemmArgs* a, void* stream) {
   p.K1 = a->K1;
   p.num_kb = p.kb1 + (K2 + p.BK - 1) / p.BK;
   p.tiles_m = (a->M + kTileM - 1) / kTileM;
-  for (int cap = (K <= 320 && a->act != SDB_ACT_GEGLU) ? 128 : kMaxBN;; cap = 128) {
+  static int bncap = -1;   // experiments: SDB_GEMM_BNCAP=<n> caps the tile width
+  if (bncap < 0) { const char* e = getenv("SDB_GEMM_BNCAP"); bncap = e ? atoi(e) : 0; }
+  int cap0 = (K <= 320 && a->act != SDB_ACT_GEGLU) ? 128 : kMaxBN;
+  if (bncap && bncap < cap0) cap0 = bncap;
+  for (int cap = cap0;; cap = 128) {
     p.BN = pick_bn(a->N, cap);
-    if (K <= 320 && a->N <= 192) p.BN = a->N;   // one n-tile: the whole weight matrix stays resident
+    if (K <= 320 && a->N <= 192 && !(bncap && bncap < a->N)) p.BN = a->N;   // one n-tile: the whole weight matrix stays resident
     plan_staging(p, a->out_dtype == SDB_BF16, !a->residual || a->res_dtype == SDB_BF16, true);
     p.tiles_n = (a->N + p.BN - 1) / p.BN;
     finish_stages(p);
-    if (p.resB || cap == 128 || K > 320) break;   // a narrower tile may make the weights fit
+    if (p.resB || cap <= 128 || K > 320) break;   // a narrower tile may make the weights fit
   }
   p.M = a->M;
   p.N = a->N;
