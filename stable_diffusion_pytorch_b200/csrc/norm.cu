@@ -54,7 +54,24 @@ gn_partial_kernel(const T* __restrict__ x1, int C1, const T* __restrict__ x2, in
     long long pitch;
     if (c < C1) { base = x1 + (long long)b * hw * C1 + c; pitch = C1; }
     else { base = x2 + (long long)b * hw * C2 + (c - C1); pitch = C2; }
-    for (long long px = p0 + r; px < p1; px += R) {
+    // four independent 16-byte loads in flight per thread: the kernel is a pure HBM stream
+    long long px = p0 + r;
+    for (; px + 3LL * R < p1; px += 4LL * R) {
+      float v0[8], v1[8], v2[8], v3[8];
+      Vec8<T>::load(base + px * pitch, v0);
+      Vec8<T>::load(base + (px + R) * pitch, v1);
+      Vec8<T>::load(base + (px + 2LL * R) * pitch, v2);
+      Vec8<T>::load(base + (px + 3LL * R) * pitch, v3);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        s[j] += (v0[j] + v1[j]) + (v2[j] + v3[j]);
+        ss[j] = fmaf(v0[j], v0[j], ss[j]);
+        ss[j] = fmaf(v1[j], v1[j], ss[j]);
+        ss[j] = fmaf(v2[j], v2[j], ss[j]);
+        ss[j] = fmaf(v3[j], v3[j], ss[j]);
+      }
+    }
+    for (; px < p1; px += R) {
       float v[8];
       Vec8<T>::load(base + px * pitch, v);
 #pragma unroll
@@ -109,86 +126,120 @@ gn_finalize_kernel(const float* __restrict__ scratch, int chunks, int C, int gro
 }
 
 // ---- normalise (+SiLU), writing a dense NHWC tensor with C1+C2 channels -----------------------
+// grid (pixel chunks, B); thread (r, vec) owns one 8-channel vector of the virtual concat -- its scale and
+// shift live in registers -- and walks the chunk's pixels with four 16-byte loads in flight.
 template <typename T, typename OutT>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(kGnThreads)
 gn_apply_kernel(const T* __restrict__ x1, int C1, const T* __restrict__ x2, int C2,
                 const float* __restrict__ stats, const float* __restrict__ gamma,
                 const float* __restrict__ beta, int act, OutT* __restrict__ out, long long hw,
-                int groups) {
-  extern __shared__ float sm[];  // scale[C], shift[C]
+                int groups, int chunk_px) {
   const int C = C1 + C2, V = C >> 3, cpg = C / groups;
+  const int R = kGnThreads / V;
   const int b = blockIdx.y;
-  for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    const int g = c / cpg;
+  const int vec = threadIdx.x % V, r = threadIdx.x / V;
+  if (r >= R) return;
+  const int c = vec * 8;
+  float sc[8], sh[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    const int g = (c + j) / cpg;
     const float mean = stats[((long long)b * groups + g) * 2];
     const float rstd = stats[((long long)b * groups + g) * 2 + 1];
-    const float sc = rstd * gamma[c];
-    sm[c] = sc;
-    sm[C + c] = beta[c] - mean * sc;
+    sc[j] = rstd * gamma[c + j];
+    sh[j] = beta[c + j] - mean * sc[j];
   }
-  __syncthreads();
-  const long long total = hw * V;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
-       i += (long long)gridDim.x * blockDim.x) {
-    const long long px = i / V;
-    const int c = (int)(i - px * V) * 8;
-    float v[8];
-    if (c < C1) Vec8<T>::load(x1 + ((long long)b * hw + px) * C1 + c, v);
-    else Vec8<T>::load(x2 + ((long long)b * hw + px) * C2 + (c - C1), v);
+  const T* base;
+  long long pitch;
+  if (c < C1) { base = x1 + (long long)b * hw * C1 + c; pitch = C1; }
+  else { base = x2 + (long long)b * hw * C2 + (c - C1); pitch = C2; }
+  OutT* obase = out + (long long)b * hw * C + c;
+  const long long p0 = (long long)blockIdx.x * chunk_px;
+  const long long p1 = p0 + chunk_px < hw ? p0 + chunk_px : hw;
+  auto finish = [&](float (&v)[8], long long px) {
 #pragma unroll
     for (int j = 0; j < 8; ++j) {
-      float y = fmaf(v[j], sm[c + j], sm[C + c + j]);
+      const float y = fmaf(v[j], sc[j], sh[j]);
       v[j] = act == SDB_ACT_SILU ? silu_f(y) : y;
     }
-    Vec8<OutT>::store(out + ((long long)b * hw + px) * C + c, v);
+    Vec8<OutT>::store(obase + px * C, v);
+  };
+  long long px = p0 + r;
+  for (; px + 3LL * R < p1; px += 4LL * R) {
+    float v0[8], v1[8], v2[8], v3[8];
+    Vec8<T>::load(base + px * pitch, v0);
+    Vec8<T>::load(base + (px + R) * pitch, v1);
+    Vec8<T>::load(base + (px + 2LL * R) * pitch, v2);
+    Vec8<T>::load(base + (px + 3LL * R) * pitch, v3);
+    finish(v0, px);
+    finish(v1, px + R);
+    finish(v2, px + 2LL * R);
+    finish(v3, px + 3LL * R);
+  }
+  for (; px < p1; px += R) {
+    float v[8];
+    Vec8<T>::load(base + px * pitch, v);
+    finish(v, px);
   }
 }
 
-// ---- K5: out = LayerNorm(x (+ res)) over C, one warp per row, two-pass in registers ------------
-template <typename T>
+// ---- K5: out = LayerNorm(x (+ res)) over C, two-pass in registers ------------------------------
+// kL lanes share a row (32 / kL rows per warp), each holding kVPL 8-channel vectors: every lane has
+// kVPL (x2 with a residual) independent 16-byte loads in flight and the reductions are log2(kL) shuffles.
+template <typename T, int kL, int kVPL>
 __global__ void __launch_bounds__(256)
 add_layernorm_kernel(const T* __restrict__ x, const T* __restrict__ res,
                      const float* __restrict__ gamma, const float* __restrict__ beta,
                      T* __restrict__ out, long long rows, int C, float eps) {
+  constexpr int kRowsPerWarp = 32 / kL;
   const int lane = threadIdx.x & 31;
-  const long long row = (long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-  if (row >= rows) return;
+  const int sub = lane % kL;
+  const long long row = ((long long)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5)) * kRowsPerWarp + lane / kL;
+  const bool live = row < rows;
   const int V = C >> 3;
-  float v[4][8];
+  float v[kVPL][8];
   float s = 0.f;
 #pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    const int vi = lane + 32 * k;
-    if (vi < V) {
-      Vec8<T>::load(x + row * C + vi * 8, v[k]);
-      if (res) {
+  for (int k = 0; k < kVPL; ++k) {
+    const int vi = sub + kL * k;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) v[k][j] = 0.f;
+    if (live && vi < V) Vec8<T>::load(x + row * C + vi * 8, v[k]);
+  }
+  if (res) {
+#pragma unroll
+    for (int k = 0; k < kVPL; ++k) {
+      const int vi = sub + kL * k;
+      if (live && vi < V) {
         float r[8];
         Vec8<T>::load(res + row * C + vi * 8, r);
 #pragma unroll
         for (int j = 0; j < 8; ++j) v[k][j] += r[j];
       }
-#pragma unroll
-      for (int j = 0; j < 8; ++j) s += v[k][j];
     }
   }
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+  for (int k = 0; k < kVPL; ++k)
+#pragma unroll
+    for (int j = 0; j < 8; ++j) s += v[k][j];
+#pragma unroll
+  for (int o = kL >> 1; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
   const float mean = s / (float)C;
   float ss = 0.f;
 #pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    if (lane + 32 * k < V) {
+  for (int k = 0; k < kVPL; ++k) {
+    if (sub + kL * k < V) {
 #pragma unroll
       for (int j = 0; j < 8; ++j) { const float d = v[k][j] - mean; ss = fmaf(d, d, ss); }
     }
   }
 #pragma unroll
-  for (int o = 16; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+  for (int o = kL >> 1; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
   const float rstd = rsqrtf(ss / (float)C + eps);
 #pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    const int vi = lane + 32 * k;
-    if (vi < V) {
+  for (int k = 0; k < kVPL; ++k) {
+    const int vi = sub + kL * k;
+    if (live && vi < V) {
       float g[8], bt[8], o[8];
       Vec8<float>::load(gamma + vi * 8, g);
       Vec8<float>::load(beta + vi * 8, bt);
@@ -276,7 +327,7 @@ static inline int ew_grid(long long n, int threads) {
 using namespace sdb;
 
 extern "C" int sdb_groupnorm_chunks(int64_t hw) {
-  int64_t c = (hw + 255) / 256;
+  int64_t c = (hw + 63) / 64;
   if (c < 1) c = 1;
   if (c > kGnMaxChunks) c = kGnMaxChunks;
   return (int)c;
@@ -317,15 +368,21 @@ extern "C" int sdb_groupnorm_apply(const void* x1, int C1, const void* x2, int C
   const int C = C1 + C2;
   SDB_CHECK_ARG(x1 && stats && gamma && beta && out && B > 0 && hw > 0, "groupnorm_apply: bad args");
   SDB_CHECK_ARG(C1 % 8 == 0 && C2 % 8 == 0 && groups > 0 && C % groups == 0, "groupnorm_apply: bad channels");
-  const size_t smem = (size_t)2 * C * sizeof(float);
-  long long total = hw * (C / 8);
-  long long want = (total + 255) / 256;
-  long long cap = ((long long)sdb_num_sms() * 8 + B - 1) / B;
-  dim3 grid((unsigned)(want < cap ? want : (cap > 0 ? cap : 1)), B);
+  const int V = C / 8;
+  SDB_CHECK_ARG(V <= kGnThreads, "groupnorm_apply: C (%d) too large", C);
+  // pixel chunks: enough blocks to fill the machine a few times over, >= 4 * R pixels each
+  const int R = kGnThreads / V;
+  long long chunks = ((long long)sdb_num_sms() * 8 + B - 1) / B;
+  const long long max_chunks = (hw + 4LL * R - 1) / (4LL * R);
+  if (chunks > max_chunks) chunks = max_chunks;
+  if (chunks < 1) chunks = 1;
+  const int chunk_px = (int)((hw + chunks - 1) / chunks);
+  chunks = (hw + chunk_px - 1) / chunk_px;
+  dim3 grid((unsigned)chunks, B);
   cudaStream_t st = sdb_stream(stream);
 #define SDB_GN_APPLY(T, O)                                                                       \
-  gn_apply_kernel<T, O><<<grid, 256, smem, st>>>((const T*)x1, C1, (const T*)x2, C2, stats, gamma, \
-                                                 beta, act, (O*)out, hw, groups)
+  gn_apply_kernel<T, O><<<grid, kGnThreads, 0, st>>>((const T*)x1, C1, (const T*)x2, C2, stats, gamma, \
+                                                     beta, act, (O*)out, hw, groups, chunk_px)
   if (dtype == SDB_BF16 && out_dtype == SDB_BF16) SDB_GN_APPLY(__nv_bfloat16, __nv_bfloat16);
   else if (dtype == SDB_BF16) SDB_GN_APPLY(__nv_bfloat16, float);
   else if (out_dtype == SDB_BF16) SDB_GN_APPLY(float, __nv_bfloat16);
@@ -339,14 +396,27 @@ extern "C" int sdb_add_layernorm(const void* x, const void* res, const float* ga
                                  void* out, int64_t rows, int C, float eps, int dtype, void* stream) {
   SDB_CHECK_ARG(x && gamma && beta && out && rows > 0, "add_layernorm: bad args");
   SDB_CHECK_ARG(C % 8 == 0 && C <= 1024, "add_layernorm: C (%d) must be a multiple of 8, <= 1024", C);
-  const int wpb = 8;
-  const unsigned grid = (unsigned)((rows + wpb - 1) / wpb);
-  if (dtype == SDB_BF16)
-    add_layernorm_kernel<__nv_bfloat16><<<grid, wpb * 32, 0, sdb_stream(stream)>>>(
-        (const __nv_bfloat16*)x, (const __nv_bfloat16*)res, gamma, beta, (__nv_bfloat16*)out, rows, C, eps);
-  else
-    add_layernorm_kernel<float><<<grid, wpb * 32, 0, sdb_stream(stream)>>>(
-        (const float*)x, (const float*)res, gamma, beta, (float*)out, rows, C, eps);
+  // lanes per row: the smallest power of two >= 4 that keeps <= 5 vectors per lane
+  const int V = C / 8;
+  int L = 4;
+  while (L < 32 && (V + L - 1) / L > 5) L *= 2;
+  const int vpl = (V + L - 1) / L;
+  const long long rows_per_block = 8LL * (32 / L);
+  const unsigned grid = (unsigned)((rows + rows_per_block - 1) / rows_per_block);
+  cudaStream_t st = sdb_stream(stream);
+#define SDB_LN(T, LL, VP)                                                                          \
+  add_layernorm_kernel<T, LL, VP><<<grid, 256, 0, st>>>((const T*)x, (const T*)res, gamma, beta, (T*)out, rows, C, eps)
+#define SDB_LN_T(T)                                                                                \
+  do {                                                                                             \
+    if (L == 4) { if (vpl <= 2) SDB_LN(T, 4, 2); else if (vpl <= 4) SDB_LN(T, 4, 4); else SDB_LN(T, 4, 5); }       \
+    else if (L == 8) { if (vpl <= 3) SDB_LN(T, 8, 3); else SDB_LN(T, 8, 5); }                      \
+    else if (L == 16) { if (vpl <= 3) SDB_LN(T, 16, 3); else SDB_LN(T, 16, 5); }                   \
+    else { if (vpl <= 3) SDB_LN(T, 32, 3); else SDB_LN(T, 32, 4); }                                \
+  } while (0)
+  if (dtype == SDB_BF16) SDB_LN_T(__nv_bfloat16);
+  else SDB_LN_T(float);
+#undef SDB_LN_T
+#undef SDB_LN
   SDB_LAUNCH_OK();
   return SDB_OK;
 }
