@@ -1,0 +1,198 @@
+// K4 (short context): cross-attention over a context of <= 128 tokens (CLIP: 77), head-padded operands
+// (same layout as sdb_attention_p32).  softmax(Q K^T * scale) V for one (batch, head) per CTA:
+//   * K and V of the head are staged once into shared memory (2 x m x 64 B) and re-used by every query,
+//   * each warp owns 16 query rows per iteration: Q fragments straight from global memory (prefetched one
+//     iteration ahead), S = Q K^T with mma.sync m16n8k16, a single-pass softmax in registers (the whole
+//     context is one tile -- no online rescale), O = P V, 8-byte stores.
+// The work is ~80 flop per (query, key) pair and the context is tiny: the kernel is bound by streaming Q
+// in and O out, so it runs many small CTAs per SM instead of the tcgen05 pipeline of attention_umma.cu
+// (whose per-CTA set-up cost dominated at m = 77: 174 us per layer vs the ~20 us the bytes need).
+#include "common.cuh"
+
+namespace sdb {
+
+constexpr int kCtxThreads = 256;
+constexpr int kCtxPitch = 40;   // bf16 elements per staged K/V row (32 + 8: ldmatrix rows hit distinct banks)
+
+template <int KG>   // key groups of 16
+__global__ void __launch_bounds__(kCtxThreads)
+attention_ctx_kernel(const __nv_bfloat16* __restrict__ q, long long ldq, const __nv_bfloat16* __restrict__ k,
+                     long long ldk, const __nv_bfloat16* __restrict__ v, long long ldv,
+                     __nv_bfloat16* __restrict__ out, long long ldo, int n, int m, int d, float scale_log2e,
+                     int q_per_cta) {
+  __shared__ __align__(16) __nv_bfloat16 sK[KG * 16 * kCtxPitch];
+  __shared__ __align__(16) __nv_bfloat16 sV[KG * 16 * kCtxPitch];
+  const int b = blockIdx.z, h = blockIdx.y;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const __nv_bfloat16* qg = q + (long long)b * n * ldq + h * 32;
+  const __nv_bfloat16* kg = k + (long long)b * m * ldk + h * 32;
+  const __nv_bfloat16* vg = v + (long long)b * m * ldv + h * 32;
+
+  // ---- stage K, V: 4 x 16-byte chunks per row, rows >= m zero ------------------------------------
+  for (int i = threadIdx.x; i < KG * 16 * 4; i += kCtxThreads) {
+    const int row = i >> 2, ch = i & 3;
+    uint4 kk = make_uint4(0u, 0u, 0u, 0u), vv = kk;
+    if (row < m) {
+      kk = __ldg(reinterpret_cast<const uint4*>(kg + (long long)row * ldk + ch * 8));
+      vv = __ldg(reinterpret_cast<const uint4*>(vg + (long long)row * ldv + ch * 8));
+    }
+    *reinterpret_cast<uint4*>(sK + row * kCtxPitch + ch * 8) = kk;
+    *reinterpret_cast<uint4*>(sV + row * kCtxPitch + ch * 8) = vv;
+  }
+  __syncthreads();
+
+  const int q_begin = blockIdx.x * q_per_cta;
+  const int q_end = q_begin + q_per_cta < n ? q_begin + q_per_cta : n;
+  const int g = lane >> 2, c2 = (lane & 3) * 2;
+
+  // A fragments of 16 query rows x 32 columns (two k-steps), zero beyond n
+  auto load_q = [&](int q0, uint32_t (&qf)[2][4]) {
+    const int r0 = q0 + g, r1 = r0 + 8;
+    const __nv_bfloat16* p0 = qg + (long long)r0 * ldq + c2;
+    const __nv_bfloat16* p1 = qg + (long long)r1 * ldq + c2;
+#pragma unroll
+    for (int ks = 0; ks < 2; ++ks) {
+      qf[ks][0] = r0 < q_end ? __ldg(reinterpret_cast<const uint32_t*>(p0 + ks * 16)) : 0u;
+      qf[ks][1] = r1 < q_end ? __ldg(reinterpret_cast<const uint32_t*>(p1 + ks * 16)) : 0u;
+      qf[ks][2] = r0 < q_end ? __ldg(reinterpret_cast<const uint32_t*>(p0 + ks * 16 + 8)) : 0u;
+      qf[ks][3] = r1 < q_end ? __ldg(reinterpret_cast<const uint32_t*>(p1 + ks * 16 + 8)) : 0u;
+    }
+  };
+
+  uint32_t qf[2][4], qn[2][4];
+  int q0 = q_begin + warp * 16;
+  if (q0 < q_end) load_q(q0, qf);
+  for (; q0 < q_end; q0 += (kCtxThreads / 32) * 16) {
+    const int qnext = q0 + (kCtxThreads / 32) * 16;
+    if (qnext < q_end) load_q(qnext, qn);
+    // ---- S = Q K^T : 16 x (KG*16) ---------------------------------------------------------------
+    float s[KG * 2][4];
+#pragma unroll
+    for (int t = 0; t < KG * 2; ++t) { s[t][0] = s[t][1] = s[t][2] = s[t][3] = 0.f; }
+#pragma unroll
+    for (int np = 0; np < KG; ++np) {
+#pragma unroll
+      for (int ks = 0; ks < 2; ++ks) {
+        const int key = np * 16 + (lane & 7) + ((lane >> 4) & 1) * 8;
+        const int col = ks * 16 + ((lane >> 3) & 1) * 8;
+        uint32_t b0, b1, b2, b3;
+        ldsm_x4(smem_u32(sK + key * kCtxPitch + col), b0, b1, b2, b3);
+        mma_bf16(s[2 * np], qf[ks][0], qf[ks][1], qf[ks][2], qf[ks][3], b0, b1);
+        mma_bf16(s[2 * np + 1], qf[ks][0], qf[ks][1], qf[ks][2], qf[ks][3], b2, b3);
+      }
+    }
+    // ---- mask the key tail, softmax over the whole context ---------------------------------------
+    if ((m & 15) != 0 || m < KG * 16) {
+#pragma unroll
+      for (int t = 0; t < KG * 2; ++t) {
+        const int key = t * 8 + c2;
+        if (key >= m) { s[t][0] = -INFINITY; s[t][2] = -INFINITY; }
+        if (key + 1 >= m) { s[t][1] = -INFINITY; s[t][3] = -INFINITY; }
+      }
+    }
+    float mx[2] = {-INFINITY, -INFINITY};
+#pragma unroll
+    for (int t = 0; t < KG * 2; ++t) {
+      mx[0] = fmaxf(mx[0], fmaxf(s[t][0], s[t][1]));
+      mx[1] = fmaxf(mx[1], fmaxf(s[t][2], s[t][3]));
+    }
+#pragma unroll
+    for (int r = 0; r < 2; ++r) {
+      mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 1));
+      mx[r] = fmaxf(mx[r], __shfl_xor_sync(0xffffffffu, mx[r], 2));
+    }
+    const float msc0 = mx[0] * scale_log2e, msc1 = mx[1] * scale_log2e;
+    float sum0 = 0.f, sum1 = 0.f;
+    uint32_t pf[KG][4];
+#pragma unroll
+    for (int t = 0; t < KG * 2; ++t) {
+      const float p0 = fast_exp2(fmaf(s[t][0], scale_log2e, -msc0));
+      const float p1 = fast_exp2(fmaf(s[t][1], scale_log2e, -msc0));
+      const float p2 = fast_exp2(fmaf(s[t][2], scale_log2e, -msc1));
+      const float p3 = fast_exp2(fmaf(s[t][3], scale_log2e, -msc1));
+      sum0 += p0 + p1;
+      sum1 += p2 + p3;
+      // C fragments of two adjacent key tiles form one A fragment of P for the P.V k-step
+      pf[t >> 1][(t & 1) * 2] = pack_bf16x2(p0, p1);
+      pf[t >> 1][(t & 1) * 2 + 1] = pack_bf16x2(p2, p3);
+    }
+    // ---- O = P V : 16 x 32 -------------------------------------------------------------------------
+    float o[4][4];
+#pragma unroll
+    for (int t = 0; t < 4; ++t) { o[t][0] = o[t][1] = o[t][2] = o[t][3] = 0.f; }
+#pragma unroll
+    for (int kk = 0; kk < KG; ++kk) {
+#pragma unroll
+      for (int dp = 0; dp < 2; ++dp) {
+        const int key = kk * 16 + (lane & 7) + ((lane >> 3) & 1) * 8;
+        const int col = dp * 16 + (lane >> 4) * 8;
+        uint32_t b0, b1, b2, b3;
+        ldsm_x4_t(smem_u32(sV + key * kCtxPitch + col), b0, b1, b2, b3);
+        mma_bf16(o[2 * dp], pf[kk][0], pf[kk][1], pf[kk][2], pf[kk][3], b0, b1);
+        mma_bf16(o[2 * dp + 1], pf[kk][0], pf[kk][1], pf[kk][2], pf[kk][3], b2, b3);
+      }
+    }
+    // ---- normalise and store (lane pairs trade halves: 8-byte stores) ---------------------------------
+    sum0 += __shfl_xor_sync(0xffffffffu, sum0, 1);
+    sum0 += __shfl_xor_sync(0xffffffffu, sum0, 2);
+    sum1 += __shfl_xor_sync(0xffffffffu, sum1, 1);
+    sum1 += __shfl_xor_sync(0xffffffffu, sum1, 2);
+    const float inv0 = 1.0f / sum0, inv1 = 1.0f / sum1;
+    const int r0 = q0 + g, r1 = r0 + 8;
+    __nv_bfloat16* og = out + (long long)b * n * ldo + h * d;
+    const bool odd = lane & 1;
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      const uint32_t v0 = pack_bf16x2(o[t][0] * inv0, o[t][1] * inv0);   // row r0, cols c, c+1
+      const uint32_t v1 = pack_bf16x2(o[t][2] * inv1, o[t][3] * inv1);   // row r1
+      const uint32_t got = __shfl_xor_sync(0xffffffffu, odd ? v0 : v1, 1);
+      const int col = t * 8 + (c2 & ~3);                                 // 4-column group of the lane pair
+      const int row = odd ? r1 : r0;
+      if (col < d && row < q_end) {
+        const uint2 w = odd ? make_uint2(got, v1) : make_uint2(v0, got);
+        *reinterpret_cast<uint2*>(og + (long long)row * ldo + col) = w;
+      }
+    }
+    if (qnext < q_end) {
+#pragma unroll
+      for (int ks = 0; ks < 2; ++ks)
+#pragma unroll
+        for (int i = 0; i < 4; ++i) qf[ks][i] = qn[ks][i];
+    }
+  }
+}
+
+template <int KG>
+static int launch_attention_ctx(const void* q, long long ldq, const void* k, long long ldk, const void* v,
+                                long long ldv, void* out, long long ldo, int B, int heads, int n, int m, int d,
+                                float scale, cudaStream_t st) {
+  // ~8 CTAs' worth of queries per (batch, head) row of the grid keeps K/V re-staging small and the
+  // grid several waves deep
+  int q_per_cta = 512;
+  while (q_per_cta > 128 && (long long)((n + q_per_cta - 1) / q_per_cta) * heads * B < 4LL * sdb_num_sms())
+    q_per_cta >>= 1;
+  dim3 grid((n + q_per_cta - 1) / q_per_cta, heads, B);
+  attention_ctx_kernel<KG><<<grid, kCtxThreads, 0, st>>>(
+      (const __nv_bfloat16*)q, ldq, (const __nv_bfloat16*)k, ldk, (const __nv_bfloat16*)v, ldv,
+      (__nv_bfloat16*)out, ldo, n, m, d, scale * 1.4426950408889634f, q_per_cta);
+  SDB_LAUNCH_OK();
+  return SDB_OK;
+}
+
+// m <= 128; same operand contract as sdb_attention_p32 (the ones column of V is ignored)
+static int attention_ctx_dispatch(const void* q, long long ldq, const void* k, long long ldk, const void* v,
+                                  long long ldv, void* out, long long ldo, int B, int heads, int n, int m, int d,
+                                  float scale, cudaStream_t st) {
+  switch ((m + 15) / 16) {
+    case 1: return launch_attention_ctx<1>(q, ldq, k, ldk, v, ldv, out, ldo, B, heads, n, m, d, scale, st);
+    case 2: return launch_attention_ctx<2>(q, ldq, k, ldk, v, ldv, out, ldo, B, heads, n, m, d, scale, st);
+    case 3: return launch_attention_ctx<3>(q, ldq, k, ldk, v, ldv, out, ldo, B, heads, n, m, d, scale, st);
+    case 4: return launch_attention_ctx<4>(q, ldq, k, ldk, v, ldv, out, ldo, B, heads, n, m, d, scale, st);
+    case 5: return launch_attention_ctx<5>(q, ldq, k, ldk, v, ldv, out, ldo, B, heads, n, m, d, scale, st);
+    case 6: return launch_attention_ctx<6>(q, ldq, k, ldk, v, ldv, out, ldo, B, heads, n, m, d, scale, st);
+    case 7: return launch_attention_ctx<7>(q, ldq, k, ldk, v, ldv, out, ldo, B, heads, n, m, d, scale, st);
+    default: return launch_attention_ctx<8>(q, ldq, k, ldk, v, ldv, out, ldo, B, heads, n, m, d, scale, st);
+  }
+}
+
+}  // namespace sdb

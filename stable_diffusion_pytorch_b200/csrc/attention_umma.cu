@@ -409,6 +409,12 @@ extern "C" int sdb_attention_p32(const void* q, int64_t ldq, const void* k, int6
                     ((uintptr_t)out & 7) == 0,
                 "attention_p32: q/k/v must be 16-byte aligned, out 8-byte aligned");
   SDB_CHECK_ARG(heads <= 65535 && B <= 65535, "attention_p32: grid too large");
+  // a context of <= 128 tokens (cross-attention over CLIP's 77) is one key tile: the streaming mma.sync
+  // kernel beats this pipeline's per-CTA set-up by an order of magnitude there
+  static int no_ctx = -1;
+  if (no_ctx < 0) { const char* e = getenv("SDB_FA_NO_CTX"); no_ctx = e ? atoi(e) : 0; }
+  if (m <= 128 && !no_ctx)
+    return attention_ctx_dispatch(q, ldq, k, ldk, v, ldv, out, ldo, B, heads, n, m, d, scale, sdb_stream(stream));
   FaParams p;
   memset(&p, 0, sizeof(p));
   const uint32_t box[3] = {32, 128, 1};

@@ -5,5 +5,6 @@
 #include "norm.cu"
 #include "conv_small.cu"
 #include "attention.cu"
+#include "attention_ctx.cu"
 #include "attention_umma.cu"
 #include "gemm_umma.cu"

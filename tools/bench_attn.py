@@ -20,6 +20,14 @@ ms = timeit(lambda: ops.attention_p32(q, k, v, H, d, 1 / math.sqrt(d)))
 pairs = B * H * n * n
 print(f"attention_p32 poly={os.environ.get('SDB_FA_POLY','3')}: {ms:.3f} ms  {pairs/ms/1e9:.2f} Gpairs/ms... "
       f"{pairs/(ms*1e-3)/148/1.965e9:.2f} pairs/clk/SM  {4*pairs*d/(ms*1e-3)/1e12:.1f} TFLOP/s(alg)")
+# cross-attention over a 77-token context (same queries)
+ctx = torch.randn(B, 77, 2 * H * 32, device="cuda").to(torch.bfloat16)
+ctx.view(B, 77, 2, H, 32)[..., d:] = 0
+ctx.view(B, 77, 2, H, 32)[:, :, 1, :, d] = 1
+kc, vc = ctx[:, :, :256], ctx[:, :, 256:]
+ms = timeit(lambda: ops.attention_p32(q, kc, vc, H, d, 1 / math.sqrt(d)))
+by = (q.numel() + B * n * H * d) * 2
+print(f"attention_p32 m=77: {ms*1e3:.1f} us  {by/ms/1e6:.0f} GB/s (Q in + O out)")
 if os.environ.get("OLD"):
     qkv2 = torch.randn(B, n, 480, device="cuda").to(torch.bfloat16)
     ms = timeit(lambda: ops.attention(qkv2[:, :, :160], qkv2[:, :, 160:320], qkv2[:, :, 320:], H, d, 1 / math.sqrt(d)))
