@@ -28,19 +28,6 @@ attention_ctx_kernel(const __nv_bfloat16* __restrict__ q, long long ldq, const _
   const __nv_bfloat16* kg = k + (long long)b * m * ldk + h * 32;
   const __nv_bfloat16* vg = v + (long long)b * m * ldv + h * 32;
 
-  // ---- stage K, V: 4 x 16-byte chunks per row, rows >= m zero ------------------------------------
-  for (int i = threadIdx.x; i < KG * 16 * 4; i += kCtxThreads) {
-    const int row = i >> 2, ch = i & 3;
-    uint4 kk = make_uint4(0u, 0u, 0u, 0u), vv = kk;
-    if (row < m) {
-      kk = __ldg(reinterpret_cast<const uint4*>(kg + (long long)row * ldk + ch * 8));
-      vv = __ldg(reinterpret_cast<const uint4*>(vg + (long long)row * ldv + ch * 8));
-    }
-    *reinterpret_cast<uint4*>(sK + row * kCtxPitch + ch * 8) = kk;
-    *reinterpret_cast<uint4*>(sV + row * kCtxPitch + ch * 8) = vv;
-  }
-  __syncthreads();
-
   const int q_begin = blockIdx.x * q_per_cta;
   const int q_end = q_begin + q_per_cta < n ? q_begin + q_per_cta : n;
   const int g = lane >> 2, c2 = (lane & 3) * 2;
@@ -59,9 +46,39 @@ attention_ctx_kernel(const __nv_bfloat16* __restrict__ q, long long ldq, const _
     }
   };
 
+  // the first Q fragments are requested before K/V are staged: one global round trip instead of two
   uint32_t qf[2][4], qn[2][4];
   int q0 = q_begin + warp * 16;
   if (q0 < q_end) load_q(q0, qf);
+
+  // ---- stage K, V: 4 x 16-byte chunks per row, rows >= m zero; all loads in flight before the stores ----
+  {
+    constexpr int kChunks = KG * 16 * 4;
+    constexpr int kPer = (kChunks + kCtxThreads - 1) / kCtxThreads;
+    uint4 kk[kPer], vv[kPer];
+#pragma unroll
+    for (int u = 0; u < kPer; ++u) {
+      const int i = threadIdx.x + u * kCtxThreads;
+      const int row = i >> 2, ch = i & 3;
+      kk[u] = make_uint4(0u, 0u, 0u, 0u);
+      vv[u] = kk[u];
+      if (i < kChunks && row < m) {
+        kk[u] = __ldg(reinterpret_cast<const uint4*>(kg + (long long)row * ldk + ch * 8));
+        vv[u] = __ldg(reinterpret_cast<const uint4*>(vg + (long long)row * ldv + ch * 8));
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kPer; ++u) {
+      const int i = threadIdx.x + u * kCtxThreads;
+      const int row = i >> 2, ch = i & 3;
+      if (i < kChunks) {
+        *reinterpret_cast<uint4*>(sK + row * kCtxPitch + ch * 8) = kk[u];
+        *reinterpret_cast<uint4*>(sV + row * kCtxPitch + ch * 8) = vv[u];
+      }
+    }
+  }
+  __syncthreads();
+
   for (; q0 < q_end; q0 += (kCtxThreads / 32) * 16) {
     const int qnext = q0 + (kCtxThreads / 32) * 16;
     if (qnext < q_end) load_q(qnext, qn);
@@ -168,7 +185,7 @@ static int launch_attention_ctx(const void* q, long long ldq, const void* k, lon
                                 float scale, cudaStream_t st) {
   // ~8 CTAs' worth of queries per (batch, head) row of the grid keeps K/V re-staging small and the
   // grid several waves deep
-  int q_per_cta = 512;
+  int q_per_cta = 1024;
   while (q_per_cta > 128 && (long long)((n + q_per_cta - 1) / q_per_cta) * heads * B < 4LL * sdb_num_sms())
     q_per_cta >>= 1;
   dim3 grid((n + q_per_cta - 1) / q_per_cta, heads, B);
