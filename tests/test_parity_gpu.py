@@ -169,3 +169,23 @@ def test_vae_decode_vs_reference_golden(golden, name):
     e = rel_l2(y, golden[f"vae_{name}"])
     print(f"vae {name}: {e:.3e}")
     assert e < VAE_BF16_TOL
+
+
+def test_vae_decode_kl_shape_vs_oracle():
+    """AutoencoderKL-shape decoder ([128, 256, 512, 512], config 3 of BASELINE.json) at a latent the CPU oracle
+    finishes in seconds: 8x8 -> 64x64.  Same kernels and tile shapes per layer as the 64x64 -> 512x512 run."""
+    from stable_diffusion_pytorch_b200.models import AutoEncoderKL, AutoencoderConfig
+    cfg = O.VaeCfg(autoencoder_channels_list=(128, 256, 512, 512), groups=32)
+    m = AutoEncoderKL(AutoencoderConfig(autoencoder_channels_list=list(cfg.autoencoder_channels_list),
+                                        groups=cfg.groups)).eval()
+    sd = O.seeded_state_dict(O.vae_decoder_param_shapes(cfg), 23)
+    m.load_state_dict(sd, strict=False)
+    m = m.to(DEV)
+    z = cases.vae_inputs(cfg, 1, 8, 8, 23)
+    with torch.no_grad():
+        y = m.decode(z.to(DEV))
+        ref = O.vae_decode(sd, cfg, z)
+    assert tuple(y.shape) == (1, 3, 64, 64)
+    e = rel_l2(y, ref)
+    print(f"vae kl-shape 8x8: {e:.3e}")
+    assert e < VAE_BF16_TOL
