@@ -63,10 +63,13 @@ class LatentDiffusion(nn.Module):
     @torch.no_grad()
     def sample(self, noised_sample: Tensor, context_emb: Tensor, guidance_scale: float = 7.5,
                repeat_noise: bool = False, scale_factor: float = 1.0, time_steps: Optional[int] = None,
-               sampler: str = "ddpm", device_noise: bool = False, seed: int = 0):
+               sampler: str = "ddpm", device_noise: bool = False, seed: int = 0,
+               host_noise: Optional[Tensor] = None):
         """Reverse process from x_T.  ``sampler`` = "ddpm" (the reference's) or "ddim" (eta = 0).
         ``device_noise=False`` draws every step's noise on the host from torch's global CPU generator
-        in the reference's order (seeded parity); True uses the in-kernel Philox stream."""
+        in the reference's order (seeded parity); True uses the in-kernel Philox stream.  ``host_noise``
+        ([n_steps, B, C, H, W], e.g. ``sharding.host_noise_table``) replaces the per-step draw: a rank that owns
+        a slice of a larger batch passes its rows of the full-batch noise."""
         _pack.require_cuda(noised_sample, "LatentDiffusion.sample")
         sch = self.noise_scheduler
         x = noised_sample.contiguous()
@@ -79,11 +82,13 @@ class LatentDiffusion(nn.Module):
         do_cfg = guidance_scale > 1
         c_in = self._c_in(context_emb) if do_cfg else context_emb
         kind = {"ddpm": 0, "ddim": 1}[sampler]
-        for step in steps:
+        for i, step in enumerate(steps):
             t = torch.full((bsz * (2 if do_cfg else 1),), step, dtype=torch.long, device=x.device)
             eps = self.unet(x, t, c_in, x_repeat=2 if do_cfg else 1)
             noise = None
-            if kind == 0 and step != 0 and not device_noise:
+            if kind == 0 and step != 0 and host_noise is not None:
+                noise = host_noise[i].to(x.device, dtype=x.dtype).contiguous()
+            elif kind == 0 and step != 0 and not device_noise:
                 shape = (1, *x.shape[1:]) if repeat_noise else x.shape
                 noise = torch.randn(shape).expand(x.shape).to(x.device, dtype=x.dtype).contiguous()
             # (the sigma entry of row 0 is 0: no noise is added at step 0, scheduler.py:200-201)
