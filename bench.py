@@ -35,6 +35,7 @@ def parse():
     ap.add_argument("--sampler", default="ddim", choices=["ddim", "ddpm"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--no-decode", action="store_true", help="skip the VAE-decode (images/s) leg")
     ap.add_argument("--profile-step", action="store_true",
                     help="after warm-up run ONE eager step between cudaProfilerStart/Stop and exit "
                          "(for `ncu --profile-from-start off`; prints no bench line)")
@@ -183,6 +184,33 @@ def time_kernel(fn, iters=10, warm=3):
     return e0.elapsed_time(e1) / iters  # ms
 
 
+def time_vae_decode(latents, dev, iters=3):
+    """ms per decode of `latents` [B,4,64,64] with the AutoencoderKL-shape decoder (random init)."""
+    import torch
+    from stable_diffusion_pytorch_b200.models import AutoEncoderKL, AutoencoderConfig
+    g = torch.Generator().manual_seed(11)
+    vae = AutoEncoderKL(AutoencoderConfig(autoencoder_channels_list=[128, 256, 512, 512], groups=32)).eval()
+    with torch.no_grad():
+        for p in vae.parameters():
+            if p.abs().sum() == 0:
+                p.copy_(torch.randn(p.shape, generator=g) * 0.02)
+    vae = vae.to(dev)
+    z = latents.detach().clone()
+    with torch.no_grad():
+        for _ in range(2):
+            vae.decode(z)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record()
+        for _ in range(iters):
+            y = vae.decode(z)
+        e1.record()
+        torch.cuda.synchronize()
+    del vae, y
+    torch.cuda.empty_cache()
+    return e0.elapsed_time(e1) / iters
+
+
 def kernel_rooflines(B2, size, pk):
     """Isolated timings (CUDA events, current stream) of the three dominant kernel families at the
     workload's shapes; algorithmic flops in the reference's formulation."""
@@ -306,10 +334,15 @@ def run_b200(args):
     e1.record()
     barrier()
     ms_e2e = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    # ---- images/s: 50 latent-steps + one AutoencoderKL-shape decode (config 3) of this rank's latents ----
+    ms_dec = torch.tensor([float("nan")], device=dev)
+    if not args.no_decode and S == 64:
+        ms_dec = torch.tensor([time_vae_decode(gs.x, dev)], device=dev)
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         dist.all_reduce(ms_e2e, op=dist.ReduceOp.MAX)
-    ms, ms_e2e = float(ms), float(ms_e2e)
+        dist.all_reduce(ms_dec, op=dist.ReduceOp.MAX)
+    ms, ms_e2e, ms_dec = float(ms), float(ms_e2e), float(ms_dec)
     finite = bool(torch.isfinite(gs.x.float()).all())
     flag = ops.debug_timeout_flag()
     if rank != 0:
@@ -351,6 +384,11 @@ def run_b200(args):
         "kernels": kr,
         "step_roofline": {"algorithmic_tflops": step_tf, "peak_sustained": pk["bf16_tflops_sustained"],
                           "frac": step_tf / pk["bf16_tflops_sustained"]},
+        "images": None if ms_dec != ms_dec else {
+            "images_per_sec": n_lat / ((50 * ms / args.steps + ms_dec) * 1e-3), "ms_decode": ms_dec,
+            "decoder": "AutoencoderKL-shape [128,256,512,512], 64x64x4 -> 512x512x3, bf16",
+            "decode_alg_tflops": 38306.0 * (B / 16.0) / ms_dec,
+            "formula": "latents / (50 x ms_per_step + ms_decode), max over ranks"},
         "finite": finite, "timeout_flag": flag,
     }
     if world == 1 and not args.no_cpu_baseline:

@@ -10,22 +10,26 @@ template <typename T> __device__ __forceinline__ float ld_f(const T* p);
 template <> __device__ __forceinline__ float ld_f<float>(const float* p) { return __ldg(p); }
 template <> __device__ __forceinline__ float ld_f<__nv_bfloat16>(const __nv_bfloat16* p) { return __bfloat162float(*p); }
 
-// ---- conv_in: NCHW [B,Cin,H,W] -> NHWC [B,H,W,Cout];  CTA = 32 pixels of one row x 64 couts ----
-constexpr int kCinMax = 8, kInPx = 32, kInCo = 64;
+// ---- conv_in: NCHW [B,Cin,H,W] -> NHWC [B,H,W,Cout] --------------------------------------------
+// CTA = 32 pixels wide x kInRows rows x 64 couts: the 64-cout weight slab is staged once and re-used for
+// every row (it used to be re-staged per 32 pixels, which cost as much as the arithmetic); the input
+// window slides down one row at a time.  Thread = one pixel column x 8 couts.
+constexpr int kCinMax = 8, kInPx = 32, kInCo = 64, kInRows = 8;
 
 template <typename TI, typename TO>
 __global__ void __launch_bounds__(256)
 conv3x3_in_kernel(const TI* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
                   TO* __restrict__ out, int src_B, int H, int W, int Cin, int Cout) {
-  __shared__ float s_in[kCinMax][3][kInPx + 2];
-  __shared__ float s_w[kCinMax * 9][kInCo];  // [ci*9 + tap][co]
-  const int wt = blockIdx.x % ((W + kInPx - 1) / kInPx);
-  const int h = blockIdx.x / ((W + kInPx - 1) / kInPx);
+  __shared__ float s_in[kCinMax][kInRows + 2][kInPx + 2];
+  __shared__ __align__(16) float s_w[kCinMax * 9][kInCo];  // [ci*9 + tap][co]
+  const int tiles_w = (W + kInPx - 1) / kInPx;
+  const int wt = blockIdx.x % tiles_w;
+  const int h0 = (blockIdx.x / tiles_w) * kInRows;
   const int b = blockIdx.z, co0 = blockIdx.y * kInCo, w0 = wt * kInPx;
-  for (int i = threadIdx.x; i < Cin * 3 * (kInPx + 2); i += 256) {
-    const int ci = i / (3 * (kInPx + 2)), rem = i - ci * 3 * (kInPx + 2);
+  for (int i = threadIdx.x; i < Cin * (kInRows + 2) * (kInPx + 2); i += 256) {
+    const int ci = i / ((kInRows + 2) * (kInPx + 2)), rem = i - ci * (kInRows + 2) * (kInPx + 2);
     const int dy = rem / (kInPx + 2), dx = rem - dy * (kInPx + 2);
-    const int hh = h + dy - 1, ww = w0 + dx - 1;
+    const int hh = h0 + dy - 1, ww = w0 + dx - 1;
     float v = 0.f;
     if (hh >= 0 && hh < H && ww >= 0 && ww < W)
       v = ld_f<TI>(x + (((long long)(b % src_B) * Cin + ci) * H + hh) * W + ww);
@@ -37,30 +41,38 @@ conv3x3_in_kernel(const TI* __restrict__ x, const float* __restrict__ w, const f
   }
   __syncthreads();
   const int cg = threadIdx.x & 7, px = threadIdx.x >> 3;  // 8 couts per thread, 32 pixels
-  float acc[8];
-#pragma unroll
-  for (int j = 0; j < 8; ++j) acc[j] = (co0 + cg * 8 + j < Cout) ? bias[co0 + cg * 8 + j] : 0.f;
-  for (int ci = 0; ci < Cin; ++ci) {
-#pragma unroll
-    for (int t = 0; t < 9; ++t) {
-      const float a = s_in[ci][t / 3][px + t % 3];
-      const float4 w0v = *reinterpret_cast<const float4*>(&s_w[ci * 9 + t][cg * 8]);
-      const float4 w1v = *reinterpret_cast<const float4*>(&s_w[ci * 9 + t][cg * 8 + 4]);
-      acc[0] = fmaf(a, w0v.x, acc[0]); acc[1] = fmaf(a, w0v.y, acc[1]);
-      acc[2] = fmaf(a, w0v.z, acc[2]); acc[3] = fmaf(a, w0v.w, acc[3]);
-      acc[4] = fmaf(a, w1v.x, acc[4]); acc[5] = fmaf(a, w1v.y, acc[5]);
-      acc[6] = fmaf(a, w1v.z, acc[6]); acc[7] = fmaf(a, w1v.w, acc[7]);
-    }
-  }
   const int wo = w0 + px, co = co0 + cg * 8;
-  if (wo < W && co < Cout) {  // Cout % 8 == 0 is checked on the host
-    TO* dst = out + (((long long)b * H + h) * W + wo) * Cout + co;
-    if constexpr (sizeof(TO) == 2) {
-      *reinterpret_cast<uint4*>(dst) = make_uint4(pack_bf16x2(acc[0], acc[1]), pack_bf16x2(acc[2], acc[3]),
-                                                  pack_bf16x2(acc[4], acc[5]), pack_bf16x2(acc[6], acc[7]));
-    } else {
-      reinterpret_cast<float4*>(dst)[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
-      reinterpret_cast<float4*>(dst)[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
+  float bv[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) bv[j] = (co + j < Cout) ? bias[co + j] : 0.f;
+#pragma unroll 1
+  for (int r = 0; r < kInRows; ++r) {
+    const int h = h0 + r;
+    if (h >= H) break;
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = bv[j];
+    for (int ci = 0; ci < Cin; ++ci) {
+#pragma unroll
+      for (int t = 0; t < 9; ++t) {
+        const float a = s_in[ci][r + t / 3][px + t % 3];
+        const float4 w0v = *reinterpret_cast<const float4*>(&s_w[ci * 9 + t][cg * 8]);
+        const float4 w1v = *reinterpret_cast<const float4*>(&s_w[ci * 9 + t][cg * 8 + 4]);
+        acc[0] = fmaf(a, w0v.x, acc[0]); acc[1] = fmaf(a, w0v.y, acc[1]);
+        acc[2] = fmaf(a, w0v.z, acc[2]); acc[3] = fmaf(a, w0v.w, acc[3]);
+        acc[4] = fmaf(a, w1v.x, acc[4]); acc[5] = fmaf(a, w1v.y, acc[5]);
+        acc[6] = fmaf(a, w1v.z, acc[6]); acc[7] = fmaf(a, w1v.w, acc[7]);
+      }
+    }
+    if (wo < W && co < Cout) {  // Cout % 8 == 0 is checked on the host
+      TO* dst = out + (((long long)b * H + h) * W + wo) * Cout + co;
+      if constexpr (sizeof(TO) == 2) {
+        *reinterpret_cast<uint4*>(dst) = make_uint4(pack_bf16x2(acc[0], acc[1]), pack_bf16x2(acc[2], acc[3]),
+                                                    pack_bf16x2(acc[4], acc[5]), pack_bf16x2(acc[6], acc[7]));
+      } else {
+        reinterpret_cast<float4*>(dst)[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
+        reinterpret_cast<float4*>(dst)[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
+      }
     }
   }
 }
@@ -167,7 +179,7 @@ extern "C" int sdb_conv3x3_in(const void* x_nchw, int src_dtype, const float* w,
   SDB_CHECK_ARG(src_B > 0 && B % src_B == 0, "conv3x3_in: B (%d) must be a multiple of src_B (%d)", B, src_B);
   SDB_CHECK_ARG(Cin >= 1 && Cin <= kCinMax, "conv3x3_in: Cin (%d) must be <= %d", Cin, kCinMax);
   SDB_CHECK_ARG(Cout % 8 == 0, "conv3x3_in: Cout (%d) must be a multiple of 8", Cout);
-  dim3 grid(((W + kInPx - 1) / kInPx) * H, (Cout + kInCo - 1) / kInCo, B);
+  dim3 grid(((W + kInPx - 1) / kInPx) * ((H + kInRows - 1) / kInRows), (Cout + kInCo - 1) / kInCo, B);
   cudaStream_t st = sdb_stream(stream);
 #define SDB_CIN(TI, TO) conv3x3_in_kernel<TI, TO><<<grid, 256, 0, st>>>((const TI*)x_nchw, w, bias, (TO*)out_nhwc, src_B, H, W, Cin, Cout)
   if (src_dtype == SDB_F32 && out_dtype == SDB_F32) SDB_CIN(float, float);

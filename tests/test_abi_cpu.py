@@ -33,7 +33,7 @@ def test_argument_errors_surface_without_gpu():
     assert L.sdb_gemm(None, None) == -1
     assert b"null" in L.sdb_last_error()
     assert L.sdb_attention(None, 0, None, 0, None, 0, None, 0, 1, 1, 1, 1, 20, 1.0, 1, None) == -1
-    assert L.sdb_groupnorm_chunks(4096) == 16
+    assert L.sdb_groupnorm_chunks(4096) == 64 and L.sdb_groupnorm_chunks(256) == 4 and L.sdb_groupnorm_chunks(1) == 1
 
 
 def test_no_cpu_fallback():
