@@ -56,6 +56,8 @@ def unet_inputs(cfg, B, H, W, seed, ctx_len=77):
 SAMPLE_CASES = {
     "tiny_16": (TINY, 11, 2, 16, 16, 6, 7.5),
     "default_16": (DEFAULT, 13, 1, 16, 16, 4, 7.5),
+    # BASELINE.json configs[0]: repo-default UNet, 1 prompt, 32x32x4 latent, 50 DDPM steps with CFG, fp32 on CPU
+    "config1_32_50": (DEFAULT, 14, 1, 32, 32, 50, 7.5),
 }
 SAMPLE_NOISE_SEED = 4321
 
