@@ -268,7 +268,7 @@ attention_umma_kernel(const __grid_constant__ FaParams p) {
 #pragma unroll
           for (int kk = 0; kk < kFaBN / 16; ++kk)
             umma_f16_ts(tcol + 192u, tcol + 128u + (uint32_t)kk * 8u, vdesc + (uint64_t)(kk * 64), idesc_o,
-                        kk ? 1u : 0u);
+                        (j | kk) ? 1u : 0u);   // O accumulates in TMEM across the key tiles
           umma_commit(bar_o_full(w));
           umma_commit(bar_kv_empty(s));   // one arrival per warpgroup
         }
@@ -281,9 +281,11 @@ attention_umma_kernel(const __grid_constant__ FaParams p) {
     const int w = (warp - 4) >> 2, quarter = warp & 3;
     const uint32_t tw = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)w * 256u;
     const float c = p.scale_log2;
-    float acc[kFaDP];
-#pragma unroll
-    for (int i = 0; i < kFaDP; ++i) acc[i] = 0.f;
+    // O stays in TMEM for the whole key loop, relative to a LAGGING reference maximum m_run: it is only
+    // rescaled (TMEM load / multiply / store) when some row of the warp saw its maximum grow by more than
+    // 2^kLazyLog2 -- until then P = exp2((s - m_run) c) may exceed 1 by at most that factor, harmless in
+    // bf16 / fp32.  Typical rows settle after the first few tiles, so the per-tile cost is one barrier probe.
+    constexpr float kLazyLog2 = 8.0f;
     float m_run = -INFINITY;
     bool ok = true;
     for (int j = 0; j < T; ++j) {
@@ -299,16 +301,6 @@ attention_umma_kernel(const __grid_constant__ FaParams p) {
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar_s_free(w));
-      // fold the previous tile's P.V (relative to m_run) into the register accumulator
-      if (j > 0) {
-        if (ok) ok = mbar_wait(bar_o_full(w), par ^ 1u);
-        tc_fence_after();
-        uint32_t o[32];
-        tmem_ld_32x32(tw + 192, o);
-        tmem_ld_wait();
-#pragma unroll
-        for (int i = 0; i < 24; ++i) acc[i] += __uint_as_float(o[i]);
-      }
       // ragged key tail: keys >= m contribute exp2(-inf) = 0
       if (j == T - 1 && (p.m & (kFaBN - 1)) != 0) {
         const int valid = p.m - j * kFaBN;
@@ -317,20 +309,41 @@ attention_umma_kernel(const __grid_constant__ FaParams p) {
           if (i >= valid) su[i] = 0xff800000u;
       }
       // row max (3-input max, 4 independent chains)
-      float mx[4] = {m_run, -INFINITY, -INFINITY, -INFINITY};
+      float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
 #pragma unroll
       for (int i = 0; i < 128; i += 8) {
 #pragma unroll
         for (int k = 0; k < 4; ++k)
           mx[k] = max3(mx[k], __uint_as_float(su[i + 2 * k]), __uint_as_float(su[i + 2 * k + 1]));
       }
-      const float m_new = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
-      const float alpha = ex2_mufu((m_run - m_new) * c);  // first tile: exp2(-inf) = 0
-      m_run = m_new;
-      const float negm = -m_new * c;
+      const float m_tile = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+      // the previous tile's P.V must have finished reading P (and writing O) before either is touched
+      if (j > 0) {
+        if (ok) ok = mbar_wait(bar_o_full(w), par ^ 1u);
+        tc_fence_after();
+      }
+      const bool grow = (m_tile - m_run) * c > kLazyLog2;   // first tile: m_run = -inf -> true
+      if (j == 0) {
+        m_run = m_tile;
+      } else if (__any_sync(0xffffffffu, grow)) {
+        const float m_new = grow ? m_tile : m_run;
+        const float alpha = ex2_mufu((m_run - m_new) * c);
+        m_run = m_new;
+        uint32_t oa[16], ob[16];
+        tmem_ld_32x16(tw + 192, oa);
+        tmem_ld_32x16(tw + 208, ob);
+        tmem_ld_wait();
 #pragma unroll
-      for (int i = 0; i < 24; ++i) acc[i] *= alpha;
-      // P = exp2(s*c - m*c) -> packed bf16 -> TMEM (A operand of P.V)
+        for (int i = 0; i < 16; ++i) {
+          oa[i] = __float_as_uint(__uint_as_float(oa[i]) * alpha);
+          ob[i] = __float_as_uint(__uint_as_float(ob[i]) * alpha);
+        }
+        tmem_st_32x16(tw + 192, oa);
+        tmem_st_32x16(tw + 208, ob);
+      }
+      const float negm = -m_run * c;
+      // P = exp2(s*c - m*c) -> bf16 by truncation (one PRMT per pair instead of a half-rate F2FP; numerator
+      // and denominator -- the ones column of V -- see the same P, so the bias cancels) -> TMEM (A operand)
 #pragma unroll
       for (int ch = 0; ch < 4; ++ch) {
         uint32_t pk[16];
@@ -347,7 +360,7 @@ attention_umma_kernel(const __grid_constant__ FaParams p) {
               x0 = ex2_mufu(x0);
               x1 = ex2_mufu(x1);
             }
-            pk[g * 8 + k] = pack_bf16x2(x0, x1);
+            pk[g * 8 + k] = __byte_perm(__float_as_uint(x0), __float_as_uint(x1), 0x7632);
           }
         }
         tmem_st_32x16(tw + 128 + ch * 16, pk);
@@ -360,12 +373,13 @@ attention_umma_kernel(const __grid_constant__ FaParams p) {
     // ---- last tile's P.V, normalise, store ---------------------------------------------------
     if (ok) ok = mbar_wait(bar_o_full(w), ((uint32_t)(T - 1)) & 1u);
     tc_fence_after();
+    float acc[kFaDP];
     {
       uint32_t o[32];
       tmem_ld_32x32(tw + 192, o);
       tmem_ld_wait();
 #pragma unroll
-      for (int i = 0; i < 24; ++i) acc[i] += __uint_as_float(o[i]);
+      for (int i = 0; i < kFaDP; ++i) acc[i] = __uint_as_float(o[i]);
     }
     const int row = q0 + w * kFaBM + quarter * 32 + lane;
     if (row < p.n && ok) {
@@ -443,7 +457,7 @@ extern "C" int sdb_attention_p32(const void* q, int64_t ldq, const void* k, int6
   if (poly < 0) {
     const char* e = getenv("SDB_FA_POLY");
     poly = e ? atoi(e) : 3;
-    if (poly < 0 || poly > 5) poly = 3;
+    if (poly < 0 || poly > 6) poly = 3;
   }
   dim3 grid((n + 2 * kFaBM - 1) / (2 * kFaBM), heads, B);
 #define SDB_FA_LAUNCH(P)                                                                                   \
@@ -464,6 +478,7 @@ extern "C" int sdb_attention_p32(const void* q, int64_t ldq, const void* k, int6
     SDB_FA_LAUNCH(2)
     SDB_FA_LAUNCH(3)
     SDB_FA_LAUNCH(4)
+    SDB_FA_LAUNCH(6)
     SDB_FA_LAUNCH(5)
   }
 #undef SDB_FA_LAUNCH
