@@ -942,10 +942,20 @@ extern "C" int sdb_conv3x3(const SdbConvArgs* a, void* stream) {
   p.Cin = a->Cin;
   p.kb_per_tap = (a->Cin + p.BK - 1) / p.BK;
   p.num_kb = 9 * p.kb_per_tap;
-  // tile = TW x TH x TN pixels with TW*TH*TN = 128
+  // tile = TW x TH x TN pixels with TW*TH*TN = 128, all powers of two.  TW = the largest power-of-two factor
+  // of W when that is >= 8 (no waste); otherwise the width in {8..128} that wastes the fewest clipped
+  // columns (the TMA unit zero-fills the loads and clips the stores of a box that overhangs the image).
   int tw = 1;
   while (tw < 128 && a->W % (tw * 2) == 0) tw *= 2;
-  SDB_CHECK_ARG(tw >= 8 || tw == a->W, "conv3x3: W (%d) needs a power-of-two factor >= 8", a->W);
+  if (tw < 8) {
+    int best = 8;
+    double best_waste = 1e30;
+    for (int c = 8; c <= 128; c *= 2) {
+      const double waste = (double)((a->W + c - 1) / c * c) / a->W;
+      if (waste < best_waste - 1e-9) { best_waste = waste; best = c; }
+    }
+    tw = best;
+  }
   int th = 1;
   while (tw * th < 128 && th < a->H) th *= 2;
   int tn = 128 / (tw * th);
@@ -954,7 +964,7 @@ extern "C" int sdb_conv3x3(const SdbConvArgs* a, void* stream) {
     return SDB_EUNSUPPORTED;
   }
   p.TW = tw; p.TH = th; p.TN = tn;
-  p.tiles_w = a->W / tw;
+  p.tiles_w = (a->W + tw - 1) / tw;
   p.tiles_h = (a->H + th - 1) / th;
   const int tiles_b = (a->B + tn - 1) / tn;
   p.tiles_m = p.tiles_w * p.tiles_h * tiles_b;

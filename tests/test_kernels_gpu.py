@@ -81,6 +81,11 @@ def test_gemm_two_segments_fp32_out():
     out = ops.gemm(a1, w, bias, a2=a2, out_dtype=torch.float32)
     ref = torch.cat([a1, a2], 1).float() @ w.float().t() + bias
     assert rel_l2(out, ref) < 1e-5
+    # bf16 output: the staged epilogue (swizzled smem tile + TMA store, TMA-loaded residual) when the
+    # output keeps the input resolution, the direct one otherwise
+    outb = ops.conv3x3(x, w, bias, temb, res, down2=down2, out_dtype=torch.bfloat16)
+    assert outb.dtype == torch.bfloat16 and outb.shape == ref.shape
+    assert rel_l2(outb.float(), ref) < 4e-3
 
 
 def test_gemm_strided_views():
@@ -105,6 +110,10 @@ CONV_CASES = [
     (1, 4, 4, 32, 32, False, False, False),     # tiny map
     (2, 16, 16, 96, 96, False, False, False),
     (1, 128, 128, 64, 64, False, False, False), # W = 128: one image row per tile
+    (2, 12, 20, 64, 64, True, True, False),     # W without a power-of-two factor >= 8: clipped 8-wide boxes
+    (1, 10, 6, 32, 48, False, True, False),     # W < 8
+    (3, 6, 12, 64, 32, True, False, True),      # ragged + DownSample
+    (1, 24, 40, 160, 160, True, True, False),
 ]
 
 

@@ -189,3 +189,50 @@ def test_vae_decode_kl_shape_vs_oracle():
     e = rel_l2(y, ref)
     print(f"vae kl-shape 8x8: {e:.3e}")
     assert e < VAE_BF16_TOL
+
+
+# ---------------------------------------------------------------- ragged shapes / edge cases
+@pytest.mark.parametrize("B,H,W,ctx_len", [
+    (1, 8, 8, 77),       # smallest latent the reference runs at (64 px / 8)
+    (3, 24, 40, 77),     # odd batch, non-square, tiles clipped in both directions
+    (2, 16, 16, 5),      # very short context (one key group)
+    (2, 16, 16, 200),    # context longer than one key tile: tcgen05 attention path for cross-attention
+    (5, 8, 16, 128),     # context exactly one full tile
+])
+def test_unet_forward_ragged_shapes_vs_oracle(B, H, W, ctx_len):
+    cfg = cases.DEFAULT
+    m, sd = build_unet(cfg, 31)
+    g = torch.Generator().manual_seed(B * 1000 + H * 10 + ctx_len)
+    x = torch.randn(B, cfg.latent_channels, H, W, generator=g)
+    t = torch.randint(0, 1000, (B,), generator=g, dtype=torch.long)
+    ctx = torch.randn(B, ctx_len, cfg.context_dim, generator=g)
+    with torch.no_grad():
+        y = m(x.to(DEV), t.to(DEV), ctx.to(DEV))
+        ref = O.unet_forward(sd, cfg, x, t, ctx)
+    assert tuple(y.shape) == tuple(x.shape)
+    e = rel_l2(y, ref)
+    print(f"unet ragged B={B} {H}x{W} ctx={ctx_len}: {e:.3e}")
+    assert e < UNET_BF16_TOL
+
+
+def test_unet_and_sampler_argument_errors_on_gpu():
+    """The reference's asserts, mirrored (unet.py:286-289, scheduler.py:167-169, autoencoder.py:157-159) plus
+    the extra constraints of this implementation (even H, W; CUDA tensors only)."""
+    from stable_diffusion_pytorch_b200.models import (AutoEncoderKL, AutoencoderConfig, DDPMConfig,
+                                                      DDPMScheduler)
+    cfg = cases.TINY
+    m, _ = build_unet(cfg, 5)
+    x = torch.randn(1, 4, 8, 8, device=DEV)
+    t = torch.zeros(1, dtype=torch.long, device=DEV)
+    with pytest.raises(AssertionError, match="context dim"):
+        m(x, t, torch.randn(1, 77, cfg.context_dim + 1, device=DEV))
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        m(x.cpu(), t.cpu(), torch.randn(1, 77, cfg.context_dim))
+    with pytest.raises((AssertionError, ValueError, RuntimeError)):
+        m(torch.randn(1, 4, 7, 8, device=DEV), t, torch.randn(1, 77, cfg.context_dim, device=DEV))
+    sch = DDPMScheduler(DDPMConfig())
+    with pytest.raises(AssertionError, match="should be less than"):
+        sch.step(x, x, 1000)
+    vae = AutoEncoderKL(AutoencoderConfig()).to(DEV)
+    with pytest.raises(AssertionError, match="Expected latent"):
+        vae.decode(torch.randn(1, 5, 8, 8, device=DEV))
