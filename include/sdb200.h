@@ -168,6 +168,10 @@ int sdb_conv3x3_out(const void* x_nhwc, int src_dtype, const float* w, const flo
 int sdb_conv1x1_nchw_small(const void* x, const float* w, const float* bias, void* out, int dtype,
                            int B, int H, int W, int Cin, int Cout, void* stream);
 /* nearest x2 upsample NHWC (resnet2d.py:61), used ahead of sdb_conv3x3 when up2 is not fused */
+/* fp32 channels-last [B,H,W,Cp] -> NCHW [B,C,H,W] keeping the first C <= Cp channels (output head: the
+ * tensor-core conv pads Cout to 16; reference layer: models/utils.py:197). */
+int sdb_nhwc_slice_to_nchw(const float* src, int Cp, void* dst, int dst_dtype, int B, int C, int H, int W,
+                           void* stream);
 int sdb_upsample2x(const void* x, void* out, int dtype, int B, int H, int W, int C, void* stream);
 
 /* ---- K4: fused attention --------------------------------------------------------------------

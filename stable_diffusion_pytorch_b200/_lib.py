@@ -57,6 +57,7 @@ SIGNATURES = {
     "sdb_cfg_combine": (_i, [_p, _f, _p, _i64, _i, _p]),
     "sdb_conv3x3_out": (_i, [_p, _i, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p]),
     "sdb_conv1x1_nchw_small": (_i, [_p, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p]),
+    "sdb_nhwc_slice_to_nchw": (_i, [_p, _i, _p, _i, _i, _i, _i, _i, _p]),
     "sdb_upsample2x": (_i, [_p, _p, _i, _i, _i, _i, _i, _p]),
     "sdb_attention": (_i, [_p, _i64, _p, _i64, _p, _i64, _p, _i64, _i, _i, _i, _i, _i, _f, _i, _p]),
     "sdb_attention_p32": (_i, [_p, _i64, _p, _i64, _p, _i64, _p, _i64, _i, _i, _i, _i, _i, _f, _p]),

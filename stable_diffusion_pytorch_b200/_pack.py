@@ -99,3 +99,15 @@ def zero_module(module: nn.Module) -> nn.Module:
     for p in module.parameters():
         p.detach().zero_()
     return module
+
+
+def head_w16(w: Tensor, b: Tensor) -> Tuple[Tensor, Tensor]:
+    """Output-head conv OIHW [Cout <= 16, Cin, 3, 3] -> bf16 [16, 3, 3, Cin] with zero rows for the padding
+    channels (the tensor-core conv needs Cout % 16 == 0), bias -> fp32 [16]."""
+    cout = w.shape[0]
+    assert cout <= 16
+    wp = torch.zeros(16, 3, 3, w.shape[1], device=w.device, dtype=torch.bfloat16)
+    wp[:cout] = conv3x3_w(w)
+    bp = torch.zeros(16, device=w.device, dtype=torch.float32)
+    bp[:cout] = b.detach().float()
+    return wp.contiguous(), bp

@@ -45,33 +45,42 @@ conv3x3_in_kernel(const TI* __restrict__ x, const float* __restrict__ w, const f
   float bv[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) bv[j] = (co + j < Cout) ? bias[co + j] : 0.f;
+  // four rows at a time: every weight vector fetched from shared memory feeds 4 x 8 FMAs
 #pragma unroll 1
-  for (int r = 0; r < kInRows; ++r) {
-    const int h = h0 + r;
-    if (h >= H) break;
-    float acc[8];
+  for (int r0 = 0; r0 < kInRows; r0 += 4) {
+    if (h0 + r0 >= H) break;
+    float acc[4][8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) acc[j] = bv[j];
+    for (int r = 0; r < 4; ++r)
+#pragma unroll
+      for (int j = 0; j < 8; ++j) acc[r][j] = bv[j];
     for (int ci = 0; ci < Cin; ++ci) {
 #pragma unroll
       for (int t = 0; t < 9; ++t) {
-        const float a = s_in[ci][r + t / 3][px + t % 3];
         const float4 w0v = *reinterpret_cast<const float4*>(&s_w[ci * 9 + t][cg * 8]);
         const float4 w1v = *reinterpret_cast<const float4*>(&s_w[ci * 9 + t][cg * 8 + 4]);
-        acc[0] = fmaf(a, w0v.x, acc[0]); acc[1] = fmaf(a, w0v.y, acc[1]);
-        acc[2] = fmaf(a, w0v.z, acc[2]); acc[3] = fmaf(a, w0v.w, acc[3]);
-        acc[4] = fmaf(a, w1v.x, acc[4]); acc[5] = fmaf(a, w1v.y, acc[5]);
-        acc[6] = fmaf(a, w1v.z, acc[6]); acc[7] = fmaf(a, w1v.w, acc[7]);
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+          const float a = s_in[ci][r0 + r + t / 3][px + t % 3];
+          acc[r][0] = fmaf(a, w0v.x, acc[r][0]); acc[r][1] = fmaf(a, w0v.y, acc[r][1]);
+          acc[r][2] = fmaf(a, w0v.z, acc[r][2]); acc[r][3] = fmaf(a, w0v.w, acc[r][3]);
+          acc[r][4] = fmaf(a, w1v.x, acc[r][4]); acc[r][5] = fmaf(a, w1v.y, acc[r][5]);
+          acc[r][6] = fmaf(a, w1v.z, acc[r][6]); acc[r][7] = fmaf(a, w1v.w, acc[r][7]);
+        }
       }
     }
-    if (wo < W && co < Cout) {  // Cout % 8 == 0 is checked on the host
-      TO* dst = out + (((long long)b * H + h) * W + wo) * Cout + co;
-      if constexpr (sizeof(TO) == 2) {
-        *reinterpret_cast<uint4*>(dst) = make_uint4(pack_bf16x2(acc[0], acc[1]), pack_bf16x2(acc[2], acc[3]),
-                                                    pack_bf16x2(acc[4], acc[5]), pack_bf16x2(acc[6], acc[7]));
-      } else {
-        reinterpret_cast<float4*>(dst)[0] = make_float4(acc[0], acc[1], acc[2], acc[3]);
-        reinterpret_cast<float4*>(dst)[1] = make_float4(acc[4], acc[5], acc[6], acc[7]);
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      const int h = h0 + r0 + r;
+      if (h < H && wo < W && co < Cout) {  // Cout % 8 == 0 is checked on the host
+        TO* dst = out + (((long long)b * H + h) * W + wo) * Cout + co;
+        if constexpr (sizeof(TO) == 2) {
+          *reinterpret_cast<uint4*>(dst) = make_uint4(pack_bf16x2(acc[r][0], acc[r][1]), pack_bf16x2(acc[r][2], acc[r][3]),
+                                                      pack_bf16x2(acc[r][4], acc[r][5]), pack_bf16x2(acc[r][6], acc[r][7]));
+        } else {
+          reinterpret_cast<float4*>(dst)[0] = make_float4(acc[r][0], acc[r][1], acc[r][2], acc[r][3]);
+          reinterpret_cast<float4*>(dst)[1] = make_float4(acc[r][4], acc[r][5], acc[r][6], acc[r][7]);
+        }
       }
     }
   }

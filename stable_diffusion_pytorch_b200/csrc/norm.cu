@@ -274,6 +274,26 @@ __global__ void transpose_kernel(const S* __restrict__ src, D* __restrict__ dst,
   }
 }
 
+// [B, HW, Cp] (channels-last, Cp >= C padded channels, fp32) -> [B, C, HW]: the output head runs on the tensor
+// cores with its 3..8 output channels padded to 16; this drops the padding and restores NCHW.  Thread = pixel:
+// 16-byte reads of its channel vector, plane-wise coalesced writes.
+template <typename D>
+__global__ void nhwc_slice_to_nchw_kernel(const float* __restrict__ src, D* __restrict__ dst, long long hw,
+                                          int Cp, int C, long long total /* B*hw */) {
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
+       i += (long long)gridDim.x * blockDim.x) {
+    const long long b = i / hw, px = i - b * hw;
+    const float4* s = reinterpret_cast<const float4*>(src + i * Cp);
+    for (int c4 = 0; c4 * 4 < C; ++c4) {
+      const float4 v = __ldg(s + c4);
+      const float vv[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int j = 0; j < 4; ++j)
+        if (c4 * 4 + j < C) dst[(b * C + c4 * 4 + j) * hw + px] = cvt<float, D>(vv[j]);
+    }
+  }
+}
+
 template <typename T>
 __global__ void upsample2x_kernel(const T* __restrict__ x, T* __restrict__ out, int H, int W, int C,
                                   long long total_vec) {
@@ -441,6 +461,18 @@ extern "C" int sdb_nhwc_to_nchw(const void* src, int src_dtype, void* dst, int d
                                 int H, int W, void* stream) {
   SDB_CHECK_ARG(src && dst && B > 0 && C > 0 && H > 0 && W > 0, "nhwc_to_nchw: bad args");
   return launch_transpose(src, src_dtype, dst, dst_dtype, B, H * W, C, sdb_stream(stream));
+}
+
+extern "C" int sdb_nhwc_slice_to_nchw(const float* src, int Cp, void* dst, int dst_dtype, int B, int C, int H,
+                                      int W, void* stream) {
+  SDB_CHECK_ARG(src && dst && B > 0 && H > 0 && W > 0 && C > 0 && C <= Cp && Cp % 4 == 0, "nhwc_slice_to_nchw: bad args");
+  const long long hw = (long long)H * W, total = hw * B;
+  if (dst_dtype == SDB_BF16)
+    nhwc_slice_to_nchw_kernel<__nv_bfloat16><<<ew_grid(total, 256), 256, 0, sdb_stream(stream)>>>(src, (__nv_bfloat16*)dst, hw, Cp, C, total);
+  else
+    nhwc_slice_to_nchw_kernel<float><<<ew_grid(total, 256), 256, 0, sdb_stream(stream)>>>(src, (float*)dst, hw, Cp, C, total);
+  SDB_LAUNCH_OK();
+  return SDB_OK;
 }
 
 extern "C" int sdb_upsample2x(const void* x, void* out, int dtype, int B, int H, int W, int C, void* stream) {

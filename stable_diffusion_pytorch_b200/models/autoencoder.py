@@ -64,13 +64,13 @@ class _ConvNet(nn.Module):
             "bci": c.get("bci", [self.conv_in.bias], lambda: _pack.f32(self.conv_in.bias)),
             "go": c.get("go", [gn.weight], lambda: _pack.f32(gn.weight)),
             "bo": c.get("bo", [gn.bias], lambda: _pack.f32(gn.bias)),
-            "wh": c.get("wh", [head.weight], lambda: _pack.f32(head.weight)),
-            "bh": c.get("bh", [head.bias], lambda: _pack.f32(head.bias)),
+            "wh": c.get("wh", [head.weight, head.bias], lambda: _pack.head_w16(head.weight, head.bias)),
         }
 
     def _head(self, h: Tensor, p, out_dtype) -> Tensor:
         h = ops.group_norm(h, p["go"], p["bo"], self.groups, ACT_SILU)
-        return ops.conv3x3_out(h, p["wh"], p["bh"], out_dtype)
+        w16, b16 = p["wh"]
+        return ops.conv3x3_head(h, w16, b16, self.out[2].weight.shape[0], out_dtype)
 
 
 class Encoder(_ConvNet):

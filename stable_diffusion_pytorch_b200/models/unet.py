@@ -101,8 +101,7 @@ class UNetModel(nn.Module):
             "bci": c.get("bci", [self.conv_in.bias], lambda: _pack.f32(self.conv_in.bias)),
             "go": c.get("go", [gn.weight], lambda: _pack.f32(gn.weight)),
             "bo": c.get("bo", [gn.bias], lambda: _pack.f32(gn.bias)),
-            "wh": c.get("wh", [head.weight], lambda: _pack.f32(head.weight)),
-            "bh": c.get("bh", [head.bias], lambda: _pack.f32(head.bias)),
+            "wh": c.get("wh", [head.weight, head.bias], lambda: _pack.head_w16(head.weight, head.bias)),
         }
         offs, o = {}, 0
         for rb in rbs:
@@ -179,4 +178,4 @@ class UNetModel(nn.Module):
             h = module.forward_nhwc(h, temb_of, None, kv_of, x2=skips.pop())
         # 4. head
         h = ops.group_norm(h, p["go"], p["bo"], self.groups, ACT_SILU)
-        return ops.conv3x3_out(h, p["wh"], p["bh"], x.dtype)
+        return ops.conv3x3_head(h, p["wh"][0], p["wh"][1], self.latent_channels, x.dtype)

@@ -245,6 +245,17 @@ def conv3x3_out(x_nhwc: Tensor, w: Tensor, bias: Tensor, out_dtype=torch.float32
     return out
 
 
+def conv3x3_head(x_nhwc: Tensor, w16: Tensor, bias16: Tensor, cout: int, out_dtype=torch.float32) -> Tensor:
+    """Output head on the tensor cores: 3x3 conv with Cout padded to 16 (``_pack.head_w16``), fp32 channels-last
+    result, then the padding is dropped and the layout restored to NCHW [B, cout, H, W]."""
+    B, H, W, _ = x_nhwc.shape
+    y = conv3x3(x_nhwc, w16, bias16, out_dtype=torch.float32)
+    out = torch.empty(B, cout, H, W, device=x_nhwc.device, dtype=out_dtype)
+    check(_lib.lib().sdb_nhwc_slice_to_nchw(_ptr(y), y.shape[-1], _ptr(out), _dt(out), B, cout, H, W, _stream()),
+          "nhwc_slice_to_nchw")
+    return out
+
+
 def conv1x1_nchw_small(x: Tensor, w: Tensor, bias: Tensor) -> Tensor:
     B, Cin, H, W = x.shape
     Cout = w.shape[0]

@@ -44,3 +44,14 @@ ln("LN 160 rows=131072", 131072, 160, 30)
 ln("LN 320 rows=32768", 32768, 320, 6)
 ln("add+LN 160 rows=131072", 131072, 160, 0, res=True)
 print("sum of (ms x count):", round(tot, 3), "ms")
+# thin 4-channel ends (CUDA-core kernels, NCHW <-> NHWC)
+x = torch.randn(16, 4, 64, 64, device="cuda").to(torch.bfloat16)
+w = torch.randn(160, 4, 3, 3, device="cuda") * 0.1
+bi = torch.zeros(160, device="cuda")
+ms = timeit(lambda: ops.conv3x3_in(x, w, bi, torch.bfloat16, repeat=2))
+print(f"{'conv3x3_in 4->160 @64 (x2 virtual repeat)':44s} {ms:8.4f} {2.0*B*64*64*160/ms/1e6:8.1f}")
+y = torch.randn(B, 64, 64, 160, device="cuda").to(torch.bfloat16)
+wo = torch.randn(4, 160, 3, 3, device="cuda") * 0.05
+bo = torch.zeros(4, device="cuda")
+ms = timeit(lambda: ops.conv3x3_out(y, wo, bo, torch.float32))
+print(f"{'conv3x3_out 160->4 @64':44s} {ms:8.4f} {2.0*B*64*64*160/ms/1e6:8.1f}")
