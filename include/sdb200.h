@@ -201,6 +201,52 @@ int sdb_cast(const void* x, int src_dtype, void* out, int dst_dtype, int64_t n, 
 int sdb_to_uint8_image(const void* x_nchw, int dtype, uint8_t* out_nhwc, int B, int C, int H, int W,
                        void* stream);
 
+/* ---- train step T1 (train_unet.py:489-529): backward kernels ------------------------------------
+ * Gradients of every GEMM / convolution re-use sdb_gemm / sdb_conv3x3 (dgrad with transposed weights,
+ * wgrad over transposed operands; convolutions through sdb_im2col3x3).  `*_acc` / `*_zeroed` outputs are
+ * accumulated with atomics into caller-zeroed fp32 buffers. */
+/* out[g, c] += sum over the rows_per_group rows of group g of x[row, c]  (bias / time-embedding grads) */
+int sdb_colsum(const void* x, int dtype, int64_t ld, int64_t groups, int64_t rows_per_group, int cols,
+               float* out_zeroed, void* stream);
+/* GEGLU on pair-interleaved columns (a0,a1,g0,g1,..) kept unfused in training: transformer.py:179-192 */
+int sdb_geglu_fwd(const void* h, void* out, int64_t M, int F, void* stream);
+int sdb_geglu_bwd(const void* h, const void* dout, void* dh, int64_t M, int F, void* stream);
+int sdb_silu_bwd(const void* x, int x_dtype, const void* dy, void* dx, int g_dtype, int64_t n, void* stream);
+/* nn.GroupNorm(+SiLU) backward over the virtual concat [x1, x2]; stats = [B, groups, (mean, rstd)] from
+ * sdb_groupnorm_stats; sums_scratch = [B, groups, 2] floats */
+int sdb_groupnorm_bwd(const void* x1, int C1, const void* x2, int C2, int dtype, const float* stats,
+                      const float* gamma, const float* beta, int act, const void* dy, void* dx1, void* dx2,
+                      float* dgamma_acc, float* dbeta_acc, float* sums_scratch, int B, int64_t hw, int groups,
+                      void* stream);
+int sdb_layernorm_bwd(const void* x, const float* gamma, const void* dy, void* dx, float* dgamma_acc,
+                      float* dbeta_acc, int64_t rows, int C, float eps, int dtype, void* stream);
+/* softmax(QK^T scale)V backward (autograd of transformer.py:93-114), any n / m, d <= 32 (SDB_EUNSUPPORTED beyond):
+ * flash-style recomputation, no [n, m] tensor.  head_pitch = columns per head in q/k/v and their gradients (32 for
+ * the head-padded operands of sdb_attention_p32, d for dense ones); o / dO dense [B, n, heads*d];
+ * lse_scratch / delta_scratch: fp32 [B * heads * n] each. */
+int sdb_attention_bwd(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
+                      const void* o, int64_t ldo, const void* dO, int64_t lddo, void* dq, int64_t lddq, void* dk,
+                      int64_t lddk, void* dv, int64_t lddv, float* lse_scratch, float* delta_scratch, int B,
+                      int heads, int n, int m, int d, int head_pitch, float scale, void* stream);
+int sdb_upsample2x_bwd(const void* dy, void* dx, int dtype, int B, int H, int W, int C, void* stream);
+/* DownSample backward: dy [B,H/2,W/2,C] lands on the even pixels of out [B,H,W,C], zeros elsewhere */
+int sdb_scatter_even(const void* dy, void* out, int dtype, int B, int H, int W, int C, void* stream);
+/* [B,H,W,C] bf16 -> [B*H*W, ldc] bf16, columns (tap, c), zero padding (3x3, pad 1) and zero tail columns */
+int sdb_im2col3x3(const void* x, void* out, int B, int H, int W, int C, int ldc, void* stream);
+int sdb_nchw_to_nhwc_pad(const void* src, int src_dtype, void* dst, int dst_dtype, int B, int C, int Cp, int H,
+                         int W, void* stream);
+/* loss = mean((pred - target)^2) in fp32 (train_unet.py:517), dpred = 2 (pred - target) / n * dloss */
+int sdb_mse(const void* pred, const void* target, int dtype, int64_t n, float dloss, float* loss_zeroed,
+            void* dpred_or_null, void* stream);
+/* eps = e0 + g (e0 - e1) (latent_diffusion.py:62-65): de2 = [(1+g) d | -g d] */
+int sdb_cfg_combine_bwd(const void* d, void* de2, int dtype, int64_t half, float guidance, void* stream);
+int sdb_sumsq(const float* x, int64_t n, float* out_zeroed, void* stream);
+/* flat-bucket AdamW (torch.optim.AdamW semantics) with the gradient pre-scale (all-reduce mean) and
+ * clip_grad_norm_(max_norm) folded in; gnorm_sq = device pointer to sum of squares of the UNSCALED flat grad */
+int sdb_adamw(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
+              float eps, float weight_decay, int step, float grad_scale, const float* gnorm_sq_or_null,
+              float max_norm, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -503,3 +503,60 @@ def sample(unet_fn, tab, x: Tensor, ctx: Tensor, uncond_ctx: Tensor, guidance_sc
             nz = None if step == 0 else torch.randn(x.shape)
         x, _ = ddpm_step(tab, eps, x, step, nz, scale_factor)
     return x
+
+
+# ----------------------------------------------------------------------------
+# train step (row T1): train_unet.py:489-529 (__one_step) and :359-375
+# ----------------------------------------------------------------------------
+def train_loss(sd: StateDict, cfg: UnetCfg, x_t: Tensor, timesteps: Tensor, ctx: Tensor, uncond_ctx: Tensor,
+               noise: Tensor, guidance_scale: float = 7.5) -> Tensor:
+    """train_unet.py:524-529: F.mse_loss(pred_noise(x_t, t, ctx, guidance).float(), noise.float(), 'mean');
+    pred_noise doubles the batch for guidance > 1 exactly as in sampling (latent_diffusion.py:27-65)."""
+    fn = lambda x, t, c: unet_forward(sd, cfg, x, t, c)  # noqa: E731
+    pred = pred_noise(fn, x_t, timesteps, ctx, uncond_ctx, guidance_scale)
+    return ((pred.float() - noise.float()) ** 2).mean()
+
+
+def clip_grad_norm(grads: Sequence[Tensor], max_norm: float) -> Tensor:
+    """torch.nn.utils.clip_grad_norm_ (train_unet.py:369-371): global L2 norm over all tensors,
+    every gradient scaled in place by min(1, max_norm / (norm + 1e-6)).  Returns the pre-clip norm."""
+    total = torch.sqrt(sum((g.double() ** 2).sum() for g in grads)).float()
+    coef = torch.clamp(max_norm / (total + 1e-6), max=1.0)
+    for g in grads:
+        g.mul_(coef)
+    return total
+
+
+def adamw_update(p: Tensor, g: Tensor, m: Tensor, v: Tensor, step: int, lr: float = 4e-5, beta1: float = 0.9,
+                 beta2: float = 0.999, eps: float = 1e-8, weight_decay: float = 0.1) -> None:
+    """torch.optim.AdamW single-tensor update (train_unet.py:231-236 builds it with lr and weight_decay only,
+    trainer_args.py:71-76 defaults), in place on p, m, v; ``step`` counts from 1."""
+    p.mul_(1.0 - lr * weight_decay)
+    m.mul_(beta1).add_(g, alpha=1.0 - beta1)
+    v.mul_(beta2).addcmul_(g, g, value=1.0 - beta2)
+    bc1 = 1.0 - beta1 ** step
+    bc2 = 1.0 - beta2 ** step
+    denom = (v.sqrt() / math.sqrt(bc2)).add_(eps)
+    p.addcdiv_(m, denom, value=-lr / bc1)
+
+
+def train_steps(sd: StateDict, cfg: UnetCfg, batches, uncond_ctx: Tensor, guidance_scale: float = 7.5,
+                max_grad_norm: float = 0.1, lr: float = 4e-5, weight_decay: float = 0.1):
+    """Runs len(batches) optimiser steps on a copy of ``sd``; batches = [(x_t, t, ctx, noise), ...].
+    Returns (losses, pre-clip grad norms, per-step list of {name: grad}, final params)."""
+    params = {k: v.detach().clone().requires_grad_(True) for k, v in sd.items()}
+    ms = {k: torch.zeros_like(v) for k, v in params.items()}
+    vs = {k: torch.zeros_like(v) for k, v in params.items()}
+    losses, norms, all_grads = [], [], []
+    for i, (x_t, t, ctx, noise) in enumerate(batches, start=1):
+        loss = train_loss(params, cfg, x_t, t, ctx, uncond_ctx.expand(x_t.shape[0], -1, -1), noise, guidance_scale)
+        names = list(params)
+        grads = torch.autograd.grad(loss, [params[k] for k in names])
+        grads = [g.clone() for g in grads]
+        all_grads.append({k: g.clone() for k, g in zip(names, grads)})
+        norms.append(float(clip_grad_norm(grads, max_grad_norm)))
+        with torch.no_grad():
+            for k, g in zip(names, grads):
+                adamw_update(params[k], g, ms[k], vs[k], i, lr=lr, weight_decay=weight_decay)
+        losses.append(float(loss.detach()))
+    return losses, norms, all_grads, {k: v.detach() for k, v in params.items()}

@@ -61,6 +61,22 @@ SIGNATURES = {
     "sdb_upsample2x": (_i, [_p, _p, _i, _i, _i, _i, _i, _p]),
     "sdb_attention": (_i, [_p, _i64, _p, _i64, _p, _i64, _p, _i64, _i, _i, _i, _i, _i, _f, _i, _p]),
     "sdb_attention_p32": (_i, [_p, _i64, _p, _i64, _p, _i64, _p, _i64, _i, _i, _i, _i, _i, _f, _p]),
+    "sdb_colsum": (_i, [_p, _i, _i64, _i64, _i64, _i, _p, _p]),
+    "sdb_geglu_fwd": (_i, [_p, _p, _i64, _i, _p]),
+    "sdb_geglu_bwd": (_i, [_p, _p, _p, _i64, _i, _p]),
+    "sdb_silu_bwd": (_i, [_p, _i, _p, _p, _i, _i64, _p]),
+    "sdb_groupnorm_bwd": (_i, [_p, _i, _p, _i, _i, _p, _p, _p, _i, _p, _p, _p, _p, _p, _p, _i, _i64, _i, _p]),
+    "sdb_layernorm_bwd": (_i, [_p, _p, _p, _p, _p, _p, _i64, _i, _f, _i, _p]),
+    "sdb_attention_bwd": (_i, [_p, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _p,
+                                _i, _i, _i, _i, _i, _i, _f, _p]),
+    "sdb_upsample2x_bwd": (_i, [_p, _p, _i, _i, _i, _i, _i, _p]),
+    "sdb_scatter_even": (_i, [_p, _p, _i, _i, _i, _i, _i, _p]),
+    "sdb_im2col3x3": (_i, [_p, _p, _i, _i, _i, _i, _i, _p]),
+    "sdb_nchw_to_nhwc_pad": (_i, [_p, _i, _p, _i, _i, _i, _i, _i, _i, _p]),
+    "sdb_mse": (_i, [_p, _p, _i, _i64, _f, _p, _p, _p]),
+    "sdb_cfg_combine_bwd": (_i, [_p, _p, _i, _i64, _f, _p]),
+    "sdb_sumsq": (_i, [_p, _i64, _p, _p]),
+    "sdb_adamw": (_i, [_p, _p, _p, _p, _i64, _f, _f, _f, _f, _f, _i, _f, _p, _f, _p]),
     "sdb_silu": (_i, [_p, _p, _i64, _i, _i, _p]),
     "sdb_cast": (_i, [_p, _i, _p, _i, _i64, _p]),
     "sdb_to_uint8_image": (_i, [_p, _i, _p, _i, _i, _i, _i, _p]),

@@ -24,6 +24,8 @@ class PackCache:
         return tuple((p.data_ptr(), p._version, str(p.device), p.dtype) for p in params)
 
     def get(self, key: str, params: Sequence[Tensor], builder: Callable[[], object]):
+        if _GRAPH:          # training graph: fresh, differentiable packing every forward
+            return builder()
         sig = self._sig(params)
         hit = self._store.get(key)
         if hit is not None and hit[0] == sig:
@@ -37,23 +39,50 @@ class PackCache:
         self._store.clear()
 
 
+# Training (T1): the packing below must stay inside torch's autograd graph -- the gradient of a packed
+# operand (bf16, permuted / padded / interleaved) flows back to the fp32 parameter through torch's own
+# permute / cat / cast backward (weight-layout plumbing on 33 M parameters, not activation compute).
+# ``with graph_mode():`` switches ``d()`` from detach to identity and makes PackCache build fresh.
+_GRAPH = False
+
+
+class graph_mode:
+    def __enter__(self):
+        global _GRAPH
+        self._prev, _GRAPH = _GRAPH, True
+        return self
+
+    def __exit__(self, *exc):
+        global _GRAPH
+        _GRAPH = self._prev
+        return False
+
+
+def in_graph_mode() -> bool:
+    return _GRAPH
+
+
+def d(p: Tensor) -> Tensor:
+    return p if _GRAPH else p.detach()
+
+
 def f32(p: Tensor) -> Tensor:
-    return p.detach().to(torch.float32).contiguous()
+    return d(p).to(torch.float32).contiguous()
 
 
 def linear_w(p: Tensor) -> Tensor:
     """[out, in] -> bf16 [N, K] (already K-major)."""
-    return p.detach().to(torch.bfloat16).contiguous()
+    return d(p).to(torch.bfloat16).contiguous()
 
 
 def conv1x1_w(p: Tensor) -> Tensor:
     """[Cout, Cin, 1, 1] -> bf16 [Cout, Cin]."""
-    return p.detach().reshape(p.shape[0], p.shape[1]).to(torch.bfloat16).contiguous()
+    return d(p).reshape(p.shape[0], p.shape[1]).to(torch.bfloat16).contiguous()
 
 
 def conv3x3_w(p: Tensor) -> Tensor:
     """OIHW [Cout, Cin, 3, 3] -> bf16 [Cout, 3, 3, Cin] (tap-major, channels innermost)."""
-    return p.detach().permute(0, 2, 3, 1).to(torch.bfloat16).contiguous()
+    return d(p).permute(0, 2, 3, 1).to(torch.bfloat16).contiguous()
 
 
 def geglu_w(w: Tensor, b: Tensor) -> Tuple[Tensor, Tensor]:
@@ -63,7 +92,7 @@ def geglu_w(w: Tensor, b: Tensor) -> Tuple[Tensor, Tensor]:
     F2 = w.shape[0]
     half = F2 // 2
     assert half % 2 == 0
-    wd, bd = w.detach(), b.detach()
+    wd, bd = d(w), d(b)
     wi = torch.stack([wd[:half].reshape(half // 2, 2, -1), wd[half:].reshape(half // 2, 2, -1)], dim=1)
     bi = torch.stack([bd[:half].reshape(half // 2, 2), bd[half:].reshape(half // 2, 2)], dim=1)
     return wi.reshape(F2, w.shape[1]).to(torch.bfloat16).contiguous(), bi.reshape(F2).to(torch.float32).contiguous()
@@ -76,9 +105,8 @@ def head_pad_w(w: Tensor, heads: int, d: int) -> Tensor:
     """Projection weight [heads*d, K] -> [heads*32, K]: head h's rows move to [32h, 32h+d), the rest are
     zero, so the GEMM writes zero-padded 64-byte head rows (what the attention TMA boxes load)."""
     K = w.shape[1]
-    out = torch.zeros(heads, HEAD_PAD, K, dtype=w.dtype, device=w.device)
-    out[:, :d] = w.detach().reshape(heads, d, K)
-    return out.reshape(heads * HEAD_PAD, K)
+    pad = torch.zeros(heads, HEAD_PAD - d, K, dtype=w.dtype, device=w.device)
+    return torch.cat([globals()["d"](w).reshape(heads, d, K), pad], dim=1).reshape(heads * HEAD_PAD, K)
 
 
 def head_pad_ones_bias(heads: int, d: int, device) -> Tensor:
@@ -106,8 +134,6 @@ def head_w16(w: Tensor, b: Tensor) -> Tuple[Tensor, Tensor]:
     channels (the tensor-core conv needs Cout % 16 == 0), bias -> fp32 [16]."""
     cout = w.shape[0]
     assert cout <= 16
-    wp = torch.zeros(16, 3, 3, w.shape[1], device=w.device, dtype=torch.bfloat16)
-    wp[:cout] = conv3x3_w(w)
-    bp = torch.zeros(16, device=w.device, dtype=torch.float32)
-    bp[:cout] = b.detach().float()
+    wp = torch.cat([conv3x3_w(w), torch.zeros(16 - cout, 3, 3, w.shape[1], device=w.device, dtype=torch.bfloat16)])
+    bp = torch.cat([d(b).float(), torch.zeros(16 - cout, device=w.device, dtype=torch.float32)])
     return wp.contiguous(), bp

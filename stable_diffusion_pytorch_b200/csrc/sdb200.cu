@@ -6,5 +6,7 @@
 #include "conv_small.cu"
 #include "attention.cu"
 #include "attention_ctx.cu"
+#include "attention_bwd.cu"
 #include "attention_umma.cu"
 #include "gemm_umma.cu"
+#include "backward.cu"

@@ -95,8 +95,8 @@ class UNetModel(nn.Module):
             "b0": c.get("b0", [l0.bias], lambda: _pack.f32(l0.bias)),
             "w2": c.get("w2", [l2.weight], lambda: _pack.linear_w(l2.weight)),
             "b2": c.get("b2", [l2.bias], lambda: _pack.f32(l2.bias)),
-            "wt": c.get("wt", [w for w, _ in tw], lambda: _pack.linear_w(torch.cat([w.detach() for w, _ in tw], 0))),
-            "bt": c.get("bt", [b for _, b in tw], lambda: _pack.f32(torch.cat([b.detach() for _, b in tw], 0))),
+            "wt": c.get("wt", [w for w, _ in tw], lambda: _pack.linear_w(torch.cat([_pack.d(w) for w, _ in tw], 0))),
+            "bt": c.get("bt", [b for _, b in tw], lambda: _pack.f32(torch.cat([_pack.d(b) for _, b in tw], 0))),
             "wci": c.get("wci", [self.conv_in.weight], lambda: _pack.f32(self.conv_in.weight)),
             "bci": c.get("bci", [self.conv_in.bias], lambda: _pack.f32(self.conv_in.bias)),
             "go": c.get("go", [gn.weight], lambda: _pack.f32(gn.weight)),
@@ -128,14 +128,15 @@ class UNetModel(nn.Module):
         """All cross-attention K/V of ``ctx`` in one GEMM; reused while the same context tensor
         (same storage and version) comes back, i.e. across the steps of a sampling loop."""
         key = (ctx.data_ptr(), ctx._version, tuple(ctx.shape), ctx.dtype, id(p["wkv"]))
-        if self._ctx_cache is not None and self._ctx_cache[0] == key and not torch.cuda.is_current_stream_capturing():
+        cacheable = not (torch.cuda.is_current_stream_capturing() or _pack.in_graph_mode())
+        if cacheable and self._ctx_cache is not None and self._ctx_cache[0] == key:
             return self._ctx_cache[1]
         B, m, cd = ctx.shape
         c16 = ctx.contiguous() if ctx.dtype == torch.bfloat16 else ops.cast(ctx.contiguous(), torch.bfloat16)
         kv = ops.gemm(c16.view(B * m, cd), p["wkv"], p["bkv"]).view(B, m, -1)
         views = {sid: [(kv[:, :, o:o + dm], kv[:, :, o + dm:o + 2 * dm]) for (o, dm) in lay]
                  for sid, lay in p["kv_offsets"].items()}
-        if not torch.cuda.is_current_stream_capturing():
+        if cacheable:
             self._ctx_cache = (key, views, ctx)
         return views
 

@@ -69,7 +69,7 @@ class CrossAttention(nn.Module):
         def build_w():
             if self.use_p32:
                 return _pack.linear_w(torch.cat([_pack.head_pad_w(k, H, d), _pack.head_pad_w(v, H, d)], 0))
-            return _pack.linear_w(torch.cat([k.detach(), v.detach()], 0))
+            return _pack.linear_w(torch.cat([_pack.d(k), _pack.d(v)], 0))
 
         def build_b():
             kw = self.kv_width
@@ -84,7 +84,7 @@ class CrossAttention(nn.Module):
         c = self._cache
         q, k, v, o = self.to_q.weight, self.to_k.weight, self.to_v.weight, self.out[0]
         H, dh = self.n_heads, self.d_head
-        pad = (lambda w: _pack.head_pad_w(w, H, dh)) if self.use_p32 else (lambda w: w.detach())
+        pad = (lambda w: _pack.head_pad_w(w, H, dh)) if self.use_p32 else (lambda w: _pack.d(w))
         d = {
             "wq": c.get("wq", [q], lambda: _pack.linear_w(pad(q))),
             "wo": c.get("wo", [o.weight], lambda: _pack.linear_w(o.weight)),

@@ -8,6 +8,7 @@ from typing import Optional
 import torch
 
 from . import _lib
+from . import autograd_ops as _ag
 from ._lib import ACT_GEGLU, ACT_NONE, ACT_SILU, SDB_BF16, SDB_F32, SdbConvArgs, SdbGemmArgs, check
 
 Tensor = torch.Tensor
@@ -71,6 +72,7 @@ def sampler_advance(slot_dev: Tensor, t_table: Tensor, t_out: Tensor) -> None:
 
 
 def add_noise(x0: Tensor, noise: Tensor, t: Tensor, alphas_cumprod: Tensor) -> Tensor:
+    _ag.refuse("add_noise", x0, noise)
     B = x0.shape[0]
     out = torch.empty_like(x0)
     check(_lib.lib().sdb_add_noise(_ptr(x0.contiguous()), _ptr(noise.contiguous()), _ptr(t), _ptr(alphas_cumprod),
@@ -80,6 +82,7 @@ def add_noise(x0: Tensor, noise: Tensor, t: Tensor, alphas_cumprod: Tensor) -> T
 
 
 def nchw_to_nhwc(x: Tensor, out_dtype=None) -> Tensor:
+    _ag.refuse("nchw_to_nhwc", x)
     B, Cc, H, W = x.shape
     out = torch.empty(B, H, W, Cc, device=x.device, dtype=out_dtype or x.dtype)
     check(_lib.lib().sdb_nchw_to_nhwc(_ptr(x.contiguous()), _dt(x), _ptr(out), _dt(out), B, Cc, H, W, _stream()),
@@ -88,10 +91,20 @@ def nchw_to_nhwc(x: Tensor, out_dtype=None) -> Tensor:
 
 
 def nhwc_to_nchw(x: Tensor, out_dtype=None) -> Tensor:
+    _ag.refuse("nhwc_to_nchw", x)
     B, H, W, Cc = x.shape
     out = torch.empty(B, Cc, H, W, device=x.device, dtype=out_dtype or x.dtype)
     check(_lib.lib().sdb_nhwc_to_nchw(_ptr(x.contiguous()), _dt(x), _ptr(out), _dt(out), B, Cc, H, W, _stream()),
           "nhwc_to_nchw")
+    return out
+
+
+def transpose2d(x: Tensor, out_dtype=None) -> Tensor:
+    """[R, C] -> [C, R] (the batch-1 case of the layout kernel); feeds the weight-gradient GEMMs."""
+    R, Cc = x.shape
+    out = torch.empty(Cc, R, device=x.device, dtype=out_dtype or x.dtype)
+    check(_lib.lib().sdb_nchw_to_nhwc(_ptr(x.contiguous()), _dt(x), _ptr(out), _dt(out), 1, R, Cc, 1, _stream()),
+          "transpose2d")
     return out
 
 
@@ -119,6 +132,8 @@ def group_norm(x1: Tensor, gamma: Tensor, beta: Tensor, groups: int, act: int = 
                x2: Optional[Tensor] = None, out_dtype=None, eps: float = 1e-5,
                scratch: Optional[GroupNormScratch] = None, out: Optional[Tensor] = None) -> Tensor:
     """GroupNorm(+SiLU) of the virtual channel concat [x1, x2]; NHWC in, dense NHWC out."""
+    if _ag.wants(x1, x2, gamma, beta):
+        return _ag.group_norm(x1, gamma, beta, groups, act, x2, out_dtype, eps)
     B, H, W, C1 = x1.shape
     C2 = x2.shape[-1] if x2 is not None else 0
     assert x1.is_contiguous() and (x2 is None or (x2.is_contiguous() and x2.dtype == x1.dtype))
@@ -142,6 +157,8 @@ def group_norm(x1: Tensor, gamma: Tensor, beta: Tensor, groups: int, act: int = 
 def add_layernorm(x: Tensor, res: Optional[Tensor], gamma: Tensor, beta: Tensor, eps: float = 1e-5,
                   out: Optional[Tensor] = None) -> Tensor:
     Cc = x.shape[-1]
+    if _ag.wants(x, res, gamma, beta):
+        return _ag.add_layernorm(x, res, gamma, beta, eps)
     rows = x.numel() // Cc
     assert x.is_contiguous() and (res is None or (res.is_contiguous() and res.dtype == x.dtype))
     if out is None:
@@ -154,6 +171,8 @@ def add_layernorm(x: Tensor, res: Optional[Tensor], gamma: Tensor, beta: Tensor,
 def gemm(a: Tensor, w: Tensor, bias: Optional[Tensor] = None, residual: Optional[Tensor] = None,
          act: int = ACT_NONE, a2: Optional[Tensor] = None, out_dtype=None, out: Optional[Tensor] = None) -> Tensor:
     """out[M, N] = act(a[M, K] @ w[N, K]^T + bias) + residual; ``a``/``a2`` may be row-strided 2-D views."""
+    if _ag.wants(a, w, bias, residual, a2):
+        return _ag.gemm(a, w, bias, residual, act, a2, out_dtype)
     assert a.dim() == 2 and w.dim() == 2 and a.dtype == torch.bfloat16 and w.dtype == torch.bfloat16
     assert a.stride(1) == 1 and w.is_contiguous()
     M, K1 = a.shape
@@ -188,6 +207,8 @@ def conv3x3(x: Tensor, w: Tensor, bias: Optional[Tensor], temb: Optional[Tensor]
             residual: Optional[Tensor] = None, down2: bool = False, out_dtype=None,
             out: Optional[Tensor] = None) -> Tensor:
     """3x3 / pad 1 convolution, NHWC bf16 ``x`` [B,H,W,Cin], ``w`` bf16 [Cout,3,3,Cin]."""
+    if _ag.wants(x, w, bias, temb, residual):
+        return _ag.conv3x3(x, w, bias, temb, residual, down2, out_dtype)
     B, H, W, Cin = x.shape
     Cout = w.shape[0]
     assert x.is_contiguous() and w.is_contiguous() and x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16
@@ -216,6 +237,9 @@ def conv3x3(x: Tensor, w: Tensor, bias: Optional[Tensor], temb: Optional[Tensor]
 
 def conv3x3_in(x_nchw: Tensor, w: Tensor, bias: Tensor, out_dtype=torch.bfloat16, repeat: int = 1) -> Tensor:
     """``repeat`` > 1: output batch = repeat * input batch, image b reads input b % B_in (virtual cat)."""
+    _ag.refuse("conv3x3_in (gradient w.r.t. the latent)", x_nchw)
+    if _ag.wants(w, bias):
+        return _ag.conv3x3_in(x_nchw, w, bias, out_dtype, repeat)
     Bs, Cin, H, W = x_nchw.shape
     B = Bs * repeat
     Cout = w.shape[0]
@@ -228,6 +252,8 @@ def conv3x3_in(x_nchw: Tensor, w: Tensor, bias: Tensor, out_dtype=torch.bfloat16
 
 def cfg_combine(eps2: Tensor, guidance: float) -> Tensor:
     """first + g * (first - second) over the two batch halves (latent_diffusion.py:62-65)."""
+    if _ag.wants(eps2):
+        return _ag.cfg_combine(eps2, guidance)
     assert eps2.is_contiguous() and eps2.shape[0] % 2 == 0
     out = torch.empty((eps2.shape[0] // 2, *eps2.shape[1:]), device=eps2.device, dtype=eps2.dtype)
     check(_lib.lib().sdb_cfg_combine(_ptr(eps2), guidance, _ptr(out), out.numel(), _dt(eps2), _stream()),
@@ -236,6 +262,7 @@ def cfg_combine(eps2: Tensor, guidance: float) -> Tensor:
 
 
 def conv3x3_out(x_nhwc: Tensor, w: Tensor, bias: Tensor, out_dtype=torch.float32) -> Tensor:
+    _ag.refuse("conv3x3_out", x_nhwc, w, bias)
     B, H, W, Cin = x_nhwc.shape
     Cout = w.shape[0]
     assert w.dtype == torch.float32 and w.is_contiguous() and x_nhwc.is_contiguous()
@@ -248,6 +275,8 @@ def conv3x3_out(x_nhwc: Tensor, w: Tensor, bias: Tensor, out_dtype=torch.float32
 def conv3x3_head(x_nhwc: Tensor, w16: Tensor, bias16: Tensor, cout: int, out_dtype=torch.float32) -> Tensor:
     """Output head on the tensor cores: 3x3 conv with Cout padded to 16 (``_pack.head_w16``), fp32 channels-last
     result, then the padding is dropped and the layout restored to NCHW [B, cout, H, W]."""
+    if _ag.wants(x_nhwc, w16, bias16):
+        return _ag.conv3x3_head(x_nhwc, w16, bias16, cout, out_dtype)
     B, H, W, _ = x_nhwc.shape
     y = conv3x3(x_nhwc, w16, bias16, out_dtype=torch.float32)
     out = torch.empty(B, cout, H, W, device=x_nhwc.device, dtype=out_dtype)
@@ -257,6 +286,7 @@ def conv3x3_head(x_nhwc: Tensor, w16: Tensor, bias16: Tensor, cout: int, out_dty
 
 
 def conv1x1_nchw_small(x: Tensor, w: Tensor, bias: Tensor) -> Tensor:
+    _ag.refuse("conv1x1_nchw_small", x, w, bias)
     B, Cin, H, W = x.shape
     Cout = w.shape[0]
     out = torch.empty(B, Cout, H, W, device=x.device, dtype=x.dtype)
@@ -266,6 +296,8 @@ def conv1x1_nchw_small(x: Tensor, w: Tensor, bias: Tensor) -> Tensor:
 
 
 def upsample2x(x: Tensor) -> Tensor:
+    if _ag.wants(x):
+        return _ag.upsample2x(x)
     B, H, W, Cc = x.shape
     assert x.is_contiguous()
     out = torch.empty(B, 2 * H, 2 * W, Cc, device=x.device, dtype=x.dtype)
@@ -276,6 +308,8 @@ def upsample2x(x: Tensor) -> Tensor:
 def attention(q: Tensor, k: Tensor, v: Tensor, heads: int, d: int, scale: float,
               out: Optional[Tensor] = None) -> Tensor:
     """q [B, n, >=heads*d] (last-dim stride 1, row-strided views allowed), k/v [B, m, ...]."""
+    if _ag.wants(q, k, v):
+        return _ag.attention(q, k, v, heads, d, scale)
     B, n = q.shape[0], q.shape[1]
     m = k.shape[1]
     for t in (q, k, v):
@@ -291,6 +325,8 @@ def attention_p32(q: Tensor, k: Tensor, v: Tensor, heads: int, d: int, scale: fl
                   out: Optional[Tensor] = None) -> Tensor:
     """tcgen05 attention over head-padded operands: q [B, n, >=heads*32], k/v [B, m, >=heads*32] (row-strided
     views allowed); head h at columns [32h, 32h+32), q/k zero beyond d, v[..., 32h+d] == 1."""
+    if _ag.wants(q, k, v):
+        return _ag.attention_p32(q, k, v, heads, d, scale)
     B, n = q.shape[0], q.shape[1]
     m = k.shape[1]
     for t in (q, k, v):
@@ -303,18 +339,23 @@ def attention_p32(q: Tensor, k: Tensor, v: Tensor, heads: int, d: int, scale: fl
 
 
 def silu(x: Tensor, out_dtype=None) -> Tensor:
+    if _ag.wants(x):
+        return _ag.silu(x, out_dtype)
     out = torch.empty(x.shape, device=x.device, dtype=out_dtype or x.dtype)
     check(_lib.lib().sdb_silu(_ptr(x.contiguous()), _ptr(out), x.numel(), _dt(x), _dt(out), _stream()), "silu")
     return out
 
 
 def cast(x: Tensor, dtype) -> Tensor:
+    if _ag.wants(x):
+        return _ag.cast(x, dtype)
     out = torch.empty(x.shape, device=x.device, dtype=dtype)
     check(_lib.lib().sdb_cast(_ptr(x.contiguous()), _dt(x), _ptr(out), _dt(out), x.numel(), _stream()), "cast")
     return out
 
 
 def to_uint8_image(x_nchw: Tensor) -> Tensor:
+    _ag.refuse("to_uint8_image", x_nchw)
     B, Cc, H, W = x_nchw.shape
     out = torch.empty(B, H, W, Cc, device=x_nchw.device, dtype=torch.uint8)
     check(_lib.lib().sdb_to_uint8_image(_ptr(x_nchw.contiguous()), _dt(x_nchw), _ptr(out), B, Cc, H, W, _stream()),
@@ -328,3 +369,16 @@ def debug_timeout_flag() -> int:
 
 def launch_count() -> int:
     return _lib.lib().sdb_launch_count()
+
+
+def mse_loss(pred: Tensor, target: Tensor) -> Tensor:
+    """Mean squared error in fp32 (train_unet.py:517); the gradient is produced by the same kernel."""
+    return _ag.mse_loss(pred, target)
+
+
+def sumsq(x: Tensor, out: Optional[Tensor] = None) -> Tensor:
+    """Adds sum(x^2) of a flat fp32 buffer into ``out`` (zeroed if not given): the grad-norm of the clip."""
+    if out is None:
+        out = torch.zeros(1, device=x.device, dtype=torch.float32)
+    check(_lib.lib().sdb_sumsq(_ptr(x), x.numel(), _ptr(out), _stream()), "sumsq")
+    return out

@@ -17,3 +17,10 @@ def golden():
     import numpy as np
     path = os.path.join(ROOT, "tests", "golden", "reference_outputs.npz")
     return dict(np.load(path))
+
+
+@pytest.fixture(scope="session")
+def golden_train():
+    import numpy as np
+    path = os.path.join(ROOT, "tests", "golden", "reference_train.npz")
+    return dict(np.load(path))

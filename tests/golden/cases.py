@@ -80,3 +80,30 @@ VAE_CASES = {
 
 def vae_inputs(cfg, B, H, W, seed):
     return torch.randn(B, cfg.latent_channels, H, W, generator=_g(3000 + seed))
+
+
+# ---- train step (row T1) -------------------------------------------------------------------------
+# name -> (cfg, seed, B, H, W, n_steps, guidance); lr raised so two steps move the weights measurably
+TRAIN_CASES = {
+    "tiny_8": (TINY, 11, 4, 8, 8, 2, 7.5),
+    "tiny3_16_nocfg": (TINY3, 12, 2, 16, 16, 2, 1.0),   # heads 16 and 32 wide (dense-head attention backward)
+}
+TRAIN_LR = 1e-3
+TRAIN_WD = 0.1
+TRAIN_CLIP = 0.1
+# parameters whose full gradient / updated value is stored (the rest is covered by per-tensor norms)
+TRAIN_PROBE = ["out.2.bias", "time_embedding.0.bias", "conv_in.weight", "out.0.weight"]
+
+
+def train_batches(cfg, B, H, W, seed, n_steps, ctx_len=77):
+    """[(x_t, t, ctx, noise)] * n_steps and the empty-prompt embedding [1, L, D]."""
+    g = _g(5000 + seed)
+    uncond = torch.randn(1, ctx_len, cfg.context_dim, generator=g)
+    out = []
+    for _ in range(n_steps):
+        x_t = torch.randn(B, cfg.latent_channels, H, W, generator=g)
+        t = torch.randint(0, 1000, (B,), generator=g, dtype=torch.long)
+        ctx = torch.randn(B, ctx_len, cfg.context_dim, generator=g)
+        noise = torch.randn(B, cfg.latent_channels, H, W, generator=g)
+        out.append((x_t, t, ctx, noise))
+    return out, uncond

@@ -128,5 +128,48 @@ def main():
     print("wrote", path, os.path.getsize(path), "bytes,", len(out), "arrays")
 
 
+def main_train():
+    """Row T1: the reference's own modules, F.mse_loss, clip_grad_norm_ and torch.optim.AdamW
+    (train_unet.py:489-529, :359-375, :231-236) on seeded batches -> ``reference_train.npz``."""
+    import torch.nn.functional as F
+    torch.set_num_threads(8)
+    out = {}
+    sch = DDPMScheduler(DDPMConfig())
+    for name, (ucfg, seed, B, H, W, n_steps, g) in cases.TRAIN_CASES.items():
+        m = ref_unet(ucfg, seed).train()
+        batches, uncond = cases.train_batches(ucfg, B, H, W, seed, n_steps)
+        ld = LatentDiffusion(m, None, StubTextEncoder(uncond), sch)
+        opt = torch.optim.AdamW(m.parameters(), lr=cases.TRAIN_LR, weight_decay=cases.TRAIN_WD)
+        names = [k for k, _ in m.named_parameters()]
+        losses, norms = [], []
+        for i, (x_t, t, ctx, noise) in enumerate(batches):
+            pred = ld.pred_noise(x_t, t, ctx, guidance_scale=g)
+            loss = F.mse_loss(pred.float(), noise.float(), reduction="mean")
+            loss.backward()
+            if i == 0:
+                out[f"train_{name}_gradnorms"] = np.array([float(p.grad.norm()) for p in m.parameters()], np.float32)
+                for k in cases.TRAIN_PROBE:
+                    out[f"train_{name}_grad_{k}"] = dict(m.named_parameters())[k].grad.numpy().copy()
+            norms.append(float(torch.nn.utils.clip_grad_norm_(m.parameters(), cases.TRAIN_CLIP)))
+            opt.step()
+            opt.zero_grad()
+            losses.append(float(loss))
+        out[f"train_{name}_loss"] = np.array(losses, np.float32)
+        out[f"train_{name}_gnorm"] = np.array(norms, np.float32)
+        sd0 = O.seeded_state_dict(O.unet_param_shapes(ucfg), seed)
+        pd = dict(m.named_parameters())
+        out[f"train_{name}_deltanorms"] = np.array([float((pd[k].detach() - sd0[k]).norm()) for k in names], np.float32)
+        for k in cases.TRAIN_PROBE:
+            out[f"train_{name}_param_{k}"] = pd[k].detach().numpy().copy()
+        out[f"train_{name}_names"] = np.array(names)
+        print("train", name, losses, norms)
+    path = os.path.join(HERE, "reference_train.npz")
+    np.savez_compressed(path, **out)
+    print("wrote", path, os.path.getsize(path), "bytes,", len(out), "arrays")
+
+
 if __name__ == "__main__":
-    main()
+    if len(sys.argv) > 1 and sys.argv[1] == "train":
+        main_train()
+    else:
+        main()

@@ -91,3 +91,27 @@ def test_cfg_combine_is_mislabelled_like_reference():
     e_unc, e_cond = torch.full((1, 1), 1.0), torch.full((1, 1), 3.0)
     out = O.cfg_combine(torch.cat([e_unc, e_cond]), 2.0)
     assert out.item() == 1.0 + 2.0 * (1.0 - 3.0)
+
+
+@pytest.mark.parametrize("name", list(cases.TRAIN_CASES))
+def test_train_steps_vs_reference(golden_train, name):
+    """Row T1: oracle loss / autograd gradients / clip / AdamW restatement vs the reference's modules run with
+    F.mse_loss, clip_grad_norm_ and torch.optim.AdamW (make_golden.py train)."""
+    cfg, seed, B, H, W, n_steps, g = cases.TRAIN_CASES[name]
+    sd = O.seeded_state_dict(O.unet_param_shapes(cfg), seed)
+    batches, uncond = cases.train_batches(cfg, B, H, W, seed, n_steps)
+    torch.set_num_threads(8)
+    losses, norms, grads, params = O.train_steps(sd, cfg, batches, uncond, g, cases.TRAIN_CLIP, cases.TRAIN_LR,
+                                                 cases.TRAIN_WD)
+    G = golden_train
+    np.testing.assert_allclose(losses, G[f"train_{name}_loss"], rtol=2e-5)
+    np.testing.assert_allclose(norms, G[f"train_{name}_gnorm"], rtol=2e-4)
+    names = [str(k) for k in G[f"train_{name}_names"]]
+    assert sorted(names) == sorted(sd)                         # same parameter set as the reference's module tree
+    gn = np.array([float(grads[0][k].norm()) for k in names])
+    np.testing.assert_allclose(gn, G[f"train_{name}_gradnorms"], rtol=2e-3, atol=1e-6)
+    dn = np.array([float((params[k] - sd[k]).norm()) for k in names])
+    np.testing.assert_allclose(dn, G[f"train_{name}_deltanorms"], rtol=2e-3, atol=1e-7)
+    for k in cases.TRAIN_PROBE:
+        assert rel_l2(grads[0][k], G[f"train_{name}_grad_{k}"]) < 1e-4, k
+        assert rel_l2(params[k], G[f"train_{name}_param_{k}"]) < 1e-6, k
