@@ -155,6 +155,13 @@ typedef struct SdbConvArgs {
 } SdbConvArgs;
 int sdb_conv3x3(const SdbConvArgs* args, void* stream);
 
+/* fp32 parity mode of K3 / K1 (north_star: one UNet forward within 1e-3 relative L2 in fp32; the reference
+ * run with `--dtype float32`, scripts/txt2img.py:23): same argument structs, but a / a2 / w (x / w) are fp32 and
+ * the products are fp32 FMAs on the CUDA cores; residual / out dtypes as given.  No alignment or shape limits
+ * beyond GEGLU's N % 4 == 0; up2 is honoured.  sdb_attention(dtype = SDB_F32) is the matching attention. */
+int sdb_gemm_f32(const SdbGemmArgs* args, void* stream);
+int sdb_conv3x3_f32(const SdbConvArgs* args, void* stream);
+
 /* small-channel 3x3 convs on CUDA cores (HBM-bound): conv_in (models/utils.py:31-32, Cin = latent
  * channels; reads NCHW `src_dtype`, writes NHWC; the input holds src_B images and output image b reads
  * input image b %% src_B, which is the `torch.cat([x] * 2)` of latent_diffusion.py:53 for free) and the output head conv (models/utils.py:197,
@@ -178,7 +185,8 @@ int sdb_upsample2x(const void* x, void* out, int dtype, int B, int H, int W, int
  * modules/transformer.py:93-114: softmax(Q K^T * scale) V per (batch, head) without
  * materialising `sim`.  q [B, n, *] with head h at columns [h*d, (h+1)*d) and row stride ldq
  * elements (so a fused QKV GEMM output can be passed as three offset pointers); k, v [B, m, *].
- * out [B, n, heads*d] row stride ldo.  bf16 in/out, fp32 softmax state.  d <= 128, d % 4 == 0. */
+ * out [B, n, heads*d] row stride ldo.  bf16 in/out, fp32 softmax state.  d <= 128, d % 4 == 0.
+ * dtype = SDB_F32: fp32 in/out on the CUDA cores (parity mode), any d <= 128, no alignment rules. */
 int sdb_attention(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
                   int64_t ldv, void* out, int64_t ldo, int B, int heads, int n, int m, int d,
                   float scale, int dtype, void* stream);

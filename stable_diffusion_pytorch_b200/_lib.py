@@ -53,6 +53,8 @@ SIGNATURES = {
     "sdb_add_layernorm": (_i, [_p, _p, _p, _p, _p, _i64, _i, _f, _i, _p]),
     "sdb_gemm": (_i, [C.POINTER(SdbGemmArgs), _p]),
     "sdb_conv3x3": (_i, [C.POINTER(SdbConvArgs), _p]),
+    "sdb_gemm_f32": (_i, [C.POINTER(SdbGemmArgs), _p]),
+    "sdb_conv3x3_f32": (_i, [C.POINTER(SdbConvArgs), _p]),
     "sdb_conv3x3_in": (_i, [_p, _i, _p, _p, _p, _i, _i, _i, _i, _i, _i, _i, _p]),
     "sdb_cfg_combine": (_i, [_p, _f, _p, _i64, _i, _p]),
     "sdb_conv3x3_out": (_i, [_p, _i, _p, _p, _p, _i, _i, _i, _i, _i, _i, _p]),

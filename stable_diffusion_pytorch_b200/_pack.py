@@ -21,7 +21,7 @@ class PackCache:
 
     @staticmethod
     def _sig(params: Sequence[Tensor]) -> tuple:
-        return tuple((p.data_ptr(), p._version, str(p.device), p.dtype) for p in params)
+        return (_COMPUTE,) + tuple((p.data_ptr(), p._version, str(p.device), p.dtype) for p in params)
 
     def get(self, key: str, params: Sequence[Tensor], builder: Callable[[], object]):
         if _GRAPH:          # training graph: fresh, differentiable packing every forward
@@ -62,6 +62,43 @@ def in_graph_mode() -> bool:
     return _GRAPH
 
 
+# Compute precision of the hot path.  bf16 (default) = the tcgen05 tensor-core kernels, what bench.py measures.
+# fp32 = the parity mode north_star asks for ("a single UNet forward within 1e-3 relative L2 in fp32"; the
+# reference run with `--dtype float32`, scripts/txt2img.py:23): activations and packed weights stay fp32 and
+# GEMM / conv / attention run as fp32 FMAs on the CUDA cores (csrc/precise_f32.cu).  Inference only.
+_COMPUTE = torch.bfloat16
+
+
+def compute_dtype() -> torch.dtype:
+    return _COMPUTE
+
+
+def set_precision(dtype) -> torch.dtype:
+    """``"bf16"`` / ``torch.bfloat16`` or ``"fp32"`` / ``torch.float32``; returns the previous setting."""
+    global _COMPUTE
+    table = {"bf16": torch.bfloat16, "bfloat16": torch.bfloat16, "fp32": torch.float32, "float32": torch.float32,
+             torch.bfloat16: torch.bfloat16, torch.float32: torch.float32}
+    if dtype not in table:
+        raise ValueError(f"precision must be bf16 or fp32, got {dtype!r}")
+    prev, _COMPUTE = _COMPUTE, table[dtype]
+    return prev
+
+
+class precision:
+    """``with precision("fp32"): unet(x, t, ctx)`` -- scoped ``set_precision``."""
+
+    def __init__(self, dtype):
+        self._dtype = dtype
+
+    def __enter__(self):
+        self._prev = set_precision(self._dtype)
+        return self
+
+    def __exit__(self, *exc):
+        set_precision(self._prev)
+        return False
+
+
 def d(p: Tensor) -> Tensor:
     return p if _GRAPH else p.detach()
 
@@ -72,17 +109,17 @@ def f32(p: Tensor) -> Tensor:
 
 def linear_w(p: Tensor) -> Tensor:
     """[out, in] -> bf16 [N, K] (already K-major)."""
-    return d(p).to(torch.bfloat16).contiguous()
+    return d(p).to(_COMPUTE).contiguous()
 
 
 def conv1x1_w(p: Tensor) -> Tensor:
     """[Cout, Cin, 1, 1] -> bf16 [Cout, Cin]."""
-    return d(p).reshape(p.shape[0], p.shape[1]).to(torch.bfloat16).contiguous()
+    return d(p).reshape(p.shape[0], p.shape[1]).to(_COMPUTE).contiguous()
 
 
 def conv3x3_w(p: Tensor) -> Tensor:
     """OIHW [Cout, Cin, 3, 3] -> bf16 [Cout, 3, 3, Cin] (tap-major, channels innermost)."""
-    return d(p).permute(0, 2, 3, 1).to(torch.bfloat16).contiguous()
+    return d(p).permute(0, 2, 3, 1).to(_COMPUTE).contiguous()
 
 
 def geglu_w(w: Tensor, b: Tensor) -> Tuple[Tensor, Tensor]:
@@ -95,7 +132,7 @@ def geglu_w(w: Tensor, b: Tensor) -> Tuple[Tensor, Tensor]:
     wd, bd = d(w), d(b)
     wi = torch.stack([wd[:half].reshape(half // 2, 2, -1), wd[half:].reshape(half // 2, 2, -1)], dim=1)
     bi = torch.stack([bd[:half].reshape(half // 2, 2), bd[half:].reshape(half // 2, 2)], dim=1)
-    return wi.reshape(F2, w.shape[1]).to(torch.bfloat16).contiguous(), bi.reshape(F2).to(torch.float32).contiguous()
+    return wi.reshape(F2, w.shape[1]).to(_COMPUTE).contiguous(), bi.reshape(F2).to(torch.float32).contiguous()
 
 
 HEAD_PAD = 32  # padded head width of the tcgen05 attention operands (sdb_attention_p32)
@@ -134,6 +171,6 @@ def head_w16(w: Tensor, b: Tensor) -> Tuple[Tensor, Tensor]:
     channels (the tensor-core conv needs Cout % 16 == 0), bias -> fp32 [16]."""
     cout = w.shape[0]
     assert cout <= 16
-    wp = torch.cat([conv3x3_w(w), torch.zeros(16 - cout, 3, 3, w.shape[1], device=w.device, dtype=torch.bfloat16)])
+    wp = torch.cat([conv3x3_w(w), torch.zeros(16 - cout, 3, 3, w.shape[1], device=w.device, dtype=_COMPUTE)])
     bp = torch.cat([d(b).float(), torch.zeros(16 - cout, device=w.device, dtype=torch.float32)])
     return wp.contiguous(), bp

@@ -1,0 +1,286 @@
+// fp32 parity mode of the hot path (north_star: "a single UNet forward within 1e-3 relative L2 in fp32").
+//
+// The product path computes in bf16 on the tensor cores; one bf16 rounding of an activation is already
+// 2^-9 = 2e-3 relative, so the 1e-3 bound needs fp32 activations AND fp32 products.  These kernels are
+// that mode: the same operators with the same epilogues (bias, time embedding, residual, SiLU, GEGLU on
+// pair-interleaved rows, stride-2 / nearest-x2 sampling), fp32 operands, fp32 FMA on the CUDA cores.
+// They reproduce the reference's fp32 module dtype (scripts/txt2img.py:23 `--dtype float32`), not its speed:
+// this is the verification mode, the bf16 tcgen05 kernels are what bench.py measures.
+//
+//   sdb_gemm_f32      nn.Linear / 1x1 conv  (transformer.py:55-58,151,176,330,347; resnet2d.py:182,202)
+//   sdb_conv3x3_f32   nn.Conv2d 3x3 pad 1   (resnet2d.py:41,103,174,195), implicit GEMM, k = tap*Cin + c
+//   attention_f32     softmax(QK^T s)V      (transformer.py:93-114), one query per thread, 32-key tiles
+#include "common.cuh"
+
+namespace sdb {
+
+struct F32Params {
+  const float* a;  long long lda;  int K1;
+  const float* a2; long long lda2; int K2;
+  const float* w;                       // [N][K] row-major (K-major)
+  const float* bias;                    // [N] or null
+  const float* temb; long long ld_temb; // [B][ld_temb] or null, row b = m / rows_per_image
+  int rows_per_image;
+  const void* res; long long ldr; int res_dtype;
+  void* out; long long ldo; int out_dtype;
+  int M, N, K, act;
+  // conv mode (conv != 0): a = x NHWC [B,H,W,Cin], M = B*Ho*Wo, K = 9*Cin
+  int conv, H, W, Cin, Ho, Wo, stride, up2;
+};
+
+constexpr int kBM = 64, kBN = 64, kBK = 16;
+
+__device__ __forceinline__ float gelu_erf_f32(float g) { return 0.5f * g * (1.f + erff(g * 0.70710678118654752440f)); }
+__device__ __forceinline__ float silu_f32(float x) { return x / (1.f + expf(-x)); }
+
+__global__ void __launch_bounds__(256) gemm_f32_kernel(const F32Params p) {
+  __shared__ float As[kBK][kBM + 4];
+  __shared__ float Ws[kBK][kBN + 4];
+  const int tid = threadIdx.x;
+  const int m0 = blockIdx.x * kBM, n0 = blockIdx.y * kBN;
+  const int ty = tid >> 4, tx = tid & 15;
+  // loader coordinates: row r of the tile, four consecutive k
+  const int lr = tid >> 2, lk = (tid & 3) * 4;
+  const int am = m0 + lr, wn = n0 + lr;
+  // conv: decompose the output pixel once
+  int cb = 0, coh = 0, cow = 0;
+  if (p.conv && am < p.M) {
+    cb = am / (p.Ho * p.Wo);
+    const int r = am - cb * p.Ho * p.Wo;
+    coh = r / p.Wo;
+    cow = r - coh * p.Wo;
+  }
+  float acc[4][4];
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
+
+  for (int k0 = 0; k0 < p.K; k0 += kBK) {
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const int k = k0 + lk + e;
+      float av = 0.f, wv = 0.f;
+      if (k < p.K) {
+        if (am < p.M) {
+          if (!p.conv) {
+            av = k < p.K1 ? p.a[(long long)am * p.lda + k] : p.a2[(long long)am * p.lda2 + (k - p.K1)];
+          } else {
+            const int tap = k / p.Cin, c = k - tap * p.Cin;
+            const int dy = tap / 3, dx = tap - dy * 3;
+            int ih = coh * p.stride + dy - 1, iw = cow * p.stride + dx - 1;
+            const int Hs = p.up2 ? 2 * p.H : p.H, Wsrc = p.up2 ? 2 * p.W : p.W;
+            if (ih >= 0 && ih < Hs && iw >= 0 && iw < Wsrc) {
+              if (p.up2) { ih >>= 1; iw >>= 1; }
+              av = p.a[(((long long)cb * p.H + ih) * p.W + iw) * p.Cin + c];
+            }
+          }
+        }
+        if (wn < p.N) wv = p.w[(long long)wn * p.K + k];
+      }
+      As[lk + e][lr] = av;
+      Ws[lk + e][lr] = wv;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int kk = 0; kk < kBK; ++kk) {
+      const float4 a4 = *reinterpret_cast<const float4*>(&As[kk][ty * 4]);
+      const float4 w4 = *reinterpret_cast<const float4*>(&Ws[kk][tx * 4]);
+      const float av[4] = {a4.x, a4.y, a4.z, a4.w};
+      const float wv[4] = {w4.x, w4.y, w4.z, w4.w};
+#pragma unroll
+      for (int i = 0; i < 4; ++i)
+#pragma unroll
+        for (int j = 0; j < 4; ++j) acc[i][j] = fmaf(av[i], wv[j], acc[i][j]);
+    }
+    __syncthreads();
+  }
+
+  // epilogue
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int m = m0 + ty * 4 + i;
+    if (m >= p.M) continue;
+    const float* trow = p.temb ? p.temb + (long long)(m / p.rows_per_image) * p.ld_temb : nullptr;
+    float v[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int n = n0 + tx * 4 + j;
+      float x = acc[i][j];
+      if (n < p.N) {
+        if (p.bias) x += p.bias[n];
+        if (trow) x += trow[n];
+      }
+      v[j] = x;
+    }
+    if (p.act == SDB_ACT_GEGLU) {
+      // columns (a0, a1, g0, g1) -> two outputs at (n0 + 4 tx) / 2
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const int n = n0 + tx * 4 + j;
+        if (n + 2 >= p.N) continue;   // N % 4 == 0: a tile column group is all in or all out
+        const int no = (n0 + tx * 4) / 2 + j;
+        float y = v[j] * gelu_erf_f32(v[j + 2]);
+        if (p.res) {
+          y += p.res_dtype == SDB_F32 ? ((const float*)p.res)[(long long)m * p.ldr + no]
+                                      : __bfloat162float(((const __nv_bfloat16*)p.res)[(long long)m * p.ldr + no]);
+        }
+        if (p.out_dtype == SDB_F32) ((float*)p.out)[(long long)m * p.ldo + no] = y;
+        else ((__nv_bfloat16*)p.out)[(long long)m * p.ldo + no] = __float2bfloat16(y);
+      }
+      continue;
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const int n = n0 + tx * 4 + j;
+      if (n >= p.N) continue;
+      float y = v[j];
+      if (p.act == SDB_ACT_SILU) y = silu_f32(y);
+      if (p.res) {
+        y += p.res_dtype == SDB_F32 ? ((const float*)p.res)[(long long)m * p.ldr + n]
+                                    : __bfloat162float(((const __nv_bfloat16*)p.res)[(long long)m * p.ldr + n]);
+      }
+      if (p.out_dtype == SDB_F32) ((float*)p.out)[(long long)m * p.ldo + n] = y;
+      else ((__nv_bfloat16*)p.out)[(long long)m * p.ldo + n] = __float2bfloat16(y);
+    }
+  }
+}
+
+static int launch_f32(const F32Params& p, cudaStream_t st) {
+  dim3 grid((p.M + kBM - 1) / kBM, (p.N + kBN - 1) / kBN);   // M on x: no 65535 limit
+  gemm_f32_kernel<<<grid, 256, 0, st>>>(p);
+  SDB_LAUNCH_OK();
+  return SDB_OK;
+}
+
+// ---- attention ------------------------------------------------------------------------------------
+// One query row per thread (q and the output accumulator in registers), keys / values of the (batch, head)
+// staged 32 at a time in shared memory and read as broadcasts; running max / sum in fp32 with expf.
+template <int D>
+__global__ void __launch_bounds__(128) attention_f32_kernel(const float* __restrict__ q, long long ldq,
+                                                            const float* __restrict__ k, long long ldk,
+                                                            const float* __restrict__ v, long long ldv,
+                                                            float* __restrict__ out, long long ldo, int heads,
+                                                            int n, int m, int d, float scale) {
+  constexpr int KT = 32;
+  __shared__ __align__(16) float Ks[KT][D];
+  __shared__ __align__(16) float Vs[KT][D];
+  const int b = blockIdx.z, h = blockIdx.y;
+  const int row = blockIdx.x * 128 + threadIdx.x;
+  const bool live = row < n;
+  float qr[D], o[D];
+#pragma unroll
+  for (int c = 0; c < D; ++c) {
+    qr[c] = (live && c < d) ? q[((long long)b * n + row) * ldq + h * d + c] * scale : 0.f;
+    o[c] = 0.f;
+  }
+  float mx = -INFINITY, l = 0.f;
+  for (int j0 = 0; j0 < m; j0 += KT) {
+    __syncthreads();
+    for (int e = threadIdx.x; e < KT * D; e += 128) {
+      const int j = e / D, c = e - j * D;
+      float kv = 0.f, vv = 0.f;
+      if (j0 + j < m && c < d) {
+        kv = k[((long long)b * m + j0 + j) * ldk + h * d + c];
+        vv = v[((long long)b * m + j0 + j) * ldv + h * d + c];
+      }
+      Ks[j][c] = kv;
+      Vs[j][c] = vv;
+    }
+    __syncthreads();
+    float s[KT];
+    float tmax = mx;
+#pragma unroll
+    for (int j = 0; j < KT; ++j) {
+      float acc = 0.f;
+#pragma unroll
+      for (int c = 0; c < D; c += 4) {
+        const float4 k4 = *reinterpret_cast<const float4*>(&Ks[j][c]);
+        acc = fmaf(qr[c], k4.x, acc);
+        acc = fmaf(qr[c + 1], k4.y, acc);
+        acc = fmaf(qr[c + 2], k4.z, acc);
+        acc = fmaf(qr[c + 3], k4.w, acc);
+      }
+      s[j] = (j0 + j < m) ? acc : -INFINITY;
+      tmax = fmaxf(tmax, s[j]);
+    }
+    const float corr = expf(mx - tmax);   // mx = -inf on the first tile -> 0
+    mx = tmax;
+    l *= corr;
+#pragma unroll
+    for (int c = 0; c < D; ++c) o[c] *= corr;
+#pragma unroll
+    for (int j = 0; j < KT; ++j) {
+      const float pj = expf(s[j] - mx);
+      l += pj;
+#pragma unroll
+      for (int c = 0; c < D; c += 4) {
+        const float4 v4 = *reinterpret_cast<const float4*>(&Vs[j][c]);
+        o[c] = fmaf(pj, v4.x, o[c]);
+        o[c + 1] = fmaf(pj, v4.y, o[c + 1]);
+        o[c + 2] = fmaf(pj, v4.z, o[c + 2]);
+        o[c + 3] = fmaf(pj, v4.w, o[c + 3]);
+      }
+    }
+  }
+  if (live) {
+    const float inv = 1.f / l;
+#pragma unroll
+    for (int c = 0; c < D; ++c)
+      if (c < d) out[((long long)b * n + row) * ldo + h * d + c] = o[c] * inv;
+  }
+}
+
+static int attention_f32(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
+                         void* out, int64_t ldo, int B, int heads, int n, int m, int d, float scale,
+                         cudaStream_t st) {
+  SDB_CHECK_ARG(d >= 1 && d <= 128, "attention (fp32): d (%d) must be <= 128", d);
+  dim3 grid((n + 127) / 128, heads, B);
+#define SDB_AF32(DD)                                                                                           \
+  attention_f32_kernel<DD><<<grid, 128, 0, st>>>((const float*)q, ldq, (const float*)k, ldk, (const float*)v, \
+                                                 ldv, (float*)out, ldo, heads, n, m, d, scale)
+  if (d <= 32) SDB_AF32(32);
+  else if (d <= 64) SDB_AF32(64);
+  else SDB_AF32(128);
+#undef SDB_AF32
+  SDB_LAUNCH_OK();
+  return SDB_OK;
+}
+
+}  // namespace sdb
+
+extern "C" int sdb_gemm_f32(const SdbGemmArgs* a, void* stream) {
+  using namespace sdb;
+  SDB_CHECK_ARG(a && a->a && a->w && a->out && a->M > 0 && a->N > 0 && a->K1 > 0, "gemm_f32: bad args");
+  SDB_CHECK_ARG(a->act != SDB_ACT_GEGLU || a->N % 4 == 0, "gemm_f32: GEGLU needs N %% 4 == 0 (N = %d)", a->N);
+  SDB_CHECK_ARG(a->act >= SDB_ACT_NONE && a->act <= SDB_ACT_GEGLU, "gemm_f32: unknown act %d", a->act);
+  F32Params p{};
+  p.a = (const float*)a->a; p.lda = a->lda; p.K1 = a->K1;
+  p.a2 = (const float*)a->a2; p.lda2 = a->lda2; p.K2 = a->a2 ? a->K2 : 0;
+  p.w = (const float*)a->w; p.bias = a->bias;
+  p.temb = nullptr; p.ld_temb = 0; p.rows_per_image = 1;
+  p.res = a->residual; p.ldr = a->ldr; p.res_dtype = a->res_dtype;
+  p.out = a->out; p.ldo = a->ldo; p.out_dtype = a->out_dtype;
+  p.M = a->M; p.N = a->N; p.K = p.K1 + p.K2; p.act = a->act;
+  p.conv = 0;
+  return launch_f32(p, sdb_stream(stream));
+}
+
+extern "C" int sdb_conv3x3_f32(const SdbConvArgs* a, void* stream) {
+  using namespace sdb;
+  SDB_CHECK_ARG(a && a->x && a->w && a->out && a->B > 0 && a->H > 0 && a->W > 0 && a->Cin > 0 && a->Cout > 0,
+                "conv3x3_f32: bad args");
+  SDB_CHECK_ARG(!(a->down2 && a->up2), "conv3x3_f32: down2 and up2 are exclusive");
+  SDB_CHECK_ARG(!a->down2 || (a->H % 2 == 0 && a->W % 2 == 0), "conv3x3_f32: down2 needs even H, W");
+  F32Params p{};
+  p.a = (const float*)a->x; p.w = (const float*)a->w; p.bias = a->bias;
+  p.temb = a->temb; p.ld_temb = a->ld_temb;
+  p.Ho = a->down2 ? a->H / 2 : (a->up2 ? 2 * a->H : a->H);
+  p.Wo = a->down2 ? a->W / 2 : (a->up2 ? 2 * a->W : a->W);
+  p.rows_per_image = p.Ho * p.Wo;
+  p.res = a->residual; p.ldr = a->Cout; p.res_dtype = a->res_dtype;
+  p.out = a->out; p.ldo = a->Cout; p.out_dtype = a->out_dtype;
+  p.M = a->B * p.Ho * p.Wo; p.N = a->Cout; p.K = 9 * a->Cin; p.K1 = p.K; p.act = SDB_ACT_NONE;
+  p.conv = 1; p.H = a->H; p.W = a->W; p.Cin = a->Cin; p.stride = a->down2 ? 2 : 1; p.up2 = a->up2;
+  return launch_f32(p, sdb_stream(stream));
+}

@@ -4,6 +4,7 @@
 #include "sampler.cu"
 #include "norm.cu"
 #include "conv_small.cu"
+#include "precise_f32.cu"
 #include "attention.cu"
 #include "attention_ctx.cu"
 #include "attention_bwd.cu"

@@ -87,7 +87,7 @@ class Encoder(_ConvNet):
     def forward(self, x: Tensor) -> Tensor:
         _pack.require_cuda(x, "Encoder")
         p = self._thin()
-        h = ops.conv3x3_in(x, p["wci"], p["bci"], torch.bfloat16)
+        h = ops.conv3x3_in(x, p["wci"], p["bci"], _pack.compute_dtype())
         for module in self.down:
             h = module.forward_nhwc(h)
         h = self.bottleneck.forward_nhwc(h)
@@ -108,7 +108,7 @@ class Decoder(_ConvNet):
     def forward(self, x: Tensor) -> Tensor:
         _pack.require_cuda(x, "Decoder")
         p = self._thin()
-        h = ops.conv3x3_in(x, p["wci"], p["bci"], torch.bfloat16)
+        h = ops.conv3x3_in(x, p["wci"], p["bci"], _pack.compute_dtype())
         h = self.bottleneck.forward_nhwc(h)
         for module in self.up:
             h = module.forward_nhwc(h)

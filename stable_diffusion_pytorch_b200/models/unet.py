@@ -132,7 +132,8 @@ class UNetModel(nn.Module):
         if cacheable and self._ctx_cache is not None and self._ctx_cache[0] == key:
             return self._ctx_cache[1]
         B, m, cd = ctx.shape
-        c16 = ctx.contiguous() if ctx.dtype == torch.bfloat16 else ops.cast(ctx.contiguous(), torch.bfloat16)
+        act = _pack.compute_dtype()
+        c16 = ctx.contiguous() if ctx.dtype == act else ops.cast(ctx.contiguous(), act)
         kv = ops.gemm(c16.view(B * m, cd), p["wkv"], p["bkv"]).view(B, m, -1)
         views = {sid: [(kv[:, :, o:o + dm], kv[:, :, o + dm:o + 2 * dm]) for (o, dm) in lay]
                  for sid, lay in p["kv_offsets"].items()}
@@ -153,7 +154,7 @@ class UNetModel(nn.Module):
         assert timesteps.shape[0] == x.shape[0] * x_repeat, "timesteps must cover the (repeated) batch"
         # 1. time embedding chain
         t = timesteps if timesteps.dtype == torch.int64 else timesteps.to(torch.int64)
-        emb = ops.timestep_embed(t.contiguous(), sinusoidal_freq(self.channels, 10000, x.device), torch.bfloat16)
+        emb = ops.timestep_embed(t.contiguous(), sinusoidal_freq(self.channels, 10000, x.device), _pack.compute_dtype())
         h1 = ops.gemm(emb, p["w0"], p["b0"], act=ACT_SILU)
         st = ops.gemm(h1, p["w2"], p["b2"], act=ACT_SILU)          # SiLU(time_emb), shared by all ResBlocks
         temb_all = ops.gemm(st, p["wt"], p["bt"], out_dtype=torch.float32)
@@ -169,7 +170,7 @@ class UNetModel(nn.Module):
             views = self._context_kv(p, context_emb)
             kv_of = lambda st_mod: views[id(st_mod)]  # noqa: E731
         # 3. block chain
-        h = ops.conv3x3_in(x, p["wci"], p["bci"], torch.bfloat16, repeat=x_repeat)
+        h = ops.conv3x3_in(x, p["wci"], p["bci"], _pack.compute_dtype(), repeat=x_repeat)
         skips = [h]
         for module in self.input_blocks:
             h = module.forward_nhwc(h, temb_of, None, kv_of)

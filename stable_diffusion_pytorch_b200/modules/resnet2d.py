@@ -22,7 +22,9 @@ Tensor = torch.Tensor
 class _NhwcModule(nn.Module):
     """NCHW facade over a channels-last implementation."""
 
-    act_dtype = torch.bfloat16  # activations between kernels
+    @property
+    def act_dtype(self):  # activations between kernels: bf16, or fp32 in the parity mode
+        return _pack.compute_dtype()
 
     def __init__(self):
         super().__init__()
@@ -177,7 +179,7 @@ class ResBlock(_NhwcModule):
         lin = self.time_embedding[1]
         w = self._cache.get("wt", [lin.weight], lambda: _pack.linear_w(lin.weight))
         b = self._cache.get("bt", [lin.bias], lambda: _pack.f32(lin.bias))
-        return ops.gemm(ops.silu(time_emb, torch.bfloat16), w, b, out_dtype=torch.float32)
+        return ops.gemm(ops.silu(time_emb, _pack.compute_dtype()), w, b, out_dtype=torch.float32)
 
     def forward(self, x: Tensor, time_emb: Optional[Tensor] = None) -> Tensor:
         tp = None

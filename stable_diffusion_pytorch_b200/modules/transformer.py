@@ -23,7 +23,8 @@ Tensor = torch.Tensor
 def _tokens_bf16(x: Tensor) -> Tensor:
     _pack.require_cuda(x, "transformer")
     x = x.contiguous()
-    return x if x.dtype == torch.bfloat16 else ops.cast(x, torch.bfloat16)
+    cd = _pack.compute_dtype()
+    return x if x.dtype == cd else ops.cast(x, cd)
 
 
 class CrossAttention(nn.Module):
@@ -50,7 +51,7 @@ class CrossAttention(nn.Module):
     @property
     def use_p32(self) -> bool:
         """Small head dims run on the tcgen05 attention kernel over head-padded operands."""
-        return self.d_head <= 20 and self.d_head % 4 == 0
+        return self.d_head <= 20 and self.d_head % 4 == 0 and _pack.compute_dtype() == torch.bfloat16
 
     @property
     def kv_width(self) -> int:
@@ -137,14 +138,14 @@ class CrossAttention(nn.Module):
         in_dtype = query.dtype
         if query.dim() == 4:
             B, C, H, W = query.shape
-            t = ops.nchw_to_nhwc(query, torch.bfloat16).view(B, H * W, C)
+            t = ops.nchw_to_nhwc(query, _pack.compute_dtype()).view(B, H * W, C)
             ctx = None if context_emb is None else _tokens_bf16(context_emb)
             o = self.forward_tokens(t, ctx)
             return ops.nhwc_to_nchw(o.view(B, H, W, C), in_dtype)
         t = _tokens_bf16(query)
         ctx = None if context_emb is None else _tokens_bf16(context_emb)
         o = self.forward_tokens(t, ctx)
-        return o if in_dtype == torch.bfloat16 else ops.cast(o, in_dtype)
+        return o if in_dtype == o.dtype else ops.cast(o, in_dtype)
 
 
 class GEGLU(nn.Module):
@@ -165,7 +166,7 @@ class GEGLU(nn.Module):
     def forward(self, x: Tensor) -> Tensor:
         t = _tokens_bf16(x)
         o = self.forward_tokens(t.view(-1, t.shape[-1])).view(*x.shape[:-1], -1)
-        return o if x.dtype == torch.bfloat16 else ops.cast(o, x.dtype)
+        return o if x.dtype == o.dtype else ops.cast(o, x.dtype)
 
 
 class FeedForward(nn.Module):
@@ -188,7 +189,7 @@ class FeedForward(nn.Module):
     def forward(self, x: Tensor) -> Tensor:
         t = _tokens_bf16(x)
         o = self.forward_tokens(t.view(-1, t.shape[-1])).view(x.shape)
-        return o if x.dtype == torch.bfloat16 else ops.cast(o, x.dtype)
+        return o if x.dtype == o.dtype else ops.cast(o, x.dtype)
 
 
 class BasicTransformerBlock(nn.Module):
@@ -234,14 +235,16 @@ class BasicTransformerBlock(nn.Module):
         t = _tokens_bf16(x)
         ctx = None if context_emb is None else _tokens_bf16(context_emb)
         o = self.forward_tokens(t, ctx)
-        return o if x.dtype == torch.bfloat16 else ops.cast(o, x.dtype)
+        return o if x.dtype == o.dtype else ops.cast(o, x.dtype)
 
 
 class SpatialTransformer(nn.Module):
     """GN (no SiLU) -> 1x1 conv -> n_layers blocks -> 1x1 conv (zero-init) -> + x_in
     (transformer.py:282-383)."""
 
-    act_dtype = torch.bfloat16
+    @property
+    def act_dtype(self):
+        return _pack.compute_dtype()
 
     def __init__(self, in_channels: int, n_heads: int, d_head: int, n_layers: int = 1, dropout: float = 0.0,
                  context_dim: int = None, groups: int = 2):

@@ -35,6 +35,11 @@ def _stream() -> int:
     return torch.cuda.current_stream().cuda_stream
 
 
+def _no_f32_grad(x: Tensor) -> None:
+    if x.dtype == torch.float32:
+        raise NotImplementedError("the fp32 parity mode is inference-only: backward kernels exist for the bf16 path")
+
+
 def timestep_embed(t: Tensor, freq: Tensor, out_dtype=torch.float32) -> Tensor:
     assert t.dtype == torch.int64 and freq.dtype == torch.float32
     B, half = t.shape[0], freq.shape[0]
@@ -172,14 +177,15 @@ def gemm(a: Tensor, w: Tensor, bias: Optional[Tensor] = None, residual: Optional
          act: int = ACT_NONE, a2: Optional[Tensor] = None, out_dtype=None, out: Optional[Tensor] = None) -> Tensor:
     """out[M, N] = act(a[M, K] @ w[N, K]^T + bias) + residual; ``a``/``a2`` may be row-strided 2-D views."""
     if _ag.wants(a, w, bias, residual, a2):
+        _no_f32_grad(a)
         return _ag.gemm(a, w, bias, residual, act, a2, out_dtype)
-    assert a.dim() == 2 and w.dim() == 2 and a.dtype == torch.bfloat16 and w.dtype == torch.bfloat16
+    assert a.dim() == 2 and w.dim() == 2 and a.dtype in (torch.bfloat16, torch.float32) and w.dtype == a.dtype
     assert a.stride(1) == 1 and w.is_contiguous()
     M, K1 = a.shape
     N = w.shape[0]
     K2 = 0
     if a2 is not None:
-        assert a2.dim() == 2 and a2.shape[0] == M and a2.stride(1) == 1 and a2.dtype == torch.bfloat16
+        assert a2.dim() == 2 and a2.shape[0] == M and a2.stride(1) == 1 and a2.dtype == a.dtype
         K2 = a2.shape[1]
     assert w.shape[1] == K1 + K2, f"weight K {w.shape[1]} != {K1}+{K2}"
     n_out = N // 2 if act == ACT_GEGLU else N
@@ -199,7 +205,8 @@ def gemm(a: Tensor, w: Tensor, bias: Optional[Tensor] = None, residual: Optional
     args.M, args.N, args.act = M, N, act
     if bias is not None:
         assert bias.dtype == torch.float32 and bias.numel() == N
-    check(_lib.lib().sdb_gemm(C.byref(args), _stream()), "gemm")
+    fn = _lib.lib().sdb_gemm_f32 if a.dtype == torch.float32 else _lib.lib().sdb_gemm   # fp32 = parity mode
+    check(fn(C.byref(args), _stream()), "gemm")
     return out
 
 
@@ -208,10 +215,11 @@ def conv3x3(x: Tensor, w: Tensor, bias: Optional[Tensor], temb: Optional[Tensor]
             out: Optional[Tensor] = None) -> Tensor:
     """3x3 / pad 1 convolution, NHWC bf16 ``x`` [B,H,W,Cin], ``w`` bf16 [Cout,3,3,Cin]."""
     if _ag.wants(x, w, bias, temb, residual):
+        _no_f32_grad(x)
         return _ag.conv3x3(x, w, bias, temb, residual, down2, out_dtype)
     B, H, W, Cin = x.shape
     Cout = w.shape[0]
-    assert x.is_contiguous() and w.is_contiguous() and x.dtype == torch.bfloat16 and w.dtype == torch.bfloat16
+    assert x.is_contiguous() and w.is_contiguous() and x.dtype in (torch.bfloat16, torch.float32) and w.dtype == x.dtype
     assert tuple(w.shape) == (Cout, 3, 3, Cin)
     Ho, Wo = (H // 2, W // 2) if down2 else (H, W)
     if out is None:
@@ -231,7 +239,8 @@ def conv3x3(x: Tensor, w: Tensor, bias: Optional[Tensor], temb: Optional[Tensor]
     a.out, a.out_dtype = _ptr(out), _dt(out)
     a.B, a.H, a.W, a.Cin, a.Cout = B, H, W, Cin, Cout
     a.down2, a.up2 = int(down2), 0
-    check(_lib.lib().sdb_conv3x3(C.byref(a), _stream()), "conv3x3")
+    fn = _lib.lib().sdb_conv3x3_f32 if x.dtype == torch.float32 else _lib.lib().sdb_conv3x3
+    check(fn(C.byref(a), _stream()), "conv3x3")
     return out
 
 
@@ -309,11 +318,13 @@ def attention(q: Tensor, k: Tensor, v: Tensor, heads: int, d: int, scale: float,
               out: Optional[Tensor] = None) -> Tensor:
     """q [B, n, >=heads*d] (last-dim stride 1, row-strided views allowed), k/v [B, m, ...]."""
     if _ag.wants(q, k, v):
+        _no_f32_grad(q)
         return _ag.attention(q, k, v, heads, d, scale)
     B, n = q.shape[0], q.shape[1]
     m = k.shape[1]
     for t in (q, k, v):
-        assert t.dtype == torch.bfloat16 and t.stride(2) == 1 and t.stride(0) == t.shape[1] * t.stride(1)
+        assert t.dtype == q.dtype and t.stride(2) == 1 and t.stride(0) == t.shape[1] * t.stride(1)
+    assert q.dtype in (torch.bfloat16, torch.float32)
     if out is None:
         out = torch.empty(B, n, heads * d, device=q.device, dtype=q.dtype)
     check(_lib.lib().sdb_attention(_ptr(q), q.stride(1), _ptr(k), k.stride(1), _ptr(v), v.stride(1), _ptr(out),
