@@ -239,6 +239,18 @@ int sdb_attention_bwd(const void* q, int64_t ldq, const void* k, int64_t ldk, co
 int sdb_upsample2x_bwd(const void* dy, void* dx, int dtype, int B, int H, int W, int C, void* stream);
 /* DownSample backward: dy [B,H/2,W/2,C] lands on the even pixels of out [B,H,W,C], zeros elsewhere */
 int sdb_scatter_even(const void* dy, void* out, int dtype, int B, int H, int W, int C, void* stream);
+/* Weight gradients on the tensor cores (tcgen05, MN-major operands read as they lie in HBM; split over the pixel
+ * dimension, fp32 atomics into `dw`, which the caller zeroes).  autograd of nn.Conv2d 3x3 (resnet2d.py:41,103,174,195)
+ * and nn.Linear / 1x1 conv.  dy, x bf16.
+ *   conv:   dw[n][ky][kx][c] += sum_{b,h,w} dy[b,h,w,n] * x[b,h+ky-1,w+kx-1,c]   (zero padding), NHWC operands
+ *   linear: dw[n*lddw + c]   += sum_r dy[r*lddy + n] * x[r*ldx + c]
+ * SDB_EUNSUPPORTED for shapes outside the kernel (W must divide 64, Cin / K a multiple of 64): the caller then
+ * uses the transpose + GEMM route. */
+int sdb_wgrad_conv3x3(const void* dy, const void* x, float* dw, int B, int H, int W, int Cin, int Cout,
+                      void* stream);
+int sdb_wgrad_linear(const void* dy, int64_t lddy, const void* x, int64_t ldx, float* dw, int64_t lddw, int M,
+                     int N, int K, void* stream);
+
 /* [B,H,W,C] bf16 -> [B*H*W, ldc] bf16, columns (tap, c), zero padding (3x3, pad 1) and zero tail columns */
 int sdb_im2col3x3(const void* x, void* out, int B, int H, int W, int C, int ldc, void* stream);
 int sdb_nchw_to_nhwc_pad(const void* src, int src_dtype, void* dst, int dst_dtype, int B, int C, int Cp, int H,

@@ -73,6 +73,8 @@ SIGNATURES = {
                                 _i, _i, _i, _i, _i, _i, _f, _p]),
     "sdb_upsample2x_bwd": (_i, [_p, _p, _i, _i, _i, _i, _i, _p]),
     "sdb_scatter_even": (_i, [_p, _p, _i, _i, _i, _i, _i, _p]),
+    "sdb_wgrad_conv3x3": (_i, [_p, _p, _p, _i, _i, _i, _i, _i, _p]),
+    "sdb_wgrad_linear": (_i, [_p, _i64, _p, _i64, _p, _i64, _i, _i, _i, _p]),
     "sdb_im2col3x3": (_i, [_p, _p, _i, _i, _i, _i, _i, _p]),
     "sdb_nchw_to_nhwc_pad": (_i, [_p, _i, _p, _i, _i, _i, _i, _i, _i, _p]),
     "sdb_mse": (_i, [_p, _p, _i, _i64, _f, _p, _p, _p]),

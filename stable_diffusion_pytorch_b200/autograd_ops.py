@@ -5,9 +5,9 @@ grad mode is on and an input requires grad.  Every forward is the inference kern
 library's kernels as well:
 
 * dgrad of a GEMM / 3x3 conv = the same tcgen05 kernel with transposed (and flipped) weights,
-* wgrad = the same GEMM kernel over transposed operands (``out[N, K] = dY^T[N, M] . X^T[K, M]^T``, fp32 output),
-  convolutions through an explicit im2col (``sdb_im2col3x3``) -- correct and simple; the dedicated
-  implicit-GEMM wgrad kernel is the round-2 replacement,
+* wgrad = ``csrc/wgrad_umma.cu``: dY^T . X on the tensor cores with both operands read as MN-major tiles straight
+  from their channels-last rows (conv taps through shifted TMA boxes), split over the pixel dimension with fp32
+  atomics; shapes outside it (thin conv_in / head) go through transposed copies / im2col and the forward GEMM,
 * attention: flash-style recomputation (``csrc/attention_bwd.cu``); norms, GEGLU, SiLU, resampling:
   ``csrc/backward.cu``.
 
@@ -94,11 +94,19 @@ class _Gemm(Function):
         if a2 is not None and need[4]:
             da2 = ops.gemm(dyb, w[:, K1:].t().contiguous())
         if need[1]:
-            dyt = _t2d(dyb)
-            parts = [ops.gemm(dyt, _t2d(a), out_dtype=torch.float32)]
-            if a2 is not None:
-                parts.append(ops.gemm(dyt, _t2d(a2), out_dtype=torch.float32))
-            dw = (parts[0] if len(parts) == 1 else torch.cat(parts, dim=1)).to(w.dtype)
+            # tcgen05 weight-gradient kernel: dy^T . a straight from the row-major operands (split over the rows)
+            dw32 = torch.zeros(w.shape[0], w.shape[1], device=w.device, dtype=torch.float32)
+            done = ops.wgrad_linear(dyb, a, out=dw32[:, :K1]) is not None
+            if done and a2 is not None:
+                done = ops.wgrad_linear(dyb, a2, out=dw32[:, K1:]) is not None
+            if done:
+                dw = dw32.to(w.dtype)
+            else:   # shapes outside that kernel: K-major copies + the forward GEMM kernel
+                dyt = _t2d(dyb)
+                parts = [ops.gemm(dyt, _t2d(a), out_dtype=torch.float32)]
+                if a2 is not None:
+                    parts.append(ops.gemm(dyt, _t2d(a2), out_dtype=torch.float32))
+                dw = (parts[0] if len(parts) == 1 else torch.cat(parts, dim=1)).to(w.dtype)
         if ctx.has_bias and need[2]:
             db = colsum(dyb)[0]
         if ctx.res_dtype is not None and need[3]:
@@ -197,10 +205,13 @@ class _Conv3x3(Function):
             w_flip = w.flip(1, 2).permute(3, 1, 2, 0).contiguous()          # [Cin, 3, 3, Cout]
             dx = ops.conv3x3(dyf, w_flip, None)
         if need[1]:
-            M = B * H * W
-            col = torch.empty(M, 9 * Cin, device=x.device, dtype=torch.bfloat16)
-            check(_lib.lib().sdb_im2col3x3(ops._ptr(x), ops._ptr(col), B, H, W, Cin, 9 * Cin, ops._stream()), "im2col3x3")
-            dw = ops.gemm(_t2d(dyf.view(M, Cout)), _t2d(col), out_dtype=torch.float32).view(Cout, 3, 3, Cin).to(w.dtype)
+            dw32 = ops.wgrad_conv3x3(dyf, x)              # tcgen05 implicit weight-gradient GEMM (no im2col)
+            if dw32 is None:                              # geometry outside that kernel: explicit im2col + GEMM
+                M = B * H * W
+                col = torch.empty(M, 9 * Cin, device=x.device, dtype=torch.bfloat16)
+                check(_lib.lib().sdb_im2col3x3(ops._ptr(x), ops._ptr(col), B, H, W, Cin, 9 * Cin, ops._stream()), "im2col3x3")
+                dw32 = ops.gemm(_t2d(dyf.view(M, Cout)), _t2d(col), out_dtype=torch.float32).view(Cout, 3, 3, Cin)
+            dw = dw32.to(w.dtype)
         if ctx.has_bias and need[2]:
             db = colsum(dyb.view(B * Ho * Wo, Cout))[0]
         if ctx.has_temb and need[3]:

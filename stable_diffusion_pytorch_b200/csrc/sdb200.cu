@@ -11,3 +11,4 @@
 #include "attention_umma.cu"
 #include "gemm_umma.cu"
 #include "backward.cu"
+#include "wgrad_umma.cu"

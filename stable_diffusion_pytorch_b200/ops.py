@@ -393,3 +393,36 @@ def sumsq(x: Tensor, out: Optional[Tensor] = None) -> Tensor:
         out = torch.zeros(1, device=x.device, dtype=torch.float32)
     check(_lib.lib().sdb_sumsq(_ptr(x), x.numel(), _ptr(out), _stream()), "sumsq")
     return out
+
+
+def wgrad_linear(dy: Tensor, x: Tensor, out: Optional[Tensor] = None) -> Optional[Tensor]:
+    """dW [N, K] (fp32) = dy[M, N]^T @ x[M, K] on the tcgen05 weight-gradient kernel (row-strided bf16 views allowed;
+    accumulates into ``out`` when given).  Returns None when the shape is outside the kernel (caller falls back to
+    the transpose + GEMM route)."""
+    M, N = dy.shape
+    K = x.shape[1]
+    assert x.shape[0] == M and dy.dtype == torch.bfloat16 and x.dtype == torch.bfloat16
+    assert dy.stride(1) == 1 and x.stride(1) == 1
+    if (K % 160 and K % 64) or dy.stride(0) % 8 or x.stride(0) % 8 or dy.data_ptr() % 16 or x.data_ptr() % 16:
+        return None
+    if out is None:
+        out = torch.zeros(N, K, device=dy.device, dtype=torch.float32)
+    assert out.dtype == torch.float32 and out.stride(1) == 1 and tuple(out.shape) == (N, K)
+    check(_lib.lib().sdb_wgrad_linear(_ptr(dy), dy.stride(0), _ptr(x), x.stride(0), _ptr(out), out.stride(0), M, N, K,
+                                      _stream()), "wgrad_linear")
+    return out
+
+
+def wgrad_conv3x3(dy: Tensor, x: Tensor) -> Optional[Tensor]:
+    """dW [Cout, 3, 3, Cin] (fp32) of a 3x3 / pad 1 convolution from NHWC bf16 ``dy`` [B,H,W,Cout] and ``x``
+    [B,H,W,Cin]; None when the geometry is outside the kernel."""
+    B, H, W, Cin = x.shape
+    Cout = dy.shape[-1]
+    assert tuple(dy.shape[:3]) == (B, H, W) and dy.is_contiguous() and x.is_contiguous()
+    assert dy.dtype == torch.bfloat16 and x.dtype == torch.bfloat16
+    th = min(H, 64 // W) if W <= 64 and 64 % W == 0 else 0
+    if (Cin % 160 and Cin % 64) or Cout % 8 or not th or H % th or 64 % (W * th):
+        return None
+    out = torch.zeros(Cout, 3, 3, Cin, device=x.device, dtype=torch.float32)
+    check(_lib.lib().sdb_wgrad_conv3x3(_ptr(dy), _ptr(x), _ptr(out), B, H, W, Cin, Cout, _stream()), "wgrad_conv3x3")
+    return out
