@@ -231,11 +231,17 @@ int sdb_layernorm_bwd(const void* x, const float* gamma, const void* dy, void* d
 /* softmax(QK^T scale)V backward (autograd of transformer.py:93-114), any n / m, d <= 32 (SDB_EUNSUPPORTED beyond):
  * flash-style recomputation, no [n, m] tensor.  head_pitch = columns per head in q/k/v and their gradients (32 for
  * the head-padded operands of sdb_attention_p32, d for dense ones); o / dO dense [B, n, heads*d];
- * lse_scratch / delta_scratch: fp32 [B * heads * n] each. */
+ * lse_scratch / delta_scratch: fp32 [B * heads * n] each.  lse_valid != 0: lse_scratch already holds the row
+ * log-sum-exp (log2 domain) written by sdb_attention_p32_lse, and the recomputation pass is skipped. */
 int sdb_attention_bwd(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
                       const void* o, int64_t ldo, const void* dO, int64_t lddo, void* dq, int64_t lddq, void* dk,
-                      int64_t lddk, void* dv, int64_t lddv, float* lse_scratch, float* delta_scratch, int B,
-                      int heads, int n, int m, int d, int head_pitch, float scale, void* stream);
+                      int64_t lddk, void* dv, int64_t lddv, float* lse_scratch, float* delta_scratch, int lse_valid,
+                      int B, int heads, int n, int m, int d, int head_pitch, float scale, void* stream);
+/* sdb_attention_p32 that also keeps lse[b, h, row] = log2(sum_j exp2(s_ij * scale * log2 e)) for the backward.
+ * *lse_written = 1 if the buffer was filled (the short-context kernel for m <= 128 does not keep it). */
+int sdb_attention_p32_lse(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
+                          void* out, int64_t ldo, int B, int heads, int n, int m, int d, float scale, float* lse,
+                          int* lse_written, void* stream);
 int sdb_upsample2x_bwd(const void* dy, void* dx, int dtype, int B, int H, int W, int C, void* stream);
 /* DownSample backward: dy [B,H/2,W/2,C] lands on the even pixels of out [B,H,W,C], zeros elsewhere */
 int sdb_scatter_even(const void* dy, void* out, int dtype, int B, int H, int W, int C, void* stream);

@@ -364,26 +364,29 @@ def add_layernorm(x, res, gamma, beta, eps=1e-5):
 class _AttentionP32(Function):
     @staticmethod
     def forward(ctx, q, k, v, heads, d, scale):
-        o = _ops().attention_p32(q, k, v, heads, d, scale)
-        ctx.save_for_backward(q, k, v, o)
+        # the tcgen05 forward keeps the row log-sum-exp, so the backward does not rebuild it
+        o, lse = _ops().attention_p32_lse(q, k, v, heads, d, scale)
+        ctx.has_lse = lse is not None
+        ctx.save_for_backward(q, k, v, o, *([lse] if lse is not None else []))
         ctx.heads, ctx.d, ctx.scale = heads, d, scale
         return o
 
     @staticmethod
     def backward(ctx, do):
         ops = _ops()
-        q, k, v, o = ctx.saved_tensors
+        q, k, v, o = ctx.saved_tensors[:4]
         B, n, m = q.shape[0], q.shape[1], k.shape[1]
         hp = 32
         do = _bf16(do)
         dq = torch.empty(B, n, ctx.heads * hp, device=q.device, dtype=torch.bfloat16)
         dk = torch.empty(B, m, ctx.heads * hp, device=q.device, dtype=torch.bfloat16)
         dv = torch.empty_like(dk)
-        scratch = torch.empty(2, B * ctx.heads * n, device=q.device, dtype=torch.float32)
+        delta = torch.empty(B * ctx.heads * n, device=q.device, dtype=torch.float32)
+        lse = ctx.saved_tensors[4] if ctx.has_lse else torch.empty_like(delta)
         check(_lib.lib().sdb_attention_bwd(
             ops._ptr(q), q.stride(1), ops._ptr(k), k.stride(1), ops._ptr(v), v.stride(1), ops._ptr(o), o.stride(1),
             ops._ptr(do), do.stride(1), ops._ptr(dq), dq.stride(1), ops._ptr(dk), dk.stride(1), ops._ptr(dv), dv.stride(1),
-            ops._ptr(scratch[0]), ops._ptr(scratch[1]), B, ctx.heads, n, m, ctx.d, hp, ctx.scale, ops._stream()),
+            ops._ptr(lse), ops._ptr(delta), int(ctx.has_lse), B, ctx.heads, n, m, ctx.d, hp, ctx.scale, ops._stream()),
             "attention_bwd")
         return dq, dk, dv, None, None, None
 
@@ -411,7 +414,7 @@ class _Attention(Function):
         check(_lib.lib().sdb_attention_bwd(
             ops._ptr(q), q.stride(1), ops._ptr(k), k.stride(1), ops._ptr(v), v.stride(1), ops._ptr(o), o.stride(1),
             ops._ptr(do), do.stride(1), ops._ptr(dq), dq.stride(1), ops._ptr(dk), dk.stride(1), ops._ptr(dv), dv.stride(1),
-            ops._ptr(scratch[0]), ops._ptr(scratch[1]), B, ctx.heads, n, m, ctx.d, ctx.d, ctx.scale, ops._stream()),
+            ops._ptr(scratch[0]), ops._ptr(scratch[1]), 0, B, ctx.heads, n, m, ctx.d, ctx.d, ctx.scale, ops._stream()),
             "attention_bwd")
         return dq, dk, dv, None, None, None
 

@@ -66,7 +66,7 @@ attn_bwd_dq_kernel(const __nv_bfloat16* __restrict__ q, long long ldq, const __n
                    const __nv_bfloat16* __restrict__ v, long long ldv, const __nv_bfloat16* __restrict__ o, long long ldo,
                    const __nv_bfloat16* __restrict__ dO, long long lddo, __nv_bfloat16* __restrict__ dq, long long lddq,
                    float* __restrict__ lse_out, float* __restrict__ delta_out, int n, int m, int d, int hp, float scale,
-                   float scale_log2e) {
+                   float scale_log2e, int have_lse) {
   __shared__ __align__(16) __nv_bfloat16 sQ[64 * kAbPitch], sdO[64 * kAbPitch], sK[2][64 * kAbPitch], sV[2][64 * kAbPitch];
   __shared__ float sDelta[64];
   const int b = blockIdx.z, h = blockIdx.y, q0 = blockIdx.x * 64, heads = gridDim.y;
@@ -118,9 +118,10 @@ attn_bwd_dq_kernel(const __nv_bfloat16* __restrict__ q, long long ldq, const __n
   __syncthreads();
 
   // ---- pass 1: row log-sum-exp (log2 domain, of the scaled scores) ---------------------------------
+  // (skipped when the forward kernel kept the row log-sum-exp: have_lse)
   float row_max[2] = {-INFINITY, -INFINITY}, row_sum[2] = {0.f, 0.f};
   float s[8][4];
-  for (int j = 0; j < n_tiles; ++j) {
+  for (int j = 0; j < (have_lse ? 0 : n_tiles); ++j) {
     const int buf = j & 1;
     if (j + 1 < n_tiles) {
       stage_rows<kAbPitch>(sK[buf ^ 1], kg, ldk, (j + 1) * 64, m, 64, w);
@@ -169,7 +170,11 @@ attn_bwd_dq_kernel(const __nv_bfloat16* __restrict__ q, long long ldq, const __n
     lse2[r] = row_max[r] * scale_log2e + log2f(row_sum[r]);
   }
   const int r0 = q0 + warp * 16 + (lane >> 2), r1 = r0 + 8;
-  if ((lane & 3) == 0) {
+  if (have_lse) {
+    const float* lg = lse_out + ((long long)b * heads + h) * n;
+    lse2[0] = r0 < n ? lg[r0] : 0.f;
+    lse2[1] = r1 < n ? lg[r1] : 0.f;
+  } else if ((lane & 3) == 0) {
     float* lg = lse_out + ((long long)b * heads + h) * n;
     if (r0 < n) lg[r0] = lse2[0];
     if (r1 < n) lg[r1] = lse2[1];
@@ -324,8 +329,8 @@ attn_bwd_dkv_kernel(const __nv_bfloat16* __restrict__ q, long long ldq, const __
 
 extern "C" int sdb_attention_bwd(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
                                  const void* o, int64_t ldo, const void* dO, int64_t lddo, void* dq, int64_t lddq, void* dk,
-                                 int64_t lddk, void* dv, int64_t lddv, float* lse_scratch, float* delta_scratch, int B,
-                                 int heads, int n, int m, int d, int head_pitch, float scale, void* stream) {
+                                 int64_t lddk, void* dv, int64_t lddv, float* lse_scratch, float* delta_scratch, int lse_valid,
+                                 int B, int heads, int n, int m, int d, int head_pitch, float scale, void* stream) {
   using namespace sdb;
   SDB_CHECK_ARG(q && k && v && o && dO && dq && dk && dv && lse_scratch && delta_scratch, "attention_bwd: null pointer");
   SDB_CHECK_ARG(B > 0 && heads > 0 && n > 0 && m > 0 && d > 0 && d % 4 == 0 && head_pitch >= d && head_pitch % 4 == 0,
@@ -341,7 +346,8 @@ extern "C" int sdb_attention_bwd(const void* q, int64_t ldq, const void* k, int6
   const float sl2e = scale * 1.4426950408889634f;
   attn_bwd_dq_kernel<<<dim3((n + 63) / 64, heads, B), kAttThreads, 0, st>>>(
       (const __nv_bfloat16*)q, ldq, (const __nv_bfloat16*)k, ldk, (const __nv_bfloat16*)v, ldv, (const __nv_bfloat16*)o, ldo,
-      (const __nv_bfloat16*)dO, lddo, (__nv_bfloat16*)dq, lddq, lse_scratch, delta_scratch, n, m, d, head_pitch, scale, sl2e);
+      (const __nv_bfloat16*)dO, lddo, (__nv_bfloat16*)dq, lddq, lse_scratch, delta_scratch, n, m, d, head_pitch, scale, sl2e,
+      lse_valid);
   SDB_LAUNCH_OK();
   attn_bwd_dkv_kernel<<<dim3((m + 63) / 64, heads, B), kAttThreads, 0, st>>>(
       (const __nv_bfloat16*)q, ldq, (const __nv_bfloat16*)k, ldk, (const __nv_bfloat16*)v, ldv, (const __nv_bfloat16*)dO, lddo,

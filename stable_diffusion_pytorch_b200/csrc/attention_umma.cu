@@ -38,6 +38,7 @@ struct FaParams {
   long long ldo;
   int n, m, d, heads;
   float scale_log2;
+  float* lse;   // optional [B, heads, n]: log2-domain log-sum-exp of the scaled scores (kept for the backward)
 };
 
 __device__ __forceinline__ void tma_load_3d(uint32_t dst, const void* tmap, uint32_t bar, int c0, int c1,
@@ -388,6 +389,8 @@ attention_umma_kernel(const __grid_constant__ FaParams p) {
       for (int i = 1; i < 24; ++i)
         if (i == p.d) den = acc[i];
       const float inv = 1.0f / den;
+      // O and its denominator are relative to the lagging maximum m_run: lse2 = m_run c + log2(den)
+      if (p.lse) p.lse[((long long)b * p.heads + h) * p.n + row] = fmaf(m_run, c, log2f(den));
       __nv_bfloat16* og = p.out + ((long long)b * p.n + row) * p.ldo + h * p.d;
 #pragma unroll
       for (int i = 0; i < 24; i += 4) {
@@ -409,10 +412,11 @@ attention_umma_kernel(const __grid_constant__ FaParams p) {
 
 }  // namespace sdb
 
-extern "C" int sdb_attention_p32(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
-                                 int64_t ldv, void* out, int64_t ldo, int B, int heads, int n, int m, int d,
-                                 float scale, void* stream) {
+static int attention_p32_impl(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
+                              int64_t ldv, void* out, int64_t ldo, int B, int heads, int n, int m, int d,
+                              float scale, float* lse, int* lse_written, void* stream) {
   using namespace sdb;
+  if (lse_written) *lse_written = 0;
   SDB_CHECK_ARG(q && k && v && out && B > 0 && heads > 0 && n > 0 && m > 0, "attention_p32: bad args");
   SDB_CHECK_ARG(d > 0 && d <= 20 && d % 4 == 0, "attention_p32: head dim (%d) must be a multiple of 4, <= 20", d);
   SDB_CHECK_ARG(ldq % 8 == 0 && ldk % 8 == 0 && ldv % 8 == 0 && ldo % 4 == 0,
@@ -452,6 +456,8 @@ extern "C" int sdb_attention_p32(const void* q, int64_t ldq, const void* k, int6
   p.ldo = ldo;
   p.n = n; p.m = m; p.d = d; p.heads = heads;
   p.scale_log2 = scale * 1.4426950408889634f;
+  p.lse = lse;
+  if (lse && lse_written) *lse_written = 1;
   // share of exponentials evaluated on the FMA pipe: kPoly pairs out of 8 (tuning aid: SDB_FA_POLY)
   static int poly = -1;
   if (poly < 0) {
@@ -484,4 +490,17 @@ extern "C" int sdb_attention_p32(const void* q, int64_t ldq, const void* k, int6
 #undef SDB_FA_LAUNCH
   SDB_LAUNCH_OK();
   return SDB_OK;
+}
+
+extern "C" int sdb_attention_p32(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
+                                 int64_t ldv, void* out, int64_t ldo, int B, int heads, int n, int m, int d,
+                                 float scale, void* stream) {
+  return attention_p32_impl(q, ldq, k, ldk, v, ldv, out, ldo, B, heads, n, m, d, scale, nullptr, nullptr, stream);
+}
+
+extern "C" int sdb_attention_p32_lse(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
+                                     int64_t ldv, void* out, int64_t ldo, int B, int heads, int n, int m, int d,
+                                     float scale, float* lse, int* lse_written, void* stream) {
+  SDB_CHECK_ARG(lse && lse_written, "attention_p32_lse: null lse buffer");
+  return attention_p32_impl(q, ldq, k, ldk, v, ldv, out, ldo, B, heads, n, m, d, scale, lse, lse_written, stream);
 }

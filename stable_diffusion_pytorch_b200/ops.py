@@ -349,6 +349,22 @@ def attention_p32(q: Tensor, k: Tensor, v: Tensor, heads: int, d: int, scale: fl
     return out
 
 
+def attention_p32_lse(q: Tensor, k: Tensor, v: Tensor, heads: int, d: int, scale: float):
+    """``attention_p32`` that also returns the fp32 row log-sum-exp [B*heads*n] (log2 domain) the backward needs, or
+    None when the kernel that ran does not keep it (short contexts)."""
+    B, n = q.shape[0], q.shape[1]
+    m = k.shape[1]
+    for t in (q, k, v):
+        assert t.dtype == torch.bfloat16 and t.stride(2) == 1 and t.stride(0) == t.shape[1] * t.stride(1)
+    out = torch.empty(B, n, heads * d, device=q.device, dtype=q.dtype)
+    lse = torch.empty(B * heads * n, device=q.device, dtype=torch.float32)
+    wrote = C.c_int(0)
+    check(_lib.lib().sdb_attention_p32_lse(_ptr(q), q.stride(1), _ptr(k), k.stride(1), _ptr(v), v.stride(1), _ptr(out),
+                                           out.stride(1), B, heads, n, m, d, scale, _ptr(lse), C.byref(wrote),
+                                           _stream()), "attention_p32_lse")
+    return out, (lse if wrote.value else None)
+
+
 def silu(x: Tensor, out_dtype=None) -> Tensor:
     if _ag.wants(x):
         return _ag.silu(x, out_dtype)
