@@ -273,6 +273,16 @@ int sdb_adamw(float* p, const float* g, float* m, float* v, int64_t n, float lr,
               float eps, float weight_decay, int step, float grad_scale, const float* gnorm_sq_or_null,
               float max_norm, void* stream);
 
+/* ---- CLIP text encoder pieces (models/clip_model.py:56-96 wraps transformers.CLIPTextModel) ----
+ * out[b*L + l, :] = token_embedding[ids[b, l]] + position_embedding[l]  (CLIPTextEmbeddings); ids int64. */
+int sdb_embed_tokens(const int64_t* ids, const float* tok, const float* pos, void* out, int out_dtype, int B, int L,
+                     int C, int vocab, void* stream);
+/* causal softmax(QK^T scale)V over a short sequence (CLIPAttention with is_causal): n <= 80, d <= 64; head h at
+ * columns [h*d, (h+1)*d), row strides in elements; dtype = SDB_BF16 | SDB_F32 for q, k, v and out. */
+int sdb_attention_causal_small(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
+                               void* out, int64_t ldo, int B, int heads, int n, int d, float scale, int dtype,
+                               void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -560,3 +560,67 @@ def train_steps(sd: StateDict, cfg: UnetCfg, batches, uncond_ctx: Tensor, guidan
                 adamw_update(params[k], g, ms[k], vs[k], i, lr=lr, weight_decay=weight_decay)
         losses.append(float(loss.detach()))
     return losses, norms, all_grads, {k: v.detach() for k, v in params.items()}
+
+
+# ----------------------------------------------------------------------------
+# CLIP text encoder (the context producer in front of the path)
+# ----------------------------------------------------------------------------
+# The reference does not implement it: models/clip_model.py:56-96 wraps the third-party
+# ``transformers.CLIPTextModel`` (requirements.txt:8, unpinned; the build container has transformers 5.5.0) and
+# returns its output object, of which the hot path uses ``[0]`` = last_hidden_state (latent_diffusion.py:55-60).
+# This is a restatement of that published architecture (Radford et al. 2021 text tower as implemented in
+# transformers/models/clip/modeling_clip.py: CLIPTextEmbeddings, CLIPEncoderLayer, CLIPTextTransformer.forward):
+# token + learned position embeddings; pre-LayerNorm blocks with CAUSAL multi-head self-attention (q, k, v, out
+# projections with bias, scale d^-1/2) and a quick-GELU MLP x * sigmoid(1.702 x); final LayerNorm.  Pinned by
+# tests/golden/reference_clip.npz, produced by the real CLIPTextModel on seeded weights (make_golden_clip.py).
+@dataclass(frozen=True)
+class ClipTextCfg:
+    vocab_size: int = 49408
+    hidden_size: int = 768
+    intermediate_size: int = 3072
+    num_hidden_layers: int = 12
+    num_attention_heads: int = 12
+    max_position_embeddings: int = 77
+    layer_norm_eps: float = 1e-5
+
+
+def clip_text_param_shapes(cfg: ClipTextCfg) -> Dict[str, Tuple[int, ...]]:
+    C, F = cfg.hidden_size, cfg.intermediate_size
+    s = {"text_model.embeddings.token_embedding.weight": (cfg.vocab_size, C),
+         "text_model.embeddings.position_embedding.weight": (cfg.max_position_embeddings, C),
+         "text_model.final_layer_norm.weight": (C,), "text_model.final_layer_norm.bias": (C,)}
+    for i in range(cfg.num_hidden_layers):
+        p = f"text_model.encoder.layers.{i}."
+        for n in ("q_proj", "k_proj", "v_proj", "out_proj"):
+            s[p + f"self_attn.{n}.weight"] = (C, C)
+            s[p + f"self_attn.{n}.bias"] = (C,)
+        for n in ("layer_norm1", "layer_norm2"):
+            s[p + n + ".weight"] = (C,)
+            s[p + n + ".bias"] = (C,)
+        s[p + "mlp.fc1.weight"], s[p + "mlp.fc1.bias"] = (F, C), (F,)
+        s[p + "mlp.fc2.weight"], s[p + "mlp.fc2.bias"] = (C, F), (C,)
+    return s
+
+
+def clip_text_forward(sd: StateDict, cfg: ClipTextCfg, input_ids: Tensor) -> Tensor:
+    """last_hidden_state [B, L, C] of CLIPTextModel(input_ids) (no padding mask: clip_model.py:87-96 passes ids only)."""
+    B, L = input_ids.shape
+    C, H = cfg.hidden_size, cfg.num_attention_heads
+    d = C // H
+    x = sd["text_model.embeddings.token_embedding.weight"][input_ids] \
+        + sd["text_model.embeddings.position_embedding.weight"][:L][None]
+    causal = torch.full((L, L), float("-inf")).triu(1)
+    for i in range(cfg.num_hidden_layers):
+        p = f"text_model.encoder.layers.{i}."
+        h = F.layer_norm(x, (C,), sd[p + "layer_norm1.weight"], sd[p + "layer_norm1.bias"], cfg.layer_norm_eps)
+        q, k, v = (F.linear(h, sd[p + f"self_attn.{n}.weight"], sd[p + f"self_attn.{n}.bias"])
+                   .view(B, L, H, d).transpose(1, 2) for n in ("q_proj", "k_proj", "v_proj"))
+        a = torch.softmax(q @ k.transpose(-1, -2) * d ** -0.5 + causal, dim=-1) @ v
+        a = a.transpose(1, 2).reshape(B, L, C)
+        x = x + F.linear(a, sd[p + "self_attn.out_proj.weight"], sd[p + "self_attn.out_proj.bias"])
+        h = F.layer_norm(x, (C,), sd[p + "layer_norm2.weight"], sd[p + "layer_norm2.bias"], cfg.layer_norm_eps)
+        h = F.linear(h, sd[p + "mlp.fc1.weight"], sd[p + "mlp.fc1.bias"])
+        h = h * torch.sigmoid(1.702 * h)
+        x = x + F.linear(h, sd[p + "mlp.fc2.weight"], sd[p + "mlp.fc2.bias"])
+    return F.layer_norm(x, (C,), sd["text_model.final_layer_norm.weight"], sd["text_model.final_layer_norm.bias"],
+                        cfg.layer_norm_eps)

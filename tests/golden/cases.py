@@ -107,3 +107,24 @@ def train_batches(cfg, B, H, W, seed, n_steps, ctx_len=77):
         noise = torch.randn(B, cfg.latent_channels, H, W, generator=g)
         out.append((x_t, t, ctx, noise))
     return out, uncond
+
+
+# ---- CLIP text encoder -- name -> (cfg, seed, B)
+CLIP_TINY = O.ClipTextCfg(vocab_size=1000, hidden_size=128, intermediate_size=256, num_hidden_layers=2,
+                          num_attention_heads=2)
+CLIP_SD15 = O.ClipTextCfg()     # the text tower of runwayml/stable-diffusion-v1-5 (clip_model.py:11-18)
+CLIP_CASES = {
+    "tiny": (CLIP_TINY, 21, 3),
+    "sd15": (CLIP_SD15, 22, 1),
+}
+
+
+def clip_inputs(cfg, B, seed):
+    """Token ids shaped like the tokenizer's output (clip_model.py:72-85): BOS, random tokens, EOS padding."""
+    g = _g(3000 + seed)
+    L = cfg.max_position_embeddings
+    ids = torch.randint(0, cfg.vocab_size - 2, (B, L), generator=g, dtype=torch.long)
+    ids[:, 0] = cfg.vocab_size - 2
+    for b in range(B):
+        ids[b, 5 + 11 * b:] = cfg.vocab_size - 1
+    return ids

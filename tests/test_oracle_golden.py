@@ -115,3 +115,17 @@ def test_train_steps_vs_reference(golden_train, name):
     for k in cases.TRAIN_PROBE:
         assert rel_l2(grads[0][k], G[f"train_{name}_grad_{k}"]) < 1e-4, k
         assert rel_l2(params[k], G[f"train_{name}_param_{k}"]) < 1e-6, k
+
+
+@pytest.mark.parametrize("name", list(cases.CLIP_CASES))
+def test_clip_text_oracle_vs_transformers_golden(name):
+    """The CLIP text tower restatement against the real transformers.CLIPTextModel (tests/golden/make_golden_clip.py)."""
+    import os
+    gold = dict(np.load(os.path.join(os.path.dirname(__file__), "golden", "reference_clip.npz")))
+    cfg, seed, B = cases.CLIP_CASES[name]
+    sd = O.seeded_state_dict(O.clip_text_param_shapes(cfg), seed)
+    with torch.no_grad():
+        y = O.clip_text_forward(sd, cfg, cases.clip_inputs(cfg, B, seed))
+    ref = torch.from_numpy(gold[f"clip_{name}"])
+    assert tuple(y.shape) == tuple(ref.shape)
+    assert float((y - ref).norm() / ref.norm()) < 1e-5
