@@ -10,14 +10,14 @@
 // 8 pixels; A = dY^T (128 output channels = two atoms), B = X^T shifted by the tap through the TMA coordinates
 // (out-of-image pixels are zero-filled = the conv padding).  No transposes, no im2col.
 // One CTA = (128 output channels) x (a group of up to 3 (tap, Cin-slice) accumulators side by side in TMEM, so the
-// dY tile is fetched once per group) x (a chunk of the pixels): split-K over the grid, partial sums added to the
+// dY tile is fetched once per group) x (a chunk of the pixels): split-K over one wave of CTAs, partial sums added to the
 // fp32 result with atomics (the caller zeroes it).  Warp 0 = TMA producer, warp 1 = MMA issuer, warps 4-7 = epilogue.
 #include "common.cuh"
 
 namespace sdb {
 
 constexpr int kWgThreads = 256;
-constexpr int kWgStages = 2;
+constexpr int kWgMaxStages = 4;
 constexpr int kWgAtomBytes = 64 * 128;   // 64 pixel rows x 64 channels bf16
 
 struct WgradParams {
@@ -34,7 +34,7 @@ struct WgradParams {
   int Cout, Cin;
   float* out;
   long long ld_n;     // out[n * ld_n + tap * Cin + c]
-  int stage_bytes;
+  int stage_bytes, stages;
 };
 
 // MN-major operand, SWIZZLE_128B: 64 channels (128 B) per pixel row, 8-pixel groups 1024 B apart (SBO),
@@ -52,11 +52,11 @@ __device__ __forceinline__ uint64_t umma_smem_desc_mn128(uint32_t saddr) {
 __global__ void __launch_bounds__(kWgThreads, 1) wgrad_umma_kernel(const __grid_constant__ WgradParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
-  const uint32_t bar_base = base + (uint32_t)kWgStages * (uint32_t)p.stage_bytes;
+  const uint32_t bar_base = base + (uint32_t)p.stages * (uint32_t)p.stage_bytes;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
-  auto empty_bar = [&](int s) { return bar_base + 8u * (kWgStages + s); };
-  const uint32_t tfull_bar = bar_base + 8u * (2 * kWgStages);
-  const uint32_t tmem_slot = bar_base + 8u * (2 * kWgStages + 1);
+  auto empty_bar = [&](int s) { return bar_base + 8u * (kWgMaxStages + s); };
+  const uint32_t tfull_bar = bar_base + 8u * (2 * kWgMaxStages);
+  const uint32_t tmem_slot = bar_base + 8u * (2 * kWgMaxStages + 1);
   volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(smem_raw + (tmem_slot - smem_u32(smem_raw)));
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
@@ -74,7 +74,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) wgrad_umma_kernel(const __grid_
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&p.tmY);
     prefetch_tmap(&p.tmX);
-    for (int s = 0; s < kWgStages; ++s) {
+    for (int s = 0; s < p.stages; ++s) {
       mbar_init(full_bar(s), 1);
       mbar_init(empty_bar(s), 1);
     }
@@ -94,9 +94,10 @@ __global__ void __launch_bounds__(kWgThreads, 1) wgrad_umma_kernel(const __grid_
     // ===================== TMA producer =====================
     const uint32_t tx = (uint32_t)(2 + nsub * p.atoms_b) * (uint32_t)kWgAtomBytes;
     bool ok = true;
+    int stage = 0;
+    uint32_t phase = 0;
     for (int i = 0; i < nkb && ok; ++i) {
-      const int stage = i % kWgStages;
-      ok = mbar_wait(empty_bar(stage), (((uint32_t)(i / kWgStages)) & 1u) ^ 1u);
+      ok = mbar_wait(empty_bar(stage), phase ^ 1u);
       if (!ok) break;
       const int kb = kb0 + i;
       int w0 = 0, h0 = 0, i0 = 0;
@@ -125,14 +126,16 @@ __global__ void __launch_bounds__(kWgThreads, 1) wgrad_umma_kernel(const __grid_
         }
       }
       __syncwarp();
+      if (++stage == p.stages) { stage = 0; phase ^= 1u; }
     }
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
     const uint32_t idesc = umma_idesc_bf16(128u, (uint32_t)p.NW) | (1u << 15) | (1u << 16);   // A and B MN-major
     bool ok = true;
+    int stage = 0;
+    uint32_t phase = 0;
     for (int i = 0; i < nkb && ok; ++i) {
-      const int stage = i % kWgStages;
-      ok = mbar_wait(full_bar(stage), ((uint32_t)(i / kWgStages)) & 1u);
+      ok = mbar_wait(full_bar(stage), phase);
       if (!ok) break;
       tc_fence_after();
       const uint32_t sa = base + (uint32_t)stage * (uint32_t)p.stage_bytes;
@@ -149,6 +152,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) wgrad_umma_kernel(const __grid_
         umma_commit(empty_bar(stage));
       }
       __syncwarp();
+      if (++stage == p.stages) { stage = 0; phase ^= 1u; }
     }
     if (ok && elect_one()) umma_commit(tfull_bar);
     __syncwarp();
@@ -191,20 +195,31 @@ static int wgrad_launch(WgradParams& p, int kb_total, cudaStream_t st) {
   p.atoms_b = (p.NW + 63) / 64;
   p.subs_per_tap = p.Cin / p.NW;
   p.total_subs = p.taps * p.subs_per_tap;
+  // accumulators per CTA: bounded by the 512 TMEM columns and by a double-buffered operand ring in 220 KB.
+  // Measured (tools/bench_wgrad.py, conv 640->320): 3 accumulators / 2 stages 763 TFLOP/s, 2 / 3 stages 580,
+  // 1 / 4 stages 438 -- re-fetching dY costs more than a deeper ring gains.  (SDB_WGRAD_GROUP: tuning aid)
   int group = 512 / p.NW;
+  while (group > 1 && 2 * (2 + group * p.atoms_b) * kWgAtomBytes > 220 * 1024) --group;
+  static int group_env = -1;
+  if (group_env < 0) { const char* e = getenv("SDB_WGRAD_GROUP"); group_env = e ? atoi(e) : 0; }
+  if (group_env > 0 && group_env * p.NW <= 512) group = group_env;
   if (group > p.total_subs) group = p.total_subs;
   p.group = group;
   p.n_groups = (p.total_subs + group - 1) / group;
   const int n_tiles = (p.Cout + 127) / 128;
   const int base_jobs = n_tiles * p.n_groups;
-  int chunks = (2 * sdb_num_sms() + base_jobs - 1) / base_jobs;
+  // one CTA per SM (176 KB of operand ring): exactly one wave, rounded DOWN so no nearly-empty tail wave
+  int chunks = sdb_num_sms() / base_jobs;
   if (chunks > kb_total) chunks = kb_total;
   if (chunks < 1) chunks = 1;
   p.kb_total = kb_total;
   p.kb_per_chunk = (kb_total + chunks - 1) / chunks;
   p.chunks = (kb_total + p.kb_per_chunk - 1) / p.kb_per_chunk;
   p.stage_bytes = (2 + group * p.atoms_b) * kWgAtomBytes;
-  const int smem = kWgStages * p.stage_bytes + 64 + 1024;
+  p.stages = (220 * 1024) / p.stage_bytes;
+  if (p.stages > kWgMaxStages) p.stages = kWgMaxStages;
+  SDB_CHECK_ARG(p.stages >= 2, "wgrad: operand ring does not fit");
+  const int smem = p.stages * p.stage_bytes + 128 + 1024;
   SDB_CHECK_ARG(smem <= 227 * 1024, "wgrad: smem budget exceeded (%d B)", smem);
   static int configured = 0;
   if (configured < smem) {
