@@ -36,6 +36,8 @@ def parse():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-decode", action="store_true", help="skip the VAE-decode (images/s) leg")
+    ap.add_argument("--no-train", action="store_true", help="skip the config-4 train-step leg")
+    ap.add_argument("--train-batch", type=int, default=32, help="per-GPU batch of the train-step leg (config 4: 32)")
     ap.add_argument("--profile-step", action="store_true",
                     help="after warm-up run ONE eager step between cudaProfilerStart/Stop and exit "
                          "(for `ncu --profile-from-start off`; prints no bench line)")
@@ -211,6 +213,51 @@ def time_vae_decode(latents, dev, iters=3):
     return e0.elapsed_time(e1) / iters
 
 
+def time_train_step(unet, dev, rank, batch, size, iters=3, warm=2):
+    """ms per train step (tools/bench_train.py's loop) on this rank; all ranks call it together (the step holds the
+    gradient all-reduce)."""
+    import torch
+    from stable_diffusion_pytorch_b200 import ops
+    from stable_diffusion_pytorch_b200.models import DDPMConfig, DDPMScheduler, LatentDiffusion
+    from stable_diffusion_pytorch_b200.training import FlatAdamW, train_step
+
+    class StubText:   # the empty-prompt embedding pred_noise asks for (CLIP weights are a download)
+        def __init__(self):
+            self.uncond = torch.randn(1, 77, 768, generator=torch.Generator().manual_seed(7)).to(dev)
+
+        def tokenize(self, prompts):
+            class T:
+                pass
+            t = T()
+            t.input_ids = torch.zeros(len(prompts), 77, dtype=torch.long)
+            return t
+
+        def encode_text(self, ids):
+            return (self.uncond.expand(ids.shape[0], -1, -1).clone(),)
+
+    unet.train()
+    ld = LatentDiffusion(unet, None, StubText(), DDPMScheduler(DDPMConfig()))
+    opt = FlatAdamW(unet.parameters())
+    g = torch.Generator().manual_seed(200 + rank)
+    x_t = torch.randn(batch, 4, size, size, generator=g).to(dev)
+    noise = torch.randn(batch, 4, size, size, generator=g).to(dev)
+    t = torch.randint(0, 1000, (batch,), generator=g).to(dev)
+    ctx = torch.randn(batch, 77, 768, generator=g).to(dev)
+    for _ in range(warm):
+        loss = train_step(ld, opt, x_t, t, ctx, noise, guidance_scale=7.5)
+    torch.cuda.synchronize()
+    l0 = ops.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        loss = train_step(ld, opt, x_t, t, ctx, noise, guidance_scale=7.5)
+    e1.record()
+    torch.cuda.synchronize()
+    info = {"steps": iters, "warmup": warm, "loss": float(loss), "launches_per_step": int((ops.launch_count() - l0) // iters),
+            "params": opt.numel, "peak_mem_gb": round(torch.cuda.max_memory_allocated() / 2**30, 2)}
+    return e0.elapsed_time(e1) / iters, info
+
+
 def kernel_rooflines(B2, size, pk):
     """Isolated timings (CUDA events, current stream) of the three dominant kernel families at the
     workload's shapes; algorithmic flops in the reference's formulation."""
@@ -338,12 +385,22 @@ def run_b200(args):
     ms_dec = torch.tensor([float("nan")], device=dev)
     if not args.no_decode and S == 64:
         ms_dec = torch.tensor([time_vae_decode(gs.x, dev)], device=dev)
+    finite = bool(torch.isfinite(gs.x.float()).all())
+    # ---- config 4: UNet train step (loss + backward + gradient all-reduce + clip + AdamW), batch 32 per GPU ----
+    ms_train = torch.tensor([float("nan")], device=dev)
+    train_info = None
+    graph_on, graph_lps = gs.graph is not None, gs.launches_per_step
+    if not args.no_train and S == 64:
+        del gs
+        torch.cuda.empty_cache()
+        ms_t, train_info = time_train_step(unet, dev, rank, args.train_batch, S)
+        ms_train = torch.tensor([ms_t], device=dev)
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         dist.all_reduce(ms_e2e, op=dist.ReduceOp.MAX)
         dist.all_reduce(ms_dec, op=dist.ReduceOp.MAX)
-    ms, ms_e2e, ms_dec = float(ms), float(ms_e2e), float(ms_dec)
-    finite = bool(torch.isfinite(gs.x.float()).all())
+        dist.all_reduce(ms_train, op=dist.ReduceOp.MAX)
+    ms, ms_e2e, ms_dec, ms_train = float(ms), float(ms_e2e), float(ms_dec), float(ms_train)
     flag = ops.debug_timeout_flag()
     if rank != 0:
         if world > 1:
@@ -374,8 +431,8 @@ def run_b200(args):
         "e2e": {"value": e2e, "unit": "latent-steps/s", "ms_per_step": ms_e2e / args.steps,
                 "h2d_bytes_per_step": x_host.numel() * 2 + ctx_host.numel() * 2,
                 "d2h_bytes_per_step": out_host.numel() * 2},
-        "gpu_launches": (gs.launches_per_step * args.steps) if gs.graph is not None else eager_launches,
-        "launches_per_step": gs.launches_per_step if gs.graph is not None else eager_launches // max(args.steps, 1),
+        "gpu_launches": (graph_lps * args.steps) if graph_on else eager_launches,
+        "launches_per_step": graph_lps if graph_on else eager_launches // max(args.steps, 1),
         "clocks": clocks,
         "roofline": {"bound": "tensor", "kernel": dom["kernel"], "achieved": dom["tflops"], "peak": pk["bf16_tflops"],
                      "unit": "TFLOP/s", "frac": dom["tflops"] / pk["bf16_tflops"], "traffic": traffic,
@@ -389,6 +446,13 @@ def run_b200(args):
             "decoder": "AutoencoderKL-shape [128,256,512,512], 64x64x4 -> 512x512x3, bf16",
             "decode_alg_tflops": 38306.0 * (B / 16.0) / ms_dec,
             "formula": "latents / (50 x ms_per_step + ms_decode), max over ranks"},
+        "train": None if ms_train != ms_train else {
+            "samples_per_sec": args.train_batch * world / (ms_train * 1e-3), "ms_per_step": ms_train,
+            "workload": f"BASELINE config 4: train_unet.py step, batch {args.train_batch}/GPU (CFG doubling -> UNet "
+                        f"batch {2 * args.train_batch}), {S}x{S} latents, random CLIP-shaped context, MSE, clip 0.1, "
+                        f"AdamW; fp32 master weights / gradients, bf16 compute",
+            "gradient_exchange": "one NCCL all-reduce of the flat fp32 gradient bucket" if world > 1 else "none (1 GPU)",
+            **(train_info or {})},
         "finite": finite, "timeout_flag": flag,
     }
     if world == 1 and not args.no_cpu_baseline:
