@@ -202,16 +202,24 @@ attn_bwd_dq_kernel(const __nv_bfloat16* __restrict__ q, long long ldq, const __n
     ab_mma_nt(dp, dof, sV[buf], lane);
     const int key_base = j * 64 + (lane & 3) * 2;
     uint32_t dsf[4][4];
+    // dS / scale = P o (dP - delta); the scale is applied once to the accumulated dQ.  Keys past m exist only in
+    // the ragged last tile: their scores are forced to -inf there (P = 0), every other tile runs unmasked.
+    if (j == n_tiles - 1 && (m & 63) != 0) {
+#pragma unroll
+      for (int t = 0; t < 8; ++t) {
+        const int key = key_base + t * 8;
+        if (key >= m) { s[t][0] = -INFINITY; s[t][2] = -INFINITY; }
+        if (key + 1 >= m) { s[t][1] = -INFINITY; s[t][3] = -INFINITY; }
+      }
+    }
 #pragma unroll
     for (int t = 0; t < 8; ++t) {
-      const int key = key_base + t * 8;
-      const bool ok0 = key < m, ok1 = key + 1 < m;
-      const float p0 = ok0 ? fast_exp2(fmaf(s[t][0], scale_log2e, -lse2[0])) : 0.f;
-      const float p1 = ok1 ? fast_exp2(fmaf(s[t][1], scale_log2e, -lse2[0])) : 0.f;
-      const float p2 = ok0 ? fast_exp2(fmaf(s[t][2], scale_log2e, -lse2[1])) : 0.f;
-      const float p3 = ok1 ? fast_exp2(fmaf(s[t][3], scale_log2e, -lse2[1])) : 0.f;
-      dsf[t >> 1][(t & 1) * 2] = pack_bf16x2(p0 * (dp[t][0] - dl0) * scale, p1 * (dp[t][1] - dl0) * scale);
-      dsf[t >> 1][(t & 1) * 2 + 1] = pack_bf16x2(p2 * (dp[t][2] - dl1) * scale, p3 * (dp[t][3] - dl1) * scale);
+      const float p0 = fast_exp2(fmaf(s[t][0], scale_log2e, -lse2[0]));
+      const float p1 = fast_exp2(fmaf(s[t][1], scale_log2e, -lse2[0]));
+      const float p2 = fast_exp2(fmaf(s[t][2], scale_log2e, -lse2[1]));
+      const float p3 = fast_exp2(fmaf(s[t][3], scale_log2e, -lse2[1]));
+      dsf[t >> 1][(t & 1) * 2] = pack_bf16x2(p0 * (dp[t][0] - dl0), p1 * (dp[t][1] - dl0));
+      dsf[t >> 1][(t & 1) * 2 + 1] = pack_bf16x2(p2 * (dp[t][2] - dl1), p3 * (dp[t][3] - dl1));
     }
     ab_mma_nn(acc, dsf, sK[buf], lane);
     cp_async_wait<0>();
@@ -222,8 +230,8 @@ attn_bwd_dq_kernel(const __nv_bfloat16* __restrict__ q, long long ldq, const __n
   for (int t = 0; t < 4; ++t) {
     const int col = t * 8 + (lane & 3) * 2;
     if (col < w) {
-      if (r0 < n) *reinterpret_cast<uint32_t*>(dqg + (long long)r0 * lddq + col) = pack_bf16x2(acc[t][0], acc[t][1]);
-      if (r1 < n) *reinterpret_cast<uint32_t*>(dqg + (long long)r1 * lddq + col) = pack_bf16x2(acc[t][2], acc[t][3]);
+      if (r0 < n) *reinterpret_cast<uint32_t*>(dqg + (long long)r0 * lddq + col) = pack_bf16x2(acc[t][0] * scale, acc[t][1] * scale);
+      if (r1 < n) *reinterpret_cast<uint32_t*>(dqg + (long long)r1 * lddq + col) = pack_bf16x2(acc[t][2] * scale, acc[t][3] * scale);
     }
   }
 }
@@ -235,7 +243,7 @@ attn_bwd_dkv_kernel(const __nv_bfloat16* __restrict__ q, long long ldq, const __
                     long long lddk, __nv_bfloat16* __restrict__ dv, long long lddv, int n, int m, int d, int hp, float scale,
                     float scale_log2e) {
   __shared__ __align__(16) __nv_bfloat16 sK[64 * kAbPitch], sV[64 * kAbPitch], sQ[2][64 * kAbPitch], sdO[2][64 * kAbPitch];
-  __shared__ float sLse[2][64], sDelta[2][64];
+  __shared__ __align__(8) float sLse[2][64], sDelta[2][64];
   const int b = blockIdx.z, h = blockIdx.y, k0 = blockIdx.x * 64, heads = gridDim.y;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int w = hp >= 32 ? 32 : d;
@@ -259,7 +267,7 @@ attn_bwd_dkv_kernel(const __nv_bfloat16* __restrict__ q, long long ldq, const __
     stage_rows<kAbPitch>(sdO[buf], dog, lddo, row0, n, 64, d);
     if (threadIdx.x < 64) {
       const int r = row0 + threadIdx.x;
-      sLse[buf][threadIdx.x] = r < n ? lg[r] : 0.f;      // rows past n: Q = dO = 0, so P^T = 1 meets only zeros
+      sLse[buf][threadIdx.x] = r < n ? -lg[r] : 0.f;     // stored negated; rows past n: Q = dO = 0, so P^T = 1 meets only zeros
       sDelta[buf][threadIdx.x] = r < n ? dg[r] : 0.f;
     }
   };
@@ -289,17 +297,18 @@ attn_bwd_dkv_kernel(const __nv_bfloat16* __restrict__ q, long long ldq, const __
     ab_mma_nt(st, kf, sQ[buf], lane);       // S^T  [16 keys x 64 queries]
     ab_mma_nt(dpt, vf, sdO[buf], lane);     // dP^T
     uint32_t pf[4][4], dsf[4][4];
+    // dS^T / scale = P^T o (dP^T - delta); the scale is applied once to the accumulated dK
 #pragma unroll
     for (int t = 0; t < 8; ++t) {
       const int qc = t * 8 + (lane & 3) * 2;
-      const float l0 = sLse[buf][qc], l1 = sLse[buf][qc + 1];
-      const float e0 = sDelta[buf][qc], e1 = sDelta[buf][qc + 1];
-      const float p0 = fast_exp2(fmaf(st[t][0], scale_log2e, -l0)), p1 = fast_exp2(fmaf(st[t][1], scale_log2e, -l1));
-      const float p2 = fast_exp2(fmaf(st[t][2], scale_log2e, -l0)), p3 = fast_exp2(fmaf(st[t][3], scale_log2e, -l1));
+      const float2 l = *reinterpret_cast<const float2*>(&sLse[buf][qc]);      // negated log-sum-exp
+      const float2 e = *reinterpret_cast<const float2*>(&sDelta[buf][qc]);
+      const float p0 = fast_exp2(fmaf(st[t][0], scale_log2e, l.x)), p1 = fast_exp2(fmaf(st[t][1], scale_log2e, l.y));
+      const float p2 = fast_exp2(fmaf(st[t][2], scale_log2e, l.x)), p3 = fast_exp2(fmaf(st[t][3], scale_log2e, l.y));
       pf[t >> 1][(t & 1) * 2] = pack_bf16x2(p0, p1);
       pf[t >> 1][(t & 1) * 2 + 1] = pack_bf16x2(p2, p3);
-      dsf[t >> 1][(t & 1) * 2] = pack_bf16x2(p0 * (dpt[t][0] - e0) * scale, p1 * (dpt[t][1] - e1) * scale);
-      dsf[t >> 1][(t & 1) * 2 + 1] = pack_bf16x2(p2 * (dpt[t][2] - e0) * scale, p3 * (dpt[t][3] - e1) * scale);
+      dsf[t >> 1][(t & 1) * 2] = pack_bf16x2(p0 * (dpt[t][0] - e.x), p1 * (dpt[t][1] - e.y));
+      dsf[t >> 1][(t & 1) * 2 + 1] = pack_bf16x2(p2 * (dpt[t][2] - e.x), p3 * (dpt[t][3] - e.y));
     }
     ab_mma_nn(dva, pf, sdO[buf], lane);     // dV += P^T dO
     ab_mma_nn(dka, dsf, sQ[buf], lane);     // dK += dS^T Q
@@ -314,11 +323,11 @@ attn_bwd_dkv_kernel(const __nv_bfloat16* __restrict__ q, long long ldq, const __
     const int col = t * 8 + (lane & 3) * 2;
     if (col < w) {
       if (r0 < m) {
-        *reinterpret_cast<uint32_t*>(dkg + (long long)r0 * lddk + col) = pack_bf16x2(dka[t][0], dka[t][1]);
+        *reinterpret_cast<uint32_t*>(dkg + (long long)r0 * lddk + col) = pack_bf16x2(dka[t][0] * scale, dka[t][1] * scale);
         *reinterpret_cast<uint32_t*>(dvg + (long long)r0 * lddv + col) = pack_bf16x2(dva[t][0], dva[t][1]);
       }
       if (r1 < m) {
-        *reinterpret_cast<uint32_t*>(dkg + (long long)r1 * lddk + col) = pack_bf16x2(dka[t][2], dka[t][3]);
+        *reinterpret_cast<uint32_t*>(dkg + (long long)r1 * lddk + col) = pack_bf16x2(dka[t][2] * scale, dka[t][3] * scale);
         *reinterpret_cast<uint32_t*>(dvg + (long long)r1 * lddv + col) = pack_bf16x2(dva[t][2], dva[t][3]);
       }
     }
