@@ -198,14 +198,16 @@ def time_vae_decode(latents, dev, iters=3):
                 p.copy_(torch.randn(p.shape, generator=g) * 0.02)
     vae = vae.to(dev)
     z = latents.detach().clone()
+    chunks = list(z.split(16))      # config 3 is a batch of 16; larger shards decode 16 at a time (2 GB activations each)
     with torch.no_grad():
         for _ in range(2):
-            vae.decode(z)
+            vae.decode(chunks[0])
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         torch.cuda.synchronize()
         e0.record()
         for _ in range(iters):
-            y = vae.decode(z)
+            for c in chunks:
+                y = vae.decode(c)
         e1.record()
         torch.cuda.synchronize()
     del vae, y
