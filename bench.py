@@ -221,7 +221,7 @@ def time_train_step(unet, dev, rank, batch, size, iters=3, warm=2):
     import torch
     from stable_diffusion_pytorch_b200 import ops
     from stable_diffusion_pytorch_b200.models import DDPMConfig, DDPMScheduler, LatentDiffusion
-    from stable_diffusion_pytorch_b200.training import FlatAdamW, train_step
+    from stable_diffusion_pytorch_b200.training import FlatAdamW, GraphedTrainStep
 
     class StubText:   # the empty-prompt embedding pred_noise asks for (CLIP weights are a download)
         def __init__(self):
@@ -245,17 +245,18 @@ def time_train_step(unet, dev, rank, batch, size, iters=3, warm=2):
     noise = torch.randn(batch, 4, size, size, generator=g).to(dev)
     t = torch.randint(0, 1000, (batch,), generator=g).to(dev)
     ctx = torch.randn(batch, 77, 768, generator=g).to(dev)
+    gts = GraphedTrainStep(ld, opt, batch, (size, size), guidance_scale=7.5)   # fwd+bwd graph, NCCL, update graph
+    gts.capture()
     for _ in range(warm):
-        loss = train_step(ld, opt, x_t, t, ctx, noise, guidance_scale=7.5)
+        loss = gts.step(x_t, t, ctx, noise)
     torch.cuda.synchronize()
-    l0 = ops.launch_count()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(iters):
-        loss = train_step(ld, opt, x_t, t, ctx, noise, guidance_scale=7.5)
+        loss = gts.step(x_t, t, ctx, noise)
     e1.record()
     torch.cuda.synchronize()
-    info = {"steps": iters, "warmup": warm, "loss": float(loss), "launches_per_step": int((ops.launch_count() - l0) // iters),
+    info = {"steps": iters, "warmup": warm, "loss": float(loss), "cuda_graph": True,
             "params": opt.numel, "peak_mem_gb": round(torch.cuda.max_memory_allocated() / 2**30, 2)}
     return e0.elapsed_time(e1) / iters, info
 

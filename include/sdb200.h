@@ -272,6 +272,11 @@ int sdb_sumsq(const float* x, int64_t n, float* out_zeroed, void* stream);
 int sdb_adamw(float* p, const float* g, float* m, float* v, int64_t n, float lr, float beta1, float beta2,
               float eps, float weight_decay, int step, float grad_scale, const float* gnorm_sq_or_null,
               float max_norm, void* stream);
+/* sdb_adamw with the per-step scalars in device memory: hyper_dev = {lr, 1 - beta1^step, 1 - beta2^step}; lets a
+ * captured CUDA graph of the whole train step be replayed with a new step count / learning rate. */
+int sdb_adamw_dev(float* p, const float* g, float* m, float* v, int64_t n, const float* hyper_dev, float beta1,
+                  float beta2, float eps, float weight_decay, float grad_scale, const float* gnorm_sq_or_null,
+                  float max_norm, void* stream);
 
 /* ---- CLIP text encoder pieces (models/clip_model.py:56-96 wraps transformers.CLIPTextModel) ----
  * out[b*L + l, :] = token_embedding[ids[b, l]] + position_embedding[l]  (CLIPTextEmbeddings); ids int64. */

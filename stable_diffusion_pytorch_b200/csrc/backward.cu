@@ -333,6 +333,31 @@ __global__ void adamw_kernel(float* __restrict__ p, const float* __restrict__ g,
   }
 }
 
+// the same update with the per-step scalars (lr, 1 - beta1^t, 1 - beta2^t) read from device memory, so that a
+// captured CUDA graph of the train step can be replayed with a new step count / learning rate
+__global__ void adamw_dev_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
+                                 float* __restrict__ v, long long n, const float* __restrict__ hyper, float b1, float b2,
+                                 float eps, float wd, float grad_scale, const float* __restrict__ gnorm_sq,
+                                 float max_norm) {
+  const float lr = hyper[0], bc1 = hyper[1], bc2 = hyper[2];
+  float clip = 1.0f;
+  if (gnorm_sq != nullptr && max_norm > 0.f) {
+    const float norm = sqrtf(*gnorm_sq) * grad_scale;
+    clip = fminf(1.0f, max_norm / (norm + 1e-6f));
+  }
+  const float gs = grad_scale * clip;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (long long)gridDim.x * blockDim.x) {
+    const float gi = g[i] * gs;
+    float pi = p[i] * (1.0f - lr * wd);
+    const float mi = fmaf(b1, m[i], (1.0f - b1) * gi);
+    const float vi = fmaf(b2, v[i], (1.0f - b2) * gi * gi);
+    m[i] = mi;
+    v[i] = vi;
+    pi -= lr * (mi / bc1) / (sqrtf(vi / bc2) + eps);
+    p[i] = pi;
+  }
+}
+
 static inline int bw_grid(long long n, int threads) {
   long long want = (n + threads - 1) / threads;
   long long cap = (long long)sdb_num_sms() * 16;
@@ -491,6 +516,16 @@ extern "C" int sdb_adamw(float* p, const float* g, float* m, float* v, int64_t n
   const float bc1 = 1.0f - powf(beta1, (float)step), bc2 = 1.0f - powf(beta2, (float)step);
   adamw_kernel<<<bw_grid(n, 256), 256, 0, sdb_stream(stream)>>>(p, g, m, v, n, lr, beta1, beta2, eps, weight_decay, bc1, bc2,
                                                               grad_scale, gnorm_sq_or_null, max_norm);
+  SDB_LAUNCH_OK();
+  return SDB_OK;
+}
+
+extern "C" int sdb_adamw_dev(float* p, const float* g, float* m, float* v, int64_t n, const float* hyper_dev, float beta1,
+                             float beta2, float eps, float weight_decay, float grad_scale,
+                             const float* gnorm_sq_or_null, float max_norm, void* stream) {
+  SDB_CHECK_ARG(p && g && m && v && hyper_dev && n > 0, "adamw_dev: bad args");
+  adamw_dev_kernel<<<bw_grid(n, 256), 256, 0, sdb_stream(stream)>>>(p, g, m, v, n, hyper_dev, beta1, beta2, eps,
+                                                                  weight_decay, grad_scale, gnorm_sq_or_null, max_norm);
   SDB_LAUNCH_OK();
   return SDB_OK;
 }

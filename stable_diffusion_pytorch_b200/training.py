@@ -135,3 +135,90 @@ def train_step(model, opt: FlatAdamW, x_t: Tensor, timesteps: Tensor, text_condi
         opt.step(world, lr)
         opt.zero_grad()
     return loss.detach()
+
+
+class GraphedTrainStep:
+    """The train step replayed from CUDA graphs (the launch-bound case: at the reference's default 8x8 training
+    latents a step is ~1 100 kernel launches of a few microseconds each).
+
+    Graph A = loss + backward into the flat gradient bucket (static input tensors, weights re-packed inside the graph
+    so it always sees the current parameters); the data-parallel all-reduce runs between the graphs on the same
+    stream (NCCL, not captured); graph B = gradient norm + clip + AdamW + clearing the bucket, with the learning rate
+    and the bias corrections of the step count read from a 3-float device buffer that is refreshed before every
+    replay.  ``step(x_t, t, ctx, noise)`` copies the batch into the static tensors and returns the (device) loss.
+    """
+
+    def __init__(self, model, opt: FlatAdamW, batch: int, latent_hw, ctx_len: int = 77, ctx_dim: int = 768,
+                 latent_channels: int = 4, guidance_scale: float = 7.5, group=None, warmup: int = 3):
+        dev = opt.flat.device
+        H, W = latent_hw
+        self.model, self.opt, self.group, self.g = model, opt, group, guidance_scale
+        self.x_t = torch.zeros(batch, latent_channels, H, W, device=dev)
+        self.noise = torch.zeros_like(self.x_t)
+        self.t = torch.zeros(batch, dtype=torch.long, device=dev)
+        self.ctx = torch.zeros(batch, ctx_len, ctx_dim, device=dev)
+        self.hyper = torch.zeros(3, device=dev)
+        self.world = dist.get_world_size(group) if (dist.is_available() and dist.is_initialized()) else 1
+        self.graph_a = self.graph_b = None
+        self.loss = None
+        self._warmup = warmup
+
+    def _fwd_bwd(self):
+        loss = diffusion_loss(self.model, self.x_t, self.t, self.ctx, self.noise, self.g)
+        loss.backward()
+        return loss.detach()
+
+    def _update(self):
+        o, c = self.opt, self.opt.cfg
+        o.gnorm_sq.zero_()
+        ops.sumsq(o.grad, o.gnorm_sq)
+        check(_lib.lib().sdb_adamw_dev(ops._ptr(o.flat), ops._ptr(o.grad), ops._ptr(o.m), ops._ptr(o.v), o.numel,
+                                       ops._ptr(self.hyper), c.adam_beta1, c.adam_beta2, c.adam_eps, c.adam_weight_decay,
+                                       1.0 / self.world, ops._ptr(o.gnorm_sq), c.max_grad_norm, ops._stream()), "adamw_dev")
+        o.grad.zero_()
+
+    def _set_hyper(self, lr: Optional[float]) -> None:
+        o, c = self.opt, self.opt.cfg
+        o.step_count += 1
+        # a fresh pageable host tensor per step: the H2D copy is staged before copy_ returns, so the next step cannot
+        # overwrite values a queued copy has not read yet
+        self.hyper.copy_(torch.tensor([c.learning_rate if lr is None else lr, 1.0 - c.adam_beta1 ** o.step_count,
+                                       1.0 - c.adam_beta2 ** o.step_count], dtype=torch.float32))
+
+    def capture(self) -> None:
+        """Warm-up on a side stream (allocator, lazy inits), then capture the two graphs.  The warm-up steps do not
+        touch the parameters: their gradients are discarded."""
+        o = self.opt
+        s = torch.cuda.Stream()
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            for _ in range(self._warmup):
+                self._fwd_bwd()
+                o.grad.zero_()
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize()
+        o._collect_strays()
+        self.graph_a = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph_a):
+            self.loss = self._fwd_bwd()
+        o.grad.zero_()                      # the capture pass itself does not run; keep the bucket clean anyway
+        self.graph_b = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph_b):
+            self._update()
+        torch.cuda.synchronize()
+
+    def step(self, x_t: Tensor, timesteps: Tensor, text_condition: Tensor, noise: Tensor, sync: bool = True,
+             lr: Optional[float] = None) -> Tensor:
+        if self.graph_a is None:
+            self.capture()
+        self.x_t.copy_(x_t, non_blocking=True)
+        self.t.copy_(timesteps, non_blocking=True)
+        self.ctx.copy_(text_condition, non_blocking=True)
+        self.noise.copy_(noise, non_blocking=True)
+        self.graph_a.replay()
+        if sync:
+            if self.world > 1:
+                dist.all_reduce(self.opt.grad, op=dist.ReduceOp.SUM, group=self.group)
+            self._set_hyper(lr)
+            self.graph_b.replay()
+        return self.loss

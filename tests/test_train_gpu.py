@@ -386,3 +386,32 @@ def test_train_step_gradients_vs_oracle_default_unet():
     print(f"default UNet 8x8: loss {float(loss):.5f} vs {float(rl):.5f}; flat gradient rel-L2 {e:.3e}")
     assert e < 0.1
     assert abs(float(opt.grad_norm()) - float(flat_r.norm())) < 3e-2 * float(flat_r.norm())
+
+
+@pytest.mark.parametrize("name", list(cases.TRAIN_CASES)[:1])
+def test_graphed_train_step_tracks_reference_golden(golden_train, name):
+    """GraphedTrainStep (two CUDA graphs + device-side AdamW scalars) must reproduce the reference's loss sequence:
+    every replay sees the parameters the previous replay wrote and the bias corrections of the current step."""
+    from stable_diffusion_pytorch_b200.training import FlatAdamW, GraphedTrainStep, OptimConfig
+    cfg, seed, B, H, W, n_steps, g = cases.TRAIN_CASES[name]
+    batches, uncond = cases.train_batches(cfg, B, H, W, seed, n_steps)
+    ld, sd = build_ld(cfg, seed, uncond)
+    opt = FlatAdamW(ld.unet.parameters(), OptimConfig(learning_rate=cases.TRAIN_LR, adam_weight_decay=cases.TRAIN_WD,
+                                                      max_grad_norm=cases.TRAIN_CLIP))
+    gts = GraphedTrainStep(ld, opt, B, (H, W), ctx_len=batches[0][2].shape[1], ctx_dim=cfg.context_dim,
+                           latent_channels=cfg.latent_channels, guidance_scale=g)
+    gts.capture()
+    before = opt.flat.clone()
+    assert float(opt.grad.abs().max()) == 0.0 and opt.step_count == 0      # capture / warm-up left no trace
+    G = golden_train
+    for i, (x_t, t, ctx, noise) in enumerate(batches):
+        loss = float(gts.step(x_t.to(DEV), t.to(DEV), ctx.to(DEV), noise.to(DEV)))
+        print(f"graphed train {name} step {i}: loss {loss:.5f} (ref {G[f'train_{name}_loss'][i]:.5f})")
+        assert abs(loss - G[f"train_{name}_loss"][i]) < 2e-2 * G[f"train_{name}_loss"][i]
+    assert opt.step_count == len(batches) and float(opt.grad.abs().max()) == 0.0
+    pd = dict(ld.unet.named_parameters())
+    ref_delta = dict(zip([str(k) for k in G[f"train_{name}_names"]], G[f"train_{name}_deltanorms"]))
+    for k in cases.TRAIN_PROBE:
+        delta = float((pd[k].detach().cpu() - sd[k]).norm())
+        assert abs(delta - ref_delta[k]) < 2e-2 * ref_delta[k], k
+    assert float((opt.flat - before).abs().max()) > 0

@@ -43,6 +43,7 @@ def main():
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--guidance", type=float, default=7.5)
+    ap.add_argument("--graph", action="store_true", help="replay the step from CUDA graphs (GraphedTrainStep)")
     args = ap.parse_args()
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -55,7 +56,7 @@ def main():
 
     from stable_diffusion_pytorch_b200 import ops
     from stable_diffusion_pytorch_b200.models import (DDPMConfig, DDPMScheduler, LatentDiffusion, UNetModel, UnetConfig)
-    from stable_diffusion_pytorch_b200.training import FlatAdamW, train_step
+    from stable_diffusion_pytorch_b200.training import FlatAdamW, GraphedTrainStep, train_step
 
     torch.manual_seed(0)
     unet = UNetModel(4, 32, UnetConfig(dropout=0.0)).train()
@@ -74,7 +75,14 @@ def main():
     t = torch.randint(0, 1000, (B,), generator=g).to(dev)
     ctx = torch.randn(B, 77, 768, generator=g).to(dev)
 
+    gts = None
+    if args.graph:
+        gts = GraphedTrainStep(ld, opt, B, (S, S), guidance_scale=args.guidance)
+        gts.capture()
+
     def step():
+        if gts is not None:
+            return gts.step(x_t, t, ctx, noise)
         return train_step(ld, opt, x_t, t, ctx, noise, guidance_scale=args.guidance)
 
     for _ in range(args.warmup):
@@ -102,7 +110,7 @@ def main():
             "dtype": "bf16 compute, fp32 master weights / grads / AdamW", "data": "synthetic",
             "config": {"workload": f"T1 train step: repo-default UNet, per-GPU batch {B}, latent {S}x{S}, CFG doubling "
                                    f"(guidance {args.guidance}), MSE, clip 0.1, AdamW", "params": opt.numel},
-            "loss": round(float(loss), 5), "sdb_launches_per_step": int(launches),
+            "loss": round(float(loss), 5), "sdb_launches_per_step": int(launches), "cuda_graph": bool(args.graph),
             "peak_mem_gb": round(torch.cuda.max_memory_allocated() / 2**30, 2)}))
     if os.environ.get("PROFILE") and rank == 0:
         from torch.profiler import ProfilerActivity, profile
