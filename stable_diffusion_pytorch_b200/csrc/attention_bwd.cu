@@ -19,6 +19,60 @@ namespace sdb {
 
 constexpr int kAbPitch = 40;   // 32 + 8 bf16: 80-byte rows, ldmatrix conflict-free
 
+// Staging map of a 64-row operand tile: which (row, column) granules this thread copies, computed ONCE per kernel
+// (the generic stage_rows divides by the row width for every granule of every tile -- a third of the instructions
+// of these kernels before).  wide = 32-column rows at 16-byte alignment (the head-padded layout): two 16-byte
+// cp.async per thread and tile; otherwise 8-byte granules, up to four per thread.
+struct AbRowMap {
+  int rc[4];   // row << 8 | column, or -1
+  int wide;
+};
+__device__ __forceinline__ AbRowMap ab_row_map(int cols, bool wide) {
+  AbRowMap m;
+  m.wide = wide ? 1 : 0;
+  if (wide) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int i = threadIdx.x + k * kAttThreads;
+      m.rc[k] = k < 2 ? (((i >> 2) << 8) | ((i & 3) * 8)) : -1;
+    }
+  } else {
+    const int cpr = cols >> 2;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const int i = threadIdx.x + k * kAttThreads;
+      const int r = i / cpr;
+      m.rc[k] = (r < 64) ? ((r << 8) | ((i - r * cpr) * 4)) : -1;
+    }
+  }
+  return m;
+}
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(src) : "memory");
+}
+__device__ __forceinline__ bool ab_wide_ok(const void* g, long long ld, int cols) {
+  return cols == 32 && (ld & 7) == 0 && (reinterpret_cast<uintptr_t>(g) & 15) == 0;
+}
+// rows [row0, row0 + 64) of g -> smem tile; rows >= valid_rows are zero-filled
+__device__ __forceinline__ void ab_stage(__nv_bfloat16* s, const __nv_bfloat16* g, long long ld, int row0, int valid_rows,
+                                         const AbRowMap& m) {
+#pragma unroll
+  for (int k = 0; k < 4; ++k) {
+    if (m.rc[k] < 0) continue;
+    const int r = m.rc[k] >> 8, c = m.rc[k] & 255;
+    __nv_bfloat16* dst = s + r * kAbPitch + c;
+    const bool live = row0 + r < valid_rows;
+    const __nv_bfloat16* src = g + (long long)(row0 + r) * ld + c;
+    if (m.wide) {
+      if (live) cp_async16(smem_u32(dst), src);
+      else *reinterpret_cast<uint4*>(dst) = make_uint4(0u, 0u, 0u, 0u);
+    } else {
+      if (live) cp_async8(smem_u32(dst), src);
+      else *reinterpret_cast<uint2*>(dst) = make_uint2(0u, 0u);
+    }
+  }
+}
+
 // A-operand fragments (16 rows x 32 cols) of the rows [row0, row0+16) of a staged tile
 __device__ __forceinline__ void ab_load_a(const __nv_bfloat16* s, int row0, int lane, uint32_t (&f)[2][4]) {
 #pragma unroll
@@ -87,11 +141,12 @@ attn_bwd_dq_kernel(const __nv_bfloat16* __restrict__ q, long long ldq, const __n
   }
   __syncthreads();
   const int n_tiles = (m + 63) / 64;
+  const AbRowMap map_k = ab_row_map(w, ab_wide_ok(kg, ldk, w) && ab_wide_ok(vg, ldv, w));
   // O is only needed for delta: stage it where the first V tile will go later
   stage_rows<kAbPitch>(sQ, qg, ldq, q0, n, 64, w);
   stage_rows<kAbPitch>(sdO, dog, lddo, q0, n, 64, d);
   stage_rows<kAbPitch>(sV[1], og, ldo, q0, n, 64, d);
-  stage_rows<kAbPitch>(sK[0], kg, ldk, 0, m, 64, w);
+  ab_stage(sK[0], kg, ldk, 0, m, map_k);
   cp_async_commit();
   cp_async_wait<0>();
   __syncthreads();
@@ -124,7 +179,7 @@ attn_bwd_dq_kernel(const __nv_bfloat16* __restrict__ q, long long ldq, const __n
   for (int j = 0; j < (have_lse ? 0 : n_tiles); ++j) {
     const int buf = j & 1;
     if (j + 1 < n_tiles) {
-      stage_rows<kAbPitch>(sK[buf ^ 1], kg, ldk, (j + 1) * 64, m, 64, w);
+      ab_stage(sK[buf ^ 1], kg, ldk, (j + 1) * 64, m, map_k);
       cp_async_commit();
     }
     ab_mma_nt(s, qf, sK[buf], lane);
@@ -182,8 +237,8 @@ attn_bwd_dq_kernel(const __nv_bfloat16* __restrict__ q, long long ldq, const __n
   const float dl0 = sDelta[warp * 16 + (lane >> 2)], dl1 = sDelta[warp * 16 + (lane >> 2) + 8];
 
   // ---- pass 2: dQ -----------------------------------------------------------------------------------
-  stage_rows<kAbPitch>(sK[0], kg, ldk, 0, m, 64, w);
-  stage_rows<kAbPitch>(sV[0], vg, ldv, 0, m, 64, w);
+  ab_stage(sK[0], kg, ldk, 0, m, map_k);
+  ab_stage(sV[0], vg, ldv, 0, m, map_k);
   cp_async_commit();
   cp_async_wait<0>();
   __syncthreads();
@@ -193,8 +248,8 @@ attn_bwd_dq_kernel(const __nv_bfloat16* __restrict__ q, long long ldq, const __n
   for (int j = 0; j < n_tiles; ++j) {
     const int buf = j & 1;
     if (j + 1 < n_tiles) {
-      stage_rows<kAbPitch>(sK[buf ^ 1], kg, ldk, (j + 1) * 64, m, 64, w);
-      stage_rows<kAbPitch>(sV[buf ^ 1], vg, ldv, (j + 1) * 64, m, 64, w);
+      ab_stage(sK[buf ^ 1], kg, ldk, (j + 1) * 64, m, map_k);
+      ab_stage(sV[buf ^ 1], vg, ldv, (j + 1) * 64, m, map_k);
       cp_async_commit();
     }
     float dp[8][4];
@@ -262,9 +317,11 @@ attn_bwd_dkv_kernel(const __nv_bfloat16* __restrict__ q, long long ldq, const __
     }
   }
   __syncthreads();
+  const AbRowMap map_q = ab_row_map(w, ab_wide_ok(qg, ldq, w));
+  const AbRowMap map_do = ab_row_map(d, ab_wide_ok(dog, lddo, d));
   auto stage_q = [&](int buf, int row0) {
-    stage_rows<kAbPitch>(sQ[buf], qg, ldq, row0, n, 64, w);
-    stage_rows<kAbPitch>(sdO[buf], dog, lddo, row0, n, 64, d);
+    ab_stage(sQ[buf], qg, ldq, row0, n, map_q);
+    ab_stage(sdO[buf], dog, lddo, row0, n, map_do);
     if (threadIdx.x < 64) {
       const int r = row0 + threadIdx.x;
       sLse[buf][threadIdx.x] = r < n ? -lg[r] : 0.f;     // stored negated; rows past n: Q = dO = 0, so P^T = 1 meets only zeros

@@ -80,3 +80,48 @@ def test_errors_mirror_reference_asserts():
     v = AutoEncoderKL(AutoencoderConfig())
     with pytest.raises(AssertionError, match="Expected latent"):
         v.decode(torch.zeros(1, 3, 8, 8))
+
+
+def test_precision_context_and_pack_cache_follow_compute_dtype():
+    """precision("fp32") (the parity mode) is scoped, validated, and re-packs cached operands."""
+    import torch
+    import stable_diffusion_pytorch_b200 as sdb
+    from stable_diffusion_pytorch_b200 import _pack
+    assert sdb.compute_dtype() == torch.bfloat16
+    w = torch.nn.Parameter(torch.randn(8, 4))
+    cache = _pack.PackCache()
+    a = cache.get("w", [w], lambda: _pack.linear_w(w))
+    assert a.dtype == torch.bfloat16 and cache.get("w", [w], lambda: _pack.linear_w(w)) is a
+    with sdb.precision("fp32"):
+        assert sdb.compute_dtype() == torch.float32
+        b = cache.get("w", [w], lambda: _pack.linear_w(w))
+        assert b.dtype == torch.float32 and torch.equal(b, w.detach())
+        with sdb.precision(torch.bfloat16):
+            assert sdb.compute_dtype() == torch.bfloat16
+        assert sdb.compute_dtype() == torch.float32
+    assert sdb.compute_dtype() == torch.bfloat16
+    assert cache.get("w", [w], lambda: _pack.linear_w(w)).dtype == torch.bfloat16
+    import pytest
+    with pytest.raises(ValueError):
+        sdb.set_precision("fp16")
+
+
+def test_clip_text_encoder_keys_match_transformers_names():
+    """CLIPTextEncoder's parameter tree carries the transformers.CLIPTextModel key names (oracle enumeration)."""
+    from oracle import sd_oracle as O
+    from stable_diffusion_pytorch_b200.models import CLIPModel, CLIPTextEncoder, ClipTextConfig
+    cfg = O.ClipTextCfg(vocab_size=100, hidden_size=64, intermediate_size=128, num_hidden_layers=2, num_attention_heads=2)
+    m = CLIPTextEncoder(ClipTextConfig(vocab_size=100, hidden_size=64, intermediate_size=128, num_hidden_layers=2,
+                                       num_attention_heads=2))
+    want = O.clip_text_param_shapes(cfg)
+    got = {k: tuple(v.shape) for k, v in m.state_dict().items()}
+    assert got == want
+    sd = O.seeded_state_dict(want, 1)
+    sd["text_model.embeddings.position_ids"] = torch.arange(77)[None]     # buffer of older transformers releases
+    m.load_state_dict(sd, strict=True)
+    import pytest
+    with pytest.raises(RuntimeError):
+        CLIPModel(ClipTextConfig(vocab_size=100, hidden_size=64, intermediate_size=128, num_hidden_layers=1,
+                                 num_attention_heads=2)).tokenize("a prompt")        # no tokenizer given
+    with pytest.raises(RuntimeError):
+        m(torch.zeros(1, 77, dtype=torch.long))                                        # CPU module: no fallback
