@@ -56,6 +56,36 @@ __global__ void colsum_kernel(const T* __restrict__ x, long long ld, long long r
   }
 }
 
+// bf16, cols % 8 == 0 (<= 2048), 16-byte aligned rows: every thread owns one 8-column vector of a row (one 16-byte
+// load), the block walks 256 / (cols / 8) rows per pass -- full 128-byte lines instead of 64-byte column strips.
+// grid (row splits, groups).
+__global__ void __launch_bounds__(256) colsum_vec8_kernel(const __nv_bfloat16* __restrict__ x, long long ld,
+                                                          long long rows_per_group, int cols, float* __restrict__ out) {
+  __shared__ float sacc[2048];
+  const int vecs = cols >> 3;
+  const int rpp = 256 / vecs;
+  const int v = threadIdx.x % vecs, rr = threadIdx.x / vecs;
+  const int g = blockIdx.y;
+  for (int c = threadIdx.x; c < cols; c += 256) sacc[c] = 0.f;
+  __syncthreads();
+  const long long per = (rows_per_group + gridDim.x - 1) / gridDim.x;
+  const long long r0 = (long long)blockIdx.x * per, r1 = r0 + per < rows_per_group ? r0 + per : rows_per_group;
+  if (rr < rpp) {
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    const __nv_bfloat16* base = x + (long long)g * rows_per_group * ld + v * 8;
+    for (long long r = r0 + rr; r < r1; r += rpp) {
+      const uint4 u = __ldg(reinterpret_cast<const uint4*>(base + r * ld));
+      const float2 a = unpack_bf16x2(u.x), b = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
+      acc[0] += a.x; acc[1] += a.y; acc[2] += b.x; acc[3] += b.y;
+      acc[4] += c.x; acc[5] += c.y; acc[6] += d.x; acc[7] += d.y;
+    }
+#pragma unroll
+    for (int j = 0; j < 8; ++j) atomicAdd(&sacc[v * 8 + j], acc[j]);
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < cols; c += 256) atomicAdd(out + (long long)g * cols + c, sacc[c]);
+}
+
 // ---- GEGLU on pair-interleaved columns (a0, a1, g0, g1, ...): forward and backward -----------------
 __device__ __forceinline__ float gelu_exact(float g) { return 0.5f * g * (1.0f + erff(g * 0.70710678118654752440f)); }
 __device__ __forceinline__ float gelu_grad(float g) {
@@ -372,6 +402,17 @@ extern "C" int sdb_colsum(const void* x, int dtype, int64_t ld, int64_t groups, 
                           float* out_zeroed, void* stream) {
   SDB_CHECK_ARG(x && out_zeroed && groups > 0 && rows_per_group > 0 && cols > 0 && ld >= cols, "colsum: bad args");
   SDB_CHECK_ARG(groups <= 65535, "colsum: too many groups");
+  if (dtype == SDB_BF16 && cols % 8 == 0 && cols <= 2048 && ld % 8 == 0 && ((uintptr_t)x & 15) == 0) {
+    const int rpp = 256 / (cols / 8);
+    long long sp = (rows_per_group + (long long)rpp * 8 - 1) / ((long long)rpp * 8);   // >= 8 passes per block
+    long long cap = (4LL * sdb_num_sms() + groups - 1) / groups;
+    if (sp > cap) sp = cap;
+    if (sp < 1) sp = 1;
+    colsum_vec8_kernel<<<dim3((unsigned)sp, (unsigned)groups), 256, 0, sdb_stream(stream)>>>(
+        (const __nv_bfloat16*)x, ld, rows_per_group, cols, out_zeroed);
+    SDB_LAUNCH_OK();
+    return SDB_OK;
+  }
   long long splits = rows_per_group / 256;
   if (splits < 1) splits = 1;
   if (splits > 64) splits = 64;

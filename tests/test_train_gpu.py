@@ -415,3 +415,17 @@ def test_graphed_train_step_tracks_reference_golden(golden_train, name):
         delta = float((pd[k].detach().cpu() - sd[k]).norm())
         assert abs(delta - ref_delta[k]) < 2e-2 * ref_delta[k], k
     assert float((opt.flat - before).abs().max()) > 0
+
+
+@pytest.mark.parametrize("rows,cols,groups,ld_extra", [(4096, 160, 1, 0), (1000, 1280, 1, 0), (64 * 37, 320, 64, 0),
+                                                        (513, 24, 3, 8), (300, 20, 2, 0), (77, 2056, 1, 0)])
+def test_colsum_bias_and_temb_gradients(rows, cols, groups, ld_extra):
+    """Column sums behind every bias / time-embedding gradient: the 16-byte vector kernel and the strip fallback."""
+    from stable_diffusion_pytorch_b200 import autograd_ops as ag
+    g = torch.Generator().manual_seed(rows + cols)
+    full = torch.randn(rows, cols + ld_extra, generator=g).bfloat16().to(DEV)
+    x = full[:, :cols]
+    out = ag.colsum(x, groups=groups)
+    ref = x.double().reshape(groups, rows // groups, cols).sum(1)
+    assert tuple(out.shape) == (groups, cols)
+    assert float((out.double() - ref).norm() / ref.norm()) < 1e-5
