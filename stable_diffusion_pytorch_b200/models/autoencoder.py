@@ -156,3 +156,11 @@ class AutoEncoderKL(nn.Module):
         _pack.require_cuda(latent, "AutoEncoderKL.decode")
         z = ops.conv1x1_nchw_small(latent, *self._thin_conv("pq", self.post_quant_conv))
         return self.decoder(z).as_subclass(DecodedImage)
+
+    @torch.no_grad()
+    def decode_uint8(self, latent: Tensor, chunk: int = 16) -> Tensor:
+        """``decode`` followed by the reference's ``detransform`` (utils/prepare_dataset.py:145-150: (x + 1) / 2,
+        clip, * 255, uint8) on the device: [B, H, W, C] uint8, PNG-ready, a quarter of the fp32 image bytes -- what the
+        multi-GPU image gather moves.  Decodes ``chunk`` latents at a time (2 GB of activations each at 512 x 512)."""
+        outs = [ops.to_uint8_image(self.decode(z)) for z in latent.split(chunk)]
+        return outs[0] if len(outs) == 1 else torch.cat(outs)

@@ -88,3 +88,17 @@ def sharded_sample(latent_diffusion, x_full: Tensor, context_full: Tensor, world
     ctx = shard_batch(context_full, world, rank).to(dev)
     out = latent_diffusion.sample(x, ctx, **sample_kwargs)
     return gather_batch(out, x_full.shape[0]) if gather else out
+
+
+def sharded_images(latent_diffusion, x_full: Tensor, context_full: Tensor, world: Optional[int] = None,
+                   rank: Optional[int] = None, gather: bool = True, **sample_kwargs) -> Tensor:
+    """txt2img over the data-parallel group (scripts/txt2img.py:26-46 for a batch): every rank samples its rows of the
+    global latent batch, decodes them with ``latent_diffusion.autoencoder`` and converts to uint8 on the device; the
+    ONE collective of the whole job is the final all-gather of the [B, H, W, 3] uint8 images."""
+    if world is None:
+        world = dist.get_world_size() if dist.is_initialized() else 1
+    if rank is None:
+        rank = dist.get_rank() if dist.is_initialized() else 0
+    latents = sharded_sample(latent_diffusion, x_full, context_full, world, rank, gather=False, **sample_kwargs)
+    images = latent_diffusion.autoencoder.decode_uint8(latents)
+    return gather_batch(images, x_full.shape[0]) if gather else images

@@ -236,3 +236,20 @@ def test_unet_and_sampler_argument_errors_on_gpu():
     vae = AutoEncoderKL(AutoencoderConfig()).to(DEV)
     with pytest.raises(AssertionError, match="Expected latent"):
         vae.decode(torch.randn(1, 5, 8, 8, device=DEV))
+
+
+def test_decode_uint8_is_the_reference_detransform():
+    """AutoEncoderKL.decode_uint8 == utils/prepare_dataset.py:145-150 applied to the decoded image (chunked decode)."""
+    from stable_diffusion_pytorch_b200.models import AutoEncoderKL, AutoencoderConfig
+    cfg, seed, B, H, W = cases.VAE_CASES[list(cases.VAE_CASES)[0]]
+    m = AutoEncoderKL(AutoencoderConfig(autoencoder_channels_list=list(cfg.autoencoder_channels_list),
+                                        groups=cfg.groups)).eval()
+    m.load_state_dict(O.seeded_state_dict(O.vae_decoder_param_shapes(cfg), seed), strict=False)
+    m = m.to(DEV)
+    z = torch.cat([cases.vae_inputs(cfg, B, H, W, seed), 2.5 * cases.vae_inputs(cfg, B, H, W, seed + 1)])
+    with torch.no_grad():
+        img = m.decode(z.to(DEV)).float().cpu()
+        u8 = m.decode_uint8(z.to(DEV), chunk=B).cpu()
+    want = (((img + 1) / 2).clamp(0, 1) * 255).to(torch.uint8).permute(0, 2, 3, 1)
+    assert u8.dtype == torch.uint8 and tuple(u8.shape) == tuple(want.shape)
+    assert torch.equal(u8, want)

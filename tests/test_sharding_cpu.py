@@ -49,8 +49,15 @@ class _FakeUnet(torch.nn.Module):
 class _FakeLatentDiffusion:
     """Row-independent stand-in for LatentDiffusion.sample: x <- 0.9 x + 0.1 mean(ctx) + 0.01 noise per step."""
 
+    class _FakeVae:
+        @staticmethod
+        def decode_uint8(latent):       # detransform of a 2x nearest "decode": [B, H, W, C] uint8
+            img = torch.nn.functional.interpolate(latent[:, :3], scale_factor=2, mode="nearest")
+            return (((img + 1) / 2).clamp(0, 1) * 255).to(torch.uint8).permute(0, 2, 3, 1).contiguous()
+
     def __init__(self):
         self.unet = _FakeUnet()
+        self.autoencoder = self._FakeVae()
 
     def sample(self, x, ctx, host_noise=None, time_steps=4, **kw):
         for i in range(time_steps):
@@ -81,7 +88,10 @@ def _worker(rank, world, port, total, q):
         lo, hi = sharding.shard_range(total, world, rank)
         imgs = (torch.arange(total * 3 * 4 * 4) % 251).to(torch.uint8).reshape(total, 3, 4, 4)
         got = sharding.gather_batch(imgs[lo:hi].clone(), total)
-        q.put((rank, bool(torch.equal(out, ref)), bool(torch.equal(got, imgs)), tuple(out.shape)))
+        # the whole txt2img job: sample the shard, decode + uint8 on the rank, ONE final image gather
+        pics = sharding.sharded_images(_FakeLatentDiffusion(), x, ctx, host_noise=noise, time_steps=4)
+        pics_ok = pics.dtype == torch.uint8 and torch.equal(pics, _FakeLatentDiffusion._FakeVae.decode_uint8(ref))
+        q.put((rank, bool(torch.equal(out, ref)), bool(torch.equal(got, imgs)) and bool(pics_ok), tuple(out.shape)))
     finally:
         dist.destroy_process_group()
 
