@@ -278,6 +278,13 @@ int sdb_adamw_dev(float* p, const float* g, float* m, float* v, int64_t n, const
                   float beta2, float eps, float weight_decay, float grad_scale, const float* gnorm_sq_or_null,
                   float max_norm, void* stream);
 
+/* nn.Dropout in training mode (resnet2d.py:190; transformer.py:58,147): y = keep ? x / (1 - p) : 0 with a counter-based
+ * mask keyed by (state_dev[0], site).  The same call on the gradient IS the backward (no mask is stored).  state_dev:
+ * one int64 in device memory, advanced by the caller once per step (so CUDA-graph replays draw fresh masks); site: a
+ * distinct number per dropout layer call within a step.  "Not covered by any oracle" (SURVEY 8c): statistical tests. */
+int sdb_dropout(const void* x, void* y, int64_t n, float p, const int64_t* state_dev, uint64_t site, int dtype,
+                void* stream);
+
 /* ---- CLIP text encoder pieces (models/clip_model.py:56-96 wraps transformers.CLIPTextModel) ----
  * out[b*L + l, :] = token_embedding[ids[b, l]] + position_embedding[l]  (CLIPTextEmbeddings); ids int64. */
 int sdb_embed_tokens(const int64_t* ids, const float* tok, const float* pos, void* out, int out_dtype, int B, int L,

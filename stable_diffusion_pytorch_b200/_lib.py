@@ -85,6 +85,7 @@ SIGNATURES = {
     "sdb_embed_tokens": (_i, [_p, _p, _p, _p, _i, _i, _i, _i, _i, _p]),
     "sdb_attention_causal_small": (_i, [_p, _i64, _p, _i64, _p, _i64, _p, _i64, _i, _i, _i, _i, _f, _i, _p]),
     "sdb_adamw_dev": (_i, [_p, _p, _p, _p, _i64, _p, _f, _f, _f, _f, _f, _p, _f, _p]),
+    "sdb_dropout": (_i, [_p, _p, _i64, _f, _p, _u64, _i, _p]),
     "sdb_silu": (_i, [_p, _p, _i64, _i, _i, _p]),
     "sdb_cast": (_i, [_p, _i, _p, _i, _i64, _p]),
     "sdb_to_uint8_image": (_i, [_p, _i, _p, _i, _i, _i, _i, _p]),

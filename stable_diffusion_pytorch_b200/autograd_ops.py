@@ -151,6 +151,21 @@ class _Silu(Function):
         return _like(dx, x), None
 
 
+class _Dropout(Function):
+    @staticmethod
+    def forward(ctx, x, p, site):
+        ctx.p, ctx.site = p, site
+        return _ops().dropout_raw(x, p, site)
+
+    @staticmethod
+    def backward(ctx, dy):
+        return _ops().dropout_raw(dy, ctx.p, ctx.site), None, None      # same (state, site) -> same mask
+
+
+def dropout(x, p, site):
+    return _Dropout.apply(x, p, site)
+
+
 class _Cast(Function):
     @staticmethod
     def forward(ctx, x, dtype):

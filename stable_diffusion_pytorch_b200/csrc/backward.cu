@@ -388,6 +388,34 @@ __global__ void adamw_dev_kernel(float* __restrict__ p, const float* __restrict_
   }
 }
 
+// ---- dropout (nn.Dropout in training mode: resnet2d.py:190, transformer.py:58,147) ------------------------------
+// Counter-based: element i is kept iff the 16-bit slice of mix64(key + i / 4) that belongs to it is >= p * 65536,
+// key = mix64(state[0], site).  No mask is stored: the backward re-runs the same kernel on the gradient with the same
+// (state, site); `state` lives in device memory so a replayed CUDA graph draws fresh masks after state += 1.
+__device__ __forceinline__ unsigned long long mix64(unsigned long long z) {
+  z += 0x9E3779B97F4A7C15ull;
+  z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+  z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+  return z ^ (z >> 31);
+}
+template <typename T>
+__global__ void dropout_kernel(const T* __restrict__ x, T* __restrict__ y, long long n, unsigned thresh, float scale,
+                               const long long* __restrict__ state, unsigned long long site) {
+  const unsigned long long key = mix64(mix64((unsigned long long)state[0]) ^ (site * 0xD6E8FEB86659FD93ull));
+  const long long quads = (n + 3) >> 2;
+  for (long long qd = (long long)blockIdx.x * blockDim.x + threadIdx.x; qd < quads; qd += (long long)gridDim.x * blockDim.x) {
+    const unsigned long long r = mix64(key + (unsigned long long)qd);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const long long i = qd * 4 + j;
+      if (i < n) {
+        const bool keep = (unsigned)((r >> (16 * j)) & 0xffffu) >= thresh;
+        stf<T>(y + i, keep ? ldf<T>(x + i) * scale : 0.f);
+      }
+    }
+  }
+}
+
 static inline int bw_grid(long long n, int threads) {
   long long want = (n + threads - 1) / threads;
   long long cap = (long long)sdb_num_sms() * 16;
@@ -567,6 +595,20 @@ extern "C" int sdb_adamw_dev(float* p, const float* g, float* m, float* v, int64
   SDB_CHECK_ARG(p && g && m && v && hyper_dev && n > 0, "adamw_dev: bad args");
   adamw_dev_kernel<<<bw_grid(n, 256), 256, 0, sdb_stream(stream)>>>(p, g, m, v, n, hyper_dev, beta1, beta2, eps,
                                                                   weight_decay, grad_scale, gnorm_sq_or_null, max_norm);
+  SDB_LAUNCH_OK();
+  return SDB_OK;
+}
+
+extern "C" int sdb_dropout(const void* x, void* y, int64_t n, float p, const int64_t* state_dev, uint64_t site, int dtype,
+                           void* stream) {
+  SDB_CHECK_ARG(x && y && state_dev && n > 0 && p >= 0.f && p < 1.f, "dropout: bad args (0 <= p < 1)");
+  const unsigned thresh = (unsigned)(p * 65536.0f + 0.5f);
+  const float scale = 65536.0f / (65536.0f - (float)thresh);      // exact inverse of the realised keep probability
+  const int g = bw_grid((n + 3) / 4, 256);
+  if (dtype == SDB_BF16)
+    dropout_kernel<__nv_bfloat16><<<g, 256, 0, sdb_stream(stream)>>>((const __nv_bfloat16*)x, (__nv_bfloat16*)y, n, thresh, scale, (const long long*)state_dev, site);
+  else
+    dropout_kernel<float><<<g, 256, 0, sdb_stream(stream)>>>((const float*)x, (float*)y, n, thresh, scale, (const long long*)state_dev, site);
   SDB_LAUNCH_OK();
   return SDB_OK;
 }

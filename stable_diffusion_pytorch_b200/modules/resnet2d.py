@@ -156,8 +156,6 @@ class ResBlock(_NhwcModule):
 
     def forward_nhwc(self, x: Tensor, temb_proj: Optional[Tensor] = None, x2: Optional[Tensor] = None) -> Tensor:
         """x (+ x2 = UNet skip, virtual concat) NHWC; temb_proj = Linear(SiLU(time_emb)) fp32 [B, Cout]."""
-        if self.training and self.dropout:
-            raise NotImplementedError("ResBlock: dropout > 0 in training mode is not built (use dropout=0)")
         c_in = x.shape[-1] + (x2.shape[-1] if x2 is not None else 0)
         assert c_in == self.in_channels, f"input channels {c_in} != in_channels {self.in_channels}"
         p = self._p()
@@ -165,6 +163,7 @@ class ResBlock(_NhwcModule):
         h = ops.group_norm(x, p["g1"], p["b1"], self.groups, ACT_SILU, x2=x2)
         h = ops.conv3x3(h, p["w1"], p["cb1"], temb=temb_proj)
         h = ops.group_norm(h, p["g2"], p["b2"], self.groups, ACT_SILU)
+        h = ops.dropout(h, self.dropout or 0.0, self.training)             # out_layers[2] (resnet2d.py:190)
         if "ws" in p:
             c1 = x.shape[-1]
             skip = ops.gemm(x.view(B * H * W, c1), p["ws"], p["bs"],

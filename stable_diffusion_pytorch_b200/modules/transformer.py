@@ -103,8 +103,6 @@ class CrossAttention(nn.Module):
                        residual: Optional[Tensor] = None) -> Tensor:
         """x [B, n, C] bf16.  ctx [B, m, Cc] bf16 or ``kv`` = precomputed (K, V) [B, m, kv_width] views (the
         output layout of ``kv_packed``).  Returns out-proj(attn) (+ residual, fused in the GEMM epilogue)."""
-        if self.training and self.out[1].p:
-            raise NotImplementedError("CrossAttention: dropout > 0 in training mode is not built")
         B, n, C = x.shape
         dm = self.n_heads * self.d_head
         kw = self.kv_width
@@ -130,6 +128,11 @@ class CrossAttention(nn.Module):
         else:
             a = ops.attention(q, k, v, self.n_heads, self.d_head, self.scale)
         res2d = None if residual is None else residual.view(B * n, C)
+        if self.training and self.out[1].p:
+            # out = Sequential(Linear, Dropout) (transformer.py:58): the mask sits between the projection and the
+            # residual add, so the add leaves the GEMM epilogue
+            o = ops.dropout(ops.gemm(a.view(B * n, dm), w["wo"], w["bo"]), self.out[1].p, True)
+            return (o if res2d is None else o + res2d).view(B, n, C)
         return ops.gemm(a.view(B * n, dm), w["wo"], w["bo"], residual=res2d).view(B, n, C)
 
     def forward(self, query: Tensor, context_emb: Optional[Tensor] = None, mask: Optional[Tensor] = None):
@@ -179,12 +182,11 @@ class FeedForward(nn.Module):
         self._cache = _pack.PackCache()
 
     def forward_tokens(self, x2d: Tensor, residual: Optional[Tensor] = None) -> Tensor:
-        if self.training and self.net[1].p:
-            raise NotImplementedError("FeedForward: dropout > 0 in training mode is not built")
         lin = self.net[2]
         w = self._cache.get("w", [lin.weight], lambda: _pack.linear_w(lin.weight))
         b = self._cache.get("b", [lin.bias], lambda: _pack.f32(lin.bias))
-        return ops.gemm(self.net[0].forward_tokens(x2d), w, b, residual=residual)
+        g = ops.dropout(self.net[0].forward_tokens(x2d), self.net[1].p, self.training)      # net[1] (transformer.py:147)
+        return ops.gemm(g, w, b, residual=residual)
 
     def forward(self, x: Tensor) -> Tensor:
         t = _tokens_bf16(x)

@@ -365,6 +365,66 @@ def attention_p32_lse(q: Tensor, k: Tensor, v: Tensor, heads: int, d: int, scale
     return out, (lse if wrote.value else None)
 
 
+class _DropoutState:
+    """Per-device RNG state of the training-mode dropout kernels: one int64 in device memory (advanced once per train
+    step, also inside captured graphs) and a host-side counter that numbers the dropout calls of one forward."""
+
+    def __init__(self, device):
+        self.state = torch.zeros(1, device=device, dtype=torch.int64)
+        self.site = 0
+
+
+_dropout_states = {}
+
+
+def dropout_state(device) -> _DropoutState:
+    device = torch.device(device)
+    if device.type == "cuda" and device.index is None:       # "cuda" and "cuda:0" must name the same state
+        device = torch.device("cuda", torch.cuda.current_device())
+    key = str(device)
+    if key not in _dropout_states:
+        _dropout_states[key] = _DropoutState(device)
+    return _dropout_states[key]
+
+
+def dropout_seed(seed: int, device) -> None:
+    st = dropout_state(device)
+    st.state.fill_(int(seed))
+    st.site = 0
+
+
+def dropout_begin_step(device) -> None:
+    """Call at the start of every forward: dropout layers are numbered in call order from 0."""
+    dropout_state(device).site = 0
+
+
+def dropout_advance(device) -> None:
+    """Next step draws new masks (a device-side increment: legal inside CUDA-graph capture)."""
+    dropout_state(device).state.add_(1)
+
+
+def dropout_raw(x: Tensor, p: float, site: int) -> Tensor:
+    """The kernel itself: mask keyed by (device state, site); applying it to a gradient is the backward."""
+    x = x.contiguous()
+    out = torch.empty_like(x)
+    st = dropout_state(x.device)
+    check(_lib.lib().sdb_dropout(_ptr(x), _ptr(out), x.numel(), float(p), _ptr(st.state), int(site), _dt(x), _stream()),
+          "dropout")
+    return out
+
+
+def dropout(x: Tensor, p: float, training: bool = True) -> Tensor:
+    """nn.Dropout(p) (resnet2d.py:190, transformer.py:58,147): identity unless ``training`` and p > 0."""
+    if not training or not p:
+        return x
+    st = dropout_state(x.device)
+    site = st.site
+    st.site += 1
+    if _ag.wants(x):
+        return _ag.dropout(x, p, site)
+    return dropout_raw(x, p, site)
+
+
 def silu(x: Tensor, out_dtype=None) -> Tensor:
     if _ag.wants(x):
         return _ag.silu(x, out_dtype)

@@ -118,6 +118,7 @@ class FlatAdamW:
 def diffusion_loss(model, x_t: Tensor, timesteps: Tensor, text_condition: Tensor, noise: Tensor,
                    guidance_scale: float = 7.5) -> Tensor:
     """MSE(pred_noise(x_t, t, ctx, guidance).float(), noise.float()) (train_unet.py:524-529) with the graph kept."""
+    ops.dropout_begin_step(x_t.device)
     with _pack.graph_mode():
         pred = model.pred_noise(x_t, timesteps, text_condition, guidance_scale=guidance_scale)
         return ops.mse_loss(pred, noise)
@@ -130,6 +131,7 @@ def train_step(model, opt: FlatAdamW, x_t: Tensor, timesteps: Tensor, text_condi
     gradient buffer is cleared.  Returns the (device) loss of this rank's micro-batch."""
     loss = diffusion_loss(model, x_t, timesteps, text_condition, noise, guidance_scale)
     loss.backward()
+    ops.dropout_advance(x_t.device)          # the next micro-step draws new masks
     if sync:
         world = opt.all_reduce(group)
         opt.step(world, lr)
@@ -166,6 +168,7 @@ class GraphedTrainStep:
     def _fwd_bwd(self):
         loss = diffusion_loss(self.model, self.x_t, self.t, self.ctx, self.noise, self.g)
         loss.backward()
+        ops.dropout_advance(self.x_t.device)   # device-side: every replay of the graph draws new masks
         return loss.detach()
 
     def _update(self):
