@@ -226,6 +226,12 @@ int sdb_groupnorm_bwd(const void* x1, int C1, const void* x2, int C2, int dtype,
                       const float* gamma, const float* beta, int act, const void* dy, void* dx1, void* dx2,
                       float* dgamma_acc, float* dbeta_acc, float* sums_scratch, int B, int64_t hw, int groups,
                       void* stream);
+/* sdb_groupnorm_bwd on 16-byte vectors (bf16, C1 and C2 multiples of 8): same arithmetic through per-(image, channel)
+ * column sums; colbuf_zeroed = [B][2][C1 + C2] floats.  Other shapes run sdb_groupnorm_bwd. */
+int sdb_groupnorm_bwd_vec(const void* x1, int C1, const void* x2, int C2, int dtype, const float* stats,
+                          const float* gamma, const float* beta, int act, const void* dy, void* dx1, void* dx2,
+                          float* dgamma_acc, float* dbeta_acc, float* sums_scratch, float* colbuf_zeroed, int B,
+                          int64_t hw, int groups, void* stream);
 int sdb_layernorm_bwd(const void* x, const float* gamma, const void* dy, void* dx, float* dgamma_acc,
                       float* dbeta_acc, int64_t rows, int C, float eps, int dtype, void* stream);
 /* softmax(QK^T scale)V backward (autograd of transformer.py:93-114), any n / m, d <= 32 (SDB_EUNSUPPORTED beyond):

@@ -68,6 +68,7 @@ SIGNATURES = {
     "sdb_geglu_bwd": (_i, [_p, _p, _p, _i64, _i, _p]),
     "sdb_silu_bwd": (_i, [_p, _i, _p, _p, _i, _i64, _p]),
     "sdb_groupnorm_bwd": (_i, [_p, _i, _p, _i, _i, _p, _p, _p, _i, _p, _p, _p, _p, _p, _p, _i, _i64, _i, _p]),
+    "sdb_groupnorm_bwd_vec": (_i, [_p, _i, _p, _i, _i, _p, _p, _p, _i, _p, _p, _p, _p, _p, _p, _p, _i, _i64, _i, _p]),
     "sdb_layernorm_bwd": (_i, [_p, _p, _p, _p, _p, _p, _i64, _i, _f, _i, _p]),
     "sdb_attention_bwd": (_i, [_p, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _p,
                                 _i, _i, _i, _i, _i, _i, _i, _f, _p]),

@@ -337,9 +337,11 @@ class _GroupNorm(Function):
         dg = torch.zeros(C1 + C2, device=x1.device, dtype=torch.float32)
         db = torch.zeros(C1 + C2, device=x1.device, dtype=torch.float32)
         sums = torch.empty(B * ctx.groups * 2, device=x1.device, dtype=torch.float32)
-        check(_lib.lib().sdb_groupnorm_bwd(ops._ptr(x1), C1, ops._ptr(x2), C2, ops._dt(x1), ops._ptr(stats), ops._ptr(gamma),
-                                           ops._ptr(beta), ctx.act, ops._ptr(dyc), ops._ptr(dx1), ops._ptr(dx2), ops._ptr(dg),
-                                           ops._ptr(db), ops._ptr(sums), B, H * W, ctx.groups, ops._stream()), "groupnorm_bwd")
+        colbuf = torch.zeros(B * 2 * (C1 + C2), device=x1.device, dtype=torch.float32)   # per-(image, channel) sums
+        check(_lib.lib().sdb_groupnorm_bwd_vec(ops._ptr(x1), C1, ops._ptr(x2), C2, ops._dt(x1), ops._ptr(stats),
+                                               ops._ptr(gamma), ops._ptr(beta), ctx.act, ops._ptr(dyc), ops._ptr(dx1),
+                                               ops._ptr(dx2), ops._ptr(dg), ops._ptr(db), ops._ptr(sums), ops._ptr(colbuf),
+                                               B, H * W, ctx.groups, ops._stream()), "groupnorm_bwd")
         return dx1, dx2, dg.to(gamma.dtype), db.to(beta.dtype), None, None, None, None
 
 

@@ -453,12 +453,14 @@ extern "C" int sdb_colsum(const void* x, int dtype, int64_t ld, int64_t groups, 
 
 extern "C" int sdb_geglu_fwd(const void* h, void* out, int64_t M, int F, void* stream) {
   SDB_CHECK_ARG(h && out && M > 0 && F > 0 && F % 2 == 0, "geglu_fwd: bad args");
+  if (geglu_fwd_vec(h, out, M, F, sdb_stream(stream))) { SDB_LAUNCH_OK(); return SDB_OK; }
   geglu_fwd_kernel<<<bw_grid(M * F, 256), 256, 0, sdb_stream(stream)>>>((const __nv_bfloat16*)h, (__nv_bfloat16*)out, M, F);
   SDB_LAUNCH_OK();
   return SDB_OK;
 }
 extern "C" int sdb_geglu_bwd(const void* h, const void* dout, void* dh, int64_t M, int F, void* stream) {
   SDB_CHECK_ARG(h && dout && dh && M > 0 && F > 0 && F % 2 == 0, "geglu_bwd: bad args");
+  if (geglu_bwd_vec(h, dout, dh, M, F, sdb_stream(stream))) { SDB_LAUNCH_OK(); return SDB_OK; }
   geglu_bwd_kernel<<<bw_grid(M * F, 256), 256, 0, sdb_stream(stream)>>>((const __nv_bfloat16*)h, (const __nv_bfloat16*)dout, (__nv_bfloat16*)dh, M, F);
   SDB_LAUNCH_OK();
   return SDB_OK;
@@ -502,6 +504,10 @@ extern "C" int sdb_groupnorm_bwd(const void* x1, int C1, const void* x2, int C2,
 extern "C" int sdb_layernorm_bwd(const void* x, const float* gamma, const void* dy, void* dx, float* dgamma_acc,
                                  float* dbeta_acc, int64_t rows, int C, float eps, int dtype, void* stream) {
   SDB_CHECK_ARG(x && gamma && dy && dx && dgamma_acc && dbeta_acc && rows > 0 && C > 0 && C <= 4096, "layernorm_bwd: bad args");
+  if (dtype == SDB_BF16 && layernorm_bwd_vec(x, gamma, dy, dx, dgamma_acc, dbeta_acc, rows, C, eps, sdb_stream(stream))) {
+    SDB_LAUNCH_OK();
+    return SDB_OK;
+  }
   long long blocks = (rows + 7) / 8;
   const long long cap = (long long)sdb_num_sms() * 4;
   if (blocks > cap) blocks = cap;
@@ -611,4 +617,29 @@ extern "C" int sdb_dropout(const void* x, void* y, int64_t n, float p, const int
     dropout_kernel<float><<<g, 256, 0, sdb_stream(stream)>>>((const float*)x, (float*)y, n, thresh, scale, (const long long*)state_dev, site);
   SDB_LAUNCH_OK();
   return SDB_OK;
+}
+
+// sdb_groupnorm_bwd on 16-byte vectors (backward_vec.cu): needs colbuf_zeroed = [B][2][C] floats; shapes outside the
+// vector kernels (fp32, channel counts that are not multiples of 8) run the scalar kernels.
+extern "C" int sdb_groupnorm_bwd_vec(const void* x1, int C1, const void* x2, int C2, int dtype, const float* stats,
+                                     const float* gamma, const float* beta, int act, const void* dy, void* dx1, void* dx2,
+                                     float* dgamma_acc, float* dbeta_acc, float* sums_scratch, float* colbuf_zeroed, int B,
+                                     int64_t hw, int groups, void* stream) {
+  if (!x2) C2 = 0;
+  SDB_CHECK_ARG(x1 && stats && gamma && beta && dy && dx1 && (C2 == 0 || dx2) && dgamma_acc && dbeta_acc && sums_scratch &&
+                    colbuf_zeroed, "groupnorm_bwd_vec: null pointer");
+  SDB_CHECK_ARG(B > 0 && hw > 0 && groups > 0 && (C1 + C2) % groups == 0, "groupnorm_bwd_vec: bad shape");
+  if (dtype == SDB_BF16) {
+    GnVecArgs a;
+    a.x1 = (const __nv_bfloat16*)x1; a.C1 = C1; a.x2 = (const __nv_bfloat16*)x2; a.C2 = C2;
+    a.stats = stats; a.gamma = gamma; a.beta = beta; a.act = act; a.dy = (const __nv_bfloat16*)dy;
+    a.colbuf = colbuf_zeroed; a.sums = sums_scratch; a.dx1 = (__nv_bfloat16*)dx1; a.dx2 = (__nv_bfloat16*)dx2;
+    a.hw = hw; a.groups = groups;
+    if (groupnorm_bwd_vec(a, dgamma_acc, dbeta_acc, B, sdb_stream(stream))) {
+      SDB_LAUNCH_OK();
+      return SDB_OK;
+    }
+  }
+  return sdb_groupnorm_bwd(x1, C1, x2, C2, dtype, stats, gamma, beta, act, dy, dx1, dx2, dgamma_acc, dbeta_acc,
+                           sums_scratch, B, hw, groups, stream);
 }
