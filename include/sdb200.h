@@ -248,6 +248,17 @@ int sdb_attention_bwd(const void* q, int64_t ldq, const void* k, int64_t ldk, co
 int sdb_attention_p32_lse(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
                           void* out, int64_t ldo, int B, int heads, int n, int m, int d, float scale, float* lse,
                           int* lse_written, void* stream);
+/* The two halves of sdb_attention_bwd for the head-padded (tcgen05) layout when the forward kept lse:
+ *   sdb_attention_bwd_dq_p32: dQ on tcgen05 / TMEM (S and dP by UMMA, dS written back to TMEM as the A operand of
+ *     dS.K); needs dO re-laid head-padded (dO_pad, zero pad columns) and delta[b, h, row] = sum_c dO * O;
+ *   sdb_attention_bwd_dkv: the dK / dV kernel alone (dense dO).  lse, delta: fp32 [B, heads, n]. */
+int sdb_attention_bwd_dq_p32(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
+                             const void* dO_pad, int64_t lddo, const float* lse, const float* delta, void* dq,
+                             int64_t lddq, int B, int heads, int n, int m, int d, float scale, void* stream);
+int sdb_attention_bwd_dkv(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
+                          const void* dO, int64_t lddo, void* dk, int64_t lddk, void* dv, int64_t lddv, const float* lse,
+                          const float* delta, int B, int heads, int n, int m, int d, int head_pitch, float scale,
+                          void* stream);
 int sdb_upsample2x_bwd(const void* dy, void* dx, int dtype, int B, int H, int W, int C, void* stream);
 /* DownSample backward: dy [B,H/2,W/2,C] lands on the even pixels of out [B,H,W,C], zeros elsewhere */
 int sdb_scatter_even(const void* dy, void* out, int dtype, int B, int H, int W, int C, void* stream);

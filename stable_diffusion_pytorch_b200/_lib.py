@@ -72,6 +72,9 @@ SIGNATURES = {
     "sdb_layernorm_bwd": (_i, [_p, _p, _p, _p, _p, _p, _i64, _i, _f, _i, _p]),
     "sdb_attention_bwd": (_i, [_p, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _p,
                                 _i, _i, _i, _i, _i, _i, _i, _f, _p]),
+    "sdb_attention_bwd_dq_p32": (_i, [_p, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _p, _p, _i64, _i, _i, _i, _i, _i, _f, _p]),
+    "sdb_attention_bwd_dkv": (_i, [_p, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _p, _i, _i, _i, _i, _i,
+                                    _i, _f, _p]),
     "sdb_attention_p32_lse": (_i, [_p, _i64, _p, _i64, _p, _i64, _p, _i64, _i, _i, _i, _i, _i, _f, _p, _p, _p]),
     "sdb_upsample2x_bwd": (_i, [_p, _p, _i, _i, _i, _i, _i, _p]),
     "sdb_scatter_even": (_i, [_p, _p, _i, _i, _i, _i, _i, _p]),

@@ -15,6 +15,7 @@ torch is used for tensor views, allocation and the (tiny) weight-layout permutes
 """
 from __future__ import annotations
 
+import os
 from typing import Optional
 
 import torch
@@ -24,6 +25,7 @@ from . import _lib
 from ._lib import ACT_GEGLU, ACT_NONE, ACT_SILU, check
 
 Tensor = torch.Tensor
+_DQ_UMMA = os.environ.get("SDB_BWD_DQ_UMMA", "1") != "0"      # tuning / A-B aid: 0 = dQ on the mma.sync kernel
 
 
 def wants(*tensors) -> bool:
@@ -398,6 +400,22 @@ class _AttentionP32(Function):
         dq = torch.empty(B, n, ctx.heads * hp, device=q.device, dtype=torch.bfloat16)
         dk = torch.empty(B, m, ctx.heads * hp, device=q.device, dtype=torch.bfloat16)
         dv = torch.empty_like(dk)
+        if ctx.has_lse and ctx.d <= 20 and _DQ_UMMA:
+            # long sequences (the forward ran on tcgen05 and kept lse): dQ on the tensor cores, dK / dV on mma.sync
+            H, d = ctx.heads, ctx.d
+            lse = ctx.saved_tensors[4]
+            delta = (do.float() * o.float()).view(B, n, H, d).sum(-1).permute(0, 2, 1).contiguous()   # [B, H, n]
+            do_pad = torch.zeros(B, n, H, hp, device=q.device, dtype=torch.bfloat16)
+            do_pad[..., :d] = do.view(B, n, H, d)
+            L = _lib.lib()
+            check(L.sdb_attention_bwd_dq_p32(ops._ptr(q), q.stride(1), ops._ptr(k), k.stride(1), ops._ptr(v), v.stride(1),
+                                             ops._ptr(do_pad), H * hp, ops._ptr(lse), ops._ptr(delta), ops._ptr(dq),
+                                             dq.stride(1), B, H, n, m, d, ctx.scale, ops._stream()), "attention_bwd_dq_p32")
+            check(L.sdb_attention_bwd_dkv(ops._ptr(q), q.stride(1), ops._ptr(k), k.stride(1), ops._ptr(v), v.stride(1),
+                                          ops._ptr(do), do.stride(1), ops._ptr(dk), dk.stride(1), ops._ptr(dv), dv.stride(1),
+                                          ops._ptr(lse), ops._ptr(delta), B, H, n, m, d, hp, ctx.scale, ops._stream()),
+                  "attention_bwd_dkv")
+            return dq, dk, dv, None, None, None
         delta = torch.empty(B * ctx.heads * n, device=q.device, dtype=torch.float32)
         lse = ctx.saved_tensors[4] if ctx.has_lse else torch.empty_like(delta)
         check(_lib.lib().sdb_attention_bwd(

@@ -421,3 +421,23 @@ extern "C" int sdb_attention_bwd(const void* q, int64_t ldq, const void* k, int6
   SDB_LAUNCH_OK();
   return SDB_OK;
 }
+
+// dK / dV only (the dQ half runs on the tcgen05 kernel of attention_bwd_umma.cu); lse / delta: fp32 [B, heads, n], filled.
+extern "C" int sdb_attention_bwd_dkv(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
+                                     const void* dO, int64_t lddo, void* dk, int64_t lddk, void* dv, int64_t lddv,
+                                     const float* lse, const float* delta, int B, int heads, int n, int m, int d,
+                                     int head_pitch, float scale, void* stream) {
+  using namespace sdb;
+  SDB_CHECK_ARG(q && k && v && dO && dk && dv && lse && delta, "attention_bwd_dkv: null pointer");
+  SDB_CHECK_ARG(B > 0 && heads > 0 && n > 0 && m > 0 && d > 0 && d <= 32 && d % 4 == 0 && head_pitch >= d && head_pitch % 4 == 0,
+                "attention_bwd_dkv: bad shape");
+  SDB_CHECK_ARG(ldq % 4 == 0 && ldk % 4 == 0 && ldv % 4 == 0 && lddo % 4 == 0 && lddk % 2 == 0 && lddv % 2 == 0,
+                "attention_bwd_dkv: row strides must be multiples of 4 elements");
+  SDB_CHECK_ARG(heads <= 65535 && B <= 65535, "attention_bwd_dkv: grid too large");
+  const float sl2e = scale * 1.4426950408889634f;
+  attn_bwd_dkv_kernel<<<dim3((m + 63) / 64, heads, B), kAttThreads, 0, sdb_stream(stream)>>>(
+      (const __nv_bfloat16*)q, ldq, (const __nv_bfloat16*)k, ldk, (const __nv_bfloat16*)v, ldv, (const __nv_bfloat16*)dO, lddo,
+      lse, delta, (__nv_bfloat16*)dk, lddk, (__nv_bfloat16*)dv, lddv, n, m, d, head_pitch, scale, sl2e);
+  SDB_LAUNCH_OK();
+  return SDB_OK;
+}

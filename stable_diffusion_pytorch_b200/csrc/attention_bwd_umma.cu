@@ -1,0 +1,275 @@
+// Attention backward, dQ on the tensor cores (tcgen05 / TMEM / TMA), head-padded operands, d <= 20 (row T1).
+//   S = Q K^T,  P = exp2(S c - lse2),  dP = dO V^T,  dS = P o (dP - delta),  dQ = scale * dS K
+// The pipeline of the forward kernel (attention_umma.cu) with the roles re-cast: per 64-key tile the MMA warp issues
+// S = Q.K^T and dP = dO.V^T into TMEM (both operands K-major as they land from TMA; V's ones column meets the zero pad
+// column of dO), each softmax thread owns one query row -- its lse2 and delta are two scalars -- reads the two 64-column
+// rows back, forms dS in registers, writes it to TMEM as packed bf16 and the MMA warp consumes it as the A operand of
+// dQ += dS.K with the SAME K tile read as an MN-major B operand.  dQ stays in TMEM across the key loop.
+// No running maximum, no rescale: the forward kernel handed over the row log-sum-exp.
+// TMEM columns per warpgroup w (256 each): S [0,64), dP [64,128), dS [128,160), dQ [192,224).
+#include "common.cuh"
+
+namespace sdb {
+
+constexpr int kBdThreads = 384;   // warp 0: TMA, 1-2: MMA issue, 3: TMEM alloc; 4-7, 8-11: the two row warpgroups
+constexpr int kBdStages = 6;
+constexpr int kBdBM = 128;
+constexpr int kBdBN = 64;         // keys per tile (TMEM budget: S + dP + dS + dQ per warpgroup)
+constexpr int kBdQBytes = kBdBM * 32 * 2;       // 8 KB
+constexpr int kBdKVBytes = kBdBN * 32 * 2;      // 4 KB each for K and V
+constexpr int kBdStageBytes = 2 * kBdKVBytes;
+constexpr int kBdSmem = 4 * kBdQBytes + kBdStages * kBdStageBytes + 1024 + 256;
+
+struct BdParams {
+  CUtensorMap tmQ, tmdO, tmK, tmV;
+  const float* lse;     // [B, heads, n] log2-domain log-sum-exp of the scaled scores
+  const float* delta;   // [B, heads, n] rowsum(dO o O)
+  __nv_bfloat16* dq;    // [B, n, >= heads*32] head-padded
+  long long lddq;
+  int n, m, heads;
+  float scale, scale_log2;
+};
+
+__global__ void __launch_bounds__(kBdThreads, 1) attn_bwd_dq_umma_kernel(const __grid_constant__ BdParams p) {
+  extern __shared__ __align__(1024) uint8_t bd_smem[];
+  const uint32_t base = (smem_u32(bd_smem) + 1023u) & ~1023u;
+  const uint32_t sQ = base;                                  // 2 x 8 KB
+  const uint32_t sdO = base + 2 * kBdQBytes;                 // 2 x 8 KB
+  const uint32_t sKV = base + 4 * kBdQBytes;                 // stages x (K 4 KB | V 4 KB)
+  const uint32_t bars = sKV + kBdStages * kBdStageBytes;
+  const uint32_t bar_q = bars;
+  auto bar_kv_full = [&](int s) { return bars + 8u * (1 + s); };
+  auto bar_kv_empty = [&](int s) { return bars + 8u * (1 + kBdStages + s); };
+  auto bar_s_full = [&](int w) { return bars + 8u * (1 + 2 * kBdStages + w); };
+  auto bar_s_free = [&](int w) { return bars + 8u * (3 + 2 * kBdStages + w); };
+  auto bar_p_full = [&](int w) { return bars + 8u * (5 + 2 * kBdStages + w); };
+  auto bar_o_full = [&](int w) { return bars + 8u * (7 + 2 * kBdStages + w); };
+  const uint32_t tmem_slot = bars + 8u * (9 + 2 * kBdStages);
+  volatile uint32_t* tmem_slot_ptr = reinterpret_cast<volatile uint32_t*>(bd_smem + (tmem_slot - smem_u32(bd_smem)));
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int b = blockIdx.z, h = blockIdx.y, q0 = blockIdx.x * (2 * kBdBM);
+  const int T = (p.m + kBdBN - 1) / kBdBN;
+
+  if (warp == 0 && lane == 0) {
+    prefetch_tmap(&p.tmQ);
+    prefetch_tmap(&p.tmdO);
+    prefetch_tmap(&p.tmK);
+    prefetch_tmap(&p.tmV);
+    mbar_init(bar_q, 1);
+    for (int s = 0; s < kBdStages; ++s) {
+      mbar_init(bar_kv_full(s), 1);
+      mbar_init(bar_kv_empty(s), 2);
+    }
+    for (int w = 0; w < 2; ++w) {
+      mbar_init(bar_s_full(w), 1);
+      mbar_init(bar_s_free(w), 4);
+      mbar_init(bar_p_full(w), 4);
+      mbar_init(bar_o_full(w), 1);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 3) {
+    tmem_alloc(tmem_slot, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot_ptr;
+
+  if (warp < 4) {
+    setmaxnreg_dec<56>();
+    if (warp == 0 && lane == 0) {
+      // ===================== TMA producer =====================
+      mbar_arrive_expect_tx(bar_q, 4 * kBdQBytes);
+      tma_load_3d(sQ, &p.tmQ, bar_q, h * 32, q0, b);
+      tma_load_3d(sQ + kBdQBytes, &p.tmQ, bar_q, h * 32, q0 + kBdBM, b);
+      tma_load_3d(sdO, &p.tmdO, bar_q, h * 32, q0, b);
+      tma_load_3d(sdO + kBdQBytes, &p.tmdO, bar_q, h * 32, q0 + kBdBM, b);
+      bool ok = true;
+      for (int j = 0; j < T && ok; ++j) {
+        const int s = j % kBdStages;
+        ok = mbar_wait(bar_kv_empty(s), (((uint32_t)(j / kBdStages)) & 1u) ^ 1u);
+        if (!ok) break;
+        const uint32_t sk = sKV + (uint32_t)s * kBdStageBytes;
+        mbar_arrive_expect_tx(bar_kv_full(s), kBdStageBytes);
+        tma_load_3d(sk, &p.tmK, bar_kv_full(s), h * 32, j * kBdBN, b);
+        tma_load_3d(sk + kBdKVBytes, &p.tmV, bar_kv_full(s), h * 32, j * kBdBN, b);
+      }
+    } else if (warp == 1 || warp == 2) {
+      // ===================== MMA issuers: one warp per row warpgroup =====================
+      const int w = warp - 1;
+      const uint32_t idesc_s = umma_idesc_bf16(kBdBM, kBdBN);
+      const uint32_t idesc_q = umma_idesc_bf16(kBdBM, 32) | (1u << 16);   // B (= K tile) read MN-major
+      const uint64_t qdesc = umma_smem_desc(sQ + (uint32_t)w * kBdQBytes, 64);
+      const uint64_t dodesc = umma_smem_desc(sdO + (uint32_t)w * kBdQBytes, 64);
+      const uint32_t tcol = tmem_base + (uint32_t)w * 256u;
+      auto issue_s = [&](int stage) {
+        const uint32_t sk = sKV + (uint32_t)stage * kBdStageBytes;
+        const uint64_t kdesc = umma_smem_desc(sk, 64);
+        const uint64_t vdesc = umma_smem_desc(sk + kBdKVBytes, 64);
+        if (elect_one()) {
+          umma_f16(tcol, qdesc, kdesc, idesc_s, 0u);                  // S = Q K^T
+          umma_f16(tcol, qdesc + 2, kdesc + 2, idesc_s, 1u);
+          umma_f16(tcol + 64u, dodesc, vdesc, idesc_s, 0u);           // dP = dO V^T
+          umma_f16(tcol + 64u, dodesc + 2, vdesc + 2, idesc_s, 1u);
+          umma_commit(bar_s_full(w));
+        }
+        __syncwarp();
+      };
+      bool ok = mbar_wait(bar_q, 0) && mbar_wait(bar_kv_full(0), 0);
+      if (ok) {
+        tc_fence_after();
+        issue_s(0);
+      }
+      for (int j = 0; j < T && ok; ++j) {
+        const int s = j % kBdStages, sn = (j + 1) % kBdStages;
+        const uint32_t par = (uint32_t)j & 1u;
+        if (j + 1 < T) {
+          ok = mbar_wait(bar_kv_full(sn), ((uint32_t)((j + 1) / kBdStages)) & 1u) && mbar_wait(bar_s_free(w), par);
+          if (!ok) break;
+          tc_fence_after();
+          issue_s(sn);
+        }
+        ok = mbar_wait(bar_p_full(w), par);
+        if (!ok) break;
+        tc_fence_after();
+        const uint64_t kmn = umma_smem_desc_mn64(sKV + (uint32_t)s * kBdStageBytes);
+        if (elect_one()) {
+#pragma unroll
+          for (int kk = 0; kk < kBdBN / 16; ++kk)
+            umma_f16_ts(tcol + 192u, tcol + 128u + (uint32_t)kk * 8u, kmn + (uint64_t)(kk * 64), idesc_q,
+                        (j | kk) ? 1u : 0u);   // dQ accumulates in TMEM across the key tiles
+          umma_commit(bar_o_full(w));
+          umma_commit(bar_kv_empty(s));
+        }
+        __syncwarp();
+      }
+    }
+  } else {
+    // ===================== row warpgroups: one query row per thread =====================
+    setmaxnreg_inc<224>();
+    const int w = (warp - 4) >> 2, quarter = warp & 3;
+    const uint32_t tw = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)w * 256u;
+    const float c = p.scale_log2;
+    const int row = q0 + w * kBdBM + quarter * 32 + lane;
+    float neg_lse = 0.f, delta = 0.f;
+    if (row < p.n) {
+      const long long o = ((long long)b * p.heads + h) * p.n + row;
+      neg_lse = -p.lse[o];
+      delta = p.delta[o];
+    }
+    bool ok = true;
+    for (int j = 0; j < T; ++j) {
+      const uint32_t par = (uint32_t)j & 1u;
+      if (ok) ok = mbar_wait(bar_s_full(w), par);
+      tc_fence_after();
+      uint32_t su[128];                       // [0,64) = S row, [64,128) = dP row
+      tmem_ld_32x32_at<0>(tw + 0, su);
+      tmem_ld_32x32_at<32>(tw + 32, su);
+      tmem_ld_32x32_at<64>(tw + 64, su);
+      tmem_ld_32x32_at<96>(tw + 96, su);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_s_free(w));
+      if (j == T - 1 && (p.m & (kBdBN - 1)) != 0) {     // ragged key tail: P = exp2(-inf) = 0
+        const int valid = p.m - j * kBdBN;
+#pragma unroll
+        for (int i = 0; i < kBdBN; ++i)
+          if (i >= valid) su[i] = 0xff800000u;
+      }
+      // the previous tile's dS.K must have finished reading dS before it is overwritten
+      if (j > 0) {
+        if (ok) ok = mbar_wait(bar_o_full(w), par ^ 1u);
+        tc_fence_after();
+      }
+#pragma unroll
+      for (int ch = 0; ch < 2; ++ch) {
+        uint32_t pk[16];
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+          const int i = ch * 32 + 2 * k;
+          const float p0 = ex2_mufu(fmaf(__uint_as_float(su[i]), c, neg_lse));
+          const float p1 = ex2_mufu(fmaf(__uint_as_float(su[i + 1]), c, neg_lse));
+          pk[k] = pack_bf16x2(p0 * (__uint_as_float(su[64 + i]) - delta), p1 * (__uint_as_float(su[64 + i + 1]) - delta));
+        }
+        tmem_st_32x16(tw + 128 + ch * 16, pk);
+      }
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar_p_full(w));
+    }
+    if (ok) ok = mbar_wait(bar_o_full(w), ((uint32_t)(T - 1)) & 1u);
+    tc_fence_after();
+    uint32_t o[32];
+    tmem_ld_32x32(tw + 192, o);
+    tmem_ld_wait();
+    if (row < p.n && ok) {
+      uint4* dst = reinterpret_cast<uint4*>(p.dq + ((long long)b * p.n + row) * p.lddq + h * 32);
+#pragma unroll
+      for (int v = 0; v < 4; ++v) {
+        dst[v] = make_uint4(
+            pack_bf16x2(__uint_as_float(o[8 * v]) * p.scale, __uint_as_float(o[8 * v + 1]) * p.scale),
+            pack_bf16x2(__uint_as_float(o[8 * v + 2]) * p.scale, __uint_as_float(o[8 * v + 3]) * p.scale),
+            pack_bf16x2(__uint_as_float(o[8 * v + 4]) * p.scale, __uint_as_float(o[8 * v + 5]) * p.scale),
+            pack_bf16x2(__uint_as_float(o[8 * v + 6]) * p.scale, __uint_as_float(o[8 * v + 7]) * p.scale));
+      }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 3) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+}  // namespace sdb
+
+// dQ of the head-padded attention on tcgen05 (see the kernel).  q / k / v / dO_pad / dq: bf16, head h at columns
+// [32h, 32h+32) (q, k, dO_pad zero beyond d; v with its ones column at d); lse / delta: fp32 [B, heads, n].
+extern "C" int sdb_attention_bwd_dq_p32(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
+                                        const void* dO_pad, int64_t lddo, const float* lse, const float* delta, void* dq,
+                                        int64_t lddq, int B, int heads, int n, int m, int d, float scale, void* stream) {
+  using namespace sdb;
+  SDB_CHECK_ARG(q && k && v && dO_pad && lse && delta && dq && B > 0 && heads > 0 && n > 0 && m > 0,
+                "attention_bwd_dq_p32: bad args");
+  SDB_CHECK_ARG(d > 0 && d <= 20 && d % 4 == 0, "attention_bwd_dq_p32: head dim (%d) must be a multiple of 4, <= 20", d);
+  SDB_CHECK_ARG(ldq % 8 == 0 && ldk % 8 == 0 && ldv % 8 == 0 && lddo % 8 == 0 && lddq % 8 == 0 &&
+                    ldq >= heads * 32 && ldk >= heads * 32 && ldv >= heads * 32 && lddo >= heads * 32 && lddq >= heads * 32,
+                "attention_bwd_dq_p32: row strides must be multiples of 8 covering heads*32 padded columns");
+  SDB_CHECK_ARG(((uintptr_t)q & 15) == 0 && ((uintptr_t)k & 15) == 0 && ((uintptr_t)v & 15) == 0 &&
+                    ((uintptr_t)dO_pad & 15) == 0 && ((uintptr_t)dq & 15) == 0,
+                "attention_bwd_dq_p32: operands must be 16-byte aligned");
+  SDB_CHECK_ARG(heads <= 65535 && B <= 65535, "attention_bwd_dq_p32: grid too large");
+  BdParams p;
+  memset(&p, 0, sizeof(p));
+  auto make = [&](CUtensorMap* tm, const void* base, int64_t ld, int rows, uint32_t box_rows) {
+    const uint32_t box[3] = {32, box_rows, 1};
+    uint64_t dims[3] = {(uint64_t)heads * 32, (uint64_t)rows, (uint64_t)B};
+    uint64_t st[3] = {0, (uint64_t)ld * 2, (uint64_t)rows * ld * 2};
+    return sdb_make_tensor_map(tm, base, 2, 3, dims, st, box, 64);
+  };
+  int rc;
+  if ((rc = make(&p.tmQ, q, ldq, n, kBdBM))) return rc;
+  if ((rc = make(&p.tmdO, dO_pad, lddo, n, kBdBM))) return rc;
+  if ((rc = make(&p.tmK, k, ldk, m, kBdBN))) return rc;
+  if ((rc = make(&p.tmV, v, ldv, m, kBdBN))) return rc;
+  p.lse = lse; p.delta = delta; p.dq = (__nv_bfloat16*)dq; p.lddq = lddq;
+  p.n = n; p.m = m; p.heads = heads;
+  p.scale = scale; p.scale_log2 = scale * 1.4426950408889634f;
+  static bool attr_set[64] = {false};
+  int dev = 0;
+  SDB_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64 || !attr_set[dev]) {
+    SDB_CUDA_OK(cudaFuncSetAttribute(attn_bwd_dq_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBdSmem));
+    if (dev >= 0 && dev < 64) attr_set[dev] = true;
+  }
+  dim3 grid((n + 2 * kBdBM - 1) / (2 * kBdBM), heads, B);
+  attn_bwd_dq_umma_kernel<<<grid, kBdThreads, kBdSmem, sdb_stream(stream)>>>(p);
+  SDB_LAUNCH_OK();
+  return SDB_OK;
+}
