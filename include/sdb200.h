@@ -255,6 +255,12 @@ int sdb_attention_p32_lse(const void* q, int64_t ldq, const void* k, int64_t ldk
 int sdb_attention_bwd_dq_p32(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
                              const void* dO_pad, int64_t lddo, const float* lse, const float* delta, void* dq,
                              int64_t lddq, int B, int heads, int n, int m, int d, float scale, void* stream);
+/* dK / dV on tcgen05 (transposed problem: thread = key row, lse / delta per query column through TMA boxes); dk / dv
+ * head-padded; needs n % 4 == 0, SDB_EUNSUPPORTED otherwise. */
+int sdb_attention_bwd_dkv_p32(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
+                              const void* dO_pad, int64_t lddo, const float* lse, const float* delta, void* dk,
+                              int64_t lddk, void* dv, int64_t lddv, int B, int heads, int n, int m, int d, float scale,
+                              void* stream);
 int sdb_attention_bwd_dkv(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
                           const void* dO, int64_t lddo, void* dk, int64_t lddk, void* dv, int64_t lddv, const float* lse,
                           const float* delta, int B, int heads, int n, int m, int d, int head_pitch, float scale,

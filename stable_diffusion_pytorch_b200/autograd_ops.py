@@ -25,6 +25,7 @@ from . import _lib
 from ._lib import ACT_GEGLU, ACT_NONE, ACT_SILU, check
 
 Tensor = torch.Tensor
+_DKV_UMMA = os.environ.get("SDB_BWD_DKV_UMMA", "1") != "0"
 _DQ_UMMA = os.environ.get("SDB_BWD_DQ_UMMA", "1") != "0"      # tuning / A-B aid: 0 = dQ on the mma.sync kernel
 
 
@@ -411,10 +412,16 @@ class _AttentionP32(Function):
             check(L.sdb_attention_bwd_dq_p32(ops._ptr(q), q.stride(1), ops._ptr(k), k.stride(1), ops._ptr(v), v.stride(1),
                                              ops._ptr(do_pad), H * hp, ops._ptr(lse), ops._ptr(delta), ops._ptr(dq),
                                              dq.stride(1), B, H, n, m, d, ctx.scale, ops._stream()), "attention_bwd_dq_p32")
-            check(L.sdb_attention_bwd_dkv(ops._ptr(q), q.stride(1), ops._ptr(k), k.stride(1), ops._ptr(v), v.stride(1),
-                                          ops._ptr(do), do.stride(1), ops._ptr(dk), dk.stride(1), ops._ptr(dv), dv.stride(1),
-                                          ops._ptr(lse), ops._ptr(delta), B, H, n, m, d, hp, ctx.scale, ops._stream()),
-                  "attention_bwd_dkv")
+            if n % 4 == 0 and _DKV_UMMA:
+                check(L.sdb_attention_bwd_dkv_p32(ops._ptr(q), q.stride(1), ops._ptr(k), k.stride(1), ops._ptr(v),
+                                                  v.stride(1), ops._ptr(do_pad), H * hp, ops._ptr(lse), ops._ptr(delta),
+                                                  ops._ptr(dk), dk.stride(1), ops._ptr(dv), dv.stride(1), B, H, n, m, d,
+                                                  ctx.scale, ops._stream()), "attention_bwd_dkv_p32")
+            else:
+                check(L.sdb_attention_bwd_dkv(ops._ptr(q), q.stride(1), ops._ptr(k), k.stride(1), ops._ptr(v), v.stride(1),
+                                              ops._ptr(do), do.stride(1), ops._ptr(dk), dk.stride(1), ops._ptr(dv),
+                                              dv.stride(1), ops._ptr(lse), ops._ptr(delta), B, H, n, m, d, hp, ctx.scale,
+                                              ops._stream()), "attention_bwd_dkv")
             return dq, dk, dv, None, None, None
         delta = torch.empty(B * ctx.heads * n, device=q.device, dtype=torch.float32)
         lse = ctx.saved_tensors[4] if ctx.has_lse else torch.empty_like(delta)
