@@ -255,10 +255,15 @@ int sdb_attention_p32_lse(const void* q, int64_t ldq, const void* k, int64_t ldk
 int sdb_attention_bwd_dq_p32(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
                              const void* dO_pad, int64_t lddo, const float* lse, const float* delta, void* dq,
                              int64_t lddq, int B, int heads, int n, int m, int d, float scale, void* stream);
+/* One pass ahead of the tcgen05 backward kernels: do_pad [B,n,heads,32] bf16 (pad 0), delta = rowsum(dO o O), and the
+ * negated delta / lse ([B,heads,n] fp32) that sdb_attention_bwd_dkv_p32 takes. */
+int sdb_attention_bwd_prep(const void* dO, int64_t lddo, const void* O, int64_t ldo, const float* lse, void* do_pad,
+                           float* delta, float* neg_delta, float* neg_lse, int B, int heads, int n, int d, void* stream);
 /* dK / dV on tcgen05 (transposed problem: thread = key row, lse / delta per query column through TMA boxes); dk / dv
- * head-padded; needs n % 4 == 0, SDB_EUNSUPPORTED otherwise. */
+ * head-padded; lse / delta are passed NEGATED (sdb_attention_bwd_prep writes them); needs n % 4 == 0,
+ * SDB_EUNSUPPORTED otherwise. */
 int sdb_attention_bwd_dkv_p32(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
-                              const void* dO_pad, int64_t lddo, const float* lse, const float* delta, void* dk,
+                              const void* dO_pad, int64_t lddo, const float* neg_lse, const float* neg_delta, void* dk,
                               int64_t lddk, void* dv, int64_t lddv, int B, int heads, int n, int m, int d, float scale,
                               void* stream);
 int sdb_attention_bwd_dkv(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,

@@ -402,19 +402,23 @@ class _AttentionP32(Function):
         dk = torch.empty(B, m, ctx.heads * hp, device=q.device, dtype=torch.bfloat16)
         dv = torch.empty_like(dk)
         if ctx.has_lse and ctx.d <= 20 and _DQ_UMMA:
-            # long sequences (the forward ran on tcgen05 and kept lse): dQ on the tensor cores, dK / dV on mma.sync
+            # long sequences (the forward ran on tcgen05 and kept lse): dQ and dK / dV on the tensor cores
             H, d = ctx.heads, ctx.d
             lse = ctx.saved_tensors[4]
-            delta = (do.float() * o.float()).view(B, n, H, d).sum(-1).permute(0, 2, 1).contiguous()   # [B, H, n]
-            do_pad = torch.zeros(B, n, H, hp, device=q.device, dtype=torch.bfloat16)
-            do_pad[..., :d] = do.view(B, n, H, d)
             L = _lib.lib()
+            do = do if do.stride(2) == 1 and do.stride(0) == n * do.stride(1) else do.contiguous()
+            do_pad = torch.empty(B, n, H, hp, device=q.device, dtype=torch.bfloat16)
+            stats = torch.empty(3, B, H, n, device=q.device, dtype=torch.float32)
+            delta, ndelta, nlse = stats[0], stats[1], stats[2]
+            check(L.sdb_attention_bwd_prep(ops._ptr(do), do.stride(1), ops._ptr(o), o.stride(1), ops._ptr(lse),
+                                           ops._ptr(do_pad), ops._ptr(delta), ops._ptr(ndelta), ops._ptr(nlse), B, H, n, d,
+                                           ops._stream()), "attention_bwd_prep")
             check(L.sdb_attention_bwd_dq_p32(ops._ptr(q), q.stride(1), ops._ptr(k), k.stride(1), ops._ptr(v), v.stride(1),
                                              ops._ptr(do_pad), H * hp, ops._ptr(lse), ops._ptr(delta), ops._ptr(dq),
                                              dq.stride(1), B, H, n, m, d, ctx.scale, ops._stream()), "attention_bwd_dq_p32")
             if n % 4 == 0 and _DKV_UMMA:
                 check(L.sdb_attention_bwd_dkv_p32(ops._ptr(q), q.stride(1), ops._ptr(k), k.stride(1), ops._ptr(v),
-                                                  v.stride(1), ops._ptr(do_pad), H * hp, ops._ptr(lse), ops._ptr(delta),
+                                                  v.stride(1), ops._ptr(do_pad), H * hp, ops._ptr(nlse), ops._ptr(ndelta),
                                                   ops._ptr(dk), dk.stride(1), ops._ptr(dv), dv.stride(1), B, H, n, m, d,
                                                   ctx.scale, ops._stream()), "attention_bwd_dkv_p32")
             else:

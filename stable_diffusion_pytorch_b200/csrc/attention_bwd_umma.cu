@@ -20,6 +20,16 @@ constexpr int kBdKVBytes = kBdBN * 32 * 2;      // 4 KB each for K and V
 constexpr int kBdStageBytes = 2 * kBdKVBytes;
 constexpr int kBdSmem = 4 * kBdQBytes + kBdStages * kBdStageBytes + 1024 + 256;
 
+// pairs of every 8 exponentiated on the FMA pipe; SDB_BWD_POLY=0|2|3|4 overrides the default (2) for A/B timing
+static int bwd_poly_pairs() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("SDB_BWD_POLY");
+    v = e ? atoi(e) : 2;
+  }
+  return v;
+}
+
 struct BdParams {
   CUtensorMap tmQ, tmdO, tmK, tmV;
   const float* lse;     // [B, heads, n] log2-domain log-sum-exp of the scaled scores
@@ -30,6 +40,8 @@ struct BdParams {
   float scale, scale_log2;
 };
 
+// kPoly = pairs out of every 8 whose exp2 runs as a polynomial on the FMA pipe (the MUFU unit is the bound otherwise)
+template <int kPoly>
 __global__ void __launch_bounds__(kBdThreads, 1) attn_bwd_dq_umma_kernel(const __grid_constant__ BdParams p) {
   extern __shared__ __align__(1024) uint8_t bd_smem[];
   const uint32_t base = (smem_u32(bd_smem) + 1023u) & ~1023u;
@@ -154,11 +166,11 @@ __global__ void __launch_bounds__(kBdThreads, 1) attn_bwd_dq_umma_kernel(const _
     const uint32_t tw = tmem_base + ((uint32_t)(quarter * 32) << 16) + (uint32_t)w * 256u;
     const float c = p.scale_log2;
     const int row = q0 + w * kBdBM + quarter * 32 + lane;
-    float neg_lse = 0.f, delta = 0.f;
+    float neg_lse = 0.f, neg_delta = 0.f;
     if (row < p.n) {
       const long long o = ((long long)b * p.heads + h) * p.n + row;
       neg_lse = -p.lse[o];
-      delta = p.delta[o];
+      neg_delta = -p.delta[o];
     }
     bool ok = true;
     for (int j = 0; j < T; ++j) {
@@ -191,9 +203,17 @@ __global__ void __launch_bounds__(kBdThreads, 1) attn_bwd_dq_umma_kernel(const _
 #pragma unroll
         for (int k = 0; k < 16; ++k) {
           const int i = ch * 32 + 2 * k;
-          const float p0 = ex2_mufu(fmaf(__uint_as_float(su[i]), c, neg_lse));
-          const float p1 = ex2_mufu(fmaf(__uint_as_float(su[i + 1]), c, neg_lse));
-          pk[k] = pack_bf16x2(p0 * (__uint_as_float(su[64 + i]) - delta), p1 * (__uint_as_float(su[64 + i + 1]) - delta));
+          float x0, x1, d0, d1;
+          ffma2(x0, x1, __uint_as_float(su[i]), __uint_as_float(su[i + 1]), c, c, neg_lse, neg_lse);
+          if ((k & 7) < kPoly) {
+            ex2_poly2(x0, x1);
+          } else {
+            x0 = ex2_mufu(x0);
+            x1 = ex2_mufu(x1);
+          }
+          fadd2(d0, d1, __uint_as_float(su[64 + i]), __uint_as_float(su[64 + i + 1]), neg_delta, neg_delta);
+          fmul2(d0, d1, d0, d1, x0, x1);
+          pk[k] = pack_bf16x2(d0, d1);
         }
         tmem_st_32x16(tw + 128 + ch * 16, pk);
       }
@@ -265,11 +285,19 @@ extern "C" int sdb_attention_bwd_dq_p32(const void* q, int64_t ldq, const void* 
   int dev = 0;
   SDB_CUDA_OK(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-    SDB_CUDA_OK(cudaFuncSetAttribute(attn_bwd_dq_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBdSmem));
+    SDB_CUDA_OK(cudaFuncSetAttribute(attn_bwd_dq_umma_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBdSmem));
+    SDB_CUDA_OK(cudaFuncSetAttribute(attn_bwd_dq_umma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBdSmem));
+    SDB_CUDA_OK(cudaFuncSetAttribute(attn_bwd_dq_umma_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBdSmem));
+    SDB_CUDA_OK(cudaFuncSetAttribute(attn_bwd_dq_umma_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBdSmem));
     if (dev >= 0 && dev < 64) attr_set[dev] = true;
   }
   dim3 grid((n + 2 * kBdBM - 1) / (2 * kBdBM), heads, B);
-  attn_bwd_dq_umma_kernel<<<grid, kBdThreads, kBdSmem, sdb_stream(stream)>>>(p);
+  switch (bwd_poly_pairs()) {
+    case 0: attn_bwd_dq_umma_kernel<0><<<grid, kBdThreads, kBdSmem, sdb_stream(stream)>>>(p); break;
+    case 4: attn_bwd_dq_umma_kernel<4><<<grid, kBdThreads, kBdSmem, sdb_stream(stream)>>>(p); break;
+    case 3: attn_bwd_dq_umma_kernel<3><<<grid, kBdThreads, kBdSmem, sdb_stream(stream)>>>(p); break;
+    default: attn_bwd_dq_umma_kernel<2><<<grid, kBdThreads, kBdSmem, sdb_stream(stream)>>>(p); break;
+  }
   SDB_LAUNCH_OK();
   return SDB_OK;
 }
@@ -298,6 +326,7 @@ struct BkParams {
   float scale, scale_log2;
 };
 
+template <int kPoly>
 __global__ void __launch_bounds__(kBdThreads, 1) attn_bwd_dkv_umma_kernel(const __grid_constant__ BkParams p) {
   extern __shared__ __align__(1024) uint8_t bk_smem[];
   const uint32_t base = (smem_u32(bk_smem) + 1023u) & ~1023u;
@@ -464,17 +493,32 @@ __global__ void __launch_bounds__(kBdThreads, 1) attn_bwd_dkv_umma_kernel(const 
       for (int ch = 0; ch < 2; ++ch) {
         uint32_t pp[16], ps[16];
 #pragma unroll
-        for (int g4 = 0; g4 < 8; ++g4) {       // four queries per shared-memory broadcast
+        for (int g4 = 0; g4 < 8; ++g4) {       // four queries per shared-memory broadcast (-lse, -delta)
           const float4 l = sl[ch * 8 + g4], dl = sd[ch * 8 + g4];
           const int i = ch * 32 + 4 * g4;
-          const float p0 = ex2_mufu(fmaf(__uint_as_float(su[i]), c, -l.x));
-          const float p1 = ex2_mufu(fmaf(__uint_as_float(su[i + 1]), c, -l.y));
-          const float p2 = ex2_mufu(fmaf(__uint_as_float(su[i + 2]), c, -l.z));
-          const float p3 = ex2_mufu(fmaf(__uint_as_float(su[i + 3]), c, -l.w));
-          pp[2 * g4] = pack_bf16x2(p0, p1);
-          pp[2 * g4 + 1] = pack_bf16x2(p2, p3);
-          ps[2 * g4] = pack_bf16x2(p0 * (__uint_as_float(su[64 + i]) - dl.x), p1 * (__uint_as_float(su[64 + i + 1]) - dl.y));
-          ps[2 * g4 + 1] = pack_bf16x2(p2 * (__uint_as_float(su[64 + i + 2]) - dl.z), p3 * (__uint_as_float(su[64 + i + 3]) - dl.w));
+          float x0, x1, x2, x3, d0, d1, d2, d3;
+          ffma2(x0, x1, __uint_as_float(su[i]), __uint_as_float(su[i + 1]), c, c, l.x, l.y);
+          ffma2(x2, x3, __uint_as_float(su[i + 2]), __uint_as_float(su[i + 3]), c, c, l.z, l.w);
+          if (((2 * g4) & 7) < kPoly) {
+            ex2_poly2(x0, x1);
+          } else {
+            x0 = ex2_mufu(x0);
+            x1 = ex2_mufu(x1);
+          }
+          if (((2 * g4 + 1) & 7) < kPoly) {
+            ex2_poly2(x2, x3);
+          } else {
+            x2 = ex2_mufu(x2);
+            x3 = ex2_mufu(x3);
+          }
+          pp[2 * g4] = pack_bf16x2(x0, x1);
+          pp[2 * g4 + 1] = pack_bf16x2(x2, x3);
+          fadd2(d0, d1, __uint_as_float(su[64 + i]), __uint_as_float(su[64 + i + 1]), dl.x, dl.y);
+          fadd2(d2, d3, __uint_as_float(su[64 + i + 2]), __uint_as_float(su[64 + i + 3]), dl.z, dl.w);
+          fmul2(d0, d1, d0, d1, x0, x1);
+          fmul2(d2, d3, d2, d3, x2, x3);
+          ps[2 * g4] = pack_bf16x2(d0, d1);
+          ps[2 * g4 + 1] = pack_bf16x2(d2, d3);
         }
         tmem_st_32x16(tw + 128 + ch * 16, pp);
         tmem_st_32x16(tw + 160 + ch * 16, ps);
@@ -519,11 +563,14 @@ __global__ void __launch_bounds__(kBdThreads, 1) attn_bwd_dkv_umma_kernel(const 
 
 // dK / dV of the head-padded attention on tcgen05.  dk / dv head-padded [B, m, >= heads*32]; n % 4 == 0 (the lse /
 // delta rows are TMA boxes); SDB_EUNSUPPORTED otherwise (the caller then uses sdb_attention_bwd_dkv).
+// NOTE: lse and delta are passed NEGATED ([B, heads, n] fp32 of -lse2 and -delta): they are per-column operands here and
+// feed packed f32x2 adds straight from shared memory.
 extern "C" int sdb_attention_bwd_dkv_p32(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
-                                         const void* dO_pad, int64_t lddo, const float* lse, const float* delta, void* dk,
-                                         int64_t lddk, void* dv, int64_t lddv, int B, int heads, int n, int m, int d,
-                                         float scale, void* stream) {
+                                         const void* dO_pad, int64_t lddo, const float* neg_lse, const float* neg_delta,
+                                         void* dk, int64_t lddk, void* dv, int64_t lddv, int B, int heads, int n, int m,
+                                         int d, float scale, void* stream) {
   using namespace sdb;
+  const float *lse = neg_lse, *delta = neg_delta;
   SDB_CHECK_ARG(q && k && v && dO_pad && lse && delta && dk && dv && B > 0 && heads > 0 && n > 0 && m > 0,
                 "attention_bwd_dkv_p32: bad args");
   SDB_CHECK_ARG(d > 0 && d <= 20 && d % 4 == 0, "attention_bwd_dkv_p32: head dim (%d) must be a multiple of 4, <= 20", d);
@@ -567,11 +614,83 @@ extern "C" int sdb_attention_bwd_dkv_p32(const void* q, int64_t ldq, const void*
   int dev = 0;
   SDB_CUDA_OK(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-    SDB_CUDA_OK(cudaFuncSetAttribute(attn_bwd_dkv_umma_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, kBkSmem));
+    SDB_CUDA_OK(cudaFuncSetAttribute(attn_bwd_dkv_umma_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBkSmem));
+    SDB_CUDA_OK(cudaFuncSetAttribute(attn_bwd_dkv_umma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBkSmem));
+    SDB_CUDA_OK(cudaFuncSetAttribute(attn_bwd_dkv_umma_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBkSmem));
+    SDB_CUDA_OK(cudaFuncSetAttribute(attn_bwd_dkv_umma_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBkSmem));
     if (dev >= 0 && dev < 64) attr_set[dev] = true;
   }
   dim3 grid((m + 2 * kBdBM - 1) / (2 * kBdBM), heads, B);
-  attn_bwd_dkv_umma_kernel<<<grid, kBdThreads, kBkSmem, sdb_stream(stream)>>>(p);
+  switch (bwd_poly_pairs()) {
+    case 0: attn_bwd_dkv_umma_kernel<0><<<grid, kBdThreads, kBkSmem, sdb_stream(stream)>>>(p); break;
+    case 4: attn_bwd_dkv_umma_kernel<4><<<grid, kBdThreads, kBkSmem, sdb_stream(stream)>>>(p); break;
+    case 3: attn_bwd_dkv_umma_kernel<3><<<grid, kBdThreads, kBkSmem, sdb_stream(stream)>>>(p); break;
+    default: attn_bwd_dkv_umma_kernel<2><<<grid, kBdThreads, kBkSmem, sdb_stream(stream)>>>(p); break;
+  }
+  SDB_LAUNCH_OK();
+  return SDB_OK;
+}
+
+// ================================================================================================================
+// One pass over dO and O ahead of the two tcgen05 backward kernels: head-pads dO (32 columns per head, pad = 0), forms
+// delta = rowsum(dO o O) per (batch, head, query) and the negated copies the transposed dK/dV problem consumes.
+namespace sdb {
+
+__global__ void attn_bwd_prep_kernel(const __nv_bfloat16* __restrict__ dO, long long lddo, const __nv_bfloat16* __restrict__ O,
+                                     long long ldo, const float* __restrict__ lse, __nv_bfloat16* __restrict__ do_pad,
+                                     float* __restrict__ delta, float* __restrict__ neg_delta, float* __restrict__ neg_lse,
+                                     long long rows, int n, int heads, int d) {
+  const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;   // (row, head), head fastest
+  if (t >= rows * heads) return;
+  const long long r = t / heads;
+  const int h = (int)(t - r * heads);
+  const uint2* a = reinterpret_cast<const uint2*>(dO + r * lddo + h * d);
+  const uint2* o = reinterpret_cast<const uint2*>(O + r * ldo + h * d);
+  uint32_t w[16];
+#pragma unroll
+  for (int i = 0; i < 16; ++i) w[i] = 0u;
+  float acc = 0.f;
+#pragma unroll
+  for (int i = 0; i < 5; ++i) {
+    if (4 * i < d) {
+      const uint2 x = __ldg(a + i), y = __ldg(o + i);
+      w[2 * i] = x.x;
+      w[2 * i + 1] = x.y;
+      acc = fmaf(__uint_as_float(x.x << 16), __uint_as_float(y.x << 16), acc);
+      acc = fmaf(__uint_as_float(x.x & 0xffff0000u), __uint_as_float(y.x & 0xffff0000u), acc);
+      acc = fmaf(__uint_as_float(x.y << 16), __uint_as_float(y.y << 16), acc);
+      acc = fmaf(__uint_as_float(x.y & 0xffff0000u), __uint_as_float(y.y & 0xffff0000u), acc);
+    }
+  }
+  uint4* dst = reinterpret_cast<uint4*>(do_pad + t * 32);
+#pragma unroll
+  for (int v = 0; v < 4; ++v) dst[v] = make_uint4(w[4 * v], w[4 * v + 1], w[4 * v + 2], w[4 * v + 3]);
+  const long long b = r / n;
+  const long long idx = (b * heads + h) * n + (r - b * n);
+  delta[idx] = acc;
+  neg_delta[idx] = -acc;
+  neg_lse[idx] = -lse[idx];
+}
+
+}  // namespace sdb
+
+// dO, O: [B, n, heads*d] bf16 (row strides lddo / ldo, multiples of 4); lse: [B, heads, n] fp32 from the forward.
+// Writes do_pad [B, n, heads, 32] bf16 and delta, neg_delta, neg_lse [B, heads, n] fp32.  d % 4 == 0, d <= 20.
+extern "C" int sdb_attention_bwd_prep(const void* dO, int64_t lddo, const void* O, int64_t ldo, const float* lse, void* do_pad,
+                                      float* delta, float* neg_delta, float* neg_lse, int B, int heads, int n, int d,
+                                      void* stream) {
+  using namespace sdb;
+  SDB_CHECK_ARG(dO && O && lse && do_pad && delta && neg_delta && neg_lse && B > 0 && heads > 0 && n > 0,
+                "attention_bwd_prep: bad args");
+  SDB_CHECK_ARG(d > 0 && d <= 20 && d % 4 == 0, "attention_bwd_prep: head dim (%d) must be a multiple of 4, <= 20", d);
+  SDB_CHECK_ARG(lddo % 4 == 0 && ldo % 4 == 0 && lddo >= heads * d && ldo >= heads * d && ((uintptr_t)dO & 7) == 0 &&
+                    ((uintptr_t)O & 7) == 0 && ((uintptr_t)do_pad & 15) == 0,
+                "attention_bwd_prep: rows must be 8-byte aligned (strides multiples of 4), do_pad 16-byte aligned");
+  const long long rows = (long long)B * n, total = rows * heads;
+  const int threads = 256;
+  attn_bwd_prep_kernel<<<(unsigned)((total + threads - 1) / threads), threads, 0, sdb_stream(stream)>>>(
+      (const __nv_bfloat16*)dO, lddo, (const __nv_bfloat16*)O, ldo, lse, (__nv_bfloat16*)do_pad, delta, neg_delta, neg_lse,
+      rows, n, heads, d);
   SDB_LAUNCH_OK();
   return SDB_OK;
 }

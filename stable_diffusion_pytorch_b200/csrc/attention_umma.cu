@@ -126,6 +126,14 @@ __device__ __forceinline__ void fadd2(float& d0, float& d1, float a0, float a1, 
       : "=f"(d0), "=f"(d1)
       : "f"(a0), "f"(a1), "f"(b0), "f"(b1));
 }
+__device__ __forceinline__ void fmul2(float& d0, float& d1, float a0, float a1, float b0, float b1) {
+  asm("{\n\t.reg .b64 ra, rb, rd;\n\t"
+      "mov.b64 ra, {%2, %3};\n\tmov.b64 rb, {%4, %5};\n\t"
+      "mul.rn.f32x2 rd, ra, rb;\n\t"
+      "mov.b64 {%0, %1}, rd;\n\t}"
+      : "=f"(d0), "=f"(d1)
+      : "f"(a0), "f"(a1), "f"(b0), "f"(b1));
+}
 // exp2 of two non-positive arguments on the FMA pipe: x = floor(x) + f, 2^f by a degree-3 minimax
 // polynomial on [0, 1), exponent patched in with an integer add.  Relative error ~1e-4, well
 // inside the bf16 rounding of P.

@@ -72,14 +72,7 @@ struct UmmaParams {
 };
 
 // ---- packed fp32 pair helpers (one issue slot for two elements) ---------------------------------
-__device__ __forceinline__ void fmul2(float& d0, float& d1, float a0, float a1, float b0, float b1) {
-  asm("{\n\t.reg .b64 ra, rb, rd;\n\t"
-      "mov.b64 ra, {%2, %3};\n\tmov.b64 rb, {%4, %5};\n\t"
-      "mul.rn.f32x2 rd, ra, rb;\n\t"
-      "mov.b64 {%0, %1}, rd;\n\t}"
-      : "=f"(d0), "=f"(d1)
-      : "f"(a0), "f"(a1), "f"(b0), "f"(b1));
-}
+// (fmul2 / ffma2 / fadd2 live in attention_umma.cu, included first in the unity build)
 
 // a * gelu(g) for two (a, g) pairs, exact-erf GELU (transformer.py:177 uses nn.GELU()).
 //   erfc(u/sqrt2) = 2^(-u P(u)),  u = min(|g|, 6),  P = degree-5 fit of -log2(erfc(u/sqrt2))/u on [0, 6]

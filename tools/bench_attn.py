@@ -33,3 +33,14 @@ if os.environ.get("OLD"):
     ms = timeit(lambda: ops.attention(qkv2[:, :, :160], qkv2[:, :, 160:320], qkv2[:, :, 320:], H, d, 1 / math.sqrt(d)))
     print(f"attention (mma.sync): {ms:.3f} ms")
 print("timeout flag", ops.debug_timeout_flag())
+if os.environ.get("BWD"):
+    # backward of the self-attention at the same shape (dQ and dK/dV on tcgen05, lse handed over by the forward)
+    from stable_diffusion_pytorch_b200 import autograd_ops
+    Bb = int(os.environ.get("BB", 64))
+    qkvb = qkv[:1].expand(Bb, -1, -1).contiguous() if Bb != B else qkv
+    qb, kb, vb = (t.detach().requires_grad_(True) for t in (qkvb[:, :, :256], qkvb[:, :, 256:512], qkvb[:, :, 512:]))
+    out = autograd_ops.attention_p32(qb, kb, vb, H, d, 1 / math.sqrt(d))
+    g = torch.randn_like(out)
+    ms = timeit(lambda: torch.autograd.grad(out, (qb, kb, vb), g, retain_graph=True), it=5, warm=2)
+    print(f"attention_p32 backward (B={Bb}): {ms:.3f} ms  (dq + dkv kernels + delta / pad glue)")
+    print("timeout flag", ops.debug_timeout_flag())
