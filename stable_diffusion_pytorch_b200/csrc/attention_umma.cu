@@ -420,6 +420,8 @@ attention_umma_kernel(const __grid_constant__ FaParams p) {
 
 }  // namespace sdb
 
+#include "attention_umma_wg1.cu"   // the one-warpgroup-per-CTA shape of the same pipeline (uses the helpers above)
+
 static int attention_p32_impl(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
                               int64_t ldv, void* out, int64_t ldo, int B, int heads, int n, int m, int d,
                               float scale, float* lse, int* lse_written, void* stream) {
@@ -443,7 +445,16 @@ static int attention_p32_impl(const void* q, int64_t ldq, const void* k, int64_t
     return attention_ctx_dispatch(q, ldq, k, ldk, v, ldv, out, ldo, B, heads, n, m, d, scale, sdb_stream(stream));
   FaParams p;
   memset(&p, 0, sizeof(p));
+  // kernel shape: 0 = two warpgroups per CTA, 128-key tiles; 3 / 4 = one warpgroup per CTA, 64-key tiles, that many
+  // CTAs per SM.  Default 4 (config 2: 1.105 vs 1.199 ms per layer, 831 vs 795 latent-steps/s); SDB_FA_WG1 overrides
+  static int wg1 = -1;
+  if (wg1 < 0) {
+    const char* e = getenv("SDB_FA_WG1");
+    wg1 = e ? atoi(e) : 4;
+    if (wg1 != 3 && wg1 != 4) wg1 = 0;
+  }
   const uint32_t box[3] = {32, 128, 1};
+  const uint32_t box_kv[3] = {32, wg1 ? 64u : 128u, 1};
   {
     uint64_t dims[3] = {(uint64_t)heads * 32, (uint64_t)n, (uint64_t)B};
     uint64_t st[3] = {0, (uint64_t)ldq * 2, (uint64_t)n * ldq * 2};
@@ -453,11 +464,11 @@ static int attention_p32_impl(const void* q, int64_t ldq, const void* k, int64_t
   {
     uint64_t dims[3] = {(uint64_t)heads * 32, (uint64_t)m, (uint64_t)B};
     uint64_t st[3] = {0, (uint64_t)ldk * 2, (uint64_t)m * ldk * 2};
-    int rc = sdb_make_tensor_map(&p.tmK, k, 2, 3, dims, st, box, 64);
+    int rc = sdb_make_tensor_map(&p.tmK, k, 2, 3, dims, st, box_kv, 64);
     if (rc) return rc;
     st[1] = (uint64_t)ldv * 2;
     st[2] = (uint64_t)m * ldv * 2;
-    rc = sdb_make_tensor_map(&p.tmV, v, 2, 3, dims, st, box, 64);
+    rc = sdb_make_tensor_map(&p.tmV, v, 2, 3, dims, st, box_kv, 64);
     if (rc) return rc;
   }
   p.out = (__nv_bfloat16*)out;
@@ -470,8 +481,22 @@ static int attention_p32_impl(const void* q, int64_t ldq, const void* k, int64_t
   static int poly = -1;
   if (poly < 0) {
     const char* e = getenv("SDB_FA_POLY");
-    poly = e ? atoi(e) : 3;
-    if (poly < 0 || poly > 6) poly = 3;
+    poly = e ? atoi(e) : (wg1 ? 2 : 3);   // measured best per shape
+    if (poly < 0 || poly > 6) poly = wg1 ? 2 : 3;
+  }
+  if (wg1) {
+    dim3 grid1((n + kF1BM - 1) / kF1BM, heads, B);
+    int rc;
+    if (wg1 == 4) rc = poly == 2 ? launch_attention_wg1<2, 4>(p, grid1, sdb_stream(stream))
+                     : poly == 4 ? launch_attention_wg1<4, 4>(p, grid1, sdb_stream(stream))
+                     : poly == 1 ? launch_attention_wg1<1, 4>(p, grid1, sdb_stream(stream))
+                                 : launch_attention_wg1<3, 4>(p, grid1, sdb_stream(stream));
+    else rc = poly == 2 ? launch_attention_wg1<2, 3>(p, grid1, sdb_stream(stream))
+            : poly == 4 ? launch_attention_wg1<4, 3>(p, grid1, sdb_stream(stream))
+                        : launch_attention_wg1<3, 3>(p, grid1, sdb_stream(stream));
+    if (rc) return rc;
+    SDB_LAUNCH_OK();
+    return SDB_OK;
   }
   dim3 grid((n + 2 * kFaBM - 1) / (2 * kFaBM), heads, B);
 #define SDB_FA_LAUNCH(P)                                                                                   \

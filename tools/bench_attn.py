@@ -18,7 +18,7 @@ qkv.view(B, n, 3, H, 32)[:, :, 2, :, d] = 1
 q, k, v = qkv[:, :, :256], qkv[:, :, 256:512], qkv[:, :, 512:]
 ms = timeit(lambda: ops.attention_p32(q, k, v, H, d, 1 / math.sqrt(d)))
 pairs = B * H * n * n
-print(f"attention_p32 poly={os.environ.get('SDB_FA_POLY','3')}: {ms:.3f} ms  {pairs/ms/1e9:.2f} Gpairs/ms... "
+print(f"attention_p32 poly={os.environ.get('SDB_FA_POLY','default')}: {ms:.3f} ms  {pairs/ms/1e9:.2f} Gpairs/ms... "
       f"{pairs/(ms*1e-3)/148/1.965e9:.2f} pairs/clk/SM  {4*pairs*d/(ms*1e-3)/1e12:.1f} TFLOP/s(alg)")
 # cross-attention over a 77-token context (same queries)
 ctx = torch.randn(B, 77, 2 * H * 32, device="cuda").to(torch.bfloat16)
