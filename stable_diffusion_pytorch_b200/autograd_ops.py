@@ -393,48 +393,81 @@ class _AttentionP32(Function):
 
     @staticmethod
     def backward(ctx, do):
-        ops = _ops()
         q, k, v, o = ctx.saved_tensors[:4]
         B, n, m = q.shape[0], q.shape[1], k.shape[1]
-        hp = 32
-        do = _bf16(do)
-        dq = torch.empty(B, n, ctx.heads * hp, device=q.device, dtype=torch.bfloat16)
-        dk = torch.empty(B, m, ctx.heads * hp, device=q.device, dtype=torch.bfloat16)
+        dq = torch.empty(B, n, ctx.heads * 32, device=q.device, dtype=torch.bfloat16)
+        dk = torch.empty(B, m, ctx.heads * 32, device=q.device, dtype=torch.bfloat16)
         dv = torch.empty_like(dk)
-        if ctx.has_lse and ctx.d <= 20 and _DQ_UMMA:
-            # long sequences (the forward ran on tcgen05 and kept lse): dQ and dK / dV on the tensor cores
-            H, d = ctx.heads, ctx.d
-            lse = ctx.saved_tensors[4]
-            L = _lib.lib()
-            do = do if do.stride(2) == 1 and do.stride(0) == n * do.stride(1) else do.contiguous()
-            do_pad = torch.empty(B, n, H, hp, device=q.device, dtype=torch.bfloat16)
-            stats = torch.empty(3, B, H, n, device=q.device, dtype=torch.float32)
-            delta, ndelta, nlse = stats[0], stats[1], stats[2]
-            check(L.sdb_attention_bwd_prep(ops._ptr(do), do.stride(1), ops._ptr(o), o.stride(1), ops._ptr(lse),
-                                           ops._ptr(do_pad), ops._ptr(delta), ops._ptr(ndelta), ops._ptr(nlse), B, H, n, d,
-                                           ops._stream()), "attention_bwd_prep")
-            check(L.sdb_attention_bwd_dq_p32(ops._ptr(q), q.stride(1), ops._ptr(k), k.stride(1), ops._ptr(v), v.stride(1),
-                                             ops._ptr(do_pad), H * hp, ops._ptr(lse), ops._ptr(delta), ops._ptr(dq),
-                                             dq.stride(1), B, H, n, m, d, ctx.scale, ops._stream()), "attention_bwd_dq_p32")
-            if n % 4 == 0 and _DKV_UMMA:
-                check(L.sdb_attention_bwd_dkv_p32(ops._ptr(q), q.stride(1), ops._ptr(k), k.stride(1), ops._ptr(v),
-                                                  v.stride(1), ops._ptr(do_pad), H * hp, ops._ptr(nlse), ops._ptr(ndelta),
-                                                  ops._ptr(dk), dk.stride(1), ops._ptr(dv), dv.stride(1), B, H, n, m, d,
-                                                  ctx.scale, ops._stream()), "attention_bwd_dkv_p32")
-            else:
-                check(L.sdb_attention_bwd_dkv(ops._ptr(q), q.stride(1), ops._ptr(k), k.stride(1), ops._ptr(v), v.stride(1),
-                                              ops._ptr(do), do.stride(1), ops._ptr(dk), dk.stride(1), ops._ptr(dv),
-                                              dv.stride(1), ops._ptr(lse), ops._ptr(delta), B, H, n, m, d, hp, ctx.scale,
-                                              ops._stream()), "attention_bwd_dkv")
-            return dq, dk, dv, None, None, None
-        delta = torch.empty(B * ctx.heads * n, device=q.device, dtype=torch.float32)
-        lse = ctx.saved_tensors[4] if ctx.has_lse else torch.empty_like(delta)
-        check(_lib.lib().sdb_attention_bwd(
-            ops._ptr(q), q.stride(1), ops._ptr(k), k.stride(1), ops._ptr(v), v.stride(1), ops._ptr(o), o.stride(1),
-            ops._ptr(do), do.stride(1), ops._ptr(dq), dq.stride(1), ops._ptr(dk), dk.stride(1), ops._ptr(dv), dv.stride(1),
-            ops._ptr(lse), ops._ptr(delta), int(ctx.has_lse), B, ctx.heads, n, m, ctx.d, hp, ctx.scale, ops._stream()),
-            "attention_bwd")
+        _attention_p32_backward(ctx, q, k, v, o, ctx.saved_tensors[4] if ctx.has_lse else None, do, dq, dk, dv)
         return dq, dk, dv, None, None, None
+
+
+class _SelfAttentionP32(Function):
+    """``_AttentionP32`` over the packed projection output qkv [B, n, 3*heads*32]: Q / K / V are column slices of one
+    tensor, and the three backward kernels write their slices of ONE packed gradient (row stride 3*heads*32) -- as
+    three autograd inputs every slice cost a full-size zero fill, a strided copy and an add per layer."""
+
+    @staticmethod
+    def forward(ctx, qkv, heads, d, scale):
+        kw = heads * 32
+        q, k, v = qkv[:, :, :kw], qkv[:, :, kw:2 * kw], qkv[:, :, 2 * kw:]
+        o, lse = _ops().attention_p32_lse(q, k, v, heads, d, scale)
+        ctx.has_lse = lse is not None
+        ctx.save_for_backward(qkv, o, *([lse] if lse is not None else []))
+        ctx.heads, ctx.d, ctx.scale = heads, d, scale
+        return o
+
+    @staticmethod
+    def backward(ctx, do):
+        qkv, o = ctx.saved_tensors[:2]
+        kw = ctx.heads * 32
+        # the tcgen05 kernels write every padded column of their slice; the mma.sync fall-backs leave the pad alone
+        full = ctx.has_lse and ctx.d <= 20 and _DQ_UMMA and _DKV_UMMA and qkv.shape[1] % 4 == 0
+        dqkv = torch.empty_like(qkv) if full else torch.zeros_like(qkv)
+        _attention_p32_backward(ctx, qkv[:, :, :kw], qkv[:, :, kw:2 * kw], qkv[:, :, 2 * kw:], o,
+                                ctx.saved_tensors[2] if ctx.has_lse else None, do, dqkv[:, :, :kw],
+                                dqkv[:, :, kw:2 * kw], dqkv[:, :, 2 * kw:])
+        return dqkv, None, None, None
+
+
+def _attention_p32_backward(ctx, q, k, v, o, lse, do, dq, dk, dv):
+    """Fills dq / dk / dv (head-padded, row-strided views allowed)."""
+    ops = _ops()
+    B, n, m = q.shape[0], q.shape[1], k.shape[1]
+    hp = 32
+    do = _bf16(do)
+    if ctx.has_lse and ctx.d <= 20 and _DQ_UMMA:
+        # long sequences (the forward ran on tcgen05 and kept lse): dQ and dK / dV on the tensor cores
+        H, d = ctx.heads, ctx.d
+        L = _lib.lib()
+        do = do if do.stride(2) == 1 and do.stride(0) == n * do.stride(1) else do.contiguous()
+        do_pad = torch.empty(B, n, H, hp, device=q.device, dtype=torch.bfloat16)
+        stats = torch.empty(3, B, H, n, device=q.device, dtype=torch.float32)
+        delta, ndelta, nlse = stats[0], stats[1], stats[2]
+        check(L.sdb_attention_bwd_prep(ops._ptr(do), do.stride(1), ops._ptr(o), o.stride(1), ops._ptr(lse),
+                                       ops._ptr(do_pad), ops._ptr(delta), ops._ptr(ndelta), ops._ptr(nlse), B, H, n, d,
+                                       ops._stream()), "attention_bwd_prep")
+        check(L.sdb_attention_bwd_dq_p32(ops._ptr(q), q.stride(1), ops._ptr(k), k.stride(1), ops._ptr(v), v.stride(1),
+                                         ops._ptr(do_pad), H * hp, ops._ptr(lse), ops._ptr(delta), ops._ptr(dq),
+                                         dq.stride(1), B, H, n, m, d, ctx.scale, ops._stream()), "attention_bwd_dq_p32")
+        if n % 4 == 0 and _DKV_UMMA:
+            check(L.sdb_attention_bwd_dkv_p32(ops._ptr(q), q.stride(1), ops._ptr(k), k.stride(1), ops._ptr(v),
+                                              v.stride(1), ops._ptr(do_pad), H * hp, ops._ptr(nlse), ops._ptr(ndelta),
+                                              ops._ptr(dk), dk.stride(1), ops._ptr(dv), dv.stride(1), B, H, n, m, d,
+                                              ctx.scale, ops._stream()), "attention_bwd_dkv_p32")
+        else:
+            check(L.sdb_attention_bwd_dkv(ops._ptr(q), q.stride(1), ops._ptr(k), k.stride(1), ops._ptr(v), v.stride(1),
+                                          ops._ptr(do), do.stride(1), ops._ptr(dk), dk.stride(1), ops._ptr(dv),
+                                          dv.stride(1), ops._ptr(lse), ops._ptr(delta), B, H, n, m, d, hp, ctx.scale,
+                                          ops._stream()), "attention_bwd_dkv")
+        return
+    delta = torch.empty(B * ctx.heads * n, device=q.device, dtype=torch.float32)
+    lse = lse if ctx.has_lse else torch.empty_like(delta)
+    check(_lib.lib().sdb_attention_bwd(
+        ops._ptr(q), q.stride(1), ops._ptr(k), k.stride(1), ops._ptr(v), v.stride(1), ops._ptr(o), o.stride(1),
+        ops._ptr(do), do.stride(1), ops._ptr(dq), dq.stride(1), ops._ptr(dk), dk.stride(1), ops._ptr(dv), dv.stride(1),
+        ops._ptr(lse), ops._ptr(delta), int(ctx.has_lse), B, ctx.heads, n, m, ctx.d, hp, ctx.scale, ops._stream()),
+        "attention_bwd")
 
 
 class _Attention(Function):
@@ -474,6 +507,10 @@ def attention(q, k, v, heads, d, scale):
 
 def attention_p32(q, k, v, heads, d, scale):
     return _AttentionP32.apply(q, k, v, heads, d, scale)
+
+
+def attention_p32_packed(qkv, heads, d, scale):
+    return _SelfAttentionP32.apply(qkv, heads, d, scale)
 
 
 class _Upsample2x(Function):

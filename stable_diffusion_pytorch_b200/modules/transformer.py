@@ -114,7 +114,9 @@ class CrossAttention(nn.Module):
                                  "(the reference fails with a shape mismatch here too)")
             qkv = ops.gemm(x2d, w["wqkv"], w["bqkv"] if self.use_p32 else None).view(B, n, 3 * kw)
             q, k, v = qkv[:, :, :kw], qkv[:, :, kw:2 * kw], qkv[:, :, 2 * kw:]
+            packed = qkv if self.use_p32 else None
         else:
+            packed = None
             q = ops.gemm(x2d, w["wq"]).view(B, n, kw)
             if kv is None:
                 m = ctx.shape[1]
@@ -123,7 +125,9 @@ class CrossAttention(nn.Module):
                 k, v = kvt[:, :, :kw], kvt[:, :, kw:]
             else:
                 k, v = kv
-        if self.use_p32:
+        if packed is not None:
+            a = ops.attention_p32_packed(packed, self.n_heads, self.d_head, self.scale)
+        elif self.use_p32:
             a = ops.attention_p32(q, k, v, self.n_heads, self.d_head, self.scale)
         else:
             a = ops.attention(q, k, v, self.n_heads, self.d_head, self.scale)

@@ -349,6 +349,15 @@ def attention_p32(q: Tensor, k: Tensor, v: Tensor, heads: int, d: int, scale: fl
     return out
 
 
+def attention_p32_packed(qkv: Tensor, heads: int, d: int, scale: float) -> Tensor:
+    """Self-attention over the packed, head-padded projection output qkv [B, n, 3*heads*32] (Q | K | V column blocks).
+    Same kernels as ``attention_p32``; under autograd the gradient comes back as one packed tensor."""
+    if _ag.wants(qkv):
+        return _ag.attention_p32_packed(qkv, heads, d, scale)
+    kw = heads * 32
+    return attention_p32(qkv[:, :, :kw], qkv[:, :, kw:2 * kw], qkv[:, :, 2 * kw:], heads, d, scale)
+
+
 def attention_p32_lse(q: Tensor, k: Tensor, v: Tensor, heads: int, d: int, scale: float):
     """``attention_p32`` that also returns the fp32 row log-sum-exp [B*heads*n] (log2 domain) the backward needs, or
     None when the kernel that ran does not keep it (short contexts)."""

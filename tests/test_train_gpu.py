@@ -192,6 +192,31 @@ def test_attention_p32_backward(B, heads, n, m, d):
         assert float(og[..., d + 1:].abs().max()) == 0.0        # the padding carries no gradient
 
 
+@pytest.mark.parametrize("B,heads,n,d", [(2, 8, 256, 20), (1, 4, 1024, 16), (2, 3, 100, 12), (1, 2, 130, 20), (2, 8, 64, 20)])
+def test_attention_p32_packed_backward(B, heads, n, d):
+    """Self-attention over the packed QKV projection output: one packed gradient, equal to the three-slice path."""
+    from stable_diffusion_pytorch_b200 import ops
+    hp = 32
+    g = torch.Generator().manual_seed(n + d)
+    t = torch.zeros(B, n, 3, heads, hp)
+    t[..., :d] = torch.randn(B, n, 3, heads, d, generator=g)
+    t[:, :, 2, :, d] = 1.0
+    qkv = t.view(B, n, 3 * heads * hp).to(DEV, torch.bfloat16).requires_grad_(True)
+    qkv2 = qkv.detach().clone().requires_grad_(True)
+    do = rnd(B, n, heads * d, seed=11, grad=False)
+    scale = d ** -0.5
+    kw = heads * hp
+    o = ops.attention_p32_packed(qkv, heads, d, scale)
+    o.backward(do)
+    o2 = ops.attention_p32(qkv2[:, :, :kw], qkv2[:, :, kw:2 * kw], qkv2[:, :, 2 * kw:], heads, d, scale)
+    o2.backward(do)
+    assert torch.equal(o, o2)
+    assert torch.isfinite(qkv.grad).all()
+    assert torch.equal(qkv.grad, qkv2.grad)
+    with torch.no_grad():                                         # inference path: same kernels, no autograd node
+        assert torch.equal(ops.attention_p32_packed(qkv.detach(), heads, d, scale), o)
+
+
 @pytest.mark.parametrize("B,heads,n,m,d", [(2, 2, 64, 77, 32), (1, 4, 256, 256, 24), (2, 3, 50, 50, 8)])
 def test_attention_dense_backward(B, heads, n, m, d):
     from stable_diffusion_pytorch_b200 import ops
