@@ -255,6 +255,12 @@ int sdb_attention_p32_lse(const void* q, int64_t ldq, const void* k, int64_t ldk
 int sdb_attention_bwd_dq_p32(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
                              const void* dO_pad, int64_t lddo, const float* lse, const float* delta, void* dq,
                              int64_t lddq, int B, int heads, int n, int m, int d, float scale, void* stream);
+/* dQ of the head-padded attention over a short context (m <= 128; autograd of transformer.py:93-114 for the CLIP
+ * context), one pass: softmax statistics in registers, also written out (lse log2-domain, delta; [B,heads,n] fp32) for
+ * sdb_attention_bwd_dkv.  dO dense [B,n,heads*d]; dq head-padded, every column written.  SDB_EUNSUPPORTED for m > 128. */
+int sdb_attention_ctx_bwd_dq(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
+                             const void* dO, int64_t lddo, void* dq, int64_t lddq, float* lse, float* delta, int B,
+                             int heads, int n, int m, int d, float scale, void* stream);
 /* One pass ahead of the tcgen05 backward kernels: do_pad [B,n,heads,32] bf16 (pad 0), delta = rowsum(dO o O), and the
  * negated delta / lse ([B,heads,n] fp32) that sdb_attention_bwd_dkv_p32 takes. */
 int sdb_attention_bwd_prep(const void* dO, int64_t lddo, const void* O, int64_t ldo, const float* lse, void* do_pad,

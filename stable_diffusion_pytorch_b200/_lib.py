@@ -73,6 +73,7 @@ SIGNATURES = {
     "sdb_attention_bwd": (_i, [_p, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _p,
                                 _i, _i, _i, _i, _i, _i, _i, _f, _p]),
     "sdb_attention_bwd_dq_p32": (_i, [_p, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _p, _p, _i64, _i, _i, _i, _i, _i, _f, _p]),
+    "sdb_attention_ctx_bwd_dq": (_i, [_p, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _p, _i, _i, _i, _i, _i, _f, _p]),
     "sdb_attention_bwd_prep": (_i, [_p, _i64, _p, _i64, _p, _p, _p, _p, _p, _i, _i, _i, _i, _p]),
     "sdb_attention_bwd_dkv_p32": (_i, [_p, _i64, _p, _i64, _p, _i64, _p, _i64, _p, _p, _p, _i64, _p, _i64, _i, _i, _i, _i, _i,
                                         _f, _p]),

@@ -25,6 +25,7 @@ from . import _lib
 from ._lib import ACT_GEGLU, ACT_NONE, ACT_SILU, check
 
 Tensor = torch.Tensor
+_CTX_BWD = os.environ.get("SDB_BWD_CTX", "1") != "0"          # 0 = cross-attention backward on the generic flash kernels
 _DKV_UMMA = os.environ.get("SDB_BWD_DKV_UMMA", "1") != "0"
 _DQ_UMMA = os.environ.get("SDB_BWD_DQ_UMMA", "1") != "0"      # tuning / A-B aid: 0 = dQ on the mma.sync kernel
 
@@ -463,6 +464,18 @@ def _attention_p32_backward(ctx, q, k, v, o, lse, do, dq, dk, dv):
         return
     delta = torch.empty(B * ctx.heads * n, device=q.device, dtype=torch.float32)
     lse = lse if ctx.has_lse else torch.empty_like(delta)
+    if m <= 128 and ctx.d <= 20 and _CTX_BWD:
+        # short context (cross-attention over CLIP's 77 tokens): one-pass dQ kernel that also leaves lse / delta for dK / dV
+        L = _lib.lib()
+        do = do if do.stride(2) == 1 and do.stride(0) == n * do.stride(1) else do.contiguous()
+        check(L.sdb_attention_ctx_bwd_dq(ops._ptr(q), q.stride(1), ops._ptr(k), k.stride(1), ops._ptr(v), v.stride(1),
+                                         ops._ptr(do), do.stride(1), ops._ptr(dq), dq.stride(1), ops._ptr(lse), ops._ptr(delta),
+                                         B, ctx.heads, n, m, ctx.d, ctx.scale, ops._stream()), "attention_ctx_bwd_dq")
+        check(L.sdb_attention_bwd_dkv(ops._ptr(q), q.stride(1), ops._ptr(k), k.stride(1), ops._ptr(v), v.stride(1),
+                                      ops._ptr(do), do.stride(1), ops._ptr(dk), dk.stride(1), ops._ptr(dv), dv.stride(1),
+                                      ops._ptr(lse), ops._ptr(delta), B, ctx.heads, n, m, ctx.d, hp, ctx.scale,
+                                      ops._stream()), "attention_bwd_dkv")
+        return
     check(_lib.lib().sdb_attention_bwd(
         ops._ptr(q), q.stride(1), ops._ptr(k), k.stride(1), ops._ptr(v), v.stride(1), ops._ptr(o), o.stride(1),
         ops._ptr(do), do.stride(1), ops._ptr(dq), dq.stride(1), ops._ptr(dk), dk.stride(1), ops._ptr(dv), dv.stride(1),
