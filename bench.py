@@ -281,7 +281,7 @@ def kernel_rooflines(B2, size, pk):
     q, k, v = padded(False), padded(False), padded(True)
     ms = time_kernel(lambda: ops.attention_p32(q, k, v, 8, 20, 1 / math.sqrt(20)))
     fl = 4.0 * B2 * 8 * n * n * 20
-    out.append({"kernel": "attention_umma_wg1_kernel<2,4> self-attn d=20 (tcgen05, head-padded)", "ms": ms, "flops": fl,
+    out.append({"kernel": "attention_umma_wg1_kernel<2,4,spread> self-attn d=20 (tcgen05, head-padded)", "ms": ms, "flops": fl,
                 "exp_pairs_per_clk_per_sm": B2 * 8.0 * n * n / (ms * 1e-3) / 148 / 1.965e9})
     del q, k, v
     # K1 conv3x3 160->160 @ size^2

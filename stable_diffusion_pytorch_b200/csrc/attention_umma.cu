@@ -487,7 +487,11 @@ static int attention_p32_impl(const void* q, int64_t ldq, const void* k, int64_t
   if (wg1) {
     dim3 grid1((n + kF1BM - 1) / kF1BM, heads, B);
     int rc;
-    if (wg1 == 4) rc = poly == 2 ? launch_attention_wg1<2, 4>(p, grid1, sdb_stream(stream))
+    static int spread = -1;
+    if (spread < 0) { const char* e = getenv("SDB_FA_SPREAD"); spread = e ? atoi(e) : 1; }
+    if (wg1 == 4 && spread) rc = poly == 3 ? launch_attention_wg1<3, 4, true>(p, grid1, sdb_stream(stream))
+                                           : launch_attention_wg1<2, 4, true>(p, grid1, sdb_stream(stream));
+    else if (wg1 == 4) rc = poly == 2 ? launch_attention_wg1<2, 4>(p, grid1, sdb_stream(stream))
                      : poly == 4 ? launch_attention_wg1<4, 4>(p, grid1, sdb_stream(stream))
                      : poly == 1 ? launch_attention_wg1<1, 4>(p, grid1, sdb_stream(stream))
                                  : launch_attention_wg1<3, 4>(p, grid1, sdb_stream(stream));

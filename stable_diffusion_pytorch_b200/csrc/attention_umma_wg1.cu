@@ -33,8 +33,9 @@ __device__ __forceinline__ void tmem_ld_32x32_at64(uint32_t taddr, uint32_t (&v)
       : "memory");
 }
 
-// kPoly = element pairs out of every 8 exponentiated on the FMA pipe; kCtas = CTAs resident per SM (3 or 4)
-template <int kPoly, int kCtas>
+// kPoly = element pairs out of every 8 exponentiated on the FMA pipe; kCtas = CTAs resident per SM (3 or 4);
+// kSpread = the polynomial pairs are spread over the group of 8 instead of leading it (1.105 -> 1.085 ms at kPoly = 2)
+template <int kPoly, int kCtas, bool kSpread>
 __global__ void __launch_bounds__(kF1Threads, kCtas) attention_umma_wg1_kernel(const __grid_constant__ FaParams p) {
   constexpr int kStages = f1_stages(kCtas);
   constexpr int kRowRegs = kCtas >= 4 ? 104 : 136;
@@ -210,7 +211,7 @@ __global__ void __launch_bounds__(kF1Threads, kCtas) attention_umma_wg1_kernel(c
             const int i = ch * 32 + g * 16 + 2 * k;
             float x0, x1;
             ffma2(x0, x1, __uint_as_float(su[i]), __uint_as_float(su[i + 1]), c, c, negm, negm);
-            if (k < kPoly) {
+            if (kSpread ? ((k * kPoly) % 8 < kPoly) : (k < kPoly)) {
               ex2_poly2(x0, x1);
             } else {
               x0 = ex2_mufu(x0);
@@ -262,17 +263,17 @@ __global__ void __launch_bounds__(kF1Threads, kCtas) attention_umma_wg1_kernel(c
   }
 }
 
-template <int kPoly, int kCtas>
+template <int kPoly, int kCtas, bool kSpread = false>
 static int launch_attention_wg1(const FaParams& p, dim3 grid, cudaStream_t stream) {
   static bool attr_set[64] = {false};
   int dev = 0;
   SDB_CUDA_OK(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-    SDB_CUDA_OK(cudaFuncSetAttribute(attention_umma_wg1_kernel<kPoly, kCtas>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    SDB_CUDA_OK(cudaFuncSetAttribute(attention_umma_wg1_kernel<kPoly, kCtas, kSpread>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      f1_smem(kCtas)));
     if (dev >= 0 && dev < 64) attr_set[dev] = true;
   }
-  attention_umma_wg1_kernel<kPoly, kCtas><<<grid, kF1Threads, f1_smem(kCtas), stream>>>(p);
+  attention_umma_wg1_kernel<kPoly, kCtas, kSpread><<<grid, kF1Threads, f1_smem(kCtas), stream>>>(p);
   return SDB_OK;
 }
 
