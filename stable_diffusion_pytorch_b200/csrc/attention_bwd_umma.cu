@@ -20,7 +20,7 @@ constexpr int kBdKVBytes = kBdBN * 32 * 2;      // 4 KB each for K and V
 constexpr int kBdStageBytes = 2 * kBdKVBytes;
 constexpr int kBdSmem = 4 * kBdQBytes + kBdStages * kBdStageBytes + 1024 + 256;
 
-// pairs of every 8 exponentiated on the FMA pipe; SDB_BWD_POLY=0|2|3|4 overrides the default (2) for A/B timing
+// pairs of every 8 exponentiated on the FMA pipe; SDB_BWD_POLY=0|2|3 overrides the default (2) for A/B timing
 static int bwd_poly_pairs() {
   static int v = -1;
   if (v < 0) {
@@ -288,13 +288,11 @@ extern "C" int sdb_attention_bwd_dq_p32(const void* q, int64_t ldq, const void* 
     SDB_CUDA_OK(cudaFuncSetAttribute(attn_bwd_dq_umma_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBdSmem));
     SDB_CUDA_OK(cudaFuncSetAttribute(attn_bwd_dq_umma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBdSmem));
     SDB_CUDA_OK(cudaFuncSetAttribute(attn_bwd_dq_umma_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBdSmem));
-    SDB_CUDA_OK(cudaFuncSetAttribute(attn_bwd_dq_umma_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBdSmem));
     if (dev >= 0 && dev < 64) attr_set[dev] = true;
   }
   dim3 grid((n + 2 * kBdBM - 1) / (2 * kBdBM), heads, B);
   switch (bwd_poly_pairs()) {
     case 0: attn_bwd_dq_umma_kernel<0><<<grid, kBdThreads, kBdSmem, sdb_stream(stream)>>>(p); break;
-    case 4: attn_bwd_dq_umma_kernel<4><<<grid, kBdThreads, kBdSmem, sdb_stream(stream)>>>(p); break;
     case 3: attn_bwd_dq_umma_kernel<3><<<grid, kBdThreads, kBdSmem, sdb_stream(stream)>>>(p); break;
     default: attn_bwd_dq_umma_kernel<2><<<grid, kBdThreads, kBdSmem, sdb_stream(stream)>>>(p); break;
   }
@@ -617,13 +615,11 @@ extern "C" int sdb_attention_bwd_dkv_p32(const void* q, int64_t ldq, const void*
     SDB_CUDA_OK(cudaFuncSetAttribute(attn_bwd_dkv_umma_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBkSmem));
     SDB_CUDA_OK(cudaFuncSetAttribute(attn_bwd_dkv_umma_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBkSmem));
     SDB_CUDA_OK(cudaFuncSetAttribute(attn_bwd_dkv_umma_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBkSmem));
-    SDB_CUDA_OK(cudaFuncSetAttribute(attn_bwd_dkv_umma_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, kBkSmem));
     if (dev >= 0 && dev < 64) attr_set[dev] = true;
   }
   dim3 grid((m + 2 * kBdBM - 1) / (2 * kBdBM), heads, B);
   switch (bwd_poly_pairs()) {
     case 0: attn_bwd_dkv_umma_kernel<0><<<grid, kBdThreads, kBkSmem, sdb_stream(stream)>>>(p); break;
-    case 4: attn_bwd_dkv_umma_kernel<4><<<grid, kBdThreads, kBkSmem, sdb_stream(stream)>>>(p); break;
     case 3: attn_bwd_dkv_umma_kernel<3><<<grid, kBdThreads, kBkSmem, sdb_stream(stream)>>>(p); break;
     default: attn_bwd_dkv_umma_kernel<2><<<grid, kBdThreads, kBkSmem, sdb_stream(stream)>>>(p); break;
   }

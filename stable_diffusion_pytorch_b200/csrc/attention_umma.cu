@@ -489,15 +489,11 @@ static int attention_p32_impl(const void* q, int64_t ldq, const void* k, int64_t
     int rc;
     static int spread = -1;
     if (spread < 0) { const char* e = getenv("SDB_FA_SPREAD"); spread = e ? atoi(e) : 1; }
+    // instantiated shapes: the default and its A/B neighbours (tools/experiments/README.md has the full sweep)
     if (wg1 == 4 && spread) rc = poly == 3 ? launch_attention_wg1<3, 4, true>(p, grid1, sdb_stream(stream))
                                            : launch_attention_wg1<2, 4, true>(p, grid1, sdb_stream(stream));
-    else if (wg1 == 4) rc = poly == 2 ? launch_attention_wg1<2, 4>(p, grid1, sdb_stream(stream))
-                     : poly == 4 ? launch_attention_wg1<4, 4>(p, grid1, sdb_stream(stream))
-                     : poly == 1 ? launch_attention_wg1<1, 4>(p, grid1, sdb_stream(stream))
-                                 : launch_attention_wg1<3, 4>(p, grid1, sdb_stream(stream));
-    else rc = poly == 2 ? launch_attention_wg1<2, 3>(p, grid1, sdb_stream(stream))
-            : poly == 4 ? launch_attention_wg1<4, 3>(p, grid1, sdb_stream(stream))
-                        : launch_attention_wg1<3, 3>(p, grid1, sdb_stream(stream));
+    else if (wg1 == 4) rc = launch_attention_wg1<2, 4>(p, grid1, sdb_stream(stream));
+    else rc = launch_attention_wg1<2, 3>(p, grid1, sdb_stream(stream));
     if (rc) return rc;
     SDB_LAUNCH_OK();
     return SDB_OK;
@@ -517,12 +513,11 @@ static int attention_p32_impl(const void* q, int64_t ldq, const void* k, int64_t
   } break;
   switch (poly) {
     SDB_FA_LAUNCH(0)
-    SDB_FA_LAUNCH(1)
     SDB_FA_LAUNCH(2)
     SDB_FA_LAUNCH(3)
     SDB_FA_LAUNCH(4)
-    SDB_FA_LAUNCH(6)
-    SDB_FA_LAUNCH(5)
+    default: sdb_set_error("attention_p32: SDB_FA_POLY=%d is not instantiated for the two-warpgroup shape (0, 2, 3, 4)", poly);
+      return SDB_EUNSUPPORTED;
   }
 #undef SDB_FA_LAUNCH
   SDB_LAUNCH_OK();
