@@ -108,6 +108,18 @@ int sdb_groupnorm_chunks(int64_t hw);
 int sdb_groupnorm_stats(const void* x1, int C1, const void* x2, int C2, int dtype, int B,
                         int64_t hw, int groups, float eps, float* scratch, float* stats,
                         void* stream);
+/* sdb_groupnorm_stats without a caller scratch buffer.  No counterpart in the reference: added
+ * for callers that cannot allocate (CUDA graph capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  The partial sums go to a file-scope `static __device__`
+ * array of SDB_GN_STATIC_SCRATCH_FLOATS floats (4 MiB, held by every GPU that loads the library until
+ * exit); the call allocates nothing.  Limit: B * sdb_groupnorm_chunks(hw) * (C1+C2) * 2 <=
+ * SDB_GN_STATIC_SCRATCH_FLOATS, SDB_EINVAL beyond it (use sdb_groupnorm_stats).  All calls on one GPU
+ * share the array: calls that overlap on the GPU (different streams, no ordering between them) race;
+ * calls on one stream are safe.  Nothing needs clearing between calls (every element read is written
+ * first).  Same statistics, bit for bit, as sdb_groupnorm_stats. */
+#define SDB_GN_STATIC_SCRATCH_FLOATS (1u << 20)
+int sdb_groupnorm_stats_static(const void* x1, int C1, const void* x2, int C2, int dtype, int B,
+                               int64_t hw, int groups, float eps, float* stats, void* stream);
 /* out[b,p,c] = act((x-mean)*rstd*gamma[c]+beta[c]); act = SDB_ACT_NONE | SDB_ACT_SILU.
  * out is a dense NHWC tensor with C1+C2 channels, dtype out_dtype. */
 int sdb_groupnorm_apply(const void* x1, int C1, const void* x2, int C2, int dtype,

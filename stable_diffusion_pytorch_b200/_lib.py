@@ -49,6 +49,7 @@ SIGNATURES = {
     "sdb_nhwc_to_nchw": (_i, [_p, _i, _p, _i, _i, _i, _i, _i, _p]),
     "sdb_groupnorm_chunks": (_i, [_i64]),
     "sdb_groupnorm_stats": (_i, [_p, _i, _p, _i, _i, _i, _i64, _i, _f, _p, _p, _p]),
+    "sdb_groupnorm_stats_static": (_i, [_p, _i, _p, _i, _i, _i, _i64, _i, _f, _p, _p]),
     "sdb_groupnorm_apply": (_i, [_p, _i, _p, _i, _i, _p, _p, _p, _i, _p, _i, _i, _i64, _i, _p]),
     "sdb_add_layernorm": (_i, [_p, _p, _p, _p, _p, _i64, _i, _f, _i, _p]),
     "sdb_gemm": (_i, [C.POINTER(SdbGemmArgs), _p]),

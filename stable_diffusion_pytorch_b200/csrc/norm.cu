@@ -380,6 +380,45 @@ extern "C" int sdb_groupnorm_stats(const void* x1, int C1, const void* x2, int C
   return SDB_OK;
 }
 
+// ---- allocation-free variant of sdb_groupnorm_stats ---------------------------------------------
+// The partial sums live in a file-scope device array instead of a caller buffer.  Every GPU that loads
+// the library holds the 4 MiB until exit.  The host-side name `g_gn_static_scratch` is only a stand-in:
+// its device address is looked up once per device with cudaGetSymbolAddress and cached here.
+constexpr size_t kGnStaticScratchFloats = SDB_GN_STATIC_SCRATCH_FLOATS;
+static __device__ __align__(256) float g_gn_static_scratch[kGnStaticScratchFloats];
+constexpr int kGnStaticMaxDevices = 64;
+static float* g_gn_static_ptr[kGnStaticMaxDevices] = {nullptr};
+
+static int gn_static_scratch_ptr(float** out) {
+  int dev = -1;
+  SDB_CUDA_OK(cudaGetDevice(&dev));
+  SDB_CHECK_ARG(dev >= 0 && dev < kGnStaticMaxDevices, "groupnorm_stats_static: device ordinal %d out of range", dev);
+  if (!g_gn_static_ptr[dev]) {
+    float* p = nullptr;
+    SDB_CUDA_OK(cudaGetSymbolAddress((void**)&p, g_gn_static_scratch));
+    g_gn_static_ptr[dev] = p;
+  }
+  *out = g_gn_static_ptr[dev];
+  return SDB_OK;
+}
+
+extern "C" int sdb_groupnorm_stats_static(const void* x1, int C1, const void* x2, int C2, int dtype, int B,
+                                          int64_t hw, int groups, float eps, float* stats, void* stream) {
+  if (!x2) C2 = 0;
+  SDB_CHECK_ARG(B > 0 && hw > 0 && C1 > 0 && C2 >= 0, "groupnorm_stats_static: bad args");
+  const size_t need = (size_t)B * (size_t)sdb_groupnorm_chunks(hw) * (size_t)(C1 + C2) * 2;
+  SDB_CHECK_ARG(need <= kGnStaticScratchFloats,
+                "groupnorm_stats_static: B * chunks * C * 2 = %zu floats exceeds the static scratch of %zu floats "
+                "(SDB_GN_STATIC_SCRATCH_FLOATS); use sdb_groupnorm_stats with a caller buffer",
+                need, kGnStaticScratchFloats);
+  float* scratch = nullptr;
+  const int rc = gn_static_scratch_ptr(&scratch);
+  if (rc != SDB_OK) return rc;
+  // every element of scratch[0, need) is overwritten by gn_partial_kernel before gn_finalize_kernel reads it, so
+  // nothing has to start at zero; what the previous call left beyond `need` is never read.
+  return sdb_groupnorm_stats(x1, C1, x2, C2, dtype, B, hw, groups, eps, scratch, stats, stream);
+}
+
 extern "C" int sdb_groupnorm_apply(const void* x1, int C1, const void* x2, int C2, int dtype,
                                    const float* stats, const float* gamma, const float* beta, int act,
                                    void* out, int out_dtype, int B, int64_t hw, int groups,
