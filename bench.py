@@ -22,6 +22,7 @@ if ROOT not in sys.path:
 
 WORKLOAD = "unet-default bs16 64x64x4 latents, CFG g=7.5 (UNet batch 32), DDIM eta=0, bf16"
 GF_PER_LATENT_STEP = 453.46  # 2 UNet evals @64x64, reference formulation
+MUFU_EX2_PER_CLK_PER_SM = 15.84  # measured ex2.approx rate (tools/ubench.cu, profiles/r01_ubench_mufu_fma.txt)
 
 
 def parse():
@@ -37,6 +38,7 @@ def parse():
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--no-decode", action="store_true", help="skip the VAE-decode (images/s) leg")
     ap.add_argument("--no-train", action="store_true", help="skip the config-4 train-step leg")
+    ap.add_argument("--no-parity", action="store_true", help="skip the 50-step parity check and the torch-eager GPU baseline")
     ap.add_argument("--train-batch", type=int, default=32, help="per-GPU batch of the train-step leg (config 4: 32)")
     ap.add_argument("--profile-step", action="store_true",
                     help="after warm-up run ONE eager step between cudaProfilerStart/Stop and exit "
@@ -157,13 +159,14 @@ def run_reference(args):
 # ----------------------------------------------------------------------------------------------
 # B200 arm
 # ----------------------------------------------------------------------------------------------
-def build_unet(device):
+def build_unet(device, dropout=0.0):
     """Repo-default UNet, random init (reference init + every all-zero tensor re-randomised so the
-    zero_module'd convs do real work; weights differ from any checkpoint: data = synthetic)."""
+    zero_module'd convs do real work; weights differ from any checkpoint: data = synthetic).  ``dropout`` only
+    matters in train mode: the sampling legs run eval(), the train leg uses the reference default 0.1."""
     import torch
     from stable_diffusion_pytorch_b200.models import UNetModel, UnetConfig
     torch.manual_seed(0)
-    m = UNetModel(4, 32, UnetConfig(dropout=0.0)).eval()
+    m = UNetModel(4, 32, UnetConfig(dropout=dropout)).eval()
     g = torch.Generator().manual_seed(1)
     with torch.no_grad():
         for p in m.parameters():
@@ -201,17 +204,34 @@ def time_vae_decode(latents, dev, iters=3):
     chunks = list(z.split(16))      # config 3 is a batch of 16; larger shards decode 16 at a time (2 GB activations each)
     with torch.no_grad():
         for _ in range(2):
-            vae.decode(chunks[0])
+            vae.decode_uint8(chunks[0])
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         torch.cuda.synchronize()
         e0.record()
         for _ in range(iters):
-            for c in chunks:
-                y = vae.decode(c)
+            u8 = torch.cat([vae.decode_uint8(c) for c in chunks]) if len(chunks) > 1 else vae.decode_uint8(chunks[0])
         e1.record()
         torch.cuda.synchronize()
-    del vae, y
+    del vae
     torch.cuda.empty_cache()
+    return e0.elapsed_time(e1) / iters, u8
+
+
+def time_image_gather(u8, world, iters=3):
+    """The ONE collective of the sampling job: all-gather of the decoded [B, 512, 512, 3] uint8 images
+    over NCCL; ms per gather (CUDA events on this rank; the caller takes the max over ranks)."""
+    import torch
+    from stable_diffusion_pytorch_b200 import sharding
+    total = u8.shape[0] * world
+    out = sharding.gather_batch(u8, total)      # warm-up (communicator set-up)
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(iters):
+        out = sharding.gather_batch(u8, total)
+    e1.record()
+    torch.cuda.synchronize()
+    assert out.shape[0] == total and out.dtype == torch.uint8
     return e0.elapsed_time(e1) / iters
 
 
@@ -259,6 +279,109 @@ def time_train_step(unet, dev, rank, batch, size, iters=3, warm=2):
     info = {"steps": iters, "warmup": warm, "loss": float(loss), "cuda_graph": True,
             "params": opt.numel, "peak_mem_gb": round(torch.cuda.max_memory_allocated() / 2**30, 2)}
     return e0.elapsed_time(e1) / iters, info
+
+
+def oracle_state_dict(unet, device, dtype):
+    return {k: v.detach().to(device=device, dtype=dtype) for k, v in unet.state_dict().items()}
+
+
+def gpu_eager_baseline(unet, B, size, steps=3, warm=1):
+    """The number to beat ("the unmodified reference running torch-eager in bf16 on the same B200"):
+    the oracle restatement of the reference's algorithm -- pred_noise with CFG + DDIM update, every op an ATen /
+    cuDNN / cuBLAS call, `sim` materialised -- on the same GPU, same batch, bf16, CUDA events.  A baseline leg:
+    it imports oracle/, outside the timed b200 region."""
+    import torch
+    from oracle import sd_oracle as O
+    dev = next(unet.parameters()).device
+    cfg = O.UnetCfg()
+    sd = oracle_state_dict(unet, dev, torch.bfloat16)
+    tab = O.ddpm_tables(O.DdpmCfg())
+    g = torch.Generator().manual_seed(5)
+    x = torch.rand(B, 4, size, size, generator=g).to(dev, torch.bfloat16)
+    ctx = torch.randn(B, 77, 768, generator=g).to(dev, torch.bfloat16)
+    unc = torch.randn(1, 77, 768, generator=g).to(dev, torch.bfloat16).expand(B, -1, -1)
+    fn = lambda a, b, c: O.unet_forward(sd, cfg, a, b, c)  # noqa: E731
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    with torch.no_grad():
+        for i in range(warm + steps):
+            if i == warm:
+                torch.cuda.synchronize()
+                e0.record()
+            t = torch.full((B,), i, dtype=torch.long, device=dev)
+            eps = O.pred_noise(fn, x, t, ctx, unc, 7.5)
+            x, _ = O.ddim_step(tab, eps, x, i)
+        e1.record()
+        torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    peak = torch.cuda.max_memory_allocated() / 2**30
+    del sd, x, ctx, unc, eps
+    torch.cuda.empty_cache()
+    return {"value": B / (ms * 1e-3), "unit": "latent-steps/s", "ms_per_step": ms, "steps": steps, "warmup": warm,
+            "kind": "oracle restatement of the reference on torch eager (ATen/cuDNN/cuBLAS), bf16, same B200, "
+                    "same batch; `sim` materialised like the reference", "peak_mem_gb": round(peak, 1)}
+
+
+def sample_parity(gs, unet, x_host, ctx_host, unc, n_check=2):
+    """rel-L2 of the final latents of the benchmarked path (the captured graph, 50 DDIM steps with CFG, bf16) against
+    the oracle restatement run by torch eager in FP32 on the same GPU, for the first ``n_check`` latents of the batch
+    (trajectories are independent per latent).  tests/test_graphed_sampler_gpu.py ties that fp32-on-GPU run to the CPU
+    oracle (< 1e-4)."""
+    import torch
+    from oracle import sd_oracle as O
+    dev = gs.device
+    tf32 = (torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32)
+    torch.backends.cudnn.allow_tf32 = torch.backends.cuda.matmul.allow_tf32 = False
+    try:
+        got = gs.run(x_host, ctx_host, unc)[:n_check].float()
+        cfg = O.UnetCfg()
+        sd = oracle_state_dict(unet, dev, torch.float32)
+        tab = O.ddpm_tables(O.DdpmCfg())
+        fn = lambda a, b, c: O.unet_forward(sd, cfg, a, b, c)  # noqa: E731
+        with torch.no_grad():
+            ref = O.sample(fn, tab, x_host[:n_check].float().to(dev), ctx_host[:n_check].float().to(dev),
+                           unc.float().to(dev).expand(n_check, -1, -1), 7.5, time_steps=len(gs.steps), sampler="ddim")
+        err = float((got.double() - ref.double()).norm() / ref.double().norm())
+        del sd, ref
+    finally:
+        torch.backends.cudnn.allow_tf32, torch.backends.cuda.matmul.allow_tf32 = tf32
+    torch.cuda.empty_cache()
+    return {"rel_l2_final_latents": err, "steps": len(gs.steps), "latents_checked": n_check,
+            "against": "oracle restatement, fp32 torch eager on the same GPU (TF32 off)", "tolerance": 5e-2}
+
+
+def hbm_kernels(B2, size, pk):
+    """The HBM-bound kernels of the step timed alone at the workload's shapes: achieved GB/s of algorithmic bytes
+    against the measured copy peak (north_star: norm and sampler kernels against the HBM roofline)."""
+    import torch
+    from stable_diffusion_pytorch_b200 import ops
+    from stable_diffusion_pytorch_b200._lib import ACT_SILU
+    from stable_diffusion_pytorch_b200.models import DDPMConfig, DDPMScheduler
+    dev = "cuda"
+    out = []
+    x = torch.randn(B2, size, size, 160, device=dev).to(torch.bfloat16)
+    gam, bet = torch.ones(160, device=dev), torch.zeros(160, device=dev)
+    scr = ops.GroupNormScratch()
+    nbytes = x.numel() * 2.0
+    ms = time_kernel(lambda: ops.group_norm(x, gam, bet, 32, ACT_SILU, scratch=scr))
+    out.append({"kernel": f"groupnorm stats+apply(+SiLU) [{B2},{size},{size},160] bf16 (gn_partial+gn_finalize+gn_apply)",
+                "ms": ms, "bytes": 3 * nbytes})
+    tok = x.view(B2, size * size, 160)
+    res = torch.randn_like(tok)
+    ms = time_kernel(lambda: ops.add_layernorm(tok, res, gam, bet))
+    out.append({"kernel": f"add_layernorm [{B2 * size * size},160] bf16", "ms": ms, "bytes": 3 * nbytes})
+    sch = DDPMScheduler(DDPMConfig())
+    coef = sch.coef_rows(range(50)).to(dev)
+    for Bs in (B2 // 2, 512):
+        eps = torch.randn(2 * Bs, 4, size, size, device=dev).to(torch.bfloat16)
+        xt = torch.randn(Bs, 4, size, size, device=dev).to(torch.bfloat16)
+        ms = time_kernel(lambda: ops.cfg_sampler_step(eps, xt, None, coef, slot=7, kind=1, cfg_mode=1, guidance=7.5,
+                                                      x_prev=xt, want_x0=False))
+        out.append({"kernel": f"cfg_sampler_step DDIM+CFG in place, {Bs} latents bf16", "ms": ms,
+                    "bytes": xt.numel() * 2.0 * 4})      # eps x2 + x_t read, x_prev written
+    for o in out:
+        o["gbs"] = o["bytes"] / (o["ms"] * 1e-3) / 1e9
+        o["frac_of_hbm_peak"] = o["gbs"] / pk["hbm_gbs"]
+    return out
 
 
 def kernel_rooflines(B2, size, pk):
@@ -386,24 +509,37 @@ def run_b200(args):
     ms_e2e = torch.tensor([e0.elapsed_time(e1)], device=dev)
     # ---- images/s: 50 latent-steps + one AutoencoderKL-shape decode (config 3) of this rank's latents ----
     ms_dec = torch.tensor([float("nan")], device=dev)
+    ms_gather = torch.tensor([0.0], device=dev)
     if not args.no_decode and S == 64:
-        ms_dec = torch.tensor([time_vae_decode(gs.x, dev)], device=dev)
+        ms_d, u8 = time_vae_decode(gs.x, dev)
+        ms_dec = torch.tensor([ms_d], device=dev)
+        if world > 1:
+            ms_gather = torch.tensor([time_image_gather(u8, world)], device=dev)
+        del u8
     finite = bool(torch.isfinite(gs.x.float()).all())
     # ---- config 4: UNet train step (loss + backward + gradient all-reduce + clip + AdamW), batch 32 per GPU ----
     ms_train = torch.tensor([float("nan")], device=dev)
     train_info = None
     graph_on, graph_lps = gs.graph is not None, gs.launches_per_step
+    parity = eager = None
+    if rank == 0 and (B, S) == (16, 64) and not args.no_parity:
+        parity = sample_parity(gs, unet, x_host, ctx_host, unc)
+        eager = gpu_eager_baseline(unet, B, S)
     if not args.no_train and S == 64:
         del gs
         torch.cuda.empty_cache()
-        ms_t, train_info = time_train_step(unet, dev, rank, args.train_batch, S)
+        # config 4 trains the reference's default model: dropout 0.1 (models/unet.py:29-57), active in train mode
+        train_unet = build_unet(dev, dropout=0.1)
+        ms_t, train_info = time_train_step(train_unet, dev, rank, args.train_batch, S)
+        del train_unet
         ms_train = torch.tensor([ms_t], device=dev)
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
         dist.all_reduce(ms_e2e, op=dist.ReduceOp.MAX)
         dist.all_reduce(ms_dec, op=dist.ReduceOp.MAX)
+        dist.all_reduce(ms_gather, op=dist.ReduceOp.MAX)
         dist.all_reduce(ms_train, op=dist.ReduceOp.MAX)
-    ms, ms_e2e, ms_dec, ms_train = float(ms), float(ms_e2e), float(ms_dec), float(ms_train)
+    ms, ms_e2e, ms_dec, ms_train, ms_gather = float(ms), float(ms_e2e), float(ms_dec), float(ms_train), float(ms_gather)
     flag = ops.debug_timeout_flag()
     if rank != 0:
         if world > 1:
@@ -414,6 +550,7 @@ def run_b200(args):
     e2e = n_lat * args.steps / (ms_e2e * 1e-3)
     kr = kernel_rooflines(2 * B, S, pk)
     dom = kr[0]
+    kr = kr + hbm_kernels(2 * B, S, pk)
     traffic = None
     tpath = os.path.join(ROOT, "profiles", "roofline_traffic.json")
     if os.path.exists(tpath):
@@ -440,24 +577,37 @@ def run_b200(args):
         "roofline": {"bound": "tensor", "kernel": dom["kernel"], "achieved": dom["tflops"], "peak": pk["bf16_tflops"],
                      "unit": "TFLOP/s", "frac": dom["tflops"] / pk["bf16_tflops"], "traffic": traffic,
                      "peak_source": pk["source"] + " (burst: kernel timed alone)", "ms_per_launch": dom["ms"],
-                     "note": "d_head=20 attention is MUFU-exp/softmax bound, not tensor bound (DESIGN.md 4)"},
+                     "mufu_frac": dom["exp_pairs_per_clk_per_sm"] / MUFU_EX2_PER_CLK_PER_SM,
+                     "exp_pairs_per_clk_per_sm": dom["exp_pairs_per_clk_per_sm"],
+                     "note": "d_head=20 attention: 80 flops and ONE exp per (query, key) pair, so the MUFU ex2 pipe "
+                             f"({MUFU_EX2_PER_CLK_PER_SM}/clk/SM measured, profiles/r01_ubench_mufu_fma.txt) binds long "
+                             "before the tensor pipe; `frac` is the tensor-roofline fraction the contract asks for, "
+                             "`mufu_frac` = (query, key) pairs/clk/SM over the MUFU-only rate (> 1 is possible: part "
+                             "of the exponentials runs as a polynomial on the FMA pipe)"},
         "kernels": kr,
         "step_roofline": {"algorithmic_tflops": step_tf, "peak_sustained": pk["bf16_tflops_sustained"],
                           "frac": step_tf / pk["bf16_tflops_sustained"]},
         "images": None if ms_dec != ms_dec else {
-            "images_per_sec": n_lat / ((50 * ms / args.steps + ms_dec) * 1e-3), "ms_decode": ms_dec,
-            "decoder": "AutoencoderKL-shape [128,256,512,512], 64x64x4 -> 512x512x3, bf16",
+            "images_per_sec": n_lat / ((50 * ms / args.steps + ms_dec + ms_gather) * 1e-3), "ms_decode": ms_dec,
+            "ms_gather": ms_gather,
+            "decoder": "AutoencoderKL-shape [128,256,512,512], 64x64x4 -> 512x512x3 uint8 (decode + detransform), bf16",
             "decode_alg_tflops": 38306.0 * (B / 16.0) / ms_dec,
-            "formula": "latents / (50 x ms_per_step + ms_decode), max over ranks"},
+            "gather": "none (1 GPU)" if world == 1 else
+                      f"NCCL all-gather of the [{n_lat},512,512,3] uint8 images, the job's one collective",
+            "formula": "latents / (50 x ms_per_step + ms_decode + ms_gather), max over ranks"},
         "train": None if ms_train != ms_train else {
             "samples_per_sec": args.train_batch * world / (ms_train * 1e-3), "ms_per_step": ms_train,
             "workload": f"BASELINE config 4: train_unet.py step, batch {args.train_batch}/GPU (CFG doubling -> UNet "
-                        f"batch {2 * args.train_batch}), {S}x{S} latents, random CLIP-shaped context, MSE, clip 0.1, "
-                        f"AdamW; fp32 master weights / gradients, bf16 compute",
+                        f"batch {2 * args.train_batch}), {S}x{S} latents, random CLIP-shaped context, dropout 0.1 (the reference "
+                        f"default, 36 mask sites forward and backward), MSE, clip 0.1, AdamW; fp32 master weights / "
+                        f"gradients, bf16 compute",
             "gradient_exchange": "one NCCL all-reduce of the flat fp32 gradient bucket" if world > 1 else "none (1 GPU)",
             **(train_info or {})},
+        "parity": parity, "gpu_eager_baseline": eager,
         "finite": finite, "timeout_flag": flag,
     }
+    if eager:
+        line["gpu_eager_baseline"]["speedup_of_this_repo"] = value / world / eager["value"]
     if world == 1 and not args.no_cpu_baseline:
         try:
             cb = cpu_latent_steps(S, 3, 1)

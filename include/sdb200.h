@@ -197,11 +197,19 @@ int sdb_upsample2x(const void* x, void* out, int dtype, int B, int H, int W, int
  * modules/transformer.py:93-114: softmax(Q K^T * scale) V per (batch, head) without
  * materialising `sim`.  q [B, n, *] with head h at columns [h*d, (h+1)*d) and row stride ldq
  * elements (so a fused QKV GEMM output can be passed as three offset pointers); k, v [B, m, *].
- * out [B, n, heads*d] row stride ldo.  bf16 in/out, fp32 softmax state.  d <= 128, d % 4 == 0.
+ * out [B, n, heads*d] row stride ldo.  bf16 in/out, fp32 softmax state.  d <= 128, d % 4 == 0
+ * (SDB_EUNSUPPORTED beyond: see sdb_softmax_rows for the wide-head route).
  * dtype = SDB_F32: fp32 in/out on the CUDA cores (parity mode), any d <= 128, no alignment rules. */
 int sdb_attention(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
                   int64_t ldv, void* out, int64_t ldo, int B, int heads, int n, int m, int d,
                   float scale, int dtype, void* stream);
+
+/* Row softmax of a materialised fp32 score matrix: out[r, c] = softmax_c(scale * x[r, :valid_cols])[c], exact zeros
+ * for valid_cols <= c < cols (modules/transformer.py:101-111).  The wide-head route (d > 128: the VAE encoder
+ * bottleneck, d_head = mid_ch, models/autoencoder.py:181-183) runs attention as sdb_gemm(Q, K) -> sdb_softmax_rows ->
+ * sdb_gemm(P, V^T); out bf16 or fp32, row strides in elements. */
+int sdb_softmax_rows(const float* x, int64_t ldx, void* out, int64_t ldo, int out_dtype, int64_t rows, int cols,
+                     int valid_cols, float scale, void* stream);
 
 /* Tensor-core (tcgen05 + TMEM + TMA) variant for small head dims, d <= 20 (the UNet's d_head = 20).
  * Operands are HEAD-PADDED to 32 columns by the projection GEMM (weights packed once at load):

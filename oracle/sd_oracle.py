@@ -137,6 +137,19 @@ def vae_decoder_topology(cfg: VaeCfg):
     return mid, up, out_ch
 
 
+def vae_encoder_topology(cfg: VaeCfg):
+    """models/autoencoder.py:164-199: conv_in -> build_input_blocks (ResBlocks without time embedding, a DownSample
+    after every level but the last, no attention: attention_resolutions is None) -> bottleneck [ResBlock(groups
+    default 2), bare 1-head CrossAttention with d_head = mid_ch, ResBlock(groups)] -> GN + SiLU + conv head."""
+    cl = cfg.autoencoder_channels_list
+    down, _, mid_ch, _, _ = _input_blocks("encoder.down", cl[0], cfg.autoencoder_num_res_blocks, None, 1, 1,
+                                          len(cl), cl, cfg.groups, False)
+    mid = [("res", "encoder.bottleneck.0", mid_ch, mid_ch, 2, False),
+           ("attn", "encoder.bottleneck.1", mid_ch),
+           ("res", "encoder.bottleneck.2", mid_ch, mid_ch, cfg.groups, False)]
+    return down, mid, mid_ch
+
+
 # ----------------------------------------------------------------------------
 # parameter shapes + seeded init (our own recipe; every tensor non-zero so that
 # zero_module'd convs -- models/utils.py:22-28 -- do not make parity vacuous)
@@ -224,6 +237,21 @@ def vae_decoder_param_shapes(cfg: VaeCfg) -> Dict[str, Tuple[int, ...]]:
     return s
 
 
+def vae_encoder_param_shapes(cfg: VaeCfg) -> Dict[str, Tuple[int, ...]]:
+    """Keys of ``AutoEncoderKL.encoder`` and ``quant_conv`` (models/autoencoder.py:95-121,164-199)."""
+    c0 = cfg.autoencoder_channels_list[0]
+    lc = cfg.latent_channels
+    s = {"quant_conv.weight": (2 * lc, 2 * lc, 1, 1), "quant_conv.bias": (2 * lc,),
+         "encoder.conv_in.weight": (c0, cfg.in_channels, 3, 3), "encoder.conv_in.bias": (c0,)}
+    down, mid, mid_ch = vae_encoder_topology(cfg)
+    for blk in down:
+        s.update(_layers_shapes(blk, None, None))
+    s.update(_layers_shapes(mid, None, None))
+    s.update({"encoder.out.0.weight": (mid_ch,), "encoder.out.0.bias": (mid_ch,),
+              "encoder.out.2.weight": (2 * lc, mid_ch, 3, 3), "encoder.out.2.bias": (2 * lc,)})
+    return s
+
+
 def seeded_state_dict(shapes: Dict[str, Tuple[int, ...]], seed: int) -> StateDict:
     """Deterministic non-degenerate init from a CPU ``torch.Generator``.
 
@@ -259,7 +287,7 @@ def sinusoidal_freq(emb_dim: int, max_len: int = 10000) -> Tensor:
 
 def sinusoidal_time_proj(time_steps: Tensor, emb_dim: int, max_len: int = 10000) -> Tensor:
     """modules/timestep_embedding.py:73-105: cat[sin, cos] of t.float() * freq."""
-    freq = sinusoidal_freq(emb_dim, max_len)
+    freq = sinusoidal_freq(emb_dim, max_len).to(time_steps.device)      # :99 (CPU-built table, then moved)
     args = time_steps[:, None].float() * freq[None]
     return torch.cat([torch.sin(args), torch.cos(args)], dim=-1)
 
@@ -384,6 +412,37 @@ def vae_decode(sd: StateDict, cfg: VaeCfg, latent: Tensor) -> Tensor:
         x = _run_layers(sd, blk, x, None, None)
     x = F.group_norm(x, cfg.groups, sd["decoder.out.0.weight"], sd["decoder.out.0.bias"], eps=1e-5)
     return F.conv2d(F.silu(x), sd["decoder.out.2.weight"], sd["decoder.out.2.bias"], padding=1)
+
+
+def vae_encode(sd: StateDict, cfg: VaeCfg, img: Tensor) -> Tensor:
+    """models/autoencoder.py:132-146 + Encoder.forward :191-199 -> the MOMENTS [B, 2 * latent_channels, h, w] that
+    ``GaussianDistribution`` (modules/distributions.py:5-19) splits into mean | log_var."""
+    down, mid, _ = vae_encoder_topology(cfg)
+    x = F.conv2d(img, sd["encoder.conv_in.weight"], sd["encoder.conv_in.bias"], padding=1)
+    for blk in down:
+        x = _run_layers(sd, blk, x, None, None)
+    x = _run_layers(sd, mid, x, None, None)
+    x = F.group_norm(x, cfg.groups, sd["encoder.out.0.weight"], sd["encoder.out.0.bias"], eps=1e-5)
+    z = F.conv2d(F.silu(x), sd["encoder.out.2.weight"], sd["encoder.out.2.bias"], padding=1)
+    return F.conv2d(z, sd["quant_conv.weight"], sd["quant_conv.bias"])
+
+
+def gaussian_moments(moments: Tensor) -> Tuple[Tensor, Tensor]:
+    """modules/distributions.py:8: mean, log_var = chunk(moments, 2, dim=1)."""
+    mean, log_var = torch.chunk(moments, 2, dim=1)
+    return mean, log_var
+
+
+def gaussian_sample(moments: Tensor, eps: Tensor) -> Tensor:
+    """modules/distributions.py:10-13 with the ``randn_like`` draw passed in: mean + eps * exp(0.5 * log_var)."""
+    mean, log_var = gaussian_moments(moments)
+    return mean + eps * torch.exp(0.5 * log_var)
+
+
+def gaussian_kl(moments: Tensor) -> Tensor:
+    """modules/distributions.py:15-19: 0.5 * sum(mean^2 + var - 1 - log_var) over dims [1, 2, 3]."""
+    mean, log_var = gaussian_moments(moments)
+    return 0.5 * torch.sum(torch.pow(mean, 2) + torch.exp(log_var) - 1.0 - log_var, dim=[1, 2, 3])
 
 
 # ----------------------------------------------------------------------------

@@ -63,6 +63,7 @@ SIGNATURES = {
     "sdb_nhwc_slice_to_nchw": (_i, [_p, _i, _p, _i, _i, _i, _i, _i, _p]),
     "sdb_upsample2x": (_i, [_p, _p, _i, _i, _i, _i, _i, _p]),
     "sdb_attention": (_i, [_p, _i64, _p, _i64, _p, _i64, _p, _i64, _i, _i, _i, _i, _i, _f, _i, _p]),
+    "sdb_softmax_rows": (_i, [_p, _i64, _p, _i64, _i, _i64, _i, _i, _f, _p]),
     "sdb_attention_p32": (_i, [_p, _i64, _p, _i64, _p, _i64, _p, _i64, _i, _i, _i, _i, _i, _f, _p]),
     "sdb_colsum": (_i, [_p, _i, _i64, _i64, _i64, _i, _p, _p]),
     "sdb_geglu_fwd": (_i, [_p, _p, _i64, _i, _p]),

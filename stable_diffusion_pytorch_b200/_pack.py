@@ -15,13 +15,28 @@ from torch import nn
 Tensor = torch.Tensor
 
 
+# Bumped whenever parameters are rewritten behind torch's back (the fused AdamW kernel updates them through raw
+# pointers, so ``_version`` does not move): every packed copy and every captured graph keyed on it is then rebuilt.
+_EPOCH = 0
+
+
+def epoch() -> int:
+    return _EPOCH
+
+
+def bump_epoch() -> int:
+    global _EPOCH
+    _EPOCH += 1
+    return _EPOCH
+
+
 class PackCache:
     def __init__(self):
         self._store: Dict[str, Tuple[tuple, object]] = {}
 
     @staticmethod
     def _sig(params: Sequence[Tensor]) -> tuple:
-        return (_COMPUTE,) + tuple((p.data_ptr(), p._version, str(p.device), p.dtype) for p in params)
+        return (_COMPUTE, _EPOCH) + tuple((p.data_ptr(), p._version, str(p.device), p.dtype) for p in params)
 
     def get(self, key: str, params: Sequence[Tensor], builder: Callable[[], object]):
         if _GRAPH:          # training graph: fresh, differentiable packing every forward

@@ -245,7 +245,7 @@ extern "C" int sdb_attention(const void* q, int64_t ldq, const void* k, int64_t 
   using namespace sdb;
   SDB_CHECK_ARG(q && k && v && out && B > 0 && heads > 0 && n > 0 && m > 0, "attention: bad args");
   if (dtype == SDB_F32)   // fp32 parity mode (precise_f32.cu)
-    return attention_f32(q, ldq, k, ldk, v, ldv, out, ldo, B, heads, n, m, d, scale, sdb_stream(stream));
+    return sdb_attention_f32_impl(q, ldq, k, ldk, v, ldv, out, ldo, B, heads, n, m, d, scale, sdb_stream(stream));
   SDB_CHECK_ARG(dtype == SDB_BF16, "attention: unknown dtype %d", dtype);
   SDB_CHECK_ARG(d > 0 && d <= 128 && d % 4 == 0, "attention: head dim (%d) must be a multiple of 4, <= 128", d);
   SDB_CHECK_ARG(ldq % 4 == 0 && ldk % 4 == 0 && ldv % 4 == 0 && ldo % 2 == 0, "attention: row strides must be multiples of 4");

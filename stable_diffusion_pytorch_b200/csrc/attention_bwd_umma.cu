@@ -8,6 +8,7 @@
 // No running maximum, no rescale: the forward kernel handed over the row log-sum-exp.
 // TMEM columns per warpgroup w (256 each): S [0,64), dP [64,128), dS [128,160), dQ [192,224).
 #include "common.cuh"
+#include "umma_helpers.cuh"
 
 namespace sdb {
 

@@ -197,7 +197,7 @@ static int launch_attention_ctx(const void* q, long long ldq, const void* k, lon
 }
 
 // m <= 128; same operand contract as sdb_attention_p32 (the ones column of V is ignored)
-static int attention_ctx_dispatch(const void* q, long long ldq, const void* k, long long ldk, const void* v,
+int sdb_attention_ctx_dispatch(const void* q, long long ldq, const void* k, long long ldk, const void* v,
                                   long long ldv, void* out, long long ldo, int B, int heads, int n, int m, int d,
                                   float scale, cudaStream_t st) {
   switch ((m + 15) / 16) {

@@ -44,6 +44,16 @@ static inline cudaStream_t sdb_stream(void* s) { return reinterpret_cast<cudaStr
 
 int sdb_num_sms();
 
+// host functions that cross translation units
+namespace sdb {
+int sdb_attention_f32_impl(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
+                           void* out, int64_t ldo, int B, int heads, int n, int m, int d, float scale,
+                           cudaStream_t st);                                   // precise_f32.cu
+int sdb_attention_ctx_dispatch(const void* q, long long ldq, const void* k, long long ldk, const void* v,
+                               long long ldv, void* out, long long ldo, int B, int heads, int n, int m, int d,
+                               float scale, cudaStream_t st);                  // attention_ctx.cu
+}  // namespace sdb
+
 // Encodes a tiled tensor map (rank <= 5) for a bf16/fp32 tensor.  dims/strides innermost first;
 // strides in BYTES for dims 1..rank-1 (dim 0 is contiguous).  swizzle_bytes in {0, 32, 64, 128}.
 int sdb_make_tensor_map(CUtensorMap* out, const void* base, int elem_bytes, int rank,
@@ -57,8 +67,24 @@ int sdb_make_tensor_map(CUtensorMap* out, const void* base, int elem_bytes, int 
 
 // set by any kernel whose bounded mbarrier wait expired (bad descriptor / pipeline bug); host
 // reads it through sdb_debug_timeout_flag().  Never hit in a correct run.
-// (defined here: the library is built as ONE translation unit, see sdb200.cu)
-__device__ int g_sdb_timeout_flag = 0;
+// The library is a handful of translation units compiled in parallel without relocatable device code,
+// so every unit carries its own copy of the flag and registers a reader with runtime.cu
+// (sdb_register_timeout_flag) at load time.
+static __device__ int g_sdb_timeout_flag = 0;
+typedef int (*SdbFlagReader)(void);   // returns the unit's flag and clears it; -1 on a CUDA error
+void sdb_register_timeout_flag(SdbFlagReader fn);
+static int sdb_tu_read_timeout_flag() {
+  int v = 0, zero = 0;
+  if (cudaMemcpyFromSymbol(&v, g_sdb_timeout_flag, sizeof(int)) != cudaSuccess) return -1;
+  if (v) cudaMemcpyToSymbol(g_sdb_timeout_flag, &zero, sizeof(int));
+  return v;
+}
+namespace {
+struct SdbFlagRegistrar {
+  SdbFlagRegistrar() { sdb_register_timeout_flag(&sdb_tu_read_timeout_flag); }
+};
+static SdbFlagRegistrar g_sdb_flag_registrar;
+}  // namespace
 
 namespace sdb {
 

@@ -16,6 +16,7 @@
 #include <stdlib.h>
 
 #include "common.cuh"
+#include "umma_helpers.cuh"
 
 namespace sdb {
 

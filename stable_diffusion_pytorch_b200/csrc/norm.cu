@@ -480,6 +480,50 @@ extern "C" int sdb_add_layernorm(const void* x, const void* res, const float* ga
   return SDB_OK;
 }
 
+// ---- row softmax of a materialised score matrix (the wide-head attention route, d > 128) ------------------------
+// modules/transformer.py:101-111: sim * scale, softmax over the keys.  One warp per row; columns >= valid (the key
+// padding that makes the row a multiple of 16 for the GEMMs either side) come out as exact zeros.
+template <typename OutT>
+__global__ void __launch_bounds__(256)
+softmax_rows_kernel(const float* __restrict__ x, long long ldx, OutT* __restrict__ out, long long ldo, long long rows,
+                    int cols, int valid, float scale_log2) {
+  const long long row = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int lane = threadIdx.x & 31;
+  if (row >= rows) return;
+  const float* xr = x + row * ldx;
+  float mx = -INFINITY;
+  for (int c = lane; c < valid; c += 32) mx = fmaxf(mx, xr[c]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  float sum = 0.f;
+  for (int c = lane; c < valid; c += 32) sum += exp2f((xr[c] - mx) * scale_log2);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+  const float inv = 1.0f / sum;
+  OutT* orow = out + row * ldo;
+  for (int c = lane; c < cols; c += 32) {
+    const float p = c < valid ? exp2f((xr[c] - mx) * scale_log2) * inv : 0.f;
+    if constexpr (sizeof(OutT) == 2) orow[c] = __float2bfloat16(p);
+    else orow[c] = p;
+  }
+}
+
+extern "C" int sdb_softmax_rows(const float* x, int64_t ldx, void* out, int64_t ldo, int out_dtype, int64_t rows,
+                                int cols, int valid_cols, float scale, void* stream) {
+  SDB_CHECK_ARG(x && out && rows > 0 && cols > 0 && valid_cols > 0 && valid_cols <= cols && ldx >= cols && ldo >= cols,
+                "softmax_rows: bad args");
+  const unsigned grid = (unsigned)((rows + 7) / 8);
+  const float sl2 = scale * 1.4426950408889634f;
+  if (out_dtype == SDB_BF16)
+    softmax_rows_kernel<__nv_bfloat16><<<grid, 256, 0, sdb_stream(stream)>>>(x, ldx, (__nv_bfloat16*)out, ldo, rows,
+                                                                            cols, valid_cols, sl2);
+  else
+    softmax_rows_kernel<float><<<grid, 256, 0, sdb_stream(stream)>>>(x, ldx, (float*)out, ldo, rows, cols,
+                                                                    valid_cols, sl2);
+  SDB_LAUNCH_OK();
+  return SDB_OK;
+}
+
 static int launch_transpose(const void* src, int sdt, void* dst, int ddt, int Bn, int R, int Cc, cudaStream_t st) {
   dim3 grid((Cc + 31) / 32, (R + 31) / 32, Bn), block(32, 8);
   SDB_CHECK_ARG(grid.y <= 65535 && grid.z <= 65535, "transpose: dims too large");

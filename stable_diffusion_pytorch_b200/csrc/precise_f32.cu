@@ -231,7 +231,7 @@ __global__ void __launch_bounds__(128) attention_f32_kernel(const float* __restr
   }
 }
 
-static int attention_f32(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
+int sdb_attention_f32_impl(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
                          void* out, int64_t ldo, int B, int heads, int n, int m, int d, float scale,
                          cudaStream_t st) {
   SDB_CHECK_ARG(d >= 1 && d <= 128, "attention (fp32): d (%d) must be <= 128", d);

@@ -22,12 +22,23 @@ extern "C" int sdb_version(void) { return 100; }
 extern "C" const char* sdb_last_error(void) { return tl_error; }
 extern "C" int64_t sdb_launch_count(void) { return g_sdb_launches.load(); }
 
+// one reader per translation unit (each holds its own copy of the device flag, see common.cuh); filled by static
+// initialisers while the library loads, so no locking is needed afterwards
+static SdbFlagReader g_flag_readers[32];
+static int g_n_flag_readers = 0;
+void sdb_register_timeout_flag(SdbFlagReader fn) {
+  if (g_n_flag_readers < 32) g_flag_readers[g_n_flag_readers++] = fn;
+}
+
 extern "C" int sdb_debug_timeout_flag(void) {
-  int v = 0, zero = 0;
   if (cudaDeviceSynchronize() != cudaSuccess) return -1;
-  if (cudaMemcpyFromSymbol(&v, g_sdb_timeout_flag, sizeof(int)) != cudaSuccess) return -1;
-  cudaMemcpyToSymbol(g_sdb_timeout_flag, &zero, sizeof(int));
-  return v;
+  int any = 0;
+  for (int i = 0; i < g_n_flag_readers; ++i) {
+    const int v = g_flag_readers[i]();
+    if (v < 0) return -1;
+    any |= v;
+  }
+  return any;
 }
 
 int sdb_num_sms() {

@@ -13,6 +13,7 @@
 // dY tile is fetched once per group) x (a chunk of the pixels): split-K over one wave of CTAs, partial sums added to the
 // fp32 result with atomics (the caller zeroes it).  Warp 0 = TMA producer, warp 1 = MMA issuer, warps 4-7 = epilogue.
 #include "common.cuh"
+#include "umma_helpers.cuh"
 
 namespace sdb {
 

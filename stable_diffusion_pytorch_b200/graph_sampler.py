@@ -24,7 +24,7 @@ class GraphedLatentStep:
     def __init__(self, unet, scheduler, batch: int, height: int, width: int, ctx_len: int = 77,
                  steps: Optional[Sequence[int]] = None, time_steps: int = 50, guidance_scale: float = 7.5,
                  sampler: str = "ddim", dtype=torch.bfloat16, scale_factor: float = 1.0, seed: int = 0,
-                 device="cuda", host_noise: Optional[Tensor] = None):
+                 device="cuda", host_noise: Optional[Tensor] = None, ctx_dtype=None):
         self.unet, self.sch = unet, scheduler
         self.B, self.H, self.W = batch, height, width
         self.C = unet.latent_channels
@@ -39,7 +39,7 @@ class GraphedLatentStep:
         rep = 2 if self.cfg else 1
         dev = self.device
         self.x = torch.zeros(batch, self.C, height, width, device=dev, dtype=dtype)
-        self.c_in = torch.zeros(rep * batch, ctx_len, unet.context_dim, device=dev, dtype=dtype)
+        self.c_in = torch.zeros(rep * batch, ctx_len, unet.context_dim, device=dev, dtype=ctx_dtype or dtype)
         self.t_table = torch.tensor(self.steps, dtype=torch.int64, device=dev)
         self.t = torch.full((rep * batch,), self.steps[0], dtype=torch.int64, device=dev)
         self.slot = torch.zeros(1, dtype=torch.int32, device=dev)
@@ -50,6 +50,11 @@ class GraphedLatentStep:
             assert self.noise.shape[0] == n
         self.graph = None
         self.launches_per_step = 0
+
+    def set_noise(self, host_noise: Tensor):
+        """Refills the static noise table [n_steps, B, C, H, W] a captured graph reads (same storage, new draws)."""
+        assert self.noise is not None and tuple(host_noise.shape) == tuple(self.noise.shape)
+        self.noise.copy_(host_noise, non_blocking=True)
 
     # ------------------------------------------------------------------------------------------
     def _one_step(self):

@@ -29,6 +29,7 @@ class LatentDiffusion(nn.Module):
         self.text_encoder = text_encoder
         self.noise_scheduler = noise_scheduler
         self._uncond = {}
+        self._graphs = {}       # sample(): GraphedLatentStep per (shape, dtype, sampler, guidance, ...) key
 
     # ------------------------------------------------------------------------------------------
     def _uncond_emb(self, bsz: int, like: Tensor) -> Tensor:
@@ -60,16 +61,35 @@ class LatentDiffusion(nn.Module):
         t_in = torch.cat([t] * 2)
         return self.unet(x, t_in, c_in, x_repeat=2)
 
+    # noise tables above this size are not pre-staged on the device: sample() then runs the eager loop
+    GRAPH_NOISE_TABLE_MAX_BYTES = 4 << 30
+
+    def _weights_sig(self) -> tuple:
+        return (_pack.epoch(), _pack.compute_dtype()) + tuple(
+            (p.data_ptr(), p._version) for p in self.unet.parameters())
+
+    def _host_noise_table(self, x: Tensor, steps, repeat_noise: bool) -> Tensor:
+        """The draws the reference makes inside ``step`` (scheduler.py:200-210), in its order, from torch's global CPU
+        generator: one ``torch.randn`` per iteration whose time step is not 0."""
+        shape = (1, *x.shape[1:]) if repeat_noise else tuple(x.shape)
+        rows = [torch.zeros(x.shape) if step == 0 else torch.randn(shape).expand(x.shape) for step in steps]
+        return torch.stack(rows)
+
     @torch.no_grad()
     def sample(self, noised_sample: Tensor, context_emb: Tensor, guidance_scale: float = 7.5,
                repeat_noise: bool = False, scale_factor: float = 1.0, time_steps: Optional[int] = None,
                sampler: str = "ddpm", device_noise: bool = False, seed: int = 0,
-               host_noise: Optional[Tensor] = None):
+               host_noise: Optional[Tensor] = None, use_graph: Optional[bool] = None):
         """Reverse process from x_T.  ``sampler`` = "ddpm" (the reference's) or "ddim" (eta = 0).
         ``device_noise=False`` draws every step's noise on the host from torch's global CPU generator
         in the reference's order (seeded parity); True uses the in-kernel Philox stream.  ``host_noise``
         ([n_steps, B, C, H, W], e.g. ``sharding.host_noise_table``) replaces the per-step draw: a rank that owns
-        a slice of a larger batch passes its rows of the full-batch noise."""
+        a slice of a larger batch passes its rows of the full-batch noise.
+
+        The loop body (CFG pair of UNet evaluations + fused combine / update) is captured once per
+        (shape, dtype, sampler, guidance, ...) key into a CUDA graph (``GraphedLatentStep``) and replayed for every
+        step -- the path bench.py times; same kernels, so the result is bit-identical to the eager loop, which
+        ``use_graph=False`` (or fp32 parity mode, or a noise table too large to stage) still runs."""
         _pack.require_cuda(noised_sample, "LatentDiffusion.sample")
         sch = self.noise_scheduler
         x = noised_sample.contiguous()
@@ -78,10 +98,17 @@ class LatentDiffusion(nn.Module):
             steps = list(reversed(range(time_steps - 1, -1, -1)))      # ascending, like the reference
         else:
             steps = [int(s) for s in reversed(sch.noise_time_steps)]
-        tabs = sch._device_tables(x.device)
         do_cfg = guidance_scale > 1
-        c_in = self._c_in(context_emb) if do_cfg else context_emb
         kind = {"ddpm": 0, "ddim": 1}[sampler]
+        needs_table = kind == 0 and not device_noise
+        table_bytes = len(steps) * x.numel() * x.element_size() if needs_table else 0
+        if use_graph is None:
+            use_graph = table_bytes <= self.GRAPH_NOISE_TABLE_MAX_BYTES
+        if use_graph:
+            return self._sample_graphed(x, context_emb, guidance_scale, repeat_noise, scale_factor, steps, sampler,
+                                        device_noise, seed, host_noise, needs_table)
+        tabs = sch._device_tables(x.device)
+        c_in = self._c_in(context_emb) if do_cfg else context_emb
         for i, step in enumerate(steps):
             t = torch.full((bsz * (2 if do_cfg else 1),), step, dtype=torch.long, device=x.device)
             eps = self.unet(x, t, c_in, x_repeat=2 if do_cfg else 1)
@@ -96,3 +123,32 @@ class LatentDiffusion(nn.Module):
                                         guidance=guidance_scale, scale_factor=scale_factor, seed=seed,
                                         want_x0=False)
         return x
+
+    def _sample_graphed(self, x, context_emb, guidance_scale, repeat_noise, scale_factor, steps, sampler,
+                        device_noise, seed, host_noise, needs_table):
+        from ..graph_sampler import GraphedLatentStep
+        bsz = x.shape[0]
+        key = (tuple(x.shape), x.dtype, str(x.device), tuple(context_emb.shape[1:]), context_emb.dtype, sampler,
+               float(guidance_scale), float(scale_factor), tuple(steps), bool(needs_table), int(seed))
+        sig = self._weights_sig()
+        hit = self._graphs.get(key)
+        if hit is not None and hit[0] != sig:       # weights changed under a captured graph: rebuild it
+            hit = None
+        if needs_table:
+            if host_noise is None:
+                host_noise = self._host_noise_table(x, steps, repeat_noise)
+            assert host_noise.shape[0] == len(steps)
+        if hit is None:
+            gs = GraphedLatentStep(self.unet, self.noise_scheduler, bsz, x.shape[2], x.shape[3],
+                                   ctx_len=context_emb.shape[1], steps=steps, guidance_scale=guidance_scale,
+                                   sampler=sampler, dtype=x.dtype, ctx_dtype=context_emb.dtype,
+                                   scale_factor=scale_factor, seed=seed, device=x.device,
+                                   host_noise=host_noise if needs_table else None)
+            gs.reset(x, context_emb, self._uncond_emb(1, context_emb) if gs.cfg else None)
+            gs.capture()
+            self._graphs[key] = (sig, gs)
+        else:
+            gs = hit[1]
+            if needs_table:
+                gs.set_noise(host_noise)
+        return gs.run(x, context_emb, self._uncond_emb(1, context_emb) if gs.cfg else None)

@@ -127,7 +127,7 @@ class UNetModel(nn.Module):
     def _context_kv(self, p, ctx: Tensor) -> Dict[int, list]:
         """All cross-attention K/V of ``ctx`` in one GEMM; reused while the same context tensor
         (same storage and version) comes back, i.e. across the steps of a sampling loop."""
-        key = (ctx.data_ptr(), ctx._version, tuple(ctx.shape), ctx.dtype, id(p["wkv"]))
+        key = (ctx.data_ptr(), ctx._version, tuple(ctx.shape), ctx.dtype, id(p["wkv"]), _pack.epoch())
         cacheable = not (torch.cuda.is_current_stream_capturing() or _pack.in_graph_mode())
         if cacheable and self._ctx_cache is not None and self._ctx_cache[0] == key:
             return self._ctx_cache[1]

@@ -327,8 +327,37 @@ def attention(q: Tensor, k: Tensor, v: Tensor, heads: int, d: int, scale: float,
     assert q.dtype in (torch.bfloat16, torch.float32)
     if out is None:
         out = torch.empty(B, n, heads * d, device=q.device, dtype=q.dtype)
+    if d > ATTENTION_MAX_FUSED_D:
+        return _attention_wide(q, k, v, heads, d, scale, out)
     check(_lib.lib().sdb_attention(_ptr(q), q.stride(1), _ptr(k), k.stride(1), _ptr(v), v.stride(1), _ptr(out),
                                    out.stride(1), B, heads, n, m, d, scale, _dt(q), _stream()), "attention")
+    return out
+
+
+ATTENTION_MAX_FUSED_D = 128     # head dims the fused (flash-style) kernels hold in registers / shared memory
+
+
+def _attention_wide(q: Tensor, k: Tensor, v: Tensor, heads: int, d: int, scale: float, out: Tensor) -> Tensor:
+    """Head dims beyond the fused kernels (the VAE encoder bottleneck has ONE head of d = mid_ch, e.g. 512 for the
+    AutoencoderKL shape, models/autoencoder.py:181-183): per (batch, head) S = Q K^T on the GEMM kernel (fp32 out),
+    ``sdb_softmax_rows``, O = P V on the GEMM kernel.  `sim` is materialised -- the sequence there is (H/8)^2 tokens.
+    Keys are zero-padded to a multiple of 16 (the GEMM's N / K granularity); the softmax zeroes the padding."""
+    assert d % 8 == 0, f"attention: head dim {d} > {ATTENTION_MAX_FUSED_D} must be a multiple of 8"
+    B, n, m = q.shape[0], q.shape[1], k.shape[1]
+    m16 = (m + 15) // 16 * 16
+    L = _lib.lib()
+    kp = torch.zeros(m16, d, device=q.device, dtype=q.dtype)
+    vt = torch.zeros(d, m16, device=q.device, dtype=q.dtype)
+    s = torch.empty(n, m16, device=q.device, dtype=torch.float32)
+    p = torch.empty(n, m16, device=q.device, dtype=q.dtype)
+    for b in range(B):
+        for h in range(heads):
+            cols = slice(h * d, (h + 1) * d)
+            kp[:m].copy_(k[b, :, cols])
+            vt[:, :m].copy_(v[b, :, cols].t())
+            gemm(q[b, :, cols], kp, out=s)
+            check(L.sdb_softmax_rows(_ptr(s), m16, _ptr(p), m16, _dt(p), n, m16, m, scale, _stream()), "softmax_rows")
+            gemm(p, vt, out=out[b, :, cols])
     return out
 
 

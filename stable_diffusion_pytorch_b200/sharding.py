@@ -67,6 +67,14 @@ def gather_batch(local: Tensor, total: int, group=None) -> Tensor:
     if local.shape[0] != sizes[rank]:
         raise ValueError(f"rank {rank} holds {local.shape[0]} rows, expected {sizes[rank]} of {total}")
     biggest = max(sizes)
+    if min(sizes) == 0:
+        # more ranks than rows: a rank with an empty shard may not know the row shape (it decoded nothing); every
+        # rank agrees on it first so the collective below sees equal buffers everywhere
+        shapes = [None] * world
+        dist.all_gather_object(shapes, tuple(local.shape[1:]) if local.shape[0] else None, group=group)
+        row = next(s for s in shapes if s is not None)
+        if local.shape[0] == 0:
+            local = local.new_zeros(0, *row)
     padded = local
     if local.shape[0] < biggest:
         padded = torch.cat([local, local.new_zeros(biggest - local.shape[0], *local.shape[1:])])
@@ -86,7 +94,16 @@ def sharded_sample(latent_diffusion, x_full: Tensor, context_full: Tensor, world
     dev = next(latent_diffusion.unet.parameters()).device
     x = shard_batch(x_full, world, rank).to(dev)
     ctx = shard_batch(context_full, world, rank).to(dev)
-    out = latent_diffusion.sample(x, ctx, **sample_kwargs)
+    if sample_kwargs.get("device_noise"):
+        # the in-kernel Philox stream is keyed by (seed, step, LOCAL element index): give every shard its own key so
+        # row i of different ranks does not see the same noise (statistical parity only, like device_noise itself)
+        lo, _ = shard_range(x_full.shape[0], world, rank)
+        sample_kwargs = dict(sample_kwargs, seed=(int(sample_kwargs.get("seed", 0)) + 0x9E3779B97F4A7C15 * (lo + 1))
+                             & 0x7FFFFFFFFFFFFFFF)
+    if x.shape[0] == 0:     # more ranks than latents: nothing to sample here, but the gather below is collective
+        out = x.clone()
+    else:
+        out = latent_diffusion.sample(x, ctx, **sample_kwargs)
     return gather_batch(out, x_full.shape[0]) if gather else out
 
 
@@ -100,5 +117,8 @@ def sharded_images(latent_diffusion, x_full: Tensor, context_full: Tensor, world
     if rank is None:
         rank = dist.get_rank() if dist.is_initialized() else 0
     latents = sharded_sample(latent_diffusion, x_full, context_full, world, rank, gather=False, **sample_kwargs)
-    images = latent_diffusion.autoencoder.decode_uint8(latents)
+    if latents.shape[0] == 0:   # the trailing shape is learnt from the other ranks inside gather_batch
+        images = torch.zeros(0, dtype=torch.uint8, device=latents.device)
+    else:
+        images = latent_diffusion.autoencoder.decode_uint8(latents)
     return gather_batch(images, x_full.shape[0]) if gather else images

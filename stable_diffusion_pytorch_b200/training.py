@@ -40,7 +40,9 @@ class OptimConfig:
 class FlatAdamW:
     """Flat-bucket AdamW over ``params`` (all fp32, on one CUDA device)."""
 
-    def __init__(self, params: Iterable[nn.Parameter], cfg: Optional[OptimConfig] = None):
+    def __init__(self, params: Iterable[nn.Parameter], cfg: Optional[OptimConfig] = None, seed: Optional[int] = None):
+        """``seed``: seeds the training-mode dropout stream of this device from (seed, data-parallel rank), so ranks
+        draw independent masks like the reference's per-rank CUDA generators (``ops.dropout_seed`` does it by hand)."""
         self.cfg = cfg or OptimConfig()
         self.params = [p for p in params if p.requires_grad]
         if not self.params:
@@ -58,6 +60,10 @@ class FlatAdamW:
         self.v = torch.zeros(n, device=dev, dtype=torch.float32)
         self.gnorm_sq = torch.zeros(1, device=dev, dtype=torch.float32)
         self.step_count = 0
+        self.micro_steps = 0        # micro-batches accumulated into `grad` since the last update
+        if seed is not None:
+            rank = dist.get_rank() if (dist.is_available() and dist.is_initialized()) else 0
+            ops.dropout_seed((int(seed) * 0x9E3779B1 + rank * 0x85EBCA77 + 1) & 0x7FFFFFFFFFFF, dev)
         o = 0
         with torch.no_grad():
             for p in self.params:
@@ -69,6 +75,7 @@ class FlatAdamW:
 
     def zero_grad(self) -> None:
         self.grad.zero_()
+        self.micro_steps = 0
         for p, g in zip(self.params, self._grad_views()):   # a backward may have re-pointed .grad; restore the views
             if p.grad is None or p.grad.data_ptr() != g.data_ptr():
                 p.grad = g
@@ -97,22 +104,31 @@ class FlatAdamW:
             return dist.get_world_size(group)
         return 1
 
-    def grad_norm(self, world: int = 1) -> Tensor:
+    def grad_norm(self, world: int = 1, accum_steps: Optional[int] = None) -> Tensor:
         """Global L2 norm of the (mean) gradient, on the device."""
         self.gnorm_sq.zero_()
         ops.sumsq(self.grad, self.gnorm_sq)
-        return self.gnorm_sq.sqrt() / world
+        return self.gnorm_sq.sqrt() / (world * (accum_steps or max(self.micro_steps, 1)))
 
-    def step(self, world: int = 1, lr: Optional[float] = None) -> None:
-        """clip_grad_norm_(max_grad_norm) + AdamW on the whole model, one kernel after the norm kernel."""
+    def step(self, world: int = 1, lr: Optional[float] = None, accum_steps: Optional[int] = None) -> None:
+        """clip_grad_norm_(max_grad_norm) + AdamW on the whole model, one kernel after the norm kernel.
+
+        The flat buffer holds the SUM over ranks and over the micro-batches accumulated since the last update; the
+        reference's ``accelerator.backward`` divides every micro-loss by gradient_accumulation_steps and DDP averages
+        over ranks (train_unet.py:359-366), so the gradient that is clipped and applied is that sum times
+        1 / (world * accum_steps).  ``accum_steps`` defaults to the micro-steps ``train_step`` counted."""
         c = self.cfg
+        accum = accum_steps or max(self.micro_steps, 1)
         self.step_count += 1
         self.gnorm_sq.zero_()
         ops.sumsq(self.grad, self.gnorm_sq)
         check(_lib.lib().sdb_adamw(ops._ptr(self.flat), ops._ptr(self.grad), ops._ptr(self.m), ops._ptr(self.v), self.numel,
                                    c.learning_rate if lr is None else lr, c.adam_beta1, c.adam_beta2, c.adam_eps,
-                                   c.adam_weight_decay, self.step_count, 1.0 / world, ops._ptr(self.gnorm_sq),
+                                   c.adam_weight_decay, self.step_count, 1.0 / (world * accum), ops._ptr(self.gnorm_sq),
                                    c.max_grad_norm, ops._stream()), "adamw")
+        # the kernel wrote the parameters through raw pointers (torch's version counters did not move): packed bf16
+        # copies, the cached context K/V and captured sampling graphs are stale from here on
+        _pack.bump_epoch()
 
 
 def diffusion_loss(model, x_t: Tensor, timesteps: Tensor, text_condition: Tensor, noise: Tensor,
@@ -131,6 +147,7 @@ def train_step(model, opt: FlatAdamW, x_t: Tensor, timesteps: Tensor, text_condi
     gradient buffer is cleared.  Returns the (device) loss of this rank's micro-batch."""
     loss = diffusion_loss(model, x_t, timesteps, text_condition, noise, guidance_scale)
     loss.backward()
+    opt.micro_steps += 1
     ops.dropout_advance(x_t.device)          # the next micro-step draws new masks
     if sync:
         world = opt.all_reduce(group)
@@ -151,8 +168,13 @@ class GraphedTrainStep:
     """
 
     def __init__(self, model, opt: FlatAdamW, batch: int, latent_hw, ctx_len: int = 77, ctx_dim: int = 768,
-                 latent_channels: int = 4, guidance_scale: float = 7.5, group=None, warmup: int = 3):
+                 latent_channels: int = 4, guidance_scale: float = 7.5, group=None, warmup: int = 3,
+                 accum_steps: int = 1):
+        """``accum_steps``: micro-batches per update (the reference's gradient_accumulation_steps, default 4 in its
+        configs): call ``step(..., sync=False)`` for the first accum_steps - 1 of them.  Fixed at capture time -- the
+        1 / (world * accum_steps) gradient scale is an argument of the captured AdamW launch."""
         dev = opt.flat.device
+        self.accum_steps = int(accum_steps)
         H, W = latent_hw
         self.model, self.opt, self.group, self.g = model, opt, group, guidance_scale
         self.x_t = torch.zeros(batch, latent_channels, H, W, device=dev)
@@ -177,7 +199,8 @@ class GraphedTrainStep:
         ops.sumsq(o.grad, o.gnorm_sq)
         check(_lib.lib().sdb_adamw_dev(ops._ptr(o.flat), ops._ptr(o.grad), ops._ptr(o.m), ops._ptr(o.v), o.numel,
                                        ops._ptr(self.hyper), c.adam_beta1, c.adam_beta2, c.adam_eps, c.adam_weight_decay,
-                                       1.0 / self.world, ops._ptr(o.gnorm_sq), c.max_grad_norm, ops._stream()), "adamw_dev")
+                                       1.0 / (self.world * self.accum_steps), ops._ptr(o.gnorm_sq), c.max_grad_norm,
+                                       ops._stream()), "adamw_dev")
         o.grad.zero_()
 
     def _set_hyper(self, lr: Optional[float]) -> None:
@@ -224,4 +247,5 @@ class GraphedTrainStep:
                 dist.all_reduce(self.opt.grad, op=dist.ReduceOp.SUM, group=self.group)
             self._set_hyper(lr)
             self.graph_b.replay()
+            _pack.bump_epoch()      # parameters rewritten through raw pointers: see FlatAdamW.step
         return self.loss

@@ -24,3 +24,10 @@ def golden_train():
     import numpy as np
     path = os.path.join(ROOT, "tests", "golden", "reference_train.npz")
     return dict(np.load(path))
+
+
+@pytest.fixture(scope="session")
+def golden_encode():
+    import numpy as np
+    path = os.path.join(ROOT, "tests", "golden", "reference_vae_encode.npz")
+    return dict(np.load(path))

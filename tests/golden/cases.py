@@ -82,6 +82,20 @@ def vae_inputs(cfg, B, H, W, seed):
     return torch.randn(B, cfg.latent_channels, H, W, generator=_g(3000 + seed))
 
 
+# VAE encode -- name -> (cfg, seed, B, H, W) with H x W the IMAGE size
+VAE_WIDE_MID = O.VaeCfg(autoencoder_channels_list=(32, 64, 256), groups=16)   # bottleneck head dim 256 (> 128)
+VAE_ENC_CASES = {
+    "default_32": (VAE_DEFAULT, 24, 2, 32, 32),      # [64, 128]: 16 x 16 = 256 bottleneck tokens, d = 128
+    "kltiny_32": (VAE_KL_TINY, 25, 1, 32, 32),       # three DownSamples: 32 -> 4, d = 64
+    "widemid_24": (VAE_WIDE_MID, 26, 2, 24, 24),     # 24 -> 6: 36 tokens (not a multiple of 8), d = 256
+}
+VAE_ENC_EPS_SEED = 777
+
+
+def vae_encode_inputs(cfg, B, H, W, seed):
+    return torch.randn(B, cfg.in_channels, H, W, generator=_g(4000 + seed))
+
+
 # ---- train step (row T1) -------------------------------------------------------------------------
 # name -> (cfg, seed, B, H, W, n_steps, guidance); lr raised so two steps move the weights measurably
 TRAIN_CASES = {

@@ -128,6 +128,42 @@ def main():
     print("wrote", path, os.path.getsize(path), "bytes,", len(out), "arrays")
 
 
+def main_encode():
+    """AutoEncoderKL.encode (models/autoencoder.py:132-146) and GaussianDistribution.sample / .kl
+    (modules/distributions.py:5-19) of the unmodified reference -> ``reference_vae_encode.npz``."""
+    torch.set_num_threads(8)
+    out = {}
+    with torch.no_grad():
+        for name, (vcfg, seed, B, H, W) in cases.VAE_ENC_CASES.items():
+            cfg = AutoencoderConfig(in_channels=vcfg.in_channels, latent_channels=vcfg.latent_channels,
+                                    out_channels=vcfg.out_channels,
+                                    autoencoder_channels_list=list(vcfg.autoencoder_channels_list),
+                                    autoencoder_num_res_blocks=vcfg.autoencoder_num_res_blocks, groups=vcfg.groups)
+            m = AutoEncoderKL(cfg).eval()
+            sd = O.seeded_state_dict(O.vae_encoder_param_shapes(vcfg), seed)
+            missing, unexpected = m.load_state_dict(sd, strict=False)
+            assert not unexpected, unexpected          # the oracle's key / shape enumeration is the reference's
+            assert all(k.startswith(("decoder.", "post_quant_conv.")) for k in missing), missing
+            img = cases.vae_encode_inputs(vcfg, B, H, W, seed)
+            dist = m.encode(img).latent_dist
+            out[f"enc_{name}_mean"] = dist.mean.numpy().copy()
+            out[f"enc_{name}_logvar"] = dist.log_var.numpy().copy()
+            torch.manual_seed(cases.VAE_ENC_EPS_SEED)       # sample() draws randn_like(std) from the global generator
+            out[f"enc_{name}_sample"] = dist.sample().numpy().copy()
+            # the draw itself, for the tests: randn_like follows the memory format of the moments (torch's CPU conv
+            # hands back channels-last strides here), so it is recorded rather than re-derived from a shape
+            torch.manual_seed(cases.VAE_ENC_EPS_SEED)
+            eps = torch.randn_like(torch.exp(0.5 * dist.log_var))
+            assert torch.equal(dist.mean + eps * torch.exp(0.5 * dist.log_var), torch.from_numpy(out[f"enc_{name}_sample"]))
+            out[f"enc_{name}_eps"] = eps.contiguous().numpy().copy()
+            out[f"enc_{name}_kl"] = dist.kl().numpy().copy()
+            print("encode", name, out[f"enc_{name}_mean"].shape, float(np.abs(out[f"enc_{name}_mean"]).mean()),
+                  out[f"enc_{name}_kl"])
+    path = os.path.join(HERE, "reference_vae_encode.npz")
+    np.savez_compressed(path, **out)
+    print("wrote", path, os.path.getsize(path), "bytes,", len(out), "arrays")
+
+
 def main_train():
     """Row T1: the reference's own modules, F.mse_loss, clip_grad_norm_ and torch.optim.AdamW
     (train_unet.py:489-529, :359-375, :231-236) on seeded batches -> ``reference_train.npz``."""
@@ -171,5 +207,7 @@ def main_train():
 if __name__ == "__main__":
     if len(sys.argv) > 1 and sys.argv[1] == "train":
         main_train()
+    elif len(sys.argv) > 1 and sys.argv[1] == "encode":
+        main_encode()
     else:
         main()

@@ -86,6 +86,26 @@ def test_vae_decode(golden, name):
     assert rel_l2(y, golden[f"vae_{name}"]) < 1e-5
 
 
+@pytest.mark.parametrize("name", list(cases.VAE_ENC_CASES))
+def test_vae_encode_and_gaussian_distribution(golden_encode, name):
+    """encoder + quant_conv moments, GaussianDistribution.sample (same global-generator draw) and .kl
+    against the unmodified reference (make_golden.py encode)."""
+    cfg, seed, B, H, W = cases.VAE_ENC_CASES[name]
+    sd = O.seeded_state_dict(O.vae_encoder_param_shapes(cfg), seed)
+    img = cases.vae_encode_inputs(cfg, B, H, W, seed)
+    with torch.no_grad():
+        mom = O.vae_encode(sd, cfg, img)
+        mean, log_var = O.gaussian_moments(mom)
+        smp = O.gaussian_sample(mom, torch.from_numpy(golden_encode[f"enc_{name}_eps"]))
+        kl = O.gaussian_kl(mom)
+    G = golden_encode
+    assert tuple(mean.shape) == G[f"enc_{name}_mean"].shape
+    assert rel_l2(mean, G[f"enc_{name}_mean"]) < 1e-5
+    assert rel_l2(log_var, G[f"enc_{name}_logvar"]) < 1e-5
+    assert rel_l2(smp, G[f"enc_{name}_sample"]) < 1e-5
+    np.testing.assert_allclose(kl.numpy(), G[f"enc_{name}_kl"], rtol=1e-4)
+
+
 def test_cfg_combine_is_mislabelled_like_reference():
     # latent_diffusion.py:61-65: first chunk is the UNCOND half
     e_unc, e_cond = torch.full((1, 1), 1.0), torch.full((1, 1), 3.0)

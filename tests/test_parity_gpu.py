@@ -12,6 +12,7 @@ pytestmark = pytest.mark.gpu
 DEV = "cuda"
 UNET_BF16_TOL = 2e-2      # north_star: bf16 forward vs fp32 reference
 VAE_BF16_TOL = 2e-2
+VAE_ENC_BF16_TOL = 4e-2   # encoder moments: deeper than the decoder cases (3 DownSamples + attention), measured 1.5-2.8e-2
 SAMPLE_TOL = 5e-2         # final latents after a short CFG sampling run, bf16 UNet, identical host noise
 
 
@@ -253,3 +254,61 @@ def test_decode_uint8_is_the_reference_detransform():
     want = (((img + 1) / 2).clamp(0, 1) * 255).to(torch.uint8).permute(0, 2, 3, 1)
     assert u8.dtype == torch.uint8 and tuple(u8.shape) == tuple(want.shape)
     assert torch.equal(u8, want)
+
+
+# ---------------------------------------------------------------- VAE encode
+@pytest.mark.parametrize("name", list(cases.VAE_ENC_CASES))
+def test_vae_encode_vs_reference_golden(golden_encode, name):
+    """AutoEncoderKL.encode(img).latent_dist (.mean / .log_var / .sample() / .kl()) against the unmodified reference
+    (models/autoencoder.py:132-146,164-199; modules/distributions.py:5-19).  `widemid_24` has a bottleneck head dim
+    of 256: the wide-head attention route (GEMM -> sdb_softmax_rows -> GEMM) with a 36-token sequence."""
+    from stable_diffusion_pytorch_b200.models import AutoEncoderKL, AutoencoderConfig
+    cfg, seed, B, H, W = cases.VAE_ENC_CASES[name]
+    m = AutoEncoderKL(AutoencoderConfig(autoencoder_channels_list=list(cfg.autoencoder_channels_list),
+                                        groups=cfg.groups)).eval()
+    missing, unexpected = m.load_state_dict(O.seeded_state_dict(O.vae_encoder_param_shapes(cfg), seed), strict=False)
+    assert not unexpected and all(k.startswith(("decoder.", "post_quant_conv.")) for k in missing)
+    m = m.to(DEV)
+    img = cases.vae_encode_inputs(cfg, B, H, W, seed)
+    with torch.no_grad():
+        dist = m.encode(img.to(DEV)).latent_dist
+        smp = dist.sample(eps=torch.from_numpy(golden_encode[f"enc_{name}_eps"]).to(DEV))   # the reference's draw
+        kl = dist.kl()
+    G = golden_encode
+    assert tuple(dist.mean.shape) == G[f"enc_{name}_mean"].shape and dist.mean.dtype == torch.float32
+    e_m, e_v = rel_l2(dist.mean, G[f"enc_{name}_mean"]), rel_l2(dist.log_var, G[f"enc_{name}_logvar"])
+    e_s = rel_l2(smp, G[f"enc_{name}_sample"])
+    e_k = float(np.abs(kl.cpu().numpy() - G[f"enc_{name}_kl"]).max() / np.abs(G[f"enc_{name}_kl"]).max())
+    print(f"vae encode {name}: mean {e_m:.3e} log_var {e_v:.3e} sample {e_s:.3e} kl {e_k:.3e}")
+    assert max(e_m, e_v, e_s, e_k) < VAE_ENC_BF16_TOL
+    # same modules in the fp32 parity mode: the algorithm is the reference's to fp32 rounding
+    from stable_diffusion_pytorch_b200 import precision
+    with torch.no_grad(), precision("fp32"):
+        d32 = m.encode(img.to(DEV)).latent_dist
+    e32 = max(rel_l2(d32.mean, G[f"enc_{name}_mean"]), rel_l2(d32.log_var, G[f"enc_{name}_logvar"]))
+    print(f"  fp32 parity mode: {e32:.3e}")
+    assert e32 < 1e-3
+    # the reference's call shape in the trainer (train_unet.py:502-504): .latent_dist.sample() draws on the device
+    assert tuple(dist.sample().shape) == tuple(dist.mean.shape)
+
+
+def test_vae_decode_config3_size_vs_oracle():
+    """BASELINE config 3 at size for one latent: 64 x 64 -> 512 x 512 through the AutoencoderKL-shape decoder
+    [128, 256, 512, 512] (512-wide rows, upsample2x at 256^2 / 512^2, GroupNorm over the 2 GB-class tensors' layout),
+    against the CPU oracle (about 2.4 TFLOP of fp32 convolutions: tens of seconds on the box's host cores)."""
+    from stable_diffusion_pytorch_b200.models import AutoEncoderKL, AutoencoderConfig
+    cfg = O.VaeCfg(autoencoder_channels_list=(128, 256, 512, 512), groups=32)
+    m = AutoEncoderKL(AutoencoderConfig(autoencoder_channels_list=list(cfg.autoencoder_channels_list),
+                                        groups=cfg.groups)).eval()
+    sd = O.seeded_state_dict(O.vae_decoder_param_shapes(cfg), 23)
+    m.load_state_dict(sd, strict=False)
+    m = m.to(DEV)
+    z = cases.vae_inputs(cfg, 1, 64, 64, 29)
+    with torch.no_grad():
+        y = m.decode(z.to(DEV)).float().cpu()
+        torch.set_num_threads(max(torch.get_num_threads(), 16))
+        ref = O.vae_decode(sd, cfg, z)
+    assert tuple(y.shape) == (1, 3, 512, 512)
+    e = rel_l2(y, ref)
+    print(f"vae kl-shape 64x64 -> 512x512: {e:.3e}")
+    assert e < VAE_BF16_TOL

@@ -454,3 +454,94 @@ def test_colsum_bias_and_temb_gradients(rows, cols, groups, ld_extra):
     ref = x.double().reshape(groups, rows // groups, cols).sum(1)
     assert tuple(out.shape) == (groups, cols)
     assert float((out.double() - ref).norm() / ref.norm()) < 1e-5
+
+
+def test_inference_after_train_step_uses_updated_weights():
+    """the fused AdamW kernel writes the parameters through raw pointers, so the packed bf16 copies
+    (and the cached context K/V, and sample()'s captured graphs) must be invalidated by the update itself: infer,
+    train, infer again -> the output moved and equals a fresh model loaded from the same state_dict."""
+    from stable_diffusion_pytorch_b200.models import UNetModel, UnetConfig
+    from stable_diffusion_pytorch_b200.training import FlatAdamW, GraphedTrainStep, OptimConfig, train_step
+    cfg, seed, B, H, W, n_steps, g = cases.TRAIN_CASES["tiny_8"]
+    batches, uncond = cases.train_batches(cfg, B, H, W, seed, 3)
+    ld, _ = build_ld(cfg, seed, uncond)
+    opt = FlatAdamW(ld.unet.parameters(), OptimConfig(learning_rate=1e-2))
+    x, t, ctx = cases.unet_inputs(cfg, 2, H, W, 3)
+    x, t, ctx = x.to(DEV), t.to(DEV), ctx.to(DEV)
+
+    def infer(model):
+        model.eval()
+        with torch.no_grad():
+            y = model(x, t, ctx).clone()
+            s = ld.sample(x, ctx, guidance_scale=7.5, time_steps=2, sampler="ddim").clone() if model is ld.unet else None
+        model.train()
+        return y, s
+
+    def fresh():
+        m = UNetModel(cfg.latent_channels, cfg.groups, UnetConfig(
+            num_res_blocks=cfg.num_res_blocks, n_heads=cfg.n_heads, attention_resolutions=list(cfg.attention_resolutions),
+            channels_list=list(cfg.channels_list), time_emb_dim=cfg.time_emb_dim, dropout=0.0, n_layers=cfg.n_layers,
+            context_dim=cfg.context_dim))
+        m.load_state_dict({k: v.detach().cpu().clone() for k, v in ld.unet.state_dict().items()})
+        return m.to(DEV)
+
+    y0, s0 = infer(ld.unet)
+    x_t, tt, c, nz = batches[0]
+    train_step(ld, opt, x_t.to(DEV), tt.to(DEV), c.to(DEV), nz.to(DEV), guidance_scale=g)
+    y1, s1 = infer(ld.unet)
+    assert not torch.equal(y0, y1), "inference after the update still ran on the weights packed before it"
+    assert not torch.equal(s0, s1), "sample() replayed a graph captured on the old weights"
+    assert torch.equal(y1, infer(fresh())[0])
+    # the graphed train step invalidates the same way
+    gts = GraphedTrainStep(ld, opt, B, (H, W), ctx_len=c.shape[1], ctx_dim=cfg.context_dim,
+                           latent_channels=cfg.latent_channels, guidance_scale=g)
+    x_t, tt, c, nz = batches[1]
+    gts.step(x_t.to(DEV), tt.to(DEV), c.to(DEV), nz.to(DEV))
+    y2, s2 = infer(ld.unet)
+    assert not torch.equal(y1, y2) and not torch.equal(s1, s2)
+    assert torch.equal(y2, infer(fresh())[0])
+
+
+def test_gradient_accumulation_matches_the_reference_scaling():
+    """accelerate divides every micro-loss by gradient_accumulation_steps (train_unet.py:359-366),
+    so at the boundary the clipped / applied gradient is the MEAN over the micro-batches.  Two micro-batches of B
+    must therefore give the update of one batch of 2B (MSE 'mean' over the doubled batch = mean of the two means),
+    which the oracle's train_steps computes; without the 1/accum factor the pre-clip norm doubles."""
+    from stable_diffusion_pytorch_b200.training import FlatAdamW, GraphedTrainStep, OptimConfig, train_step
+    cfg, seed, B, H, W, _, g = cases.TRAIN_CASES["tiny_8"]
+    batches, uncond = cases.train_batches(cfg, B, H, W, seed, 2)
+    merged = tuple(torch.cat([batches[0][i], batches[1][i]]) for i in range(4))
+    oc = OptimConfig(learning_rate=cases.TRAIN_LR, adam_weight_decay=cases.TRAIN_WD, max_grad_norm=cases.TRAIN_CLIP)
+    sd0 = O.seeded_state_dict(O.unet_param_shapes(cfg), seed)
+    _, ref_norms, _, ref_params = O.train_steps(sd0, cfg, [merged], uncond, g, cases.TRAIN_CLIP, cases.TRAIN_LR,
+                                                cases.TRAIN_WD)
+    for graphed in (False, True):
+        ld, sd = build_ld(cfg, seed, uncond)
+        opt = FlatAdamW(ld.unet.parameters(), oc)
+        if graphed:
+            gts = GraphedTrainStep(ld, opt, B, (H, W), ctx_len=batches[0][2].shape[1], ctx_dim=cfg.context_dim,
+                                   latent_channels=cfg.latent_channels, guidance_scale=g, accum_steps=2)
+            gts.capture()
+        for i, (x_t, t, ctx, noise) in enumerate(batches):
+            args = (x_t.to(DEV), t.to(DEV), ctx.to(DEV), noise.to(DEV))
+            if graphed:
+                gts.step(*args, sync=(i == 1))
+            else:
+                if i == 1:      # boundary: look at the norm the clip will see before the step consumes the bucket
+                    from stable_diffusion_pytorch_b200.training import diffusion_loss
+                    diffusion_loss(ld, *args, g).backward()
+                    opt.micro_steps += 1
+                    gn = float(opt.grad_norm())
+                    print(f"accumulated |g| {gn:.4f} vs oracle on the merged batch {ref_norms[0]:.4f}")
+                    assert abs(gn - ref_norms[0]) < 3e-2 * ref_norms[0]
+                    opt.step(opt.all_reduce())
+                    opt.zero_grad()
+                else:
+                    train_step(ld, opt, *args, guidance_scale=g, sync=False)
+        assert opt.step_count == 1 and opt.micro_steps == 0 or graphed
+        pd = dict(ld.unet.named_parameters())
+        for k in cases.TRAIN_PROBE:
+            delta = float((pd[k].detach().cpu() - sd[k]).norm())
+            ref = float((ref_params[k] - sd[k]).norm())
+            print(f"  accumulation ({'graphed' if graphed else 'eager'}) update {k}: |delta| {delta:.3e} vs {ref:.3e}")
+            assert abs(delta - ref) < 3e-2 * ref, k
