@@ -156,7 +156,11 @@ int sdb_gemm(const SdbGemmArgs* args, void* stream);
  * residual NHWC (resnet2d.py:238).
  * down2 = 1: conv followed by nearest x0.5 (resnet2d.py:122-123) == keep even rows/cols.
  * up2 = 1:   nearest x2 THEN conv (resnet2d.py:61-62); x is the low-res tensor [B,H,W,Cin],
- *            out is [B,2H,2W,Cout]. */
+ *            out is [B,2H,2W,Cout] (residual, if any, likewise).  Runs as four 2x2-tap "phase" convolutions
+ *            (4/9 of the flops, no 4x tensor): w must then be the PHASE-COLLAPSED weights bf16
+ *            [4][Cout][2][2][Cin], phase 2a+b = output pixels (2y+a, 2x+b), taps over source rows
+ *            {y-1,y} (a = 0) / {y,y+1} (a = 1) and the same for columns, each the fp32 sum of the 3x3
+ *            taps that fall on that source pixel.  sdb_conv3x3_f32 takes the plain 3x3 weights. */
 typedef struct SdbConvArgs {
   const void* x; const void* w; const float* bias;
   const float* temb; int64_t ld_temb;          /* fp32 [B, ld_temb] or NULL                    */

@@ -137,6 +137,21 @@ def conv3x3_w(p: Tensor) -> Tensor:
     return d(p).permute(0, 2, 3, 1).to(_COMPUTE).contiguous()
 
 
+def conv3x3_up_w(p: Tensor) -> Tensor:
+    """OIHW [Cout, Cin, 3, 3] -> phase-collapsed weights of ``UpSample`` (nearest x2 then conv3x3, resnet2d.py:61-62),
+    [4, Cout, 2, 2, Cin] in the compute dtype.  Output pixel (2y+a, 2x+b) of the upsampled conv reads source rows
+    {y-1, y} when a = 0 (3x3 rows {0}, {1, 2}) and {y, y+1} when a = 1 (rows {0, 1}, {2}); columns likewise.  The taps
+    that fall on the same source pixel are summed in fp32, then rounded once."""
+    w = d(p).to(torch.float32)
+    sets = (([0], [1, 2]), ([0, 1], [2]))
+    phases = []
+    for a in range(2):
+        for b in range(2):
+            taps = [[sum(w[:, :, ky, kx] for ky in sets[a][i] for kx in sets[b][j]) for j in range(2)] for i in range(2)]
+            phases.append(torch.stack([torch.stack(r, dim=1) for r in taps], dim=1))      # [Cout, 2, 2, Cin]
+    return torch.stack(phases).to(_COMPUTE).contiguous()
+
+
 def geglu_w(w: Tensor, b: Tensor) -> Tuple[Tensor, Tensor]:
     """GEGLU proj [2*F, C] with halves (a | gate) -> rows interleaved in pairs (a0, a1, g0, g1, a2, a3, g2, g3,
     ...) so one accumulator tile holds both operands of a_j * gelu(g_j) and the epilogue's packed fp32x2

@@ -35,7 +35,7 @@ __device__ __forceinline__ void tmem_ld_32x32_at64(uint32_t taddr, uint32_t (&v)
 
 // kPoly = element pairs out of every 8 exponentiated on the FMA pipe; kCtas = CTAs resident per SM (3 or 4);
 // kSpread = the polynomial pairs are spread over the group of 8 instead of leading it (1.105 -> 1.085 ms at kPoly = 2)
-template <int kPoly, int kCtas, bool kSpread>
+template <int kPoly, int kCtas, bool kSpread, int kDbg = 0>
 __global__ void __launch_bounds__(kF1Threads, kCtas) attention_umma_wg1_kernel(const __grid_constant__ FaParams p) {
   constexpr int kStages = f1_stages(kCtas);
   constexpr int kRowRegs = kCtas >= 4 ? 104 : 136;
@@ -162,7 +162,7 @@ __global__ void __launch_bounds__(kF1Threads, kCtas) attention_umma_wg1_kernel(c
       tmem_ld_wait();
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(bar_s_free);
+      if (!(kDbg & 4) && lane == 0) mbar_arrive(bar_s_free);
       if (j == T - 1 && (p.m & (kF1BN - 1)) != 0) {     // ragged key tail
         const int valid = p.m - j * kF1BN;
 #pragma unroll
@@ -170,13 +170,21 @@ __global__ void __launch_bounds__(kF1Threads, kCtas) attention_umma_wg1_kernel(c
           if (i >= valid) su[i] = 0xff800000u;
       }
       float mx[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+      if (kDbg & 2) {
+        mx[0] = __uint_as_float(su[0]);
+      } else {
 #pragma unroll
-      for (int i = 0; i < 64; i += 8) {
+        for (int i = 0; i < 64; i += 8) {
 #pragma unroll
-        for (int k = 0; k < 4; ++k)
-          mx[k] = max3(mx[k], __uint_as_float(su[i + 2 * k]), __uint_as_float(su[i + 2 * k + 1]));
+          for (int k = 0; k < 4; ++k)
+            mx[k] = max3(mx[k], __uint_as_float(su[i + 2 * k]), __uint_as_float(su[i + 2 * k + 1]));
+        }
       }
       const float m_tile = fmaxf(fmaxf(mx[0], mx[1]), fmaxf(mx[2], mx[3]));
+      if (kDbg & 4) {
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar_s_free);
+      }
       if (j > 0) {
         if (ok) ok = mbar_wait(bar_o_full, par ^ 1u);
         tc_fence_after();
@@ -210,7 +218,11 @@ __global__ void __launch_bounds__(kF1Threads, kCtas) attention_umma_wg1_kernel(c
           for (int k = 0; k < 8; ++k) {
             const int i = ch * 32 + g * 16 + 2 * k;
             float x0, x1;
-            ffma2(x0, x1, __uint_as_float(su[i]), __uint_as_float(su[i + 1]), c, c, negm, negm);
+            if (kDbg & 1) {
+              x0 = __uint_as_float(su[i]) ; x1 = __uint_as_float(su[i + 1]);
+            } else {
+              ffma2(x0, x1, __uint_as_float(su[i]), __uint_as_float(su[i + 1]), c, c, negm, negm);
+            }
             if (kSpread ? ((k * kPoly) % 8 < kPoly) : (k < kPoly)) {
               ex2_poly2(x0, x1);
             } else {
@@ -263,17 +275,17 @@ __global__ void __launch_bounds__(kF1Threads, kCtas) attention_umma_wg1_kernel(c
   }
 }
 
-template <int kPoly, int kCtas, bool kSpread = false>
+template <int kPoly, int kCtas, bool kSpread = false, int kDbg = 0>
 static int launch_attention_wg1(const FaParams& p, dim3 grid, cudaStream_t stream) {
   static bool attr_set[64] = {false};
   int dev = 0;
   SDB_CUDA_OK(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-    SDB_CUDA_OK(cudaFuncSetAttribute(attention_umma_wg1_kernel<kPoly, kCtas, kSpread>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    SDB_CUDA_OK(cudaFuncSetAttribute(attention_umma_wg1_kernel<kPoly, kCtas, kSpread, kDbg>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      f1_smem(kCtas)));
     if (dev >= 0 && dev < 64) attr_set[dev] = true;
   }
-  attention_umma_wg1_kernel<kPoly, kCtas, kSpread><<<grid, kF1Threads, f1_smem(kCtas), stream>>>(p);
+  attention_umma_wg1_kernel<kPoly, kCtas, kSpread, kDbg><<<grid, kF1Threads, f1_smem(kCtas), stream>>>(p);
   return SDB_OK;
 }
 

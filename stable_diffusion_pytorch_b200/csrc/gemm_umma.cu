@@ -47,7 +47,9 @@ struct UmmaParams {
   int kb_per_tap, Cin;
   int TW, TH, TN, tiles_w, tiles_h;
   int B, H, W;
-  int out_mode;  // 0 = same resolution, 1 = keep even rows/cols (conv then nearest x0.5)
+  int out_mode;  // 0 = same resolution, 1 = keep even rows/cols (conv then nearest x0.5),
+                 // 2 = phase (ph_a, ph_b) of a nearest-x2 upsampled output: pixel (h, w) -> (2h + ph_a, 2w + ph_b)
+  int ph_a, ph_b;
   signed char tap_map[9], tap_dh[9], tap_dw[9];
   // epilogue
   int M, N;
@@ -619,6 +621,8 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
         img = (m_tile / (p.tiles_w * p.tiles_h)) * p.TN + tn;
         if (img < p.B && h < p.H && w < p.W) {
           if (p.out_mode == 0) out_row = ((long long)img * p.H + h) * p.W + w;
+          else if (p.out_mode == 2)
+            out_row = ((long long)img * (2 * p.H) + 2 * h + p.ph_a) * (2 * p.W) + 2 * w + p.ph_b;
           else if (((h | w) & 1) == 0)
             out_row = ((long long)img * (p.H >> 1) + (h >> 1)) * (p.W >> 1) + (w >> 1);
         }
@@ -919,13 +923,27 @@ extern "C" int sdb_conv3x3(const SdbConvArgs* a, void* stream) {
   SDB_CHECK_ARG(a->B > 0 && a->H > 0 && a->W > 0, "conv3x3: bad shape");
   SDB_CHECK_ARG(a->Cin % 8 == 0 && a->Cin >= 16, "conv3x3: Cin (%d) must be a multiple of 8, >= 16 (use sdb_conv3x3_in)", a->Cin);
   SDB_CHECK_ARG(a->Cout % 16 == 0, "conv3x3: Cout (%d) must be a multiple of 16 (use sdb_conv3x3_out)", a->Cout);
-  SDB_CHECK_ARG(!a->up2, "conv3x3: fused up2 not built; call sdb_upsample2x first");
+  SDB_CHECK_ARG(!(a->up2 && a->down2), "conv3x3: up2 and down2 are exclusive");
+  SDB_CHECK_ARG(!(a->up2 && a->temb), "conv3x3: up2 takes no time embedding");
   SDB_CHECK_ARG(!a->down2 || (a->H % 2 == 0 && a->W % 2 == 0), "conv3x3: down2 needs even H, W");
   SDB_CHECK_ARG(((uintptr_t)a->x & 15) == 0 && ((uintptr_t)a->w & 15) == 0 && ((uintptr_t)a->out & 15) == 0 &&
                     ((uintptr_t)a->residual & 15) == 0 && ((uintptr_t)a->bias & 15) == 0 &&
                     ((uintptr_t)a->temb & 15) == 0 && a->ld_temb % 4 == 0,
                 "conv3x3: pointers must be 16-byte aligned");
 
+  // up2: nearest x2 THEN conv (resnet2d.py:61-62) without the 4x tensor.  Output pixel (2y+a, 2x+b) sees only a
+  // 2x2 neighbourhood of the low-resolution input -- rows {y-1, y} for a = 0, {y, y+1} for a = 1, same for the
+  // columns -- with the 3x3 taps that land on the same source pixel summed.  So the layer is four convolutions
+  // with 2x2 taps ("phases"), 4/9 of the flops, each writing its own interleaved quarter of the output through
+  // a strided TMA store.  `w` then holds the phase-collapsed weights [4 phases = 2a+b][Cout][2][2][Cin]
+  // (taps summed in fp32 before the bf16 rounding: _pack.conv3x3_up_w).
+  const int n_phase = a->up2 ? 4 : 1;
+  const int n_tap = a->up2 ? 4 : 9;
+  for (int phase = 0; phase < n_phase; ++phase) {
+  const int ph_a = phase >> 1, ph_b = phase & 1;
+  const __nv_bfloat16* wph = reinterpret_cast<const __nv_bfloat16*>(a->w) + (size_t)phase * a->Cout * n_tap * a->Cin;
+  const int Wo = a->up2 ? 2 * a->W : a->W, Ho = a->up2 ? 2 * a->H : a->H;
+  const size_t ph_off = a->up2 ? ((size_t)ph_a * Wo + ph_b) * a->Cout : 0;
   UmmaParams p;
   memset(&p, 0, sizeof(p));
   p.mode = 1;
@@ -935,7 +953,7 @@ extern "C" int sdb_conv3x3(const SdbConvArgs* a, void* stream) {
   plan_staging(p, a->out_dtype == SDB_BF16, !a->residual || a->res_dtype == SDB_BF16, !a->down2);
   p.Cin = a->Cin;
   p.kb_per_tap = (a->Cin + p.BK - 1) / p.BK;
-  p.num_kb = 9 * p.kb_per_tap;
+  p.num_kb = n_tap * p.kb_per_tap;
   // tile = TW x TH x TN pixels with TW*TH*TN = 128, all powers of two.  TW = the largest power-of-two factor
   // of W when that is >= 8 (no waste); otherwise the width in {8..128} that wastes the fewest clipped
   // columns (the TMA unit zero-fills the loads and clips the stores of a box that overhangs the image).
@@ -966,11 +984,17 @@ extern "C" int sdb_conv3x3(const SdbConvArgs* a, void* stream) {
   finish_stages(p);
   p.temb_in_bias = (a->temb && tn == 1) ? 1 : 0;
   p.B = a->B; p.H = a->H; p.W = a->W;
-  p.out_mode = a->down2 ? 1 : 0;
-  for (int t = 0; t < 9; ++t) {
+  p.out_mode = a->down2 ? 1 : (a->up2 ? 2 : 0);
+  p.ph_a = ph_a; p.ph_b = ph_b;
+  for (int t = 0; t < n_tap; ++t) {
     p.tap_map[t] = 0;
-    p.tap_dh[t] = (signed char)(t / 3 - 1);
-    p.tap_dw[t] = (signed char)(t % 3 - 1);
+    if (a->up2) {
+      p.tap_dh[t] = (signed char)(ph_a - 1 + t / 2);
+      p.tap_dw[t] = (signed char)(ph_b - 1 + t % 2);
+    } else {
+      p.tap_dh[t] = (signed char)(t / 3 - 1);
+      p.tap_dw[t] = (signed char)(t % 3 - 1);
+    }
   }
   p.M = 0;
   p.N = a->Cout;
@@ -991,17 +1015,23 @@ extern "C" int sdb_conv3x3(const SdbConvArgs* a, void* stream) {
   uint32_t box[4] = {(uint32_t)p.BK, (uint32_t)tw, (uint32_t)th, (uint32_t)tn};
   int rc = sdb_make_tensor_map(&p.tmA[0], a->x, 2, 4, dims, strides, box, p.swz);
   if (rc) return rc;
-  uint64_t wd[2] = {(uint64_t)9 * a->Cin, (uint64_t)a->Cout};
-  uint64_t ws[2] = {0, (uint64_t)9 * a->Cin * 2};
+  uint64_t wd[2] = {(uint64_t)n_tap * a->Cin, (uint64_t)a->Cout};
+  uint64_t ws[2] = {0, (uint64_t)n_tap * a->Cin * 2};
   uint32_t wb[2] = {(uint32_t)p.BK, (uint32_t)p.BN};
-  rc = sdb_make_tensor_map(&p.tmB, a->w, 2, 2, wd, ws, wb, p.swz);
+  rc = sdb_make_tensor_map(&p.tmB, wph, 2, 2, wd, ws, wb, p.swz);
   if (rc) return rc;
   if (p.staged) {
+    // the output box of a phase lands on every second pixel of every second row: strides doubled, base shifted
+    const uint64_t ps = a->up2 ? 2 : 1;
     uint64_t od[4] = {(uint64_t)a->Cout, (uint64_t)a->W, (uint64_t)a->H, (uint64_t)a->B};
-    uint64_t so[4] = {0, (uint64_t)a->Cout * 2, (uint64_t)a->W * a->Cout * 2, (uint64_t)a->H * a->W * a->Cout * 2};
+    uint64_t so[4] = {0, ps * a->Cout * 2, ps * Wo * a->Cout * 2, (uint64_t)Ho * Wo * a->Cout * 2};
     uint32_t rows[3] = {(uint32_t)tw, (uint32_t)th, (uint32_t)tn};
-    rc = make_slab_maps(p, a->out, a->residual, 4, od, so, so, rows);
+    const void* res_ph = a->residual ? (const void*)(reinterpret_cast<const __nv_bfloat16*>(a->residual) + ph_off) : nullptr;
+    rc = make_slab_maps(p, reinterpret_cast<__nv_bfloat16*>(a->out) + ph_off, res_ph, 4, od, so, so, rows);
     if (rc) return rc;
   }
-  return launch_umma(p, sdb_stream(stream));
+  rc = launch_umma(p, sdb_stream(stream));
+  if (rc) return rc;
+  }  // phases
+  return SDB_OK;
 }

@@ -54,8 +54,13 @@ class UpSample(_NhwcModule):
     def forward_nhwc(self, x: Tensor) -> Tensor:
         assert x.shape[-1] == self.in_channels, (
             f"input channel does not match: x.shape[1]({x.shape[-1]}) != self.in_channels({self.in_channels}))")
-        w = self._cache.get("w", [self.conv.weight], lambda: _pack.conv3x3_w(self.conv.weight))
         b = self._cache.get("b", [self.conv.bias], lambda: _pack.f32(self.conv.bias))
+        if x.dtype == torch.bfloat16 and not _pack.in_graph_mode() and not (torch.is_grad_enabled() and x.requires_grad):
+            # inference: the upsampling is folded into the conv as four 2x2-tap phase convolutions (4/9 of the
+            # flops, no 4x tensor written and re-read)
+            wp = self._cache.get("wup", [self.conv.weight], lambda: _pack.conv3x3_up_w(self.conv.weight))
+            return ops.conv3x3(x, wp, b, up2=True)
+        w = self._cache.get("w", [self.conv.weight], lambda: _pack.conv3x3_w(self.conv.weight))
         return ops.conv3x3(ops.upsample2x(x), w, b)
 
     def forward(self, x: Tensor) -> Tensor:

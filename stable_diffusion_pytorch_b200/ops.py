@@ -212,16 +212,22 @@ def gemm(a: Tensor, w: Tensor, bias: Optional[Tensor] = None, residual: Optional
 
 def conv3x3(x: Tensor, w: Tensor, bias: Optional[Tensor], temb: Optional[Tensor] = None,
             residual: Optional[Tensor] = None, down2: bool = False, out_dtype=None,
-            out: Optional[Tensor] = None) -> Tensor:
-    """3x3 / pad 1 convolution, NHWC bf16 ``x`` [B,H,W,Cin], ``w`` bf16 [Cout,3,3,Cin]."""
+            out: Optional[Tensor] = None, up2: bool = False) -> Tensor:
+    """3x3 / pad 1 convolution, NHWC bf16 ``x`` [B,H,W,Cin], ``w`` bf16 [Cout,3,3,Cin].
+    ``up2``: nearest x2 upsampling folded in -- ``x`` is the low-resolution tensor, the result is [B,2H,2W,Cout] and
+    ``w`` the phase-collapsed weights [4,Cout,2,2,Cin] of ``_pack.conv3x3_up_w`` (bf16 tensor-core path only)."""
     if _ag.wants(x, w, bias, temb, residual):
         _no_f32_grad(x)
+        assert not up2, "conv3x3(up2=True) is inference-only: under autograd use upsample2x + conv3x3"
         return _ag.conv3x3(x, w, bias, temb, residual, down2, out_dtype)
     B, H, W, Cin = x.shape
-    Cout = w.shape[0]
+    Cout = w.shape[1] if up2 else w.shape[0]
     assert x.is_contiguous() and w.is_contiguous() and x.dtype in (torch.bfloat16, torch.float32) and w.dtype == x.dtype
-    assert tuple(w.shape) == (Cout, 3, 3, Cin)
-    Ho, Wo = (H // 2, W // 2) if down2 else (H, W)
+    if up2:
+        assert x.dtype == torch.bfloat16 and tuple(w.shape) == (4, Cout, 2, 2, Cin) and not down2 and temb is None
+    else:
+        assert tuple(w.shape) == (Cout, 3, 3, Cin)
+    Ho, Wo = (H // 2, W // 2) if down2 else ((2 * H, 2 * W) if up2 else (H, W))
     if out is None:
         out = torch.empty(B, Ho, Wo, Cout, device=x.device, dtype=out_dtype or x.dtype)
     a = SdbConvArgs()
@@ -238,7 +244,7 @@ def conv3x3(x: Tensor, w: Tensor, bias: Optional[Tensor], temb: Optional[Tensor]
         a.residual, a.res_dtype = None, 0
     a.out, a.out_dtype = _ptr(out), _dt(out)
     a.B, a.H, a.W, a.Cin, a.Cout = B, H, W, Cin, Cout
-    a.down2, a.up2 = int(down2), 0
+    a.down2, a.up2 = int(down2), int(up2)
     fn = _lib.lib().sdb_conv3x3_f32 if x.dtype == torch.float32 else _lib.lib().sdb_conv3x3
     check(fn(C.byref(a), _stream()), "conv3x3")
     return out

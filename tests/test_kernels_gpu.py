@@ -137,6 +137,45 @@ def test_conv3x3(B, H, W, Cin, Cout, has_temb, has_res, down2):
     assert rel_l2(outb.float(), ref) < 4e-3
 
 
+UP_CASES = [
+    # B, H, W, Cin, Cout, residual   (low-resolution input H x W -> 2H x 2W)
+    (1, 8, 8, 64, 64, False),
+    (2, 32, 32, 320, 320, False),     # the UNet's UpSample (config 2 runs it at B = 32)
+    (2, 16, 16, 160, 96, True),       # K tail (160 = 2.5 k-blocks), residual at the output resolution
+    (3, 6, 10, 64, 32, False),        # ragged: clipped boxes, W without a power-of-two factor >= 8
+    (1, 64, 64, 512, 512, False),     # VAE decoder shape: BN = 256, two N tiles
+    (1, 4, 4, 32, 48, True),
+]
+
+
+@pytest.mark.parametrize("B,H,W,Cin,Cout,has_res", UP_CASES)
+def test_conv3x3_up2_phase_collapsed(B, H, W, Cin, Cout, has_res):
+    """UpSample (resnet2d.py:46-63: nearest x2 THEN conv3x3) as four 2x2-tap phase convolutions over the
+    low-resolution tensor, against F.interpolate + F.conv2d on the same bf16-rounded inputs.  The collapsed weights
+    are sums of up to four bf16 taps rounded once more to bf16: rel-L2 stays at the bf16 level."""
+    from stable_diffusion_pytorch_b200 import _pack
+    x = rnd(B, H, W, Cin, seed=1)
+    w_oihw = rnd(Cout, Cin, 3, 3, seed=2, scale=1 / math.sqrt(9 * Cin), dtype=torch.float32)
+    bias = rnd(Cout, seed=3, dtype=torch.float32)
+    res = rnd(B, 2 * H, 2 * W, Cout, seed=5) if has_res else None
+    wp = _pack.conv3x3_up_w(w_oihw)
+    assert tuple(wp.shape) == (4, Cout, 2, 2, Cin) and wp.dtype == torch.bfloat16
+    ref = F.conv2d(F.interpolate(x.float().permute(0, 3, 1, 2), scale_factor=2, mode="nearest"), w_oihw, bias,
+                   padding=1).permute(0, 2, 3, 1)
+    # exact-arithmetic check of the collapse itself: the same phases evaluated by torch in fp32
+    if has_res:
+        ref = ref + res.float()
+    for odt, tol in ((torch.float32, 6e-3), (torch.bfloat16, 8e-3)):
+        out = ops.conv3x3(x, wp, bias, None, res, up2=True, out_dtype=odt)
+        assert out.dtype == odt and tuple(out.shape) == (B, 2 * H, 2 * W, Cout)
+        e = rel_l2(out.float(), ref)
+        assert e < tol, (odt, e)
+    # and against the un-fused route of the same library (upsample2x kernel + 3x3 conv): same answer to bf16 noise
+    w9 = w_oihw.permute(0, 2, 3, 1).to(torch.bfloat16).contiguous()
+    unf = ops.conv3x3(ops.upsample2x(x), w9, bias, None, res, out_dtype=torch.float32)
+    assert rel_l2(ops.conv3x3(x, wp, bias, None, res, up2=True, out_dtype=torch.float32), unf) < 8e-3
+
+
 def test_conv_small_in_out():
     B, H, W = 2, 24, 40
     x = rnd(B, 4, H, W, seed=1, dtype=torch.float32)
