@@ -35,6 +35,7 @@ extern "C" {
 
 #define SDB_F32 0
 #define SDB_BF16 1
+#define SDB_U8 2   /* output only: sdb_conv3x3 image head, see SdbConvArgs.out_channels */
 
 #define SDB_ACT_NONE 0
 #define SDB_ACT_SILU 1  /* x*sigmoid(x) on the result                                          */
@@ -120,6 +121,22 @@ int sdb_groupnorm_stats(const void* x1, int C1, const void* x2, int C2, int dtyp
 #define SDB_GN_STATIC_SCRATCH_FLOATS (1u << 20)
 int sdb_groupnorm_stats_static(const void* x1, int C1, const void* x2, int C2, int dtype, int B,
                                int64_t hw, int groups, float eps, float* stats, void* stream);
+/* GroupNorm(+SiLU) in ONE pass (same reference lines): a thread-block cluster per image keeps the image in shared
+ * memory, sums it as it lands, exchanges the per-group sums over distributed shared memory and normalises out of
+ * shared memory -- one HBM read and one write instead of two reads and one write in three launches.  bf16 in, bf16
+ * dense NHWC out (C1+C2 channels).  SDB_EUNSUPPORTED when the image does not fit the shared memory of a cluster of
+ * <= 16 CTAs (about 3 MB of bf16 per image): use sdb_groupnorm_stats + sdb_groupnorm_apply then. */
+int sdb_groupnorm_fused(const void* x1, int C1, const void* x2, int C2, const float* gamma, const float* beta,
+                        int act, void* out, int B, int64_t hw, int groups, float eps, void* stream);
+/* GroupNorm(+SiLU) in ONE launch for any image size (same reference lines): a persistent kernel streams the tensor
+ * for the statistics, crosses a device-wide barrier (cooperative launch) and streams it again -- out of L2 when the
+ * tensor fits there -- to write the normalised bf16 output.  `partial`: fp32 scratch of
+ * sdb_groupnorm_coop_scratch(B, hw, groups) floats; `bar`: two uint32 words, zero before the first call, reusable
+ * by later calls that do not overlap this one on the GPU. */
+int64_t sdb_groupnorm_coop_scratch(int B, int64_t hw, int groups);
+int sdb_groupnorm_coop(const void* x1, int C1, const void* x2, int C2, const float* gamma, const float* beta, int act,
+                       void* out, int B, int64_t hw, int groups, float eps, float* partial, uint32_t* bar,
+                       void* stream);
 /* out[b,p,c] = act((x-mean)*rstd*gamma[c]+beta[c]); act = SDB_ACT_NONE | SDB_ACT_SILU.
  * out is a dense NHWC tensor with C1+C2 channels, dtype out_dtype. */
 int sdb_groupnorm_apply(const void* x1, int C1, const void* x2, int C2, int dtype,
@@ -168,6 +185,11 @@ typedef struct SdbConvArgs {
   void* out; int out_dtype;
   int B, H, W, Cin, Cout;
   int down2; int up2;
+  /* out_dtype = SDB_U8 (the decoder's image head, models/utils.py:197 followed by the reference's `detransform`,
+   * utils/prepare_dataset.py:145-150, in the conv epilogue): out is uint8 NHWC [B,H,W,out_channels] holding
+   * trunc(clip((y + 1) / 2, 0, 1) * 255) of the first out_channels <= 16 = Cout output channels (the head's Cout is
+   * padded to 16 for the tensor cores).  No residual, no down2 / up2.  Ignored for other out dtypes. */
+  int out_channels;
 } SdbConvArgs;
 int sdb_conv3x3(const SdbConvArgs* args, void* stream);
 

@@ -53,6 +53,7 @@ class DdpmCfg:
     noise_steps: int = 1000
     beta_start: float = 1e-4
     beta_end: float = 0.02
+    noise_schedule: str = "linear"      # the reference builds "linear" whatever this says (scheduler.py:89-93)
 
 
 # ----------------------------------------------------------------------------
@@ -453,10 +454,25 @@ TABLE_NAMES = ("betas", "alpha", "alphas_cumprod", "sqrt_alpha_bar", "sqrt_1m_al
                "mean_xt_coef")
 
 
+def noise_schedule_betas(cfg: DdpmCfg) -> Tensor:
+    """"linear": models/scheduler.py:89-93.  "cosine" / "cubic" are advertised by DDPMConfig (:11-17) but never built
+    by the reference -- restated here from their published definitions (Nichol & Dhariwal 2021, eq. 17; the cube-root
+    analogue of the scaled-linear schedule), "parity unpinned"."""
+    T = cfg.noise_steps
+    if cfg.noise_schedule == "linear":
+        return torch.linspace(cfg.beta_start, cfg.beta_end, T)
+    if cfg.noise_schedule == "cosine":
+        f = [math.cos(((i / T) + 0.008) / 1.008 * math.pi / 2) ** 2 for i in range(T + 1)]
+        return torch.tensor([min(1 - f[i + 1] / f[i], 0.999) for i in range(T)], dtype=torch.float32)
+    if cfg.noise_schedule == "cubic":
+        return torch.linspace(cfg.beta_start ** (1 / 3), cfg.beta_end ** (1 / 3), T) ** 3
+    raise ValueError(cfg.noise_schedule)
+
+
 def ddpm_tables(cfg: DdpmCfg) -> Dict[str, Tensor]:
     """models/scheduler.py:52-93: fp32 CPU tables built with the same torch ops, same order."""
     T = cfg.noise_steps
-    betas = torch.linspace(cfg.beta_start, cfg.beta_end, T)
+    betas = noise_schedule_betas(cfg)
     alpha = 1.0 - betas
     ac = torch.cumprod(alpha, dim=0)
     ac_prev = torch.cat([ac.new_tensor([1.0]), ac[:-1]])

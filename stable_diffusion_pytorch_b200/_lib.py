@@ -11,7 +11,7 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libsdb200.so")
 
-SDB_F32, SDB_BF16 = 0, 1
+SDB_F32, SDB_BF16, SDB_U8 = 0, 1, 2
 ACT_NONE, ACT_SILU, ACT_GEGLU = 0, 1, 2
 
 _p, _i, _i64, _f, _u64 = C.c_void_p, C.c_int, C.c_int64, C.c_float, C.c_uint64
@@ -32,7 +32,7 @@ class SdbConvArgs(C.Structure):
                 ("residual", _p), ("res_dtype", _i),
                 ("out", _p), ("out_dtype", _i),
                 ("B", _i), ("H", _i), ("W", _i), ("Cin", _i), ("Cout", _i),
-                ("down2", _i), ("up2", _i)]
+                ("down2", _i), ("up2", _i), ("out_channels", _i)]
 
 
 # name -> (restype, argtypes); must list every symbol include/sdb200.h declares
@@ -50,6 +50,9 @@ SIGNATURES = {
     "sdb_groupnorm_chunks": (_i, [_i64]),
     "sdb_groupnorm_stats": (_i, [_p, _i, _p, _i, _i, _i, _i64, _i, _f, _p, _p, _p]),
     "sdb_groupnorm_stats_static": (_i, [_p, _i, _p, _i, _i, _i, _i64, _i, _f, _p, _p]),
+    "sdb_groupnorm_fused": (_i, [_p, _i, _p, _i, _p, _p, _i, _p, _i, _i64, _i, _f, _p]),
+    "sdb_groupnorm_coop_scratch": (_i64, [_i, _i64, _i]),
+    "sdb_groupnorm_coop": (_i, [_p, _i, _p, _i, _p, _p, _i, _p, _i, _i64, _i, _f, _p, _p, _p]),
     "sdb_groupnorm_apply": (_i, [_p, _i, _p, _i, _i, _p, _p, _p, _i, _p, _i, _i, _i64, _i, _p]),
     "sdb_add_layernorm": (_i, [_p, _p, _p, _p, _p, _i64, _i, _f, _i, _p]),
     "sdb_gemm": (_i, [C.POINTER(SdbGemmArgs), _p]),

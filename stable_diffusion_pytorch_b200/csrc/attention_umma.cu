@@ -371,6 +371,8 @@ static int attention_p32_impl(const void* q, int64_t ldq, const void* k, int64_t
     else if (dbg == 3) rc = launch_attention_wg1<2, 4, true, 3>(p, grid1, sdb_stream(stream));
     else if (dbg == 4) rc = launch_attention_wg1<2, 4, true, 4>(p, grid1, sdb_stream(stream));
     else if (dbg == 5) rc = launch_attention_wg1<2, 4, true, 5>(p, grid1, sdb_stream(stream));
+    else if (dbg == 8) rc = launch_attention_wg1<2, 4, true, 8>(p, grid1, sdb_stream(stream));
+    else if (dbg == 24) rc = launch_attention_wg1<2, 4, true, 24>(p, grid1, sdb_stream(stream));
     else if (dbg == 11) rc = launch_attention_wg1<1, 4, true, 1>(p, grid1, sdb_stream(stream));
     else if (dbg == 13) rc = launch_attention_wg1<3, 4, true, 1>(p, grid1, sdb_stream(stream));
     else

@@ -92,7 +92,8 @@ __global__ void __launch_bounds__(kF1Threads, kCtas) attention_umma_wg1_kernel(c
       bool ok = true;
       for (int j = 0; j < T && ok; ++j) {
         const int s = j % kStages;
-        ok = mbar_wait(bar_kv_empty(s), (((uint32_t)(j / kStages)) & 1u) ^ 1u);
+        ok = (kDbg & 8) ? mbar_wait_sleep(bar_kv_empty(s), (((uint32_t)(j / kStages)) & 1u) ^ 1u, 256)
+                        : mbar_wait(bar_kv_empty(s), (((uint32_t)(j / kStages)) & 1u) ^ 1u);
         if (!ok) break;
         const uint32_t sk = sKV + (uint32_t)s * kF1StageBytes;
         mbar_arrive_expect_tx(bar_kv_full(s), kF1StageBytes);
@@ -128,7 +129,7 @@ __global__ void __launch_bounds__(kF1Threads, kCtas) attention_umma_wg1_kernel(c
           tc_fence_after();
           issue_s(sn);
         }
-        ok = mbar_wait(bar_p_full, par);
+        ok = (kDbg & 16) ? mbar_wait_sleep(bar_p_full, par, 32) : mbar_wait(bar_p_full, par);
         if (!ok) break;
         tc_fence_after();
         const uint64_t vdesc = umma_smem_desc_mn64(sKV + (uint32_t)s * kF1StageBytes + kF1KVBytes);

@@ -193,6 +193,26 @@ __device__ __forceinline__ bool mbar_wait(uint32_t bar, uint32_t parity) {
   return true;
 }
 
+// mbar_wait for warps with slack (producers that run several stages ahead): polls with a sleep in between so the
+// polling does not take issue slots from the compute warps on the same SM sub-partition
+__device__ __forceinline__ bool mbar_wait_sleep(uint32_t bar, uint32_t parity, uint32_t ns) {
+  if (mbar_try_wait(bar, parity)) return true;
+  uint64_t t0 = 0;
+  uint32_t spins = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    __nanosleep(ns);
+    if ((++spins & 0x3ff) == 0) {
+      uint64_t now = globaltimer_ns();
+      if (t0 == 0) t0 = now;
+      if (now - t0 > 2000000000ull) {
+        atomicExch(&g_sdb_timeout_flag, 1);
+        return false;
+      }
+    }
+  }
+  return true;
+}
+
 // ---- TMA ------------------------------------------------------------------------------------
 __device__ __forceinline__ void prefetch_tmap(const void* tmap) {
   asm volatile("prefetch.tensormap [%0];" ::"l"(reinterpret_cast<uint64_t>(tmap)) : "memory");

@@ -63,6 +63,7 @@ struct UmmaParams {
   void* out;
   long long ldo;
   int out_dtype;
+  int u8_channels;   // SDB_U8 output: channels kept per pixel
   int act;
   // staged epilogue (bf16 output through swizzled smem slabs + TMA store): 0 = direct stores
   int staged;
@@ -219,6 +220,20 @@ __device__ __forceinline__ void epilogue16_direct(const UmmaParams& p, const uin
   float v[16];
   add_bias16(v, acc, bias_s + 4u * tcol);
   const int col = n0 + tcol;
+  if (p.out_dtype == SDB_U8) {
+    // image head: utils/prepare_dataset.py:145-150 -- (x + 1) / 2, clip to [0, 1], * 255, truncate -- on the fp32
+    // accumulator, same arithmetic as to_uint8_kernel; uint8 NHWC with only the real channels
+    uint8_t* d = reinterpret_cast<uint8_t*>(p.out) + out_row * p.u8_channels;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      if (col + j < p.u8_channels) {
+        float y = (v[j] + 1.0f) / 2.0f;
+        y = fminf(fmaxf(y, 0.0f), 1.0f);
+        d[col + j] = (uint8_t)(y * 255.0f);
+      }
+    }
+    return;
+  }
   if (temb_row) {
 #pragma unroll
     for (int j = 0; j < 16; j += 4) {
@@ -924,6 +939,9 @@ extern "C" int sdb_conv3x3(const SdbConvArgs* a, void* stream) {
   SDB_CHECK_ARG(a->Cin % 8 == 0 && a->Cin >= 16, "conv3x3: Cin (%d) must be a multiple of 8, >= 16 (use sdb_conv3x3_in)", a->Cin);
   SDB_CHECK_ARG(a->Cout % 16 == 0, "conv3x3: Cout (%d) must be a multiple of 16 (use sdb_conv3x3_out)", a->Cout);
   SDB_CHECK_ARG(!(a->up2 && a->down2), "conv3x3: up2 and down2 are exclusive");
+  SDB_CHECK_ARG(a->out_dtype != SDB_U8 || (a->Cout == 16 && a->out_channels > 0 && a->out_channels <= 16 && !a->residual &&
+                                           !a->down2 && !a->up2 && !a->temb),
+                "conv3x3: uint8 output is the image head only (Cout padded to 16, 1 <= out_channels <= 16, no residual)");
   SDB_CHECK_ARG(!(a->up2 && a->temb), "conv3x3: up2 takes no time embedding");
   SDB_CHECK_ARG(!a->down2 || (a->H % 2 == 0 && a->W % 2 == 0), "conv3x3: down2 needs even H, W");
   SDB_CHECK_ARG(((uintptr_t)a->x & 15) == 0 && ((uintptr_t)a->w & 15) == 0 && ((uintptr_t)a->out & 15) == 0 &&
@@ -1007,6 +1025,7 @@ extern "C" int sdb_conv3x3(const SdbConvArgs* a, void* stream) {
   p.out = a->out;
   p.ldo = a->Cout;
   p.out_dtype = a->out_dtype;
+  p.u8_channels = a->out_channels;
   p.act = SDB_ACT_NONE;
 
   uint64_t dims[4] = {(uint64_t)a->Cin, (uint64_t)a->W, (uint64_t)a->H, (uint64_t)a->B};

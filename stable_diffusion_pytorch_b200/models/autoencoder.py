@@ -67,10 +67,14 @@ class _ConvNet(nn.Module):
             "wh": c.get("wh", [head.weight, head.bias], lambda: _pack.head_w16(head.weight, head.bias)),
         }
 
-    def _head(self, h: Tensor, p, out_dtype) -> Tensor:
+    def _head(self, h: Tensor, p, out_dtype, uint8: bool = False) -> Tensor:
         h = ops.group_norm(h, p["go"], p["bo"], self.groups, ACT_SILU)
         w16, b16 = p["wh"]
-        return ops.conv3x3_head(h, w16, b16, self.out[2].weight.shape[0], out_dtype)
+        if uint8 and h.dtype == torch.bfloat16:
+            # detransform (utils/prepare_dataset.py:145-150) in the head conv's epilogue: uint8 NHWC straight out
+            return ops.conv3x3_head_uint8(h, w16, b16, self.out[2].weight.shape[0])
+        y = ops.conv3x3_head(h, w16, b16, self.out[2].weight.shape[0], out_dtype)
+        return ops.to_uint8_image(y) if uint8 else y
 
 
 class Encoder(_ConvNet):
@@ -105,14 +109,15 @@ class Decoder(_ConvNet):
                                               levels=len(channels_list), channels_list=channels_list, groups=groups)
         self.out = build_final_output(out_ch=mid_ch, out_channels=out_channels, groups=groups)
 
-    def forward(self, x: Tensor) -> Tensor:
+    def forward(self, x: Tensor, uint8: bool = False) -> Tensor:
+        """``uint8`` (extension): return the PNG-ready [B, H, W, C] uint8 image instead of the float NCHW one."""
         _pack.require_cuda(x, "Decoder")
         p = self._thin()
         h = ops.conv3x3_in(x, p["wci"], p["bci"], _pack.compute_dtype())
         h = self.bottleneck.forward_nhwc(h)
         for module in self.up:
             h = module.forward_nhwc(h)
-        return self._head(h, p, x.dtype)
+        return self._head(h, p, x.dtype, uint8)
 
 
 class AutoEncoderKL(nn.Module):
@@ -160,7 +165,11 @@ class AutoEncoderKL(nn.Module):
     @torch.no_grad()
     def decode_uint8(self, latent: Tensor, chunk: int = 16) -> Tensor:
         """``decode`` followed by the reference's ``detransform`` (utils/prepare_dataset.py:145-150: (x + 1) / 2,
-        clip, * 255, uint8) on the device: [B, H, W, C] uint8, PNG-ready, a quarter of the fp32 image bytes -- what the
-        multi-GPU image gather moves.  Decodes ``chunk`` latents at a time (2 GB of activations each at 512 x 512)."""
-        outs = [ops.to_uint8_image(self.decode(z)) for z in latent.split(chunk)]
+        clip, * 255, uint8) inside the head conv's epilogue: [B, H, W, C] uint8, PNG-ready, a quarter of the fp32 image bytes
+        -- what the multi-GPU image gather moves; no float image is materialised.  Decodes ``chunk`` latents at a time (2 GB of activations each at 512 x 512)."""
+        assert latent.shape[1] == self.latent_channels, (
+            f"Expected latent representation to have {self.latent_channels} channels, got {latent.shape[1]}")
+        _pack.require_cuda(latent, "AutoEncoderKL.decode_uint8")
+        pq = self._thin_conv("pq", self.post_quant_conv)
+        outs = [self.decoder(ops.conv1x1_nchw_small(z, *pq), uint8=True) for z in latent.split(chunk)]
         return outs[0] if len(outs) == 1 else torch.cat(outs)

@@ -3,13 +3,14 @@ every computation happens in ``libsdb200.so``.  All tensors must be CUDA tensors
 from __future__ import annotations
 
 import ctypes as C
+import os
 from typing import Optional
 
 import torch
 
 from . import _lib
 from . import autograd_ops as _ag
-from ._lib import ACT_GEGLU, ACT_NONE, ACT_SILU, SDB_BF16, SDB_F32, SdbConvArgs, SdbGemmArgs, check
+from ._lib import ACT_GEGLU, ACT_NONE, ACT_SILU, SDB_BF16, SDB_F32, SDB_U8, SdbConvArgs, SdbGemmArgs, check
 
 Tensor = torch.Tensor
 
@@ -20,6 +21,8 @@ def _dt(t_or_dtype) -> int:
         return SDB_F32
     if d == torch.bfloat16:
         return SDB_BF16
+    if d == torch.uint8:
+        return SDB_U8
     raise TypeError(f"unsupported dtype {d}: the B200 path computes in float32 or bfloat16")
 
 
@@ -131,6 +134,22 @@ class GroupNormScratch:
 
 
 _default_gn_scratch = GroupNormScratch()
+# A/B switch: "0" = always the three-kernel route, "cluster" = the cluster-resident single-pass kernel where it fits,
+# anything else = the one-launch cooperative kernel
+_GN_FUSED = {"0": False, "cluster": "cluster"}.get(os.environ.get("SDB_GN_FUSED", "1"), "coop")
+_gn_coop_state = {}
+
+
+def _gn_coop_scratch(device, n_floats: int):
+    """Per-device scratch of the cooperative GroupNorm: partial sums (grown on demand) and the two barrier words
+    (zeroed once; the kernel leaves the counter at zero).  Calls on one stream run in order, so they can share it."""
+    key = str(device)
+    st = _gn_coop_state.get(key)
+    if st is None or st[0].numel() < n_floats:
+        bar = st[1] if st is not None else torch.zeros(2, device=device, dtype=torch.int32)
+        st = (torch.empty(max(n_floats, 1 << 16), device=device, dtype=torch.float32), bar)
+        _gn_coop_state[key] = st
+    return st
 
 
 def group_norm(x1: Tensor, gamma: Tensor, beta: Tensor, groups: int, act: int = ACT_NONE,
@@ -143,15 +162,30 @@ def group_norm(x1: Tensor, gamma: Tensor, beta: Tensor, groups: int, act: int = 
     C2 = x2.shape[-1] if x2 is not None else 0
     assert x1.is_contiguous() and (x2 is None or (x2.is_contiguous() and x2.dtype == x1.dtype))
     hw = H * W
-    if scratch is not None:
-        partial, stats = scratch.get(x1.device, B, hw, C1 + C2, groups)
-    else:  # per-call scratch from torch's caching allocator: safe under CUDA-graph capture
-        chunks = _lib.lib().sdb_groupnorm_chunks(hw)
-        partial = torch.empty(B * chunks * (C1 + C2) * 2, device=x1.device, dtype=torch.float32)
-        stats = torch.empty(B * groups * 2, device=x1.device, dtype=torch.float32)
     if out is None:
         out = torch.empty(B, H, W, C1 + C2, device=x1.device, dtype=out_dtype or x1.dtype)
     L = _lib.lib()
+    if _GN_FUSED and x1.dtype == torch.bfloat16 and out.dtype == torch.bfloat16:
+        if _GN_FUSED == "cluster":
+            # single pass (cluster per image, image resident in shared memory); -3 = the image does not fit a cluster
+            rc = L.sdb_groupnorm_fused(_ptr(x1), C1, _ptr(x2), C2, _ptr(gamma), _ptr(beta), act, _ptr(out), B, hw,
+                                       groups, eps, _stream())
+            if rc == 0:
+                return out
+            if rc != -3:
+                check(rc, "groupnorm_fused")
+        else:
+            # one cooperative launch: statistics pass, grid barrier, normalise pass (second read out of L2)
+            part, bar = _gn_coop_scratch(x1.device, L.sdb_groupnorm_coop_scratch(B, hw, groups))
+            check(L.sdb_groupnorm_coop(_ptr(x1), C1, _ptr(x2), C2, _ptr(gamma), _ptr(beta), act, _ptr(out), B, hw,
+                                       groups, eps, _ptr(part), _ptr(bar), _stream()), "groupnorm_coop")
+            return out
+    if scratch is not None:
+        partial, stats = scratch.get(x1.device, B, hw, C1 + C2, groups)
+    else:  # per-call scratch from torch's caching allocator: safe under CUDA-graph capture
+        chunks = L.sdb_groupnorm_chunks(hw)
+        partial = torch.empty(B * chunks * (C1 + C2) * 2, device=x1.device, dtype=torch.float32)
+        stats = torch.empty(B * groups * 2, device=x1.device, dtype=torch.float32)
     check(L.sdb_groupnorm_stats(_ptr(x1), C1, _ptr(x2), C2, _dt(x1), B, hw, groups, eps, _ptr(partial),
                                 _ptr(stats), _stream()), "groupnorm_stats")
     check(L.sdb_groupnorm_apply(_ptr(x1), C1, _ptr(x2), C2, _dt(x1), _ptr(stats), _ptr(gamma), _ptr(beta), act,
@@ -228,6 +262,9 @@ def conv3x3(x: Tensor, w: Tensor, bias: Optional[Tensor], temb: Optional[Tensor]
     else:
         assert tuple(w.shape) == (Cout, 3, 3, Cin)
     Ho, Wo = (H // 2, W // 2) if down2 else ((2 * H, 2 * W) if up2 else (H, W))
+    if out is not None and out.dtype == torch.uint8:      # image head with the detransform in the epilogue
+        assert x.dtype == torch.bfloat16 and Cout == 16 and tuple(out.shape[:3]) == (B, H, W) and out.is_contiguous()
+        assert residual is None and temb is None and not down2 and not up2
     if out is None:
         out = torch.empty(B, Ho, Wo, Cout, device=x.device, dtype=out_dtype or x.dtype)
     a = SdbConvArgs()
@@ -245,6 +282,7 @@ def conv3x3(x: Tensor, w: Tensor, bias: Optional[Tensor], temb: Optional[Tensor]
     a.out, a.out_dtype = _ptr(out), _dt(out)
     a.B, a.H, a.W, a.Cin, a.Cout = B, H, W, Cin, Cout
     a.down2, a.up2 = int(down2), int(up2)
+    a.out_channels = out.shape[-1] if out.dtype == torch.uint8 else 0
     fn = _lib.lib().sdb_conv3x3_f32 if x.dtype == torch.float32 else _lib.lib().sdb_conv3x3
     check(fn(C.byref(a), _stream()), "conv3x3")
     return out
@@ -298,6 +336,15 @@ def conv3x3_head(x_nhwc: Tensor, w16: Tensor, bias16: Tensor, cout: int, out_dty
     check(_lib.lib().sdb_nhwc_slice_to_nchw(_ptr(y), y.shape[-1], _ptr(out), _dt(out), B, cout, H, W, _stream()),
           "nhwc_slice_to_nchw")
     return out
+
+
+def conv3x3_head_uint8(x_nhwc: Tensor, w16: Tensor, bias16: Tensor, cout: int) -> Tensor:
+    """The decoder's image head with the reference's ``detransform`` (utils/prepare_dataset.py:145-150) in the conv
+    epilogue: uint8 NHWC [B, H, W, cout], PNG-ready -- no fp32 image is written."""
+    _ag.refuse("conv3x3_head_uint8", x_nhwc, w16, bias16)
+    B, H, W, _ = x_nhwc.shape
+    out = torch.empty(B, H, W, cout, device=x_nhwc.device, dtype=torch.uint8)
+    return conv3x3(x_nhwc, w16, bias16, out=out)
 
 
 def conv1x1_nchw_small(x: Tensor, w: Tensor, bias: Tensor) -> Tensor:

@@ -125,3 +125,22 @@ def test_clip_text_encoder_keys_match_transformers_names():
                                  num_attention_heads=2)).tokenize("a prompt")        # no tokenizer given
     with pytest.raises(RuntimeError):
         m(torch.zeros(1, 77, dtype=torch.long))                                        # CPU module: no fallback
+
+
+def test_cosine_and_cubic_noise_schedules_match_the_oracle():
+    """the schedules DDPMConfig advertises (scheduler.py:11-17; the reference itself only builds linear)."""
+    from oracle import sd_oracle as O
+    from stable_diffusion_pytorch_b200.models import DDPMConfig, DDPMScheduler
+    for kind in ("linear", "cosine", "cubic"):
+        s = DDPMScheduler(DDPMConfig(noise_schedule=kind))
+        tab = O.ddpm_tables(O.DdpmCfg(noise_schedule=kind))
+        assert torch.allclose(s.betas, tab["betas"], rtol=1e-5, atol=1e-9), kind
+        assert torch.allclose(s.alphas_cumprod, tab["alphas_cumprod"], rtol=1e-4, atol=1e-12), kind
+        assert float(s.betas.min()) > 0 and float(s.betas.max()) <= 0.9990001 and torch.all(s.alphas_cumprod[1:] < s.alphas_cumprod[:-1])
+        rows = s.coef_rows(range(s.noise_steps))
+        assert torch.isfinite(rows).all() and float(rows[0, 4]) == 0.0      # no noise at step 0
+    lin = DDPMScheduler(DDPMConfig())
+    assert torch.equal(lin.betas, torch.linspace(1e-4, 0.02, 1000))         # the default stays the reference's table
+    import pytest
+    with pytest.raises(ValueError):
+        DDPMScheduler(DDPMConfig(noise_schedule="sigmoid"))

@@ -214,6 +214,54 @@ def test_groupnorm(B, H, W, C1, C2, groups, act):
     assert rel_l2(out, ref.permute(0, 2, 3, 1)) < 2e-5
 
 
+GN_FUSED_CASES = [
+    # B, H, W, C1, C2, groups, act       (bf16 in / bf16 out: the single-pass cluster kernel)
+    (2, 64, 64, 160, 0, 32, 1),       # UNet level 0: 1.3 MB per image -> 16-CTA cluster
+    (3, 32, 32, 320, 320, 32, 1),     # virtual concat, 640 channels
+    (2, 32, 32, 320, 160, 32, 1),     # 480 channels: 15 per group, concat boundary inside a group's neighbourhood
+    (2, 32, 32, 320, 0, 2, 1),        # the bottleneck's groups = 2
+    (5, 8, 8, 64, 0, 32, 0),          # tiny image: one CTA, one piece, no SiLU
+    (1, 12, 20, 96, 32, 16, 1),       # pixels not divisible by the cluster size
+    (2, 64, 64, 160, 160, 32, 0),     # 2.6 MB per image: 16 CTAs with 164 KB slices
+    (1, 128, 128, 256, 0, 32, 1),     # 8 MB per image: does not fit -> falls back to the three-kernel route
+]
+
+
+@pytest.mark.parametrize("route", ["coop", "cluster"])
+@pytest.mark.parametrize("B,H,W,C1,C2,groups,act", GN_FUSED_CASES)
+def test_groupnorm_one_launch_routes(B, H, W, C1, C2, groups, act, route):
+    """bf16 -> bf16 GroupNorm(+SiLU) in one launch: "coop" = persistent two-phase kernel with a grid barrier (the
+    default), "cluster" = image resident in the shared memory of a thread-block cluster (falls back when it does not
+    fit).  Both against torch's fp32 GroupNorm and against the three-kernel route; both deterministic."""
+    x1 = rnd(B, H, W, C1, seed=1) + 0.3
+    x2 = rnd(B, H, W, C2, seed=2, scale=2.0) if C2 else None
+    C = C1 + C2
+    gamma = 1 + 0.1 * rnd(C, seed=3, dtype=torch.float32)
+    beta = 0.1 * rnd(C, seed=4, dtype=torch.float32)
+    xc = x1 if x2 is None else torch.cat([x1, x2], -1)
+    ref = F.group_norm(xc.float().permute(0, 3, 1, 2), groups, gamma, beta, 1e-5)
+    if act:
+        ref = F.silu(ref)
+    ref = ref.permute(0, 2, 3, 1)
+    old = ops._GN_FUSED
+    try:
+        ops._GN_FUSED = route
+        n0 = ops.launch_count()
+        out = ops.group_norm(x1, gamma, beta, groups, act, x2=x2)
+        launches = ops.launch_count() - n0
+        again = ops.group_norm(x1, gamma, beta, groups, act, x2=x2)
+        ops._GN_FUSED = False
+        three = ops.group_norm(x1, gamma, beta, groups, act, x2=x2)
+    finally:
+        ops._GN_FUSED = old
+    fits_cluster = H * W * C * 2 <= 3 * 2 ** 20
+    assert launches == (1 if route == "coop" or fits_cluster else 3)
+    assert out.dtype == torch.bfloat16 and tuple(out.shape) == (B, H, W, C)
+    assert rel_l2(out.float(), ref) < 4e-3          # bf16 rounding of the output
+    assert rel_l2(out.float(), three.float()) < 3e-3
+    assert torch.equal(out, again)                  # deterministic
+
+
 @pytest.mark.parametrize("rows,C,dtype", [(1000, 160, torch.bfloat16), (513, 320, torch.float32),
                                            (64, 64, torch.bfloat16), (100, 1024, torch.float32)])
 def test_add_layernorm(rows, C, dtype):

@@ -21,8 +21,12 @@ def gn(name, H, C1, C2, count, act=1):
     g = torch.ones(C1 + C2, device="cuda"); b = torch.zeros(C1 + C2, device="cuda")
     sc = ops.GroupNormScratch()
     ms = timeit(lambda: ops.group_norm(x1, g, b, 32, act, x2=x2, scratch=sc))
-    by = 2.0 * B * H * H * (C1 + C2) * 3      # stats read + apply read + apply write
-    print(f"{name:44s} {ms:8.4f} {by/ms/1e6:8.1f}  {count:5d}  {ms*count:7.3f}")
+    by = 2.0 * B * H * H * (C1 + C2) * 2      # algorithmic: one read + one write (the three-kernel route reads twice)
+    old = ops._GN_FUSED
+    ops._GN_FUSED = False
+    ms3 = timeit(lambda: ops.group_norm(x1, g, b, 32, act, x2=x2, scratch=sc))
+    ops._GN_FUSED = old
+    print(f"{name:44s} {ms:8.4f} {by/ms/1e6:8.1f}  {count:5d}  {ms*count:7.3f}   (three-kernel route {ms3:.4f} ms)")
     tot += ms * count
 def ln(name, rows, C, count, res=False):
     global tot
