@@ -162,6 +162,10 @@ typedef struct SdbGemmArgs {
   void* out; int64_t ldo; int out_dtype;       /* [M, Nout]; Nout = N (N/2 for GEGLU)          */
   int M; int N;
   int act;                                     /* SDB_ACT_*                                    */
+  /* optional LayerNorm of every finished output row in the epilogue: out = LN(A.W^T + bias + residual) * gamma + beta
+   * -- the post-norm step of modules/transformer.py:274-278 without a second pass over HBM.  NULL = off.  Needs bf16
+   * out + bf16 residual, act NONE and N <= 256 in one tile (SDB_EUNSUPPORTED otherwise: run sdb_add_layernorm). */
+  const float* ln_gamma; const float* ln_beta; float ln_eps;
 } SdbGemmArgs;
 int sdb_gemm(const SdbGemmArgs* args, void* stream);
 

@@ -23,7 +23,8 @@ class SdbGemmArgs(C.Structure):
                 ("w", _p), ("bias", _p),
                 ("residual", _p), ("ldr", _i64), ("res_dtype", _i),
                 ("out", _p), ("ldo", _i64), ("out_dtype", _i),
-                ("M", _i), ("N", _i), ("act", _i)]
+                ("M", _i), ("N", _i), ("act", _i),
+                ("ln_gamma", _p), ("ln_beta", _p), ("ln_eps", _f)]
 
 
 class SdbConvArgs(C.Structure):

@@ -65,6 +65,10 @@ struct UmmaParams {
   int out_dtype;
   int u8_channels;   // SDB_U8 output: channels kept per pixel
   int act;
+  // LayerNorm over the output row in the epilogue (kEpiResLN: one n-tile holds whole rows)
+  const float* ln_gamma;
+  const float* ln_beta;
+  float ln_eps;
   // staged epilogue (bf16 output through swizzled smem slabs + TMA store): 0 = direct stores
   int staged;
   int nbuf;         // staging buffers, tile j uses buffer j % nbuf (3 = a store never delays the next tile,
@@ -171,7 +175,8 @@ __device__ __forceinline__ uint4 pack_bf16x8(const float* v) {
 
 // Epilogue flavours the kernel is instantiated for: the common ones are straight-line code (two warps
 // per scheduler cannot hide fetch bubbles of a branchy epilogue), the generic one branches at run time.
-enum { kEpiPlain = 0, kEpiRes = 1, kEpiGeglu = 2, kEpiGeneric = 3 };
+// kEpiResLN = kEpiRes followed by LayerNorm of the finished row (post-norm transformer block, transformer.py:274-278).
+enum { kEpiPlain = 0, kEpiRes = 1, kEpiGeglu = 2, kEpiGeneric = 3, kEpiResLN = 4 };
 
 // ---- 16 accumulator columns of one row -> staged tile ------------------------------------------
 // `tcol` = accumulator column inside the tile, `temb_row` = per-element temb (generic flavour only, when
@@ -179,7 +184,8 @@ enum { kEpiPlain = 0, kEpiRes = 1, kEpiGeglu = 2, kEpiGeneric = 3 };
 // back to) the swizzled slab the TMA unit loaded / will store.
 template <int kEpi>
 __device__ __forceinline__ void epilogue16_staged(const UmmaParams& p, const uint32_t (&acc)[16], uint32_t stg,
-                                                  uint32_t bias_s, const float* temb_row, int r, int tcol) {
+                                                  uint32_t bias_s, const float* temb_row, int r, int tcol,
+                                                  float& ln_s, float& ln_ss) {
   float v[16];
   add_bias16(v, acc, bias_s + 4u * tcol);
   if (kEpi == kEpiGeglu) {
@@ -206,9 +212,40 @@ __device__ __forceinline__ void epilogue16_staged(const UmmaParams& p, const uin
   }
   const uint32_t a = stage_addr(p, stg, r, tcol);   // 16 columns never straddle a slab: chunks c, c ^ 1
   const uint32_t a1 = a ^ 16u;
-  if (kEpi == kEpiRes || (kEpi == kEpiGeneric && p.residual)) {
+  if (kEpi == kEpiRes || kEpi == kEpiResLN || (kEpi == kEpiGeneric && p.residual)) {
     add_bf16x8(v, lds128(a));
     add_bf16x8(v + 8, lds128(a1));
+  }
+  if (kEpi == kEpiResLN) {
+    // row statistics from the fp32 values, the row itself parked as bf16 in the staging slab
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      ln_s += v[j];
+      ln_ss = fmaf(v[j], v[j], ln_ss);
+    }
+  }
+  sts128(a, pack_bf16x8(v));
+  sts128(a1, pack_bf16x8(v + 8));
+}
+
+// second pass of kEpiResLN over 16 parked columns of row r: y = (h - mean) * rstd * gamma + beta
+__device__ __forceinline__ void layernorm16_staged(const UmmaParams& p, uint32_t stg, int r, int tcol, float mean,
+                                                   float rstd) {
+  const uint32_t a = stage_addr(p, stg, r, tcol);
+  const uint32_t a1 = a ^ 16u;
+  float v[16];
+#pragma unroll
+  for (int j = 0; j < 16; ++j) v[j] = 0.f;
+  add_bf16x8(v, lds128(a));
+  add_bf16x8(v + 8, lds128(a1));
+#pragma unroll
+  for (int j = 0; j < 16; j += 4) {
+    const float4 g = __ldg(reinterpret_cast<const float4*>(p.ln_gamma + tcol + j));
+    const float4 b = __ldg(reinterpret_cast<const float4*>(p.ln_beta + tcol + j));
+    v[j] = fmaf((v[j] - mean) * rstd, g.x, b.x);
+    v[j + 1] = fmaf((v[j + 1] - mean) * rstd, g.y, b.y);
+    v[j + 2] = fmaf((v[j + 2] - mean) * rstd, g.z, b.z);
+    v[j + 3] = fmaf((v[j + 3] - mean) * rstd, g.w, b.w);
   }
   sts128(a, pack_bf16x8(v));
   sts128(a1, pack_bf16x8(v + 8));
@@ -654,9 +691,10 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
       GEMM_TRACE(3 + wg, j >> 1, 2);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)wg * kMaxBN;
+      float ln_s = 0.f, ln_ss = 0.f;
       auto process16 = [&](const uint32_t (&v)[16], int tcol) {
         if (kEpi != kEpiGeneric || p.staged) {
-          epilogue16_staged<kEpi>(p, v, stg, bias_s, temb_row, r, tcol);
+          epilogue16_staged<kEpi>(p, v, stg, bias_s, temb_row, r, tcol, ln_s, ln_ss);
         } else if (out_row >= 0 && ok && n0 + tcol < p.N) {
           epilogue16_direct(p, v, bias_s, temb_row, out_row, n0, tcol);
         }
@@ -688,6 +726,16 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
       }
       tc_fence_before();
       mbar_arrive(tempty_bar(wg));
+      if (kEpi == kEpiResLN) {
+        // the accumulator stage is already handed back: the normalise pass works on the parked bf16 row only
+        const float inv_n = 1.0f / (float)p.BN;
+        const float mean = ln_s * inv_n;
+        float var = fmaf(-mean, mean, ln_ss * inv_n);
+        var = var > 0.f ? var : 0.f;
+        const float rstd = rsqrtf(var + p.ln_eps);
+#pragma unroll 1
+        for (int tcol = 0; tcol < p.BN; tcol += 16) layernorm16_staged(p, stg, r, tcol, mean, rstd);
+      }
       if (p.staged) fence_proxy_async();                   // generic-proxy smem writes -> async proxy
       mbar_arrive(stg_full_bar(wg));
       GEMM_TRACE(3 + wg, j >> 1, 3);
@@ -835,6 +883,7 @@ static int launch_umma(UmmaParams& p, cudaStream_t st) {
   p.walk_dm = p.resB ? p.m_groups : grid / p.tiles_n;
   p.walk_dn = p.resB ? 0 : grid % p.tiles_n;
   const bool slow_temb = p.temb && !p.temb_in_bias;
+  if (p.ln_gamma) return launch_umma_epi<kEpiResLN>(p, grid, smem, st);   // (checked by sdb_gemm: staged, residual, one n-tile)
   if (p.staged && p.act == SDB_ACT_GEGLU) return launch_umma_epi<kEpiGeglu>(p, grid, smem, st);
   if (p.staged && p.act == SDB_ACT_NONE && !slow_temb)
     return p.residual ? launch_umma_epi<kEpiRes>(p, grid, smem, st) : launch_umma_epi<kEpiPlain>(p, grid, smem, st);
@@ -903,6 +952,19 @@ extern "C" int sdb_gemm(const SdbGemmArgs* a, void* stream) {
   p.ldo = a->ldo;
   p.out_dtype = a->out_dtype;
   p.act = a->act;
+  if (a->ln_gamma) {
+    SDB_CHECK_ARG(a->ln_beta && ((uintptr_t)a->ln_gamma & 15) == 0 && ((uintptr_t)a->ln_beta & 15) == 0,
+                  "gemm: ln_gamma needs ln_beta, both 16-byte aligned");
+    if (!(p.staged && p.tiles_n == 1 && p.BN == a->N && a->residual && a->res_dtype == SDB_BF16 &&
+          a->act == SDB_ACT_NONE)) {
+      sdb_set_error("gemm: the LayerNorm epilogue needs bf16 output + bf16 residual, no activation and N (%d) in one "
+                    "tile of <= 256 columns", a->N);
+      return SDB_EUNSUPPORTED;
+    }
+    p.ln_gamma = a->ln_gamma;
+    p.ln_beta = a->ln_beta;
+    p.ln_eps = a->ln_eps;
+  }
 
   uint64_t dims[2], strides[2];
   uint32_t box[2];

@@ -100,9 +100,11 @@ class CrossAttention(nn.Module):
         return d
 
     def forward_tokens(self, x: Tensor, ctx: Optional[Tensor] = None, kv: Optional[Tuple[Tensor, Tensor]] = None,
-                       residual: Optional[Tensor] = None) -> Tensor:
+                       residual: Optional[Tensor] = None, ln=None) -> Tensor:
         """x [B, n, C] bf16.  ctx [B, m, Cc] bf16 or ``kv`` = precomputed (K, V) [B, m, kv_width] views (the
-        output layout of ``kv_packed``).  Returns out-proj(attn) (+ residual, fused in the GEMM epilogue)."""
+        output layout of ``kv_packed``).  Returns out-proj(attn) (+ residual, fused in the GEMM epilogue); with
+        ``ln`` = (gamma, beta) the post-norm LayerNorm of the block (transformer.py:274-278) is applied to that sum,
+        inside the same epilogue when the row fits one tile."""
         B, n, C = x.shape
         dm = self.n_heads * self.d_head
         kw = self.kv_width
@@ -136,8 +138,9 @@ class CrossAttention(nn.Module):
             # out = Sequential(Linear, Dropout) (transformer.py:58): the mask sits between the projection and the
             # residual add, so the add leaves the GEMM epilogue
             o = ops.dropout(ops.gemm(a.view(B * n, dm), w["wo"], w["bo"]), self.out[1].p, True)
-            return (o if res2d is None else o + res2d).view(B, n, C)
-        return ops.gemm(a.view(B * n, dm), w["wo"], w["bo"], residual=res2d).view(B, n, C)
+            o = (o if res2d is None else o + res2d).view(B, n, C)
+            return o if ln is None else ops.add_layernorm(o, None, *ln)
+        return ops.gemm(a.view(B * n, dm), w["wo"], w["bo"], residual=res2d, ln=ln).view(B, n, C)
 
     def forward(self, query: Tensor, context_emb: Optional[Tensor] = None, mask: Optional[Tensor] = None):
         if mask is not None:
@@ -185,12 +188,12 @@ class FeedForward(nn.Module):
                                  nn.Linear(d_model * dim_mult, d_model))
         self._cache = _pack.PackCache()
 
-    def forward_tokens(self, x2d: Tensor, residual: Optional[Tensor] = None) -> Tensor:
+    def forward_tokens(self, x2d: Tensor, residual: Optional[Tensor] = None, ln=None) -> Tensor:
         lin = self.net[2]
         w = self._cache.get("w", [lin.weight], lambda: _pack.linear_w(lin.weight))
         b = self._cache.get("b", [lin.bias], lambda: _pack.f32(lin.bias))
         g = ops.dropout(self.net[0].forward_tokens(x2d), self.net[1].p, self.training)      # net[1] (transformer.py:147)
-        return ops.gemm(g, w, b, residual=residual)
+        return ops.gemm(g, w, b, residual=residual, ln=ln)
 
     def forward(self, x: Tensor) -> Tensor:
         t = _tokens_bf16(x)
@@ -223,15 +226,14 @@ class BasicTransformerBlock(nn.Module):
     def forward_tokens(self, x: Tensor, ctx: Optional[Tensor] = None,
                        kv: Optional[Tuple[Tensor, Tensor]] = None) -> Tensor:
         B, n, C = x.shape
-        h = self.self_attn.forward_tokens(x, None, None, residual=x)            # x + SA(x)
-        x = ops.add_layernorm(h, None, *self._ln(1))
+        # every residual add AND the LayerNorm after it ride in the epilogue of the GEMM that ends the sub-layer
+        x = self.self_attn.forward_tokens(x, None, None, residual=x, ln=self._ln(1))      # LN1(x + SA(x))
         if ctx is None and kv is None:
-            h = self.cross_attn.forward_tokens(x, None, None, residual=x)        # reference: ctx None => self-attn
+            x = self.cross_attn.forward_tokens(x, None, None, residual=x, ln=self._ln(2))  # reference: ctx None => self-attn
         else:
-            h = self.cross_attn.forward_tokens(x, ctx, kv, residual=x)
-        x = ops.add_layernorm(h, None, *self._ln(2))
-        h = self.ffn.forward_tokens(x.view(B * n, C), residual=x.view(B * n, C)).view(B, n, C)
-        return ops.add_layernorm(h, None, *self._ln(3))
+            x = self.cross_attn.forward_tokens(x, ctx, kv, residual=x, ln=self._ln(2))    # LN2(x + CA(x, ctx))
+        return self.ffn.forward_tokens(x.view(B * n, C), residual=x.view(B * n, C),
+                                       ln=self._ln(3)).view(B, n, C)                        # LN3(x + FFN(x))
 
     def forward(self, x: Tensor, context_emb: Optional[Tensor] = None) -> Tensor:
         assert x.shape[-1] == self.d_model, f"input dim {x.shape[-1]} should be equal to d_model {self.d_model}"

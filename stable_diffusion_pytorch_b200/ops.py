@@ -137,6 +137,7 @@ _default_gn_scratch = GroupNormScratch()
 # A/B switch: "0" = always the three-kernel route, "cluster" = the cluster-resident single-pass kernel where it fits,
 # anything else = the one-launch cooperative kernel
 _GN_FUSED = {"0": False, "cluster": "cluster"}.get(os.environ.get("SDB_GN_FUSED", "1"), "coop")
+_LN_FUSED = os.environ.get("SDB_LN_FUSED", "1") != "0"    # A/B switch: 0 = LayerNorm always as its own launch
 _gn_coop_state = {}
 
 
@@ -208,11 +209,15 @@ def add_layernorm(x: Tensor, res: Optional[Tensor], gamma: Tensor, beta: Tensor,
 
 
 def gemm(a: Tensor, w: Tensor, bias: Optional[Tensor] = None, residual: Optional[Tensor] = None,
-         act: int = ACT_NONE, a2: Optional[Tensor] = None, out_dtype=None, out: Optional[Tensor] = None) -> Tensor:
-    """out[M, N] = act(a[M, K] @ w[N, K]^T + bias) + residual; ``a``/``a2`` may be row-strided 2-D views."""
-    if _ag.wants(a, w, bias, residual, a2):
+         act: int = ACT_NONE, a2: Optional[Tensor] = None, out_dtype=None, out: Optional[Tensor] = None,
+         ln=None) -> Tensor:
+    """out[M, N] = act(a[M, K] @ w[N, K]^T + bias) + residual; ``a``/``a2`` may be row-strided 2-D views.
+    ``ln`` = (gamma, beta) fp32 [N]: LayerNorm (eps 1e-5) of every output row, in the GEMM epilogue when the row fits
+    one tile (bf16, N <= 256), as a separate ``add_layernorm`` launch otherwise."""
+    if _ag.wants(a, w, bias, residual, a2) or (ln is not None and _ag.wants(*ln)):
         _no_f32_grad(a)
-        return _ag.gemm(a, w, bias, residual, act, a2, out_dtype)
+        o = _ag.gemm(a, w, bias, residual, act, a2, out_dtype)
+        return o if ln is None else add_layernorm(o, None, ln[0], ln[1])
     assert a.dim() == 2 and w.dim() == 2 and a.dtype in (torch.bfloat16, torch.float32) and w.dtype == a.dtype
     assert a.stride(1) == 1 and w.is_contiguous()
     M, K1 = a.shape
@@ -240,8 +245,18 @@ def gemm(a: Tensor, w: Tensor, bias: Optional[Tensor] = None, residual: Optional
     if bias is not None:
         assert bias.dtype == torch.float32 and bias.numel() == N
     fn = _lib.lib().sdb_gemm_f32 if a.dtype == torch.float32 else _lib.lib().sdb_gemm   # fp32 = parity mode
+    fuse_ln = (ln is not None and _LN_FUSED and a.dtype == torch.bfloat16 and out.dtype == torch.bfloat16
+               and residual is not None and residual.dtype == torch.bfloat16 and act == ACT_NONE and N <= 256)
+    if fuse_ln:
+        args.ln_gamma, args.ln_beta, args.ln_eps = _ptr(ln[0]), _ptr(ln[1]), 1e-5
+        rc = fn(C.byref(args), _stream())
+        if rc == 0:
+            return out
+        if rc != -3:
+            check(rc, "gemm")
+        args.ln_gamma = args.ln_beta = None
     check(fn(C.byref(args), _stream()), "gemm")
-    return out
+    return out if ln is None else add_layernorm(out, None, ln[0], ln[1], out=out)
 
 
 def conv3x3(x: Tensor, w: Tensor, bias: Optional[Tensor], temb: Optional[Tensor] = None,

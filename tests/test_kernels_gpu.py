@@ -93,6 +93,32 @@ def test_gemm_strided_views():
     assert rel_l2(out, ref) < 1e-5
 
 
+@pytest.mark.parametrize("M,N,K", [(4096, 160, 160), (1000, 160, 640), (300, 256, 640), (128, 64, 64),
+                                   (777, 320, 160)])
+def test_gemm_layernorm_epilogue(M, N, K):
+    """out = LN(a @ w^T + bias + residual) (post-norm, transformer.py:274-278) in the GEMM epilogue when the row
+    fits one tile (N <= 256); N = 320 runs the GEMM and the LayerNorm kernel -- same result either way."""
+    a = rnd(M, K, seed=1)
+    w = rnd(N, K, seed=2, scale=1 / math.sqrt(K))
+    bias = rnd(N, seed=3, dtype=torch.float32)
+    res = rnd(M, N, seed=4)
+    gamma = 1 + 0.1 * rnd(N, seed=5, dtype=torch.float32)
+    beta = 0.1 * rnd(N, seed=6, dtype=torch.float32)
+    n0 = ops.launch_count()
+    out = ops.gemm(a, w, bias, residual=res, ln=(gamma, beta))
+    assert ops.launch_count() - n0 == (1 if N <= 256 else 2)
+    h = a.float() @ w.float().t() + bias + res.float()
+    ref = F.layer_norm(h, (N,), gamma, beta, 1e-5)
+    assert out.dtype == torch.bfloat16 and rel_l2(out.float(), ref) < 5e-3
+    old = ops._LN_FUSED
+    try:
+        ops._LN_FUSED = False
+        two = ops.gemm(a, w, bias, residual=res, ln=(gamma, beta))
+    finally:
+        ops._LN_FUSED = old
+    assert rel_l2(out.float(), two.float()) < 5e-3
+
+
 # ------------------------------------------------------------------ conv3x3 (tcgen05 implicit GEMM)
 CONV_CASES = [
     # B, H, W, Cin, Cout, temb, residual, down2
