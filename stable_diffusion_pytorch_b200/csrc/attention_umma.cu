@@ -364,18 +364,6 @@ static int attention_p32_impl(const void* q, int64_t ldq, const void* k, int64_t
     static int spread = -1;
     if (spread < 0) { const char* e = getenv("SDB_FA_SPREAD"); spread = e ? atoi(e) : 1; }
     // instantiated shapes: the default and its A/B neighbours (tools/experiments/README.md has the full sweep)
-    static int dbg = -1;
-    if (dbg < 0) { const char* e = getenv("SDB_FA_DBG"); dbg = e ? atoi(e) : 0; }
-    if (dbg == 1) rc = launch_attention_wg1<2, 4, true, 1>(p, grid1, sdb_stream(stream));
-    else if (dbg == 2) rc = launch_attention_wg1<2, 4, true, 2>(p, grid1, sdb_stream(stream));
-    else if (dbg == 3) rc = launch_attention_wg1<2, 4, true, 3>(p, grid1, sdb_stream(stream));
-    else if (dbg == 4) rc = launch_attention_wg1<2, 4, true, 4>(p, grid1, sdb_stream(stream));
-    else if (dbg == 5) rc = launch_attention_wg1<2, 4, true, 5>(p, grid1, sdb_stream(stream));
-    else if (dbg == 8) rc = launch_attention_wg1<2, 4, true, 8>(p, grid1, sdb_stream(stream));
-    else if (dbg == 24) rc = launch_attention_wg1<2, 4, true, 24>(p, grid1, sdb_stream(stream));
-    else if (dbg == 11) rc = launch_attention_wg1<1, 4, true, 1>(p, grid1, sdb_stream(stream));
-    else if (dbg == 13) rc = launch_attention_wg1<3, 4, true, 1>(p, grid1, sdb_stream(stream));
-    else
     if (wg1 == 4 && spread) rc = poly == 3 ? launch_attention_wg1<3, 4, true>(p, grid1, sdb_stream(stream))
                                            : launch_attention_wg1<2, 4, true>(p, grid1, sdb_stream(stream));
     else if (wg1 == 4) rc = launch_attention_wg1<2, 4>(p, grid1, sdb_stream(stream));

@@ -35,6 +35,9 @@ __device__ __forceinline__ void tmem_ld_32x32_at64(uint32_t taddr, uint32_t (&v)
 
 // kPoly = element pairs out of every 8 exponentiated on the FMA pipe; kCtas = CTAs resident per SM (3 or 4);
 // kSpread = the polynomial pairs are spread over the group of 8 instead of leading it (1.105 -> 1.085 ms at kPoly = 2)
+// kDbg (measurement aid, only 0 is instantiated in the library; tools/experiments/README.md has the numbers):
+// bit 0 = skip the scale/shift FFMA2, bit 1 = skip the row maximum, bit 2 = release S only after the maximum,
+// bits 3 / 4 = sleeping polls in the TMA / MMA warps.
 template <int kPoly, int kCtas, bool kSpread, int kDbg = 0>
 __global__ void __launch_bounds__(kF1Threads, kCtas) attention_umma_wg1_kernel(const __grid_constant__ FaParams p) {
   constexpr int kStages = f1_stages(kCtas);
