@@ -43,6 +43,12 @@ struct UmmaParams {
   // its whole life and streams only A; CTA c owns n-tile c % tiles_n and m-tiles c / tiles_n + j * m_groups
   int resB, bres_bytes, m_groups;
   int walk_dm, walk_dn;   // TileWalk increments (host-computed from the grid size)
+  // CTA-pair mode (conv, cta_group::2): the two CTAs of a cluster own the m-tiles 2k and 2k + 1 of ONE n-tile and run
+  // them as a single M = 256 MMA issued by the leader; each stages its own A tile and HALF of the weight tile, so a
+  // weight byte crosses L2 -> SM once per 256 output rows (the kernel is bound by that path: 90 % of the LTS cap).
+  // Tiles are enumerated n-major over tiles_m padded to even; every CTA runs `tiles_per_cta` iterations, ghosts
+  // included (zero-filled loads, clipped stores).
+  int pair, tiles_m_pad, tiles_per_cta;
   // conv geometry (GEMM-M space = input-resolution pixels)
   int kb_per_tap, Cin;
   int TW, TH, TN, tiles_w, tiles_h;
@@ -342,23 +348,44 @@ __device__ long long g_gemm_cta_ns[160 * 4];   // per CTA: globaltimer at start 
 // apart; otherwise tile t = blockIdx.x + j * gridDim.x of the row-major (m, n) enumeration.
 struct TileWalk {
   int m, n, dm, dn, tiles_m, tiles_n;
+  bool pr;                      // CTA-pair mode
+  int left, t, pad, stride;     // iterations left, linear tile index, padded m-tile count, grid size
   __device__ __forceinline__ explicit TileWalk(const UmmaParams& p) {
     tiles_m = p.tiles_m;
     tiles_n = p.tiles_n;
-    n = (int)blockIdx.x % tiles_n;
-    m = (int)blockIdx.x / tiles_n;
     dm = p.walk_dm;
     dn = p.walk_dn;
+    pr = p.pair != 0;
+    left = t = pad = stride = 0;
+    if (pr) {
+      left = p.tiles_per_cta;
+      t = (int)blockIdx.x;
+      pad = p.tiles_m_pad;
+      stride = (int)gridDim.x;
+      n = t / pad;
+      m = t - n * pad;
+    } else {
+      n = (int)blockIdx.x % tiles_n;
+      m = (int)blockIdx.x / tiles_n;
+    }
   }
-  __device__ __forceinline__ bool valid() const { return m < tiles_m; }
+  // pair mode: true for ghost tiles too (m >= tiles_m or n >= tiles_n) -- both CTAs of a pair keep walking together
+  __device__ __forceinline__ bool valid() const { return pr ? left > 0 : m < tiles_m; }
   __device__ __forceinline__ void next() {
+    if (pr) {
+      --left;
+      t += stride;
+      n = t / pad;
+      m = t - n * pad;
+      return;
+    }
     m += dm;
     n += dn;
     if (n >= tiles_n) { n -= tiles_n; ++m; }
   }
 };
 
-template <int kEpi>
+template <int kEpi, bool k2 = false>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -397,21 +424,28 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(tfull_bar(a), 1);
-      mbar_init(tempty_bar(a), 128);
+      mbar_init(tempty_bar(a), k2 ? 256 : 128);   // pair: the leader's MMA warp waits for both CTAs' epilogues
       mbar_init(res_full_bar(a), 1);
       mbar_init(stg_full_bar(a), 128);
     }
     mbar_init(bfull_bar, 1);
     fence_barrier_init();
   }
+  if (k2) sdb_cluster_sync();   // the peer's barriers exist before anything is signalled at them
   if (warp == 1) {
-    tmem_alloc(tmem_slot, 512);
-    tmem_relinquish();
+    if (k2) {
+      tmem_alloc_2cta(tmem_slot, 512);
+      tmem_relinquish_2cta();
+    } else {
+      tmem_alloc(tmem_slot, 512);
+      tmem_relinquish();
+    }
   }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
+  const uint32_t pair_rank = k2 ? sdb_cluster_ctarank() : 0u;
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -431,7 +465,9 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
       }
       __syncwarp();
     }
-    const uint32_t tx = (uint32_t)(p.resB ? p.a_bytes : p.a_bytes + p.b_bytes);
+    // pair: the leader's barrier collects both CTAs' A tile and weight half
+    const uint32_t tx = k2 ? 2u * (uint32_t)(p.a_bytes + p.b_bytes)
+                           : (uint32_t)(p.resB ? p.a_bytes : p.a_bytes + p.b_bytes);
     for (int j = 0; tw.valid() && ok; tw.next(), ++j) {
       GEMM_TRACE(0, j, 0);
       const int m_tile = tw.m;
@@ -447,7 +483,16 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
         if (!ok) break;
         const uint32_t sa = ring_base + (uint32_t)stage * p.stage_bytes;
         const uint32_t sb = sa + p.a_bytes;
-        if (elect_one()) {
+        if (k2) {
+          if (elect_one()) {
+            const uint32_t lead_full = sdb_mapa(full_bar(stage), 0u);
+            if (pair_rank == 0) mbar_arrive_expect_tx(full_bar(stage), tx);
+            const int tap = kb / p.kb_per_tap;
+            const int c0 = (kb - tap * p.kb_per_tap) * p.BK;
+            tma_load_4d_2cta(sa, &p.tmA[p.tap_map[tap]], lead_full, c0, w0 + p.tap_dw[tap], h0 + p.tap_dh[tap], i0);
+            tma_load_2d_2cta(sb, &p.tmB, lead_full, tap * p.Cin + c0, n0 + (int)pair_rank * (p.BN >> 1));
+          }
+        } else if (elect_one()) {
           mbar_arrive_expect_tx(full_bar(stage), tx);
           if (p.mode == 0) {
             if (kb < p.kb1) {
@@ -470,11 +515,11 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
       }
       GEMM_TRACE(0, j, 1);
     }
-  } else if (warp == 1) {
-    // ===================== MMA issuer =====================
+  } else if (warp == 1 && (!k2 || pair_rank == 0)) {
+    // ===================== MMA issuer (pair mode: the leader CTA only) =====================
     // Descriptors are kept as (constant high word | 14-bit address field) and advanced by adds: the loop
     // body is a barrier wait, four MMAs and a commit.
-    const uint32_t idesc = umma_idesc_bf16(kTileM, (uint32_t)p.BN);
+    const uint32_t idesc = umma_idesc_bf16(k2 ? 2 * kTileM : kTileM, (uint32_t)p.BN);
     const uint64_t desc_hi = umma_smem_desc(0u, (uint32_t)p.swz);
     const uint32_t a_step = (uint32_t)p.stage_bytes >> 4;
     const uint32_t a_lo0 = (ring_base & 0x3ffffu) >> 4;
@@ -505,20 +550,31 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
         const uint64_t bdesc = desc_hi | (uint64_t)(p.resB ? b_lo : a_lo + ((uint32_t)p.a_bytes >> 4));
         if (elect_one()) {
           // advance 16 bf16 = 32 B along K inside the swizzle atom: +2 in the (addr >> 4) field
-          umma_f16(tmem_d, adesc, bdesc, idesc, kb != 0 ? 1u : 0u);
-          umma_f16(tmem_d, adesc + 2, bdesc + 2, idesc, 1u);
-          if (bk64) {
-            umma_f16(tmem_d, adesc + 4, bdesc + 4, idesc, 1u);
-            umma_f16(tmem_d, adesc + 6, bdesc + 6, idesc, 1u);
+          if (k2) {
+            umma_f16_2cta(tmem_d, adesc, bdesc, idesc, kb != 0 ? 1u : 0u);
+            umma_f16_2cta(tmem_d, adesc + 2, bdesc + 2, idesc, 1u);
+            umma_f16_2cta(tmem_d, adesc + 4, bdesc + 4, idesc, 1u);
+            umma_f16_2cta(tmem_d, adesc + 6, bdesc + 6, idesc, 1u);
+            umma_commit_2cta(empty_bar(stage));     // frees the slot in both CTAs
+          } else {
+            umma_f16(tmem_d, adesc, bdesc, idesc, kb != 0 ? 1u : 0u);
+            umma_f16(tmem_d, adesc + 2, bdesc + 2, idesc, 1u);
+            if (bk64) {
+              umma_f16(tmem_d, adesc + 4, bdesc + 4, idesc, 1u);
+              umma_f16(tmem_d, adesc + 6, bdesc + 6, idesc, 1u);
+            }
+            umma_commit(empty_bar(stage));
           }
-          umma_commit(empty_bar(stage));
         }
         __syncwarp();
         b_lo += b_step;
         a_lo += a_step;
         if (++stage == p.num_stages) { stage = 0; phase ^= 1u; a_lo = a_lo0; }
       }
-      if (elect_one()) umma_commit(tfull_bar(acc));
+      if (elect_one()) {
+        if (k2) umma_commit_2cta(tfull_bar(acc));   // both CTAs' epilogues
+        else umma_commit(tfull_bar(acc));
+      }
       __syncwarp();
       GEMM_TRACE(1, j, 2);
     }
@@ -725,7 +781,8 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
         }
       }
       tc_fence_before();
-      mbar_arrive(tempty_bar(wg));
+      if (k2) mbar_arrive_cluster(sdb_mapa(tempty_bar(wg), 0u));   // the leader's barrier counts both CTAs' rows
+      else mbar_arrive(tempty_bar(wg));
       if (kEpi == kEpiResLN) {
         // the accumulator stage is already handed back: the normalise pass works on the parked bf16 row only
         const float inv_n = 1.0f / (float)p.BN;
@@ -751,9 +808,11 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
     g_gemm_cta_ns[blockIdx.x * 4 + 3] = clock64();
   }
 #endif
+  if (k2) sdb_cluster_sync();   // neither CTA frees TMEM / leaves while the pair still works on its shared memory
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, 512);
+    if (k2) tmem_dealloc_2cta(tmem_base, 512);
+    else tmem_dealloc(tmem_base, 512);
   }
 }
 
@@ -802,7 +861,7 @@ static void finish_stages(UmmaParams& p) {
   if (no_resb < 0) { const char* e = getenv("SDB_GEMM_NO_RESB"); no_resb = e ? atoi(e) : 0; }
   const int sms = sdb_num_sms();
   p.a_bytes = kTileM * p.BK * 2;
-  p.b_bytes = p.BN * p.BK * 2;
+  p.b_bytes = (p.pair ? p.BN / 2 : p.BN) * p.BK * 2;     // pair mode: each CTA stages half of the weight tile
   p.resB = 0;
   p.bres_bytes = 0;
   p.m_groups = 1;
@@ -857,16 +916,33 @@ static int make_slab_maps(UmmaParams& p, const void* out, const void* res, int r
   return rc;
 }
 
-template <int kEpi>
+template <int kEpi, bool k2 = false>
 static int launch_umma_epi(const UmmaParams& p, int grid, int smem, cudaStream_t st) {
   static bool attr_set[64] = {false};
   int dev = 0;
   SDB_CUDA_OK(cudaGetDevice(&dev));
   if (dev < 0 || dev >= 64 || !attr_set[dev]) {
-    SDB_CUDA_OK(cudaFuncSetAttribute(umma_gemm_kernel<kEpi>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    SDB_CUDA_OK(cudaFuncSetAttribute(umma_gemm_kernel<kEpi, k2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     if (dev >= 0 && dev < 64) attr_set[dev] = true;
   }
-  umma_gemm_kernel<kEpi><<<grid, kGemmThreads, smem, st>>>(p);
+  if (k2) {
+    cudaLaunchConfig_t cfg;
+    memset(&cfg, 0, sizeof(cfg));
+    cfg.gridDim = dim3((unsigned)grid, 1, 1);
+    cfg.blockDim = dim3(kGemmThreads, 1, 1);
+    cfg.dynamicSmemBytes = (size_t)smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    SDB_CUDA_OK(cudaLaunchKernelEx(&cfg, umma_gemm_kernel<kEpi, k2>, p));
+  } else {
+    umma_gemm_kernel<kEpi, k2><<<grid, kGemmThreads, smem, st>>>(p);
+  }
   SDB_LAUNCH_OK();
   return SDB_OK;
 }
@@ -879,10 +955,21 @@ static int launch_umma(UmmaParams& p, cudaStream_t st) {
   }
   const int total = p.tiles_m * p.tiles_n;
   const int sms = sdb_num_sms();
-  const int grid = p.resB ? p.m_groups * p.tiles_n : (total < sms ? total : sms);
+  int grid = p.resB ? p.m_groups * p.tiles_n : (total < sms ? total : sms);
+  if (p.pair) {
+    p.tiles_m_pad = (p.tiles_m + 1) / 2 * 2;
+    const int padded = p.tiles_m_pad * p.tiles_n;
+    grid = (padded < sms ? padded : sms) / 2 * 2;
+    p.tiles_per_cta = (padded + grid - 1) / grid;
+  }
   p.walk_dm = p.resB ? p.m_groups : grid / p.tiles_n;
   p.walk_dn = p.resB ? 0 : grid % p.tiles_n;
   const bool slow_temb = p.temb && !p.temb_in_bias;
+  if (p.pair) {      // conv only: plain / residual / generic epilogues
+    if (p.staged && !slow_temb)
+      return p.residual ? launch_umma_epi<kEpiRes, true>(p, grid, smem, st) : launch_umma_epi<kEpiPlain, true>(p, grid, smem, st);
+    return launch_umma_epi<kEpiGeneric, true>(p, grid, smem, st);
+  }
   if (p.ln_gamma) return launch_umma_epi<kEpiResLN>(p, grid, smem, st);   // (checked by sdb_gemm: staged, residual, one n-tile)
   if (p.staged && p.act == SDB_ACT_GEGLU) return launch_umma_epi<kEpiGeglu>(p, grid, smem, st);
   if (p.staged && p.act == SDB_ACT_NONE && !slow_temb)
@@ -1030,6 +1117,11 @@ extern "C" int sdb_conv3x3(const SdbConvArgs* a, void* stream) {
   pick_bk(a->Cin, 0, &p.BK, &p.swz);
   p.BN = pick_bn(a->Cout);
   p.act = SDB_ACT_NONE;
+  // CTA pairs (cta_group::2, M = 256): whenever the half weight tile keeps whole 8-row swizzle atoms and there is
+  // more than a handful of m-tiles (SDB_CONV_PAIR=0 switches it off: A/B measurements)
+  static int pair_on = -1;
+  if (pair_on < 0) { const char* e = getenv("SDB_CONV_PAIR"); pair_on = e ? atoi(e) : 1; }
+  p.pair = (pair_on && p.BK == 64 && p.BN % 32 == 0 && (long long)a->B * a->H * a->W >= 8 * kTileM) ? 1 : 0;
   plan_staging(p, a->out_dtype == SDB_BF16, !a->residual || a->res_dtype == SDB_BF16, !a->down2);
   p.Cin = a->Cin;
   p.kb_per_tap = (a->Cin + p.BK - 1) / p.BK;
@@ -1098,7 +1190,7 @@ extern "C" int sdb_conv3x3(const SdbConvArgs* a, void* stream) {
   if (rc) return rc;
   uint64_t wd[2] = {(uint64_t)n_tap * a->Cin, (uint64_t)a->Cout};
   uint64_t ws[2] = {0, (uint64_t)n_tap * a->Cin * 2};
-  uint32_t wb[2] = {(uint32_t)p.BK, (uint32_t)p.BN};
+  uint32_t wb[2] = {(uint32_t)p.BK, (uint32_t)(p.pair ? p.BN / 2 : p.BN)};
   rc = sdb_make_tensor_map(&p.tmB, wph, 2, 2, wd, ws, wb, p.swz);
   if (rc) return rc;
   if (p.staged) {
