@@ -374,12 +374,14 @@ def hbm_kernels(B2, size, pk):
     scr = ops.GroupNormScratch()
     nbytes = x.numel() * 2.0
     ms = time_kernel(lambda: ops.group_norm(x, gam, bet, 32, ACT_SILU, scratch=scr))
-    out.append({"kernel": f"groupnorm stats+apply(+SiLU) [{B2},{size},{size},160] bf16 (gn_partial+gn_finalize+gn_apply)",
-                "ms": ms, "bytes": 3 * nbytes})
+    out.append({"kernel": f"GroupNorm(+SiLU) [{B2},{size},{size},160] bf16, one cooperative launch (gn_coop_kernel: statistics pass, "
+                          f"grid barrier, normalise pass out of L2)",
+                "ms": ms, "bytes": 2 * nbytes, "note": "algorithmic bytes = one read + one write of the tensor"})
     tok = x.view(B2, size * size, 160)
     res = torch.randn_like(tok)
     ms = time_kernel(lambda: ops.add_layernorm(tok, res, gam, bet))
-    out.append({"kernel": f"add_layernorm [{B2 * size * size},160] bf16", "ms": ms, "bytes": 3 * nbytes})
+    out.append({"kernel": f"add_layernorm [{B2 * size * size},160] bf16 (stand-alone kernel; the UNet path runs LN in the "
+                          f"GEMM epilogue)", "ms": ms, "bytes": 3 * nbytes})
     sch = DDPMScheduler(DDPMConfig())
     coef = sch.coef_rows(range(50)).to(dev)
     for Bs in (B2 // 2, 512):
