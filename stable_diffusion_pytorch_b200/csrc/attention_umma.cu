@@ -37,6 +37,7 @@ struct FaParams {
 }  // namespace sdb
 
 #include "attention_umma_wg1.cu"   // the one-warpgroup-per-CTA shape of the same pipeline (uses the helpers above)
+#include "attention_ctx_umma.cu"   // short context (<= 96 keys): K / V resident, query tiles streamed
 
 static int attention_p32_impl(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
                               int64_t ldv, void* out, int64_t ldo, int B, int heads, int n, int m, int d,
@@ -57,6 +58,57 @@ static int attention_p32_impl(const void* q, int64_t ldq, const void* k, int64_t
   // kernel beats this pipeline's per-CTA set-up by an order of magnitude there
   static int no_ctx = -1;
   if (no_ctx < 0) { const char* e = getenv("SDB_FA_NO_CTX"); no_ctx = e ? atoi(e) : 0; }
+  // <= 96 keys: the tcgen05 short-context kernel (K / V resident per CTA, query tiles streamed); SDB_FA_CTX_UMMA=0
+  // falls back to the mma.sync one, which also serves 97..128 keys
+  static int ctx_umma = -1, ctx_tiles = 8;
+  if (ctx_umma < 0) {
+    const char* e = getenv("SDB_FA_CTX_UMMA");
+    ctx_umma = e ? atoi(e) : 1;
+    const char* t = getenv("SDB_FA_CTX_TILES");
+    if (t && atoi(t) > 0) ctx_tiles = atoi(t);
+  }
+  if (m <= kCuMaxNS && ctx_umma && !no_ctx && !lse) {
+    CuParams c;
+    memset(&c, 0, sizeof(c));
+    const int NS = (m + 15) / 16 * 16;
+    const uint32_t qbox[3] = {32, 128, 1};
+    const uint32_t kvbox[3] = {32, (uint32_t)NS, 1};
+    uint64_t dims[3] = {(uint64_t)heads * 32, (uint64_t)n, (uint64_t)B};
+    uint64_t st[3] = {0, (uint64_t)ldq * 2, (uint64_t)n * ldq * 2};
+    int rc = sdb_make_tensor_map(&c.tmQ, q, 2, 3, dims, st, qbox, 64);
+    if (rc) return rc;
+    dims[1] = (uint64_t)m;
+    st[1] = (uint64_t)ldk * 2; st[2] = (uint64_t)m * ldk * 2;
+    rc = sdb_make_tensor_map(&c.tmK, k, 2, 3, dims, st, kvbox, 64);
+    if (rc) return rc;
+    st[1] = (uint64_t)ldv * 2; st[2] = (uint64_t)m * ldv * 2;
+    rc = sdb_make_tensor_map(&c.tmV, v, 2, 3, dims, st, kvbox, 64);
+    if (rc) return rc;
+    c.out = (__nv_bfloat16*)out;
+    c.ldo = ldo;
+    c.n = n; c.m = m; c.d = d; c.heads = heads;
+    c.scale_log2 = scale * 1.4426950408889634f;
+    // query tiles per CTA: up to SDB_FA_CTX_TILES (8), at least 2 (one per softmax warpgroup), fewer when the grid would
+    // not fill the 2 x 148 CTA slots; the chunks of one (batch, head) are kept the same length
+    const int n_tiles = (n + kCuBM - 1) / kCuBM;
+    long long want = (long long)heads * B * n_tiles / 296;
+    want = want < 2 ? 2 : (want > ctx_tiles ? ctx_tiles : want);
+    const int chunks = (n_tiles + (int)want - 1) / (int)want;
+    c.tiles_per_cta = (n_tiles + chunks - 1) / chunks;
+    dim3 grid(heads, (n_tiles + c.tiles_per_cta - 1) / c.tiles_per_cta, B);
+    cudaStream_t s0 = sdb_stream(stream);
+    switch (NS) {
+      case 16: rc = launch_attention_ctx_umma<16>(c, grid, s0); break;
+      case 32: rc = launch_attention_ctx_umma<32>(c, grid, s0); break;
+      case 48: rc = launch_attention_ctx_umma<48>(c, grid, s0); break;
+      case 64: rc = launch_attention_ctx_umma<64>(c, grid, s0); break;
+      case 80: rc = launch_attention_ctx_umma<80>(c, grid, s0); break;
+      default: rc = launch_attention_ctx_umma<96>(c, grid, s0); break;
+    }
+    if (rc) return rc;
+    SDB_LAUNCH_OK();
+    return SDB_OK;
+  }
   if (m <= 128 && !no_ctx)
     return sdb_attention_ctx_dispatch(q, ldq, k, ldk, v, ldv, out, ldo, B, heads, n, m, d, scale, sdb_stream(stream));
   FaParams p;

@@ -193,6 +193,24 @@ __device__ __forceinline__ bool mbar_wait(uint32_t bar, uint32_t parity) {
   return true;
 }
 
+// mbar_wait without the suspend hint: the un-hinted try_wait returns after its short default slice, so a waiter on a
+// critical path polls at a higher rate
+__device__ __forceinline__ bool mbar_wait_spin(uint32_t bar, uint32_t parity) {
+  if (mbar_try_wait(bar, parity)) return true;
+  uint64_t t0 = 0;
+  uint32_t spins = 0;
+  while (!mbar_try_wait(bar, parity)) {
+    if ((++spins & 0x3ff) == 0) {
+      uint64_t now = globaltimer_ns();
+      if (t0 == 0) t0 = now;
+      if (now - t0 > 2000000000ull) {
+        atomicExch(&g_sdb_timeout_flag, 1);
+        return false;
+      }
+    }
+  }
+  return true;
+}
 // mbar_wait for warps with slack (producers that run several stages ahead): polls with a sleep in between so the
 // polling does not take issue slots from the compute warps on the same SM sub-partition
 __device__ __forceinline__ bool mbar_wait_sleep(uint32_t bar, uint32_t parity, uint32_t ns) {

@@ -341,8 +341,11 @@ def test_attention(B, heads, n, m, d):
 @pytest.mark.parametrize("B,heads,n,m,d", [
     (1, 1, 256, 128, 20), (1, 2, 256, 256, 20), (2, 8, 1024, 1024, 20), (2, 8, 300, 77, 20),
     (1, 8, 4096, 4096, 20), (1, 3, 128, 640, 16), (2, 4, 1000, 333, 8),
-    # short contexts (<= 128 keys) take the streaming mma.sync kernel
-    (1, 8, 4096, 77, 20), (2, 2, 50, 5, 20), (1, 2, 1000, 100, 8), (1, 1, 17, 16, 4), (3, 8, 1024, 77, 20)])
+    # short contexts: <= 96 keys take the tcgen05 short-context kernel (one template per 16 keys; odd tile counts,
+    # ragged last tiles, chunked query ranges), 97..128 the streaming mma.sync kernel
+    (1, 8, 4096, 77, 20), (2, 2, 50, 5, 20), (1, 2, 1000, 100, 8), (1, 1, 17, 16, 4), (3, 8, 1024, 77, 20),
+    (1, 2, 2500, 96, 20), (2, 3, 700, 48, 12), (1, 1, 129, 33, 16), (1, 2, 1300, 64, 20), (1, 1, 128, 1, 8),
+    (40, 8, 1200, 77, 20)])
 def test_attention_p32(B, heads, n, m, d):
     """tcgen05 attention on head-padded operands vs fp32 softmax attention of the same bf16 inputs."""
     g = torch.Generator(device="cpu").manual_seed(n + m)
