@@ -142,6 +142,14 @@ int sdb_groupnorm_coop(const void* x1, int C1, const void* x2, int C2, const flo
 int sdb_groupnorm_apply(const void* x1, int C1, const void* x2, int C2, int dtype,
                         const float* stats, const float* gamma, const float* beta, int act,
                         void* out, int out_dtype, int B, int64_t hw, int groups, void* stream);
+/* Normalise (+SiLU) with the statistics taken from per-channel (sum, sum of squares) pairs that the producers of x1
+ * (and x2) accumulated in their epilogues (SdbGemmArgs.chan_sums / SdbConvArgs.chan_sums: int64 fixed point [B][C1][2]
+ * and [B][C2][2]) -- the statistics pass over the tensor disappears.  One read + one write of the tensor, one launch.
+ * groups <= 128. */
+int sdb_groupnorm_apply_sums(const void* x1, int C1, const void* sums1, const void* x2, int C2,
+                             const void* sums2, int dtype, const float* gamma, const float* beta,
+                             float eps, int act, void* out, int out_dtype, int B, int64_t hw, int groups,
+                             void* stream);
 
 /* ---- K5: residual add + LayerNorm ------------------------------------------------------------
  * modules/transformer.py:274-278 post-norm: out = LN(x (+ res)) over the last dim C, eps 1e-5. */
@@ -166,6 +174,14 @@ typedef struct SdbGemmArgs {
    * -- the post-norm step of modules/transformer.py:274-278 without a second pass over HBM.  NULL = off.  Needs bf16
    * out + bf16 residual, act NONE and N <= 256 in one tile (SDB_EUNSUPPORTED otherwise: run sdb_add_layernorm). */
   const float* ln_gamma; const float* ln_beta; float ln_eps;
+  /* optional per-channel sums of the finished output for the GroupNorm that reads it next (resnet2d.py:171,187;
+   * transformer.py:332): chan_sums, int64 [M / rows_per_image][N][2], receives += (sum, sum of squares) over the rows
+   * of each image of the bf16-rounded output, in fixed point (sum: signed, 2^-30 steps; squares: unsigned, 2^-24
+   * steps, i.e. < 1.1e12 per image and channel) by 64-bit integer atomics -- exact, so the totals do not depend on
+   * the order the CTAs arrive in.  The caller zeroes it; sdb_groupnorm_apply_sums consumes it.  NULL = off.  Needs
+   * bf16 out, act NONE, no LayerNorm, rows_per_image %% 128 == 0 dividing M (SDB_EUNSUPPORTED otherwise: nothing was
+   * launched, call again without it). */
+  void* chan_sums; int64_t rows_per_image;
 } SdbGemmArgs;
 int sdb_gemm(const SdbGemmArgs* args, void* stream);
 
@@ -194,6 +210,10 @@ typedef struct SdbConvArgs {
    * trunc(clip((y + 1) / 2, 0, 1) * 255) of the first out_channels <= 16 = Cout output channels (the head's Cout is
    * padded to 16 for the tensor cores).  No residual, no down2 / up2.  Ignored for other out dtypes. */
   int out_channels;
+  /* optional per-channel sums of the finished output, as SdbGemmArgs.chan_sums: int64 [B][Cout][2], caller-zeroed.
+   * Needs bf16 out, no down2, H x W tiling into whole 128-pixel boxes (SDB_EUNSUPPORTED otherwise, nothing launched).
+   * With up2 the four phase launches add into the same buffer. */
+  void* chan_sums;
 } SdbConvArgs;
 int sdb_conv3x3(const SdbConvArgs* args, void* stream);
 

@@ -24,7 +24,8 @@ class SdbGemmArgs(C.Structure):
                 ("residual", _p), ("ldr", _i64), ("res_dtype", _i),
                 ("out", _p), ("ldo", _i64), ("out_dtype", _i),
                 ("M", _i), ("N", _i), ("act", _i),
-                ("ln_gamma", _p), ("ln_beta", _p), ("ln_eps", _f)]
+                ("ln_gamma", _p), ("ln_beta", _p), ("ln_eps", _f),
+                ("chan_sums", _p), ("rows_per_image", _i64)]
 
 
 class SdbConvArgs(C.Structure):
@@ -33,7 +34,8 @@ class SdbConvArgs(C.Structure):
                 ("residual", _p), ("res_dtype", _i),
                 ("out", _p), ("out_dtype", _i),
                 ("B", _i), ("H", _i), ("W", _i), ("Cin", _i), ("Cout", _i),
-                ("down2", _i), ("up2", _i), ("out_channels", _i)]
+                ("down2", _i), ("up2", _i), ("out_channels", _i),
+                ("chan_sums", _p)]
 
 
 # name -> (restype, argtypes); must list every symbol include/sdb200.h declares
@@ -55,6 +57,7 @@ SIGNATURES = {
     "sdb_groupnorm_coop_scratch": (_i64, [_i, _i64, _i]),
     "sdb_groupnorm_coop": (_i, [_p, _i, _p, _i, _p, _p, _i, _p, _i, _i64, _i, _f, _p, _p, _p]),
     "sdb_groupnorm_apply": (_i, [_p, _i, _p, _i, _i, _p, _p, _p, _i, _p, _i, _i, _i64, _i, _p]),
+    "sdb_groupnorm_apply_sums": (_i, [_p, _i, _p, _p, _i, _p, _i, _p, _p, _f, _i, _p, _i, _i, _i64, _i, _p]),
     "sdb_add_layernorm": (_i, [_p, _p, _p, _p, _p, _i64, _i, _f, _i, _p]),
     "sdb_gemm": (_i, [C.POINTER(SdbGemmArgs), _p]),
     "sdb_conv3x3": (_i, [C.POINTER(SdbConvArgs), _p]),

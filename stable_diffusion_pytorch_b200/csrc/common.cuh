@@ -409,6 +409,13 @@ __host__ __device__ __forceinline__ uint32_t umma_idesc_bf16(uint32_t M, uint32_
 // ---- misc math ------------------------------------------------------------------------------
 // x * sigmoid(x); ex2.approx + fast divide (a few ulp, far inside the bf16 rounding of every consumer)
 __device__ __forceinline__ float silu_f(float x) { return __fdividef(x, 1.0f + __expf(-x)); }
+// Channel sums handed from a conv / GEMM epilogue to the GroupNorm that follows (SdbConvArgs.chan_sums): 64-bit fixed
+// point so that the atomic accumulation is exact and order-independent.  Sum: signed, 2^-30 steps (|sum| < 8.6e9);
+// sum of squares: unsigned, 2^-24 steps (< 1.1e12 per image and channel: an rms of 2000 over a 512 x 512 image).
+// A partial sum is rounded once to that grid: <= 6e-8 / 64 elements, far inside GroupNorm's eps.
+constexpr float kChanSumScale = 1073741824.0f;   // 2^30
+constexpr float kChanSqScale = 16777216.0f;      // 2^24
+
 __device__ __forceinline__ float gelu_erf_f(float x) {
   return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f));
 }

@@ -83,6 +83,14 @@ struct UmmaParams {
   int nslab;        // full 64-column slabs per tile
   int tail_cols;    // columns of the last, narrower slab (0, 16 or 32)
   int stg_bytes;    // bytes of one staging buffer
+  // per-channel sums of the finished (bf16-rounded) output for the GroupNorm that consumes it: the epilogue warpgroup
+  // re-reads its staged tile column-wise and adds sum / sum of squares into chsum[img][N][2] (64-bit fixed-point
+  // atomics, flushed only when the CTA moves to another image or n-tile).  Needs the staged epilogue and tiles that lie
+  // inside one image.
+  unsigned long long* chsum;
+  int st_tiles_img;   // m-tiles per image
+  int st_splits;      // row ranges a column pair is split over (threads = bno / 2 * st_splits <= 128)
+  int st_rows;        // rows per range = 128 / st_splits
 };
 
 // ---- packed fp32 pair helpers (one issue slot for two elements) ---------------------------------
@@ -127,6 +135,11 @@ __device__ __forceinline__ void tma_store_wait_read1() { asm volatile("cp.async.
 __device__ __forceinline__ uint4 lds128(uint32_t a) {
   uint4 v;
   asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ uint32_t lds32(uint32_t a) {
+  uint32_t v;
+  asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v) : "r"(a));
   return v;
 }
 __device__ __forceinline__ float4 lds128f(uint32_t a) {
@@ -713,6 +726,35 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
     TileWalk tw(p);
     if (wg) tw.next();
     int buf = wg < p.nbuf ? wg : 0;                       // j % nbuf
+    // channel sums for the consuming GroupNorm: this thread's column pair and row range of every staged tile
+    const int st_ncp = p.bno >> 1;
+    const int st_cp = p.chsum ? r % st_ncp : 0, st_sp = p.chsum ? r / st_ncp : 0;
+    const bool st_on = p.chsum && st_sp < p.st_splits;
+    uint32_t st_off[8], st_blk = 0;
+    float st_s[4] = {0.f, 0.f, 0.f, 0.f}, st_q[4] = {0.f, 0.f, 0.f, 0.f};   // two interleaved chains each
+    int st_key = -1;
+    if (st_on) {
+      const int oc = 2 * st_cp;
+#pragma unroll
+      for (int i = 0; i < 8; ++i) st_off[i] = stage_addr(p, 0u, i, oc) + (uint32_t)(oc & 7) * 2u;   // swizzle period: 8 rows
+      st_blk = ((oc >> 6) < p.nslab ? 128u : (uint32_t)p.tail_cols * 2u) * 8u;
+    }
+    auto st_flush = [&]() {
+      if (st_key >= 0) {
+        const int img = st_key / p.tiles_n, col = (st_key - img * p.tiles_n) * p.BN + 2 * st_cp;
+        if (col < p.N) {
+          // fixed point (common.cuh: kChanSumScale / kChanSqScale): integer adds commute, so the totals -- and with them
+          // every downstream result -- do not depend on the order the CTAs arrive in
+          unsigned long long* d = p.chsum + ((long long)img * p.N + col) * 2;
+          atomicAdd(d, (unsigned long long)__float2ll_rn((st_s[0] + st_s[2]) * kChanSumScale));
+          atomicAdd(d + 1, __float2ull_rn((st_q[0] + st_q[2]) * kChanSqScale));
+          atomicAdd(d + 2, (unsigned long long)__float2ll_rn((st_s[1] + st_s[3]) * kChanSumScale));
+          atomicAdd(d + 3, __float2ull_rn((st_q[1] + st_q[3]) * kChanSqScale));
+        }
+      }
+#pragma unroll
+      for (int i = 0; i < 4; ++i) st_s[i] = st_q[i] = 0.f;
+    };
     for (int j = wg; tw.valid(); tw.next(), tw.next(), j += 2) {
       const int m_tile = tw.m, n_tile = tw.n;
       const int n0 = n_tile * p.BN;
@@ -793,12 +835,38 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
 #pragma unroll 1
         for (int tcol = 0; tcol < p.BN; tcol += 16) layernorm16_staged(p, stg, r, tcol, mean, rstd);
       }
+      if (p.chsum) {
+        // the whole tile is staged once all four warps are here; the store may not start before the column pass ends
+        // (the buffer goes back to the DMA warp, which may refill it with a residual tile)
+        asm volatile("bar.sync %0, 128;" ::"r"(1 + wg) : "memory");
+        if (st_on && ok && m_tile < p.tiles_m && n_tile < p.tiles_n) {   // (pair mode walks ghost tiles too)
+          const int key = (m_tile / p.st_tiles_img) * p.tiles_n + n_tile;
+          if (key != st_key) {
+            st_flush();
+            st_key = key;
+          }
+          if (n0 + 2 * st_cp < p.N) {
+            uint32_t a = stg + (uint32_t)((st_sp * p.st_rows) >> 3) * st_blk;
+            for (int rb = 0; rb < (p.st_rows >> 3); ++rb, a += st_blk) {
+#pragma unroll
+              for (int i = 0; i < 8; ++i) {
+                const uint32_t x = lds32(a + st_off[i]);
+                const float lo = __uint_as_float(x << 16), hi = __uint_as_float(x & 0xffff0000u);
+                const int c = (i & 1) * 2;
+                fadd2(st_s[c], st_s[c + 1], st_s[c], st_s[c + 1], lo, hi);
+                ffma2(st_q[c], st_q[c + 1], lo, hi, lo, hi, st_q[c], st_q[c + 1]);
+              }
+            }
+          }
+        }
+      }
       if (p.staged) fence_proxy_async();                   // generic-proxy smem writes -> async proxy
       mbar_arrive(stg_full_bar(wg));
       GEMM_TRACE(3 + wg, j >> 1, 3);
       buf += 2;
       while (buf >= p.nbuf) buf -= p.nbuf;
     }
+    if (p.chsum) st_flush();
   }
   tc_fence_before();
   __syncthreads();
@@ -977,6 +1045,22 @@ static int launch_umma(UmmaParams& p, cudaStream_t st) {
   return launch_umma_epi<kEpiGeneric>(p, grid, smem, st);
 }
 
+// Channel sums in the epilogue (UmmaParams::chsum): possible when the tile is staged as bf16 without an activation and
+// every 128-row tile lies inside one image with no clipped rows.  Returns false (and leaves p untouched) otherwise.
+static bool plan_chan_sums(UmmaParams& p, unsigned long long* chsum, int tiles_per_image, bool whole_tiles) {
+  if (!p.staged || p.act != SDB_ACT_NONE || p.ln_gamma || p.out_mode == 1 || !whole_tiles || tiles_per_image <= 0 ||
+      ((uintptr_t)chsum & 15) != 0)
+    return false;
+  p.chsum = chsum;
+  p.st_tiles_img = tiles_per_image;
+  const int ncp = p.bno / 2;
+  int splits = 1;
+  while (splits * 2 * ncp <= kTileM) splits *= 2;
+  p.st_splits = splits;
+  p.st_rows = kTileM / splits;
+  return true;
+}
+
 }  // namespace sdb
 
 #ifdef SDB_GEMM_TRACE
@@ -1051,6 +1135,15 @@ extern "C" int sdb_gemm(const SdbGemmArgs* a, void* stream) {
     p.ln_gamma = a->ln_gamma;
     p.ln_beta = a->ln_beta;
     p.ln_eps = a->ln_eps;
+  }
+  if (a->chan_sums) {
+    const long long rpi = a->rows_per_image;
+    if (!(rpi > 0 && rpi % kTileM == 0 && a->M % rpi == 0 && a->out_dtype == SDB_BF16 &&
+          plan_chan_sums(p, reinterpret_cast<unsigned long long*>(a->chan_sums), (int)(rpi / kTileM), true))) {
+      sdb_set_error("gemm: chan_sums needs bf16 output through the staged epilogue, no activation / LayerNorm, and "
+                    "rows_per_image (%lld) a multiple of 128 dividing M (%d)", rpi, a->M);
+      return SDB_EUNSUPPORTED;
+    }
   }
 
   uint64_t dims[2], strides[2];
@@ -1181,6 +1274,14 @@ extern "C" int sdb_conv3x3(const SdbConvArgs* a, void* stream) {
   p.out_dtype = a->out_dtype;
   p.u8_channels = a->out_channels;
   p.act = SDB_ACT_NONE;
+  if (a->chan_sums) {
+    const bool whole = tn == 1 && a->H % th == 0 && a->W % tw == 0;
+    if (!(a->out_dtype == SDB_BF16 && plan_chan_sums(p, reinterpret_cast<unsigned long long*>(a->chan_sums), p.tiles_w * p.tiles_h, whole))) {
+      sdb_set_error("conv3x3: chan_sums needs bf16 output through the staged epilogue, no down2, and an image that "
+                    "tiles into whole 128-pixel boxes (H=%d W=%d: box %dx%dx%d)", a->H, a->W, tn, th, tw);
+      return SDB_EUNSUPPORTED;
+    }
+  }
 
   uint64_t dims[4] = {(uint64_t)a->Cin, (uint64_t)a->W, (uint64_t)a->H, (uint64_t)a->B};
   uint64_t strides[4] = {0, (uint64_t)a->Cin * 2, (uint64_t)a->W * a->Cin * 2,

@@ -128,24 +128,49 @@ gn_finalize_kernel(const float* __restrict__ scratch, int chunks, int C, int gro
 // ---- normalise (+SiLU), writing a dense NHWC tensor with C1+C2 channels -----------------------
 // grid (pixel chunks, B); thread (r, vec) owns one 8-channel vector of the virtual concat -- its scale and
 // shift live in registers -- and walks the chunk's pixels with four 16-byte loads in flight.
+constexpr int kGnMaxGroupsSums = 128;   // groups the sums-fed variant keeps in shared memory
+
 template <typename T, typename OutT>
 __global__ void __launch_bounds__(kGnThreads)
 gn_apply_kernel(const T* __restrict__ x1, int C1, const T* __restrict__ x2, int C2,
                 const float* __restrict__ stats, const float* __restrict__ gamma,
                 const float* __restrict__ beta, int act, OutT* __restrict__ out, long long hw,
-                int groups, int chunk_px) {
+                int groups, int chunk_px, const void* __restrict__ cs1, const void* __restrict__ cs2,
+                float eps) {
   const int C = C1 + C2, V = C >> 3, cpg = C / groups;
   const int R = kGnThreads / V;
   const int b = blockIdx.y;
   const int vec = threadIdx.x % V, r = threadIdx.x / V;
+  __shared__ float s_stats[2 * kGnMaxGroupsSums];
+  if (cs1) {
+    // statistics from the per-channel sums the producing conv / GEMM epilogues left behind (sdb_groupnorm_apply_sums):
+    // a group of the virtual concat may straddle the two tensors
+    for (int g = threadIdx.x; g < groups; g += kGnThreads) {
+      long long s = 0;
+      unsigned long long ss = 0;              // fixed point (common.cuh): exact integer sums, whatever the order
+      for (int cc = g * cpg; cc < (g + 1) * cpg; ++cc) {
+        const longlong2 v = cc < C1 ? __ldg(reinterpret_cast<const longlong2*>(cs1) + (long long)b * C1 + cc)
+                                    : __ldg(reinterpret_cast<const longlong2*>(cs2) + (long long)b * C2 + (cc - C1));
+        s += v.x;
+        ss += (unsigned long long)v.y;
+      }
+      const double inv = 1.0 / ((double)cpg * (double)hw);
+      const double mean = (double)s * (1.0 / (double)kChanSumScale) * inv;
+      double var = (double)ss * (1.0 / (double)kChanSqScale) * inv - mean * mean;
+      var = var > 0.0 ? var : 0.0;
+      s_stats[2 * g] = (float)mean;
+      s_stats[2 * g + 1] = rsqrtf((float)var + eps);
+    }
+    __syncthreads();
+  }
   if (r >= R) return;
   const int c = vec * 8;
   float sc[8], sh[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
     const int g = (c + j) / cpg;
-    const float mean = stats[((long long)b * groups + g) * 2];
-    const float rstd = stats[((long long)b * groups + g) * 2 + 1];
+    const float mean = cs1 ? s_stats[2 * g] : stats[((long long)b * groups + g) * 2];
+    const float rstd = cs1 ? s_stats[2 * g + 1] : stats[((long long)b * groups + g) * 2 + 1];
     sc[j] = rstd * gamma[c + j];
     sh[j] = beta[c + j] - mean * sc[j];
   }
@@ -938,13 +963,12 @@ extern "C" int sdb_groupnorm_coop(const void* x1, int C1, const void* x2, int C2
   return SDB_OK;
 }
 
-extern "C" int sdb_groupnorm_apply(const void* x1, int C1, const void* x2, int C2, int dtype,
-                                   const float* stats, const float* gamma, const float* beta, int act,
-                                   void* out, int out_dtype, int B, int64_t hw, int groups,
-                                   void* stream) {
+static int gn_apply_launch(const void* x1, int C1, const void* x2, int C2, int dtype, const float* stats,
+                           const void* cs1, const void* cs2, float eps, const float* gamma, const float* beta,
+                           int act, void* out, int out_dtype, int B, int64_t hw, int groups, void* stream) {
   if (!x2) C2 = 0;
   const int C = C1 + C2;
-  SDB_CHECK_ARG(x1 && stats && gamma && beta && out && B > 0 && hw > 0, "groupnorm_apply: bad args");
+  SDB_CHECK_ARG(x1 && (stats || cs1) && gamma && beta && out && B > 0 && hw > 0, "groupnorm_apply: bad args");
   SDB_CHECK_ARG(C1 % 8 == 0 && C2 % 8 == 0 && groups > 0 && C % groups == 0, "groupnorm_apply: bad channels");
   const int V = C / 8;
   SDB_CHECK_ARG(V <= kGnThreads, "groupnorm_apply: C (%d) too large", C);
@@ -960,7 +984,7 @@ extern "C" int sdb_groupnorm_apply(const void* x1, int C1, const void* x2, int C
   cudaStream_t st = sdb_stream(stream);
 #define SDB_GN_APPLY(T, O)                                                                       \
   gn_apply_kernel<T, O><<<grid, kGnThreads, 0, st>>>((const T*)x1, C1, (const T*)x2, C2, stats, gamma, \
-                                                     beta, act, (O*)out, hw, groups, chunk_px)
+                                                     beta, act, (O*)out, hw, groups, chunk_px, cs1, cs2, eps)
   if (dtype == SDB_BF16 && out_dtype == SDB_BF16) SDB_GN_APPLY(__nv_bfloat16, __nv_bfloat16);
   else if (dtype == SDB_BF16) SDB_GN_APPLY(__nv_bfloat16, float);
   else if (out_dtype == SDB_BF16) SDB_GN_APPLY(float, __nv_bfloat16);
@@ -968,6 +992,27 @@ extern "C" int sdb_groupnorm_apply(const void* x1, int C1, const void* x2, int C
 #undef SDB_GN_APPLY
   SDB_LAUNCH_OK();
   return SDB_OK;
+}
+
+extern "C" int sdb_groupnorm_apply(const void* x1, int C1, const void* x2, int C2, int dtype,
+                                   const float* stats, const float* gamma, const float* beta, int act,
+                                   void* out, int out_dtype, int B, int64_t hw, int groups,
+                                   void* stream) {
+  SDB_CHECK_ARG(stats, "groupnorm_apply: stats is NULL");
+  return gn_apply_launch(x1, C1, x2, C2, dtype, stats, nullptr, nullptr, 0.f, gamma, beta, act, out, out_dtype, B, hw,
+                         groups, stream);
+}
+
+extern "C" int sdb_groupnorm_apply_sums(const void* x1, int C1, const void* sums1, const void* x2, int C2,
+                                        const void* sums2, int dtype, const float* gamma, const float* beta,
+                                        float eps, int act, void* out, int out_dtype, int B, int64_t hw, int groups,
+                                        void* stream) {
+  SDB_CHECK_ARG(sums1 && (!x2 || sums2), "groupnorm_apply_sums: every input tensor needs its channel sums");
+  SDB_CHECK_ARG(groups > 0 && groups <= kGnMaxGroupsSums, "groupnorm_apply_sums: groups (%d) must be <= %d", groups,
+                kGnMaxGroupsSums);
+  SDB_CHECK_ARG(((uintptr_t)sums1 & 15) == 0 && ((uintptr_t)sums2 & 15) == 0, "groupnorm_apply_sums: sums must be 16-byte aligned");
+  return gn_apply_launch(x1, C1, x2, C2, dtype, nullptr, sums1, x2 ? sums2 : nullptr, eps, gamma, beta, act, out,
+                         out_dtype, B, hw, groups, stream);
 }
 
 extern "C" int sdb_add_layernorm(const void* x, const void* res, const float* gamma, const float* beta,

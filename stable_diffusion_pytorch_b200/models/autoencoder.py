@@ -91,11 +91,12 @@ class Encoder(_ConvNet):
     def forward(self, x: Tensor) -> Tensor:
         _pack.require_cuda(x, "Encoder")
         p = self._thin()
-        h = ops.conv3x3_in(x, p["wci"], p["bci"], _pack.compute_dtype())
-        for module in self.down:
-            h = module.forward_nhwc(h)
-        h = self.bottleneck.forward_nhwc(h)
-        return self._head(h, p, x.dtype)
+        with ops.gn_sums_scope(x.device):      # GroupNorm statistics come out of the producing conv epilogues
+            h = ops.conv3x3_in(x, p["wci"], p["bci"], _pack.compute_dtype())
+            for module in self.down:
+                h = module.forward_nhwc(h)
+            h = self.bottleneck.forward_nhwc(h)
+            return self._head(h, p, x.dtype)
 
 
 class Decoder(_ConvNet):
@@ -113,11 +114,12 @@ class Decoder(_ConvNet):
         """``uint8`` (extension): return the PNG-ready [B, H, W, C] uint8 image instead of the float NCHW one."""
         _pack.require_cuda(x, "Decoder")
         p = self._thin()
-        h = ops.conv3x3_in(x, p["wci"], p["bci"], _pack.compute_dtype())
-        h = self.bottleneck.forward_nhwc(h)
-        for module in self.up:
-            h = module.forward_nhwc(h)
-        return self._head(h, p, x.dtype, uint8)
+        with ops.gn_sums_scope(x.device):      # GroupNorm statistics come out of the producing conv epilogues
+            h = ops.conv3x3_in(x, p["wci"], p["bci"], _pack.compute_dtype())
+            h = self.bottleneck.forward_nhwc(h)
+            for module in self.up:
+                h = module.forward_nhwc(h)
+            return self._head(h, p, x.dtype, uint8)
 
 
 class AutoEncoderKL(nn.Module):

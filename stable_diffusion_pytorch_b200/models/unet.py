@@ -170,14 +170,16 @@ class UNetModel(nn.Module):
             views = self._context_kv(p, context_emb)
             kv_of = lambda st_mod: views[id(st_mod)]  # noqa: E731
         # 3. block chain
-        h = ops.conv3x3_in(x, p["wci"], p["bci"], _pack.compute_dtype(), repeat=x_repeat)
-        skips = [h]
-        for module in self.input_blocks:
-            h = module.forward_nhwc(h, temb_of, None, kv_of)
-            skips.append(h)
-        h = self.middle_block.forward_nhwc(h, temb_of, None, kv_of)
-        for module in self.output_blocks:
-            h = module.forward_nhwc(h, temb_of, None, kv_of, x2=skips.pop())
-        # 4. head
-        h = ops.group_norm(h, p["go"], p["bo"], self.groups, ACT_SILU)
+        # (inside the scope the conv / GEMM epilogues leave per-channel sums for the GroupNorm that reads them next)
+        with ops.gn_sums_scope(x.device):
+            h = ops.conv3x3_in(x, p["wci"], p["bci"], _pack.compute_dtype(), repeat=x_repeat)
+            skips = [h]
+            for module in self.input_blocks:
+                h = module.forward_nhwc(h, temb_of, None, kv_of)
+                skips.append(h)
+            h = self.middle_block.forward_nhwc(h, temb_of, None, kv_of)
+            for module in self.output_blocks:
+                h = module.forward_nhwc(h, temb_of, None, kv_of, x2=skips.pop())
+            # 4. head
+            h = ops.group_norm(h, p["go"], p["bo"], self.groups, ACT_SILU)
         return ops.conv3x3_head(h, p["wh"][0], p["wh"][1], self.latent_channels, x.dtype)

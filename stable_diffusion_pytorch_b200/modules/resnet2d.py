@@ -59,7 +59,7 @@ class UpSample(_NhwcModule):
             # inference: the upsampling is folded into the conv as four 2x2-tap phase convolutions (4/9 of the
             # flops, no 4x tensor written and re-read)
             wp = self._cache.get("wup", [self.conv.weight], lambda: _pack.conv3x3_up_w(self.conv.weight))
-            return ops.conv3x3(x, wp, b, up2=True)
+            return ops.conv3x3(x, wp, b, up2=True, sums=True)
         w = self._cache.get("w", [self.conv.weight], lambda: _pack.conv3x3_w(self.conv.weight))
         return ops.conv3x3(ops.upsample2x(x), w, b)
 
@@ -166,7 +166,7 @@ class ResBlock(_NhwcModule):
         p = self._p()
         B, H, W, _ = x.shape
         h = ops.group_norm(x, p["g1"], p["b1"], self.groups, ACT_SILU, x2=x2)
-        h = ops.conv3x3(h, p["w1"], p["cb1"], temb=temb_proj)
+        h = ops.conv3x3(h, p["w1"], p["cb1"], temb=temb_proj, sums=True)     # GN2's statistics from this epilogue
         h = ops.group_norm(h, p["g2"], p["b2"], self.groups, ACT_SILU)
         h = ops.dropout(h, self.dropout or 0.0, self.training)             # out_layers[2] (resnet2d.py:190)
         if "ws" in p:
@@ -176,7 +176,7 @@ class ResBlock(_NhwcModule):
             skip = skip.view(B, H, W, self.out_channels)
         else:
             skip = x if x2 is None else torch.cat([x, x2], dim=-1)
-        return ops.conv3x3(h, p["w2"], p["cb2"], residual=skip)
+        return ops.conv3x3(h, p["w2"], p["cb2"], residual=skip, sums=True)  # the next block's GroupNorm reads it
 
     def project_time(self, time_emb: Tensor) -> Tensor:
         """Linear(SiLU(time_emb)) (resnet2d.py:179-183) for a stand-alone call."""

@@ -286,8 +286,8 @@ class SpatialTransformer(nn.Module):
         t = ops.gemm(h.view(B * H * W, C), wi, bi).view(B, H * W, C)
         for i, blk in enumerate(self.transformer_blocks):
             t = blk.forward_tokens(t, ctx, None if kvs is None else kvs[i])
-        o = ops.gemm(t.view(B * H * W, C), wo, bo, residual=x.view(B * H * W, C))
-        return o.view(B, H, W, C)
+        o = ops.gemm(t.view(B * H * W, C), wo, bo, residual=x.view(B * H * W, C), sums_rows=H * W)
+        return ops.carry_sums(o, o.view(B, H, W, C))      # the next ResBlock's GroupNorm reads it
 
     def forward(self, x: Tensor, context_emb: Tensor = None) -> Tensor:
         assert x.shape[1] == self.in_channels, (

@@ -163,6 +163,102 @@ def test_conv3x3(B, H, W, Cin, Cout, has_temb, has_res, down2):
     assert rel_l2(outb.float(), ref) < 4e-3
 
 
+@pytest.fixture
+def sums_any_size(monkeypatch):
+    """The product only asks for epilogue sums on tensors beyond the L2 (SDB_GN_SUMS_MIN_MB); the tests take them all."""
+    monkeypatch.setattr(ops, "_GN_SUMS_MIN_BYTES", 0)
+
+
+SUMS_CASES = [
+    # B, H, W, Cin, Cout, kind
+    (2, 16, 16, 32, 64, "plain"),
+    (2, 64, 64, 160, 160, "temb"),     # the UNet's level-0 ResBlock conv1 (BN = 160: 80 column pairs, tail slab)
+    (3, 32, 32, 64, 320, "res"),       # two n-tiles, residual
+    (2, 16, 16, 128, 128, "up2"),      # four phase launches add into one buffer
+    (1, 8, 16, 32, 80, "plain"),       # one tile per image, 16-column tail slab
+    (2, 64, 64, 128, 256, "plain"),    # BN = 256, CTA pairs, several tiles per CTA and image
+    (40, 16, 16, 64, 64, "res"),       # many images: the per-thread partials are flushed at every image change
+]
+
+
+@pytest.mark.parametrize("B,H,W,Cin,Cout,kind", SUMS_CASES)
+def test_conv3x3_channel_sums(B, H, W, Cin, Cout, kind, sums_any_size):
+    """GroupNorm statistics out of the producing conv's epilogue (resnet2d.py:171-177,187-198): inside a
+    gn_sums_scope the conv also leaves per-(image, channel) sum / sum of squares of its bf16 output; group_norm
+    then normalises without its statistics pass.  Checked: the conv output is unchanged, the sums match torch's, and
+    the normalised result matches the two-pass route."""
+    from stable_diffusion_pytorch_b200 import _pack
+    up2 = kind == "up2"
+    x = rnd(B, H, W, Cin, seed=1)
+    bias = rnd(Cout, seed=3, dtype=torch.float32)
+    temb = rnd(B, Cout, seed=4, dtype=torch.float32) if kind == "temb" else None
+    Ho, Wo = (2 * H, 2 * W) if up2 else (H, W)
+    res = rnd(B, Ho, Wo, Cout, seed=5) if kind == "res" else None
+    if up2:
+        w = _pack.conv3x3_up_w(rnd(Cout, Cin, 3, 3, seed=2, scale=1 / math.sqrt(9 * Cin), dtype=torch.float32))
+    else:
+        w = rnd(Cout, 3, 3, Cin, seed=2, scale=1 / math.sqrt(9 * Cin))
+    plain = ops.conv3x3(x, w, bias, temb, res, up2=up2)
+    gamma = rnd(Cout, seed=6, dtype=torch.float32) + 1.0
+    beta = rnd(Cout, seed=7, dtype=torch.float32)
+    groups = 16
+    want = ops.group_norm(plain, gamma, beta, groups, ops.ACT_SILU)
+    with ops.gn_sums_scope(x.device):
+        out = ops.conv3x3(x, w, bias, temb, res, up2=up2, sums=True)
+        sums = ops._sums_of(out)
+        assert sums is not None, "the epilogue did not take the channel sums for this shape"
+        got = ops.group_norm(out, gamma, beta, groups, ops.ACT_SILU)
+        sums = sums.clone().view(B, Cout, 2)
+    with ops.gn_sums_scope(x.device):         # 64-bit fixed-point atomics: bit-identical from run to run
+        out2 = ops.conv3x3(x, w, bias, temb, res, up2=up2, sums=True)
+        assert torch.equal(ops._sums_of(out2).view(B, Cout, 2), sums)
+        assert torch.equal(ops.group_norm(out2, gamma, beta, groups, ops.ACT_SILU), got)
+    assert torch.equal(out, plain)
+    o = out.double().view(B, Ho * Wo, Cout)
+    ref_s, ref_q = o.sum(1), (o * o).sum(1)
+    got_s, got_q = sums[..., 0].double() / ops.SUM_SCALE, sums[..., 1].double() / ops.SQ_SCALE
+    assert float((got_s - ref_s).abs().max()) < 1e-3 * float(ref_q.max().sqrt() * math.sqrt(Ho * Wo)) + 1e-3
+    assert rel_l2(got_q, ref_q) < 1e-5
+    assert rel_l2(got.float(), want.float()) < 2e-3
+    assert ops._sums_of(out) is None          # outside the scope the tag is void
+
+
+def test_channel_sums_fallbacks_and_concat(sums_any_size):
+    """Shapes the epilogue cannot cover keep the usual route; a GroupNorm over the virtual concat of two tagged
+    tensors (the UNet's up path) whose group straddles the boundary; a GEMM producer (SpatialTransformer.proj_out)."""
+    gamma = rnd(112, seed=6, dtype=torch.float32) + 1.0
+    beta = rnd(112, seed=7, dtype=torch.float32)
+    x = rnd(2, 16, 16, 32, seed=1)
+    wa = rnd(80, 3, 3, 32, seed=2, scale=0.06)
+    wb = rnd(32, 3, 3, 32, seed=3, scale=0.06)
+    a0, b0 = ops.conv3x3(x, wa, None), ops.conv3x3(x, wb, None)
+    want = ops.group_norm(a0, gamma, beta, 16, ops.ACT_SILU, x2=b0)            # 7 channels per group: group 11 straddles
+    with ops.gn_sums_scope(x.device):
+        a1, b1 = ops.conv3x3(x, wa, None, sums=True), ops.conv3x3(x, wb, None, sums=True)
+        assert ops._sums_of(a1) is not None and ops._sums_of(b1) is not None
+        got = ops.group_norm(a1, gamma, beta, 16, ops.ACT_SILU, x2=b1)
+        half = ops.group_norm(a1, gamma, beta, 16, ops.ACT_SILU, x2=b0)        # one side untagged: two-pass route
+        # 8 x 8 images: two images per 128-pixel tile -> not taken, no tag, same result
+        xs = rnd(4, 8, 8, 32, seed=4)
+        small = ops.conv3x3(xs, wb, None, sums=True)
+        assert ops._sums_of(small) is None
+        assert torch.equal(small, ops.conv3x3(xs, wb, None))
+        # GEMM producer with residual, rows_per_image = 256
+        t = rnd(512, 64, seed=8)
+        wg = rnd(96, 64, seed=9, scale=0.12)
+        r = rnd(512, 96, seed=10)
+        o = ops.gemm(t, wg, None, residual=r, sums_rows=256)
+        sg = ops._sums_of(o)
+        assert sg is not None
+        sg = sg.clone().view(2, 96, 2)
+    assert rel_l2(got.float(), want.float()) < 2e-3
+    assert torch.equal(half, want)
+    assert torch.equal(o, ops.gemm(t, wg, None, residual=r))
+    of = o.double().view(2, 256, 96)
+    assert rel_l2(sg[..., 1].double() / ops.SQ_SCALE, (of * of).sum(1)) < 1e-5
+    assert float((sg[..., 0].double() / ops.SUM_SCALE - of.sum(1)).abs().max()) < 5e-2
+
+
 UP_CASES = [
     # B, H, W, Cin, Cout, residual   (low-resolution input H x W -> 2H x 2W)
     (1, 8, 8, 64, 64, False),

@@ -192,6 +192,39 @@ def test_vae_decode_kl_shape_vs_oracle():
     assert e < VAE_BF16_TOL
 
 
+def test_epilogue_channel_sums_route_vs_goldens(golden, monkeypatch):
+    """GroupNorm statistics taken from the producing conv / GEMM epilogues (north_star: "GroupNorm fused with its
+    producer"; by default only for tensors beyond the L2): forced on for every tensor here, the reference goldens must
+    hold to the same tolerances, and the route must really have been taken."""
+    from stable_diffusion_pytorch_b200 import ops
+    from stable_diffusion_pytorch_b200.models import AutoEncoderKL, AutoencoderConfig
+    monkeypatch.setattr(ops, "_GN_SUMS_MIN_BYTES", 0)
+    before = dict(ops.sums_counters)
+    for name in cases.UNET_CASES:
+        cfg, seed, B, H, W = cases.UNET_CASES[name]
+        m, _ = build_unet(cfg, seed)
+        x, t, ctx = cases.unet_inputs(cfg, B, H, W, seed)
+        with torch.no_grad():
+            y = m(x.to(DEV), t.to(DEV), ctx.to(DEV))
+            y2 = m(x.to(DEV), t.to(DEV), ctx.to(DEV))
+        err = rel_l2(y, golden[f"unet_{name}"])
+        print(f"unet {name} (epilogue sums): {err:.3e}")
+        assert err < UNET_BF16_TOL
+        assert torch.equal(y, y2)                      # integer atomics: run-to-run identical
+    for name in cases.VAE_CASES:
+        cfg, seed, B, H, W = cases.VAE_CASES[name]
+        m = AutoEncoderKL(AutoencoderConfig(autoencoder_channels_list=list(cfg.autoencoder_channels_list),
+                                            groups=cfg.groups)).eval()
+        m.load_state_dict(O.seeded_state_dict(O.vae_decoder_param_shapes(cfg), seed), strict=False)
+        m = m.to(DEV)
+        with torch.no_grad():
+            y = m.decode(cases.vae_inputs(cfg, B, H, W, seed).to(DEV))
+        e = rel_l2(y, golden[f"vae_{name}"])
+        print(f"vae {name} (epilogue sums): {e:.3e}")
+        assert e < VAE_BF16_TOL
+    assert ops.sums_counters["tagged"] > before["tagged"] and ops.sums_counters["consumed"] > before["consumed"]
+
+
 # ---------------------------------------------------------------- ragged shapes / edge cases
 @pytest.mark.parametrize("B,H,W,ctx_len", [
     (1, 8, 8, 77),       # smallest latent the reference runs at (64 px / 8)
