@@ -49,6 +49,14 @@ struct UmmaParams {
   // Tiles are enumerated n-major over tiles_m padded to even; every CTA runs `tiles_per_cta` iterations, ghosts
   // included (zero-filled loads, clipped stores).
   int pair, tiles_m_pad, tiles_per_cta;
+  // halo loader (conv, W % 128 == 0: a tile = 128 pixels of ONE image row): instead of one shifted 128 x BK box per tap,
+  // ONE (rows x halo_w)-pixel block per channel block is fetched and every tap's A operand is a view into it -- a UMMA
+  // descriptor may start at any 128-byte row of a SWIZZLE_128B tile (the swizzle is a function of the address bits;
+  // tools/ubench_halo.cu) -- so an activation byte crosses L2 -> SM 3.05x instead of 9x per output tile.  Two rings:
+  // stages [0, halo_nA) hold halo blocks (warp 3 loads them), stages [halo_nA, halo_nA + halo_nB) weight tiles (warp 0).
+  int halo, halo_w, halo_nA, halo_nB, halo_stage_bytes, halo_box_bytes, halo_dw0, halo_dh0;
+  short tap_row[9];   // first halo-block row of the tap's view
+  int ring_bytes;     // operand ring(s) in shared memory
   // conv geometry (GEMM-M space = input-resolution pixels)
   int kb_per_tap, Cin;
   int TW, TH, TN, tiles_w, tiles_h;
@@ -405,7 +413,7 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
   // 1024-B aligned: [resident B][operand ring][staging buffers][bias rows][barriers]
   const uint32_t smem_base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   const uint32_t ring_base = smem_base + (uint32_t)p.bres_bytes;
-  const uint32_t stg_base = ring_base + (uint32_t)p.num_stages * (uint32_t)p.stage_bytes;
+  const uint32_t stg_base = ring_base + (uint32_t)p.ring_bytes;
   const uint32_t bias_base = stg_base + (uint32_t)p.nbuf * (uint32_t)p.stg_bytes;
   const uint32_t bar_base = bias_base + (uint32_t)kBiasBytes;
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
@@ -478,10 +486,38 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
       }
       __syncwarp();
     }
+    if (p.halo) {
+      // halo mode: this warp streams the weight tiles (tap-minor inside a channel block, the MMA warp's order)
+      const uint32_t txb = (k2 ? 2u : 1u) * (uint32_t)p.b_bytes;
+      const uint32_t bring = ring_base + (uint32_t)p.halo_nA * (uint32_t)p.halo_stage_bytes;
+      const int n_tap = p.num_kb / p.kb_per_tap;
+      for (; tw.valid() && ok; tw.next()) {
+        const int n0 = tw.n * p.BN;
+        for (int kb = 0; kb < p.kb_per_tap && ok; ++kb) {
+          for (int tap = 0; tap < n_tap; ++tap) {
+            ok = mbar_wait(empty_bar(p.halo_nA + stage), phase ^ 1u);
+            if (!ok) break;
+            const uint32_t sb = bring + (uint32_t)stage * (uint32_t)p.b_bytes;
+            if (elect_one()) {
+              if (k2) {
+                const uint32_t lead_full = sdb_mapa(full_bar(p.halo_nA + stage), 0u);
+                if (pair_rank == 0) mbar_arrive_expect_tx(full_bar(p.halo_nA + stage), txb);
+                tma_load_2d_2cta(sb, &p.tmB, lead_full, tap * p.Cin + kb * p.BK, n0 + (int)pair_rank * (p.BN >> 1));
+              } else {
+                mbar_arrive_expect_tx(full_bar(p.halo_nA + stage), txb);
+                tma_load_2d(sb, &p.tmB, full_bar(p.halo_nA + stage), tap * p.Cin + kb * p.BK, n0);
+              }
+            }
+            __syncwarp();
+            if (++stage == p.halo_nB) { stage = 0; phase ^= 1u; }
+          }
+        }
+      }
+    }
     // pair: the leader's barrier collects both CTAs' A tile and weight half
     const uint32_t tx = k2 ? 2u * (uint32_t)(p.a_bytes + p.b_bytes)
                            : (uint32_t)(p.resB ? p.a_bytes : p.a_bytes + p.b_bytes);
-    for (int j = 0; tw.valid() && ok; tw.next(), ++j) {
+    for (int j = 0; !p.halo && tw.valid() && ok; tw.next(), ++j) {
       GEMM_TRACE(0, j, 0);
       const int m_tile = tw.m;
       const int n0 = tw.n * p.BN;
@@ -539,8 +575,8 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
     const uint32_t b_step = p.resB ? ((uint32_t)p.b_bytes >> 4) : 0u;
     const uint32_t b_lo0 = p.resB ? ((smem_base & 0x3ffffu) >> 4) : a_lo0 + ((uint32_t)p.a_bytes >> 4);
     const bool bk64 = p.BK == 64;
-    int stage = 0;
-    uint32_t phase = 0;
+    int stage = 0, hb_stage = 0;
+    uint32_t phase = 0, hb_phase = 0;
     uint32_t a_lo = a_lo0;
     bool ok = true;
     TileWalk tw(p);
@@ -555,7 +591,46 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
       tc_fence_after();
       const uint32_t tmem_d = tmem_base + (uint32_t)acc * kMaxBN;
       uint32_t b_lo = b_lo0;
-      for (int kb = 0; kb < p.num_kb; ++kb) {
+      if (p.halo) {
+        // one halo block per channel block, its taps as row-shifted views; `stage` / `phase` walk the halo ring,
+        // hb_stage / hb_phase the weight ring
+        const int n_tap = p.num_kb / p.kb_per_tap;
+        const uint32_t bring = ring_base + (uint32_t)p.halo_nA * (uint32_t)p.halo_stage_bytes;
+        for (int kb = 0; kb < p.kb_per_tap && ok; ++kb) {
+          ok = mbar_wait(full_bar(stage), phase);
+          if (!ok) break;
+          const uint32_t sa = ring_base + (uint32_t)stage * (uint32_t)p.halo_stage_bytes;
+          for (int tap = 0; tap < n_tap; ++tap) {
+            ok = mbar_wait(full_bar(p.halo_nA + hb_stage), hb_phase);
+            if (!ok) break;
+            tc_fence_after();
+            const uint64_t adesc = desc_hi | (uint64_t)(((sa + (uint32_t)p.tap_row[tap] * 128u) & 0x3ffffu) >> 4);
+            const uint64_t bdesc = desc_hi | (uint64_t)(((bring + (uint32_t)hb_stage * (uint32_t)p.b_bytes) & 0x3ffffu) >> 4);
+            if (elect_one()) {
+              const uint32_t first = (kb | tap) != 0 ? 1u : 0u;
+              if (k2) {
+                umma_f16_2cta(tmem_d, adesc, bdesc, idesc, first);
+                umma_f16_2cta(tmem_d, adesc + 2, bdesc + 2, idesc, 1u);
+                umma_f16_2cta(tmem_d, adesc + 4, bdesc + 4, idesc, 1u);
+                umma_f16_2cta(tmem_d, adesc + 6, bdesc + 6, idesc, 1u);
+                umma_commit_2cta(empty_bar(p.halo_nA + hb_stage));
+                if (tap == n_tap - 1) umma_commit_2cta(empty_bar(stage));
+              } else {
+                umma_f16(tmem_d, adesc, bdesc, idesc, first);
+                umma_f16(tmem_d, adesc + 2, bdesc + 2, idesc, 1u);
+                umma_f16(tmem_d, adesc + 4, bdesc + 4, idesc, 1u);
+                umma_f16(tmem_d, adesc + 6, bdesc + 6, idesc, 1u);
+                umma_commit(empty_bar(p.halo_nA + hb_stage));
+                if (tap == n_tap - 1) umma_commit(empty_bar(stage));
+              }
+            }
+            __syncwarp();
+            if (++hb_stage == p.halo_nB) { hb_stage = 0; hb_phase ^= 1u; }
+          }
+          if (++stage == p.halo_nA) { stage = 0; phase ^= 1u; }
+        }
+      }
+      for (int kb = 0; !p.halo && kb < p.num_kb; ++kb) {
         ok = mbar_wait(full_bar(stage), phase);
         if (!ok) break;
         tc_fence_after();
@@ -714,6 +789,37 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
     if (p.staged) {
       if (elect_one()) tma_store_wait_read();            // smem must outlive the last store's reads
       __syncwarp();
+    }
+  } else if (warp == 3) {
+    // ===================== halo-block producer (halo mode only) =====================
+    if (p.halo) {
+      int stage = 0;
+      uint32_t phase = 0;
+      bool ok = true;
+      const uint32_t txa = (k2 ? 2u : 1u) * (uint32_t)p.halo_box_bytes;
+      for (TileWalk tw(p); tw.valid() && ok; tw.next()) {
+        const int m_tile = tw.m;
+        const int w0 = (m_tile % p.tiles_w) * p.TW + p.halo_dw0;
+        const int h0 = ((m_tile / p.tiles_w) % p.tiles_h) * p.TH + p.halo_dh0;
+        const int i0 = (m_tile / (p.tiles_w * p.tiles_h)) * p.TN;
+        for (int kb = 0; kb < p.kb_per_tap; ++kb) {
+          ok = mbar_wait(empty_bar(stage), phase ^ 1u);
+          if (!ok) break;
+          const uint32_t sa = ring_base + (uint32_t)stage * (uint32_t)p.halo_stage_bytes;
+          if (elect_one()) {
+            if (k2) {
+              const uint32_t lead_full = sdb_mapa(full_bar(stage), 0u);
+              if (pair_rank == 0) mbar_arrive_expect_tx(full_bar(stage), txa);
+              tma_load_4d_2cta(sa, &p.tmA[0], lead_full, kb * p.BK, w0, h0, i0);
+            } else {
+              mbar_arrive_expect_tx(full_bar(stage), txa);
+              tma_load_4d(sa, &p.tmA[0], full_bar(stage), kb * p.BK, w0, h0, i0);
+            }
+          }
+          __syncwarp();
+          if (++stage == p.halo_nA) { stage = 0; phase ^= 1u; }
+        }
+      }
     }
   } else if (warp >= 4) {
     // ===================== epilogue warpgroups =====================
@@ -962,6 +1068,41 @@ static void finish_stages(UmmaParams& p) {
     p.nbuf = 1;
   int s = (kSmemBudget - p.bres_bytes - p.nbuf * p.stg_bytes) / p.stage_bytes;
   p.num_stages = s > kMaxStages ? kMaxStages : s;
+  p.ring_bytes = p.num_stages * p.stage_bytes;
+}
+
+// Halo loader plan (UmmaParams::halo) for a conv whose tile is 128 pixels of one image row; call after finish_stages().
+// `n_tap` taps with offsets p.tap_dh / p.tap_dw.  Keeps the classic ring when the blocks do not fit.
+static void plan_halo(UmmaParams& p, int n_tap) {
+  static int halo_on = -1;
+  if (halo_on < 0) { const char* e = getenv("SDB_CONV_HALO"); halo_on = e ? atoi(e) : 1; }
+  if (!halo_on || p.mode != 1 || p.BK != 64 || p.TW != kTileM || p.TH != 1 || p.TN != 1) return;
+  int dh0 = 127, dh1 = -127, dw0 = 127, dw1 = -127;
+  for (int t = 0; t < n_tap; ++t) {
+    dh0 = p.tap_dh[t] < dh0 ? p.tap_dh[t] : dh0; dh1 = p.tap_dh[t] > dh1 ? p.tap_dh[t] : dh1;
+    dw0 = p.tap_dw[t] < dw0 ? p.tap_dw[t] : dw0; dw1 = p.tap_dw[t] > dw1 ? p.tap_dw[t] : dw1;
+  }
+  const int rows = dh1 - dh0 + 1, hw = kTileM + (dw1 - dw0);
+  const int box = rows * hw * 128;
+  const int stage = (box + 1023) & ~1023;
+  for (int nA = 3; nA >= 2; --nA) {
+    const int rem = kSmemBudget - p.nbuf * p.stg_bytes - nA * stage;
+    int nB = rem > 0 ? rem / p.b_bytes : 0;
+    if (nB > kMaxStages - nA) nB = kMaxStages - nA;
+    if (nB < (nA == 3 ? 4 : 3)) continue;
+    p.halo = 1;
+    p.halo_w = hw;
+    p.halo_nA = nA;
+    p.halo_nB = nB;
+    p.halo_stage_bytes = stage;
+    p.halo_box_bytes = box;
+    p.halo_dw0 = dw0;
+    p.halo_dh0 = dh0;
+    for (int t = 0; t < n_tap; ++t) p.tap_row[t] = (short)((p.tap_dh[t] - dh0) * hw + (p.tap_dw[t] - dw0));
+    p.num_stages = nA + nB;
+    p.ring_bytes = nA * stage + nB * p.b_bytes;
+    return;
+  }
 }
 
 // output / residual tensor maps of the staged epilogue: `rank` 2 (GEMM rows) or 4 (conv pixel boxes)
@@ -1261,6 +1402,7 @@ extern "C" int sdb_conv3x3(const SdbConvArgs* a, void* stream) {
       p.tap_dw[t] = (signed char)(t % 3 - 1);
     }
   }
+  plan_halo(p, n_tap);
   p.M = 0;
   p.N = a->Cout;
   p.bias = a->bias;
@@ -1287,6 +1429,7 @@ extern "C" int sdb_conv3x3(const SdbConvArgs* a, void* stream) {
   uint64_t strides[4] = {0, (uint64_t)a->Cin * 2, (uint64_t)a->W * a->Cin * 2,
                          (uint64_t)a->H * a->W * a->Cin * 2};
   uint32_t box[4] = {(uint32_t)p.BK, (uint32_t)tw, (uint32_t)th, (uint32_t)tn};
+  if (p.halo) { box[1] = (uint32_t)p.halo_w; box[2] = (uint32_t)(p.halo_box_bytes / (p.halo_w * 128)); }
   int rc = sdb_make_tensor_map(&p.tmA[0], a->x, 2, 4, dims, strides, box, p.swz);
   if (rc) return rc;
   uint64_t wd[2] = {(uint64_t)n_tap * a->Cin, (uint64_t)a->Cout};

@@ -130,7 +130,13 @@ CONV_CASES = [
     (1, 64, 64, 480, 320, True, True, False),   # virtual-concat sized K, 2 N tiles
     (1, 4, 4, 32, 32, False, False, False),     # tiny map
     (2, 16, 16, 96, 96, False, False, False),
-    (1, 128, 128, 64, 64, False, False, False), # W = 128: one image row per tile
+    (1, 128, 128, 64, 64, False, False, False), # W = 128: one image row per tile -> the halo loader (one 3 x 130 pixel
+                                                # block per channel block, nine row-shifted views), CTA pairs
+    (2, 8, 256, 128, 128, True, True, False),   # halo: two tiles per image row, two channel blocks, residual + temb
+    (1, 5, 128, 192, 96, True, False, False),   # halo: three channel blocks, odd tile count (a ghost tile in the pair walk)
+    (1, 2, 128, 64, 64, False, True, False),    # halo without CTA pairs (too few tiles)
+    (1, 16, 128, 256, 512, False, False, False),  # halo at BN = 256: two weight-ring stages fewer, two N tiles
+    (1, 6, 128, 64, 64, False, False, True),    # W = 128 with DownSample (direct epilogue)
     (2, 12, 20, 64, 64, True, True, False),     # W without a power-of-two factor >= 8: clipped 8-wide boxes
     (1, 10, 6, 32, 48, False, True, False),     # W < 8
     (3, 6, 12, 64, 32, True, False, True),      # ragged + DownSample
@@ -266,6 +272,8 @@ UP_CASES = [
     (2, 16, 16, 160, 96, True),       # K tail (160 = 2.5 k-blocks), residual at the output resolution
     (3, 6, 10, 64, 32, False),        # ragged: clipped boxes, W without a power-of-two factor >= 8
     (1, 64, 64, 512, 512, False),     # VAE decoder shape: BN = 256, two N tiles
+    (1, 6, 128, 64, 64, True),        # W = 128: the phases run on the halo loader (2 x 129 pixel blocks)
+    (2, 4, 256, 128, 64, False),
     (1, 4, 4, 32, 48, True),
 ]
 
