@@ -57,6 +57,7 @@ struct UmmaParams {
   int halo, halo_w, halo_nA, halo_nB, halo_stage_bytes, halo_box_bytes, halo_dw0, halo_dh0;
   short tap_row[9];   // first halo-block row of the tap's view
   int ring_bytes;     // operand ring(s) in shared memory
+  int issue_group;    // halo mode: taps the MMA warp waits for and issues per round trip (1 or 2)
   // conv geometry (GEMM-M space = input-resolution pixels)
   int kb_per_tap, Cin;
   int TW, TH, TN, tiles_w, tiles_h;
@@ -577,6 +578,7 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
     const bool bk64 = p.BK == 64;
     int stage = 0, hb_stage = 0;
     uint32_t phase = 0, hb_phase = 0;
+    const bool grp2 = p.halo && p.issue_group >= 2;
     uint32_t a_lo = a_lo0;
     bool ok = true;
     TileWalk tw(p);
@@ -600,7 +602,56 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
           ok = mbar_wait(full_bar(stage), phase);
           if (!ok) break;
           const uint32_t sa = ring_base + (uint32_t)stage * (uint32_t)p.halo_stage_bytes;
-          for (int tap = 0; tap < n_tap; ++tap) {
+          int tap = 0;
+          // narrow tiles (N <= 128): two taps per issue round trip -- barrier wait, election, descriptor set-up and commit
+          // by one thread take of the order of 400 cycles, longer than four such MMAs (the N = 16 image head most of all)
+          for (; grp2 && tap + 1 < n_tap; tap += 2) {
+            int s1 = hb_stage + 1;
+            uint32_t ph1 = hb_phase;
+            if (s1 == p.halo_nB) { s1 = 0; ph1 ^= 1u; }
+            ok = mbar_wait(full_bar(p.halo_nA + hb_stage), hb_phase);
+            if (!ok) break;
+            ok = mbar_wait(full_bar(p.halo_nA + s1), ph1);
+            if (!ok) break;
+            tc_fence_after();
+            const uint64_t ad0 = desc_hi | (uint64_t)(((sa + (uint32_t)p.tap_row[tap] * 128u) & 0x3ffffu) >> 4);
+            const uint64_t ad1 = desc_hi | (uint64_t)(((sa + (uint32_t)p.tap_row[tap + 1] * 128u) & 0x3ffffu) >> 4);
+            const uint64_t bd0 = desc_hi | (uint64_t)(((bring + (uint32_t)hb_stage * (uint32_t)p.b_bytes) & 0x3ffffu) >> 4);
+            const uint64_t bd1 = desc_hi | (uint64_t)(((bring + (uint32_t)s1 * (uint32_t)p.b_bytes) & 0x3ffffu) >> 4);
+            if (elect_one()) {
+              const uint32_t first = (kb | tap) != 0 ? 1u : 0u;
+              if (k2) {
+                umma_f16_2cta(tmem_d, ad0, bd0, idesc, first);
+                umma_f16_2cta(tmem_d, ad0 + 2, bd0 + 2, idesc, 1u);
+                umma_f16_2cta(tmem_d, ad0 + 4, bd0 + 4, idesc, 1u);
+                umma_f16_2cta(tmem_d, ad0 + 6, bd0 + 6, idesc, 1u);
+                umma_commit_2cta(empty_bar(p.halo_nA + hb_stage));
+                umma_f16_2cta(tmem_d, ad1, bd1, idesc, 1u);
+                umma_f16_2cta(tmem_d, ad1 + 2, bd1 + 2, idesc, 1u);
+                umma_f16_2cta(tmem_d, ad1 + 4, bd1 + 4, idesc, 1u);
+                umma_f16_2cta(tmem_d, ad1 + 6, bd1 + 6, idesc, 1u);
+                umma_commit_2cta(empty_bar(p.halo_nA + s1));
+                if (tap + 2 == n_tap) umma_commit_2cta(empty_bar(stage));
+              } else {
+                umma_f16(tmem_d, ad0, bd0, idesc, first);
+                umma_f16(tmem_d, ad0 + 2, bd0 + 2, idesc, 1u);
+                umma_f16(tmem_d, ad0 + 4, bd0 + 4, idesc, 1u);
+                umma_f16(tmem_d, ad0 + 6, bd0 + 6, idesc, 1u);
+                umma_commit(empty_bar(p.halo_nA + hb_stage));
+                umma_f16(tmem_d, ad1, bd1, idesc, 1u);
+                umma_f16(tmem_d, ad1 + 2, bd1 + 2, idesc, 1u);
+                umma_f16(tmem_d, ad1 + 4, bd1 + 4, idesc, 1u);
+                umma_f16(tmem_d, ad1 + 6, bd1 + 6, idesc, 1u);
+                umma_commit(empty_bar(p.halo_nA + s1));
+                if (tap + 2 == n_tap) umma_commit(empty_bar(stage));
+              }
+            }
+            __syncwarp();
+            hb_stage = s1 + 1;
+            hb_phase = ph1;
+            if (hb_stage == p.halo_nB) { hb_stage = 0; hb_phase ^= 1u; }
+          }
+          for (; ok && tap < n_tap; ++tap) {
             ok = mbar_wait(full_bar(p.halo_nA + hb_stage), hb_phase);
             if (!ok) break;
             tc_fence_after();
@@ -1158,6 +1209,9 @@ static int launch_umma_epi(const UmmaParams& p, int grid, int smem, cudaStream_t
 
 static int launch_umma(UmmaParams& p, cudaStream_t st) {
   const int smem = kSmemBudget + kBiasBytes + 1024 /* alignment */ + 512 /* barriers */;
+  static int issue_group = -1;     // SDB_MMA_GROUP=1|2: A/B measurements
+  if (issue_group < 0) { const char* e = getenv("SDB_MMA_GROUP"); issue_group = e && atoi(e) > 0 ? atoi(e) : 2; }
+  p.issue_group = (p.halo && p.halo_nB >= 3 && p.BN <= 128) ? issue_group : 1;   // wide tiles: the ring depth matters more
   if (p.num_stages < 2) {
     sdb_set_error("umma: tile %dx%d (BK %d) leaves no room for a 2-stage operand ring", kTileM, p.BN, p.BK);
     return SDB_EUNSUPPORTED;
