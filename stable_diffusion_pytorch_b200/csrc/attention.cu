@@ -253,6 +253,15 @@ extern "C" int sdb_attention(const void* q, int64_t ldq, const void* k, int64_t 
                 "attention: pointers must be 8-byte aligned");
   SDB_CHECK_ARG(heads <= 65535 && B <= 65535, "attention: grid too large");
   cudaStream_t st = sdb_stream(stream);
+  if (d == 128) {
+    // the tensor-bound shape (VAE bottleneck): tcgen05 pipeline; SDB_ATTN_D128_UMMA=0 keeps the mma.sync kernel (A/B)
+    static int umma128 = -1;
+    if (umma128 < 0) { const char* e = getenv("SDB_ATTN_D128_UMMA"); umma128 = e ? atoi(e) : 1; }
+    if (umma128) {
+      const int rc = sdb_attention_d128_dispatch(q, ldq, k, ldk, v, ldv, out, ldo, B, heads, n, m, scale, st);
+      if (rc != SDB_EUNSUPPORTED) return rc;
+    }
+  }
   if (d <= 32) return launch_attention<32>(q, ldq, k, ldk, v, ldv, out, ldo, B, heads, n, m, d, scale, st);
   if (d <= 64) return launch_attention<64>(q, ldq, k, ldk, v, ldv, out, ldo, B, heads, n, m, d, scale, st);
   return launch_attention<128>(q, ldq, k, ldk, v, ldv, out, ldo, B, heads, n, m, d, scale, st);

@@ -38,6 +38,7 @@ struct FaParams {
 
 #include "attention_umma_wg1.cu"   // the one-warpgroup-per-CTA shape of the same pipeline (uses the helpers above)
 #include "attention_ctx_umma.cu"   // short context (<= 96 keys): K / V resident, query tiles streamed
+#include "attention_d128_umma.cu"  // dense attention, head dim 128 (the VAE bottleneck)
 
 static int attention_p32_impl(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v,
                               int64_t ldv, void* out, int64_t ldo, int B, int heads, int n, int m, int d,

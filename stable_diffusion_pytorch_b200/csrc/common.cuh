@@ -51,7 +51,10 @@ int sdb_attention_f32_impl(const void* q, int64_t ldq, const void* k, int64_t ld
                            cudaStream_t st);                                   // precise_f32.cu
 int sdb_attention_ctx_dispatch(const void* q, long long ldq, const void* k, long long ldk, const void* v,
                                long long ldv, void* out, long long ldo, int B, int heads, int n, int m, int d,
-                               float scale, cudaStream_t st);                  // attention_ctx.cu
+                               float scale, cudaStream_t st);
+// tcgen05 dense attention for head dim 128 (attention_d128_umma.cu); SDB_EUNSUPPORTED = operands not TMA-addressable
+int sdb_attention_d128_dispatch(const void* q, int64_t ldq, const void* k, int64_t ldk, const void* v, int64_t ldv,
+                                void* out, int64_t ldo, int B, int heads, int n, int m, float scale, cudaStream_t stream);                  // attention_ctx.cu
 }  // namespace sdb
 
 // Encodes a tiled tensor map (rank <= 5) for a bf16/fp32 tensor.  dims/strides innermost first;

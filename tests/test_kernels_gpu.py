@@ -422,7 +422,9 @@ def test_layout_and_elementwise():
 # ------------------------------------------------------------------ attention
 @pytest.mark.parametrize("B,heads,n,m,d", [
     (2, 8, 256, 256, 20), (1, 8, 1024, 1024, 20), (2, 8, 300, 77, 20), (2, 4, 64, 64, 16),
-    (1, 1, 256, 256, 64), (1, 1, 200, 200, 128), (2, 2, 128, 77, 32)])
+    (1, 1, 256, 256, 64), (1, 1, 200, 200, 128), (2, 2, 128, 77, 32),
+    # head dim 128: the tcgen05 kernel of the VAE bottleneck (ragged rows / keys, several heads, the config-3 shape)
+    (2, 2, 1024, 1024, 128), (1, 1, 130, 77, 128), (1, 3, 64, 640, 128), (2, 1, 4096, 4096, 128)])
 def test_attention(B, heads, n, m, d):
     dm = heads * d
     qkv = rnd(B, n, 3 * dm, seed=1)
@@ -495,6 +497,26 @@ def test_attention_p32_growing_scores(growth):
     qf = q.float().view(B, n, heads, 32)[..., :d].transpose(1, 2)
     kf = k.float().view(B, m, heads, 32)[..., :d].transpose(1, 2)
     vf = v.float().view(B, m, heads, 32)[..., :d].transpose(1, 2)
+    ref = (torch.softmax(qf @ kf.transpose(-1, -2) * scale, -1) @ vf).transpose(1, 2).reshape(B, n, heads * d)
+    assert torch.isfinite(out.float()).all()
+    assert rel_l2(out.float(), ref) < 1e-2
+
+
+@pytest.mark.parametrize("growth", [0.3, 2.0, 12.0])
+def test_attention_d128_growing_scores(growth):
+    """Head dim 128 (tcgen05 kernel): scores that keep growing along the keys exercise the lazy rescale of the
+    128-column accumulator and of the register row sum."""
+    B, heads, n, m, d = 1, 2, 256, 512, 128
+    g = torch.Generator(device="cpu").manual_seed(9)
+    q = 0.02 * torch.randn(B, n, heads, d, generator=g)
+    k = 0.02 * torch.randn(B, m, heads, d, generator=g)
+    q[..., 0] = 4.0
+    k[..., 0] = growth * torch.arange(m).float()[None, :, None] / 4.0
+    v = torch.randn(B, m, heads, d, generator=g)
+    q, k, v = (t.reshape(B, -1, heads * d).to("cuda", torch.bfloat16) for t in (q, k, v))
+    scale = 1 / math.sqrt(d)
+    out = ops.attention(q, k, v, heads, d, scale)
+    qf, kf, vf = (t.float().view(B, -1, heads, d).transpose(1, 2) for t in (q, k, v))
     ref = (torch.softmax(qf @ kf.transpose(-1, -2) * scale, -1) @ vf).transpose(1, 2).reshape(B, n, heads * d)
     assert torch.isfinite(out.float()).all()
     assert rel_l2(out.float(), ref) < 1e-2
