@@ -348,6 +348,14 @@ __device__ __forceinline__ void tma_load_2d_2cta(uint32_t dst, const void* tmap,
       ::"r"(dst), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(cluster_bar), "r"(c0), "r"(c1)
       : "memory");
 }
+__device__ __forceinline__ void tma_load_3d_2cta(uint32_t dst, const void* tmap, uint32_t cluster_bar, int c0, int c1,
+                                                 int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5}], [%2];"
+      ::"r"(dst), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(cluster_bar), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
 __device__ __forceinline__ void tma_load_4d_2cta(uint32_t dst, const void* tmap, uint32_t cluster_bar, int c0, int c1,
                                                  int c2, int c3) {
   asm volatile(

@@ -55,9 +55,9 @@ struct UmmaParams {
   // tools/ubench_halo.cu) -- so an activation byte crosses L2 -> SM 3.05x instead of 9x per output tile.  Two rings:
   // stages [0, halo_nA) hold halo blocks (warp 3 loads them), stages [halo_nA, halo_nA + halo_nB) weight tiles (warp 0).
   int halo, halo_w, halo_nA, halo_nB, halo_stage_bytes, halo_box_bytes, halo_dw0, halo_dh0;
-  short tap_row[9];   // first halo-block row of the tap's view
+  short tap_row[12];  // first halo-block row of the tap's view (padded: the issue loop reads two ahead)
   int ring_bytes;     // operand ring(s) in shared memory
-  int issue_group;    // halo mode: taps the MMA warp waits for and issues per round trip (1 or 2)
+  int halo_tg;        // halo mode: taps per weight-ring stage (1, 2 or 3; divides the tap count)
   // conv geometry (GEMM-M space = input-resolution pixels)
   int kb_per_tap, Cin;
   int TW, TH, TN, tiles_w, tiles_h;
@@ -488,25 +488,27 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
       __syncwarp();
     }
     if (p.halo) {
-      // halo mode: this warp streams the weight tiles (tap-minor inside a channel block, the MMA warp's order)
-      const uint32_t txb = (k2 ? 2u : 1u) * (uint32_t)p.b_bytes;
+      // halo mode: this warp streams the weight tiles, `halo_tg` taps of one channel block per load (the weights seen as
+      // [Cin][Cout][tap]: one 3-D box lands as halo_tg consecutive K-major tiles) in the MMA warp's order
+      const uint32_t sbytes = (uint32_t)p.halo_tg * (uint32_t)p.b_bytes;
+      const uint32_t txb = (k2 ? 2u : 1u) * sbytes;
       const uint32_t bring = ring_base + (uint32_t)p.halo_nA * (uint32_t)p.halo_stage_bytes;
       const int n_tap = p.num_kb / p.kb_per_tap;
       for (; tw.valid() && ok; tw.next()) {
         const int n0 = tw.n * p.BN;
         for (int kb = 0; kb < p.kb_per_tap && ok; ++kb) {
-          for (int tap = 0; tap < n_tap; ++tap) {
+          for (int tap = 0; tap < n_tap; tap += p.halo_tg) {
             ok = mbar_wait(empty_bar(p.halo_nA + stage), phase ^ 1u);
             if (!ok) break;
-            const uint32_t sb = bring + (uint32_t)stage * (uint32_t)p.b_bytes;
+            const uint32_t sb = bring + (uint32_t)stage * sbytes;
             if (elect_one()) {
               if (k2) {
                 const uint32_t lead_full = sdb_mapa(full_bar(p.halo_nA + stage), 0u);
                 if (pair_rank == 0) mbar_arrive_expect_tx(full_bar(p.halo_nA + stage), txb);
-                tma_load_2d_2cta(sb, &p.tmB, lead_full, tap * p.Cin + kb * p.BK, n0 + (int)pair_rank * (p.BN >> 1));
+                tma_load_3d_2cta(sb, &p.tmB, lead_full, kb * p.BK, n0 + (int)pair_rank * (p.BN >> 1), tap);
               } else {
                 mbar_arrive_expect_tx(full_bar(p.halo_nA + stage), txb);
-                tma_load_2d(sb, &p.tmB, full_bar(p.halo_nA + stage), tap * p.Cin + kb * p.BK, n0);
+                tma_load_3d(sb, &p.tmB, full_bar(p.halo_nA + stage), kb * p.BK, n0, tap);
               }
             }
             __syncwarp();
@@ -578,7 +580,6 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
     const bool bk64 = p.BK == 64;
     int stage = 0, hb_stage = 0;
     uint32_t phase = 0, hb_phase = 0;
-    const bool grp2 = p.halo && p.issue_group >= 2;
     uint32_t a_lo = a_lo0;
     bool ok = true;
     TileWalk tw(p);
@@ -595,29 +596,26 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
       uint32_t b_lo = b_lo0;
       if (p.halo) {
         // one halo block per channel block, its taps as row-shifted views; `stage` / `phase` walk the halo ring,
-        // hb_stage / hb_phase the weight ring
+        // hb_stage / hb_phase the weight ring, whose stages hold `halo_tg` taps: one barrier wait, election and commit
+        // per tap group -- that round trip is of the order of 400 cycles for the one issuing thread, longer than the
+        // four MMAs of a single tap on tiles of <= 128 columns
         const int n_tap = p.num_kb / p.kb_per_tap;
+        const int tg = p.halo_tg;
+        const uint32_t sbytes = (uint32_t)tg * (uint32_t)p.b_bytes;
         const uint32_t bring = ring_base + (uint32_t)p.halo_nA * (uint32_t)p.halo_stage_bytes;
+        const uint32_t bstep = (uint32_t)p.b_bytes >> 4;
         for (int kb = 0; kb < p.kb_per_tap && ok; ++kb) {
           ok = mbar_wait(full_bar(stage), phase);
           if (!ok) break;
           const uint32_t sa = ring_base + (uint32_t)stage * (uint32_t)p.halo_stage_bytes;
-          int tap = 0;
-          // narrow tiles (N <= 128): two taps per issue round trip -- barrier wait, election, descriptor set-up and commit
-          // by one thread take of the order of 400 cycles, longer than four such MMAs (the N = 16 image head most of all)
-          for (; grp2 && tap + 1 < n_tap; tap += 2) {
-            int s1 = hb_stage + 1;
-            uint32_t ph1 = hb_phase;
-            if (s1 == p.halo_nB) { s1 = 0; ph1 ^= 1u; }
+          for (int tap = 0; tap < n_tap; tap += tg) {
             ok = mbar_wait(full_bar(p.halo_nA + hb_stage), hb_phase);
-            if (!ok) break;
-            ok = mbar_wait(full_bar(p.halo_nA + s1), ph1);
             if (!ok) break;
             tc_fence_after();
             const uint64_t ad0 = desc_hi | (uint64_t)(((sa + (uint32_t)p.tap_row[tap] * 128u) & 0x3ffffu) >> 4);
             const uint64_t ad1 = desc_hi | (uint64_t)(((sa + (uint32_t)p.tap_row[tap + 1] * 128u) & 0x3ffffu) >> 4);
-            const uint64_t bd0 = desc_hi | (uint64_t)(((bring + (uint32_t)hb_stage * (uint32_t)p.b_bytes) & 0x3ffffu) >> 4);
-            const uint64_t bd1 = desc_hi | (uint64_t)(((bring + (uint32_t)s1 * (uint32_t)p.b_bytes) & 0x3ffffu) >> 4);
+            const uint64_t ad2 = desc_hi | (uint64_t)(((sa + (uint32_t)p.tap_row[tap + 2] * 128u) & 0x3ffffu) >> 4);
+            const uint64_t bd0 = desc_hi | (uint64_t)(((bring + (uint32_t)hb_stage * sbytes) & 0x3ffffu) >> 4);
             if (elect_one()) {
               const uint32_t first = (kb | tap) != 0 ? 1u : 0u;
               if (k2) {
@@ -625,54 +623,43 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
                 umma_f16_2cta(tmem_d, ad0 + 2, bd0 + 2, idesc, 1u);
                 umma_f16_2cta(tmem_d, ad0 + 4, bd0 + 4, idesc, 1u);
                 umma_f16_2cta(tmem_d, ad0 + 6, bd0 + 6, idesc, 1u);
+                if (tg > 1) {
+                  const uint64_t bd1 = bd0 + bstep;
+                  umma_f16_2cta(tmem_d, ad1, bd1, idesc, 1u);
+                  umma_f16_2cta(tmem_d, ad1 + 2, bd1 + 2, idesc, 1u);
+                  umma_f16_2cta(tmem_d, ad1 + 4, bd1 + 4, idesc, 1u);
+                  umma_f16_2cta(tmem_d, ad1 + 6, bd1 + 6, idesc, 1u);
+                }
+                if (tg > 2) {
+                  const uint64_t bd2 = bd0 + 2u * bstep;
+                  umma_f16_2cta(tmem_d, ad2, bd2, idesc, 1u);
+                  umma_f16_2cta(tmem_d, ad2 + 2, bd2 + 2, idesc, 1u);
+                  umma_f16_2cta(tmem_d, ad2 + 4, bd2 + 4, idesc, 1u);
+                  umma_f16_2cta(tmem_d, ad2 + 6, bd2 + 6, idesc, 1u);
+                }
                 umma_commit_2cta(empty_bar(p.halo_nA + hb_stage));
-                umma_f16_2cta(tmem_d, ad1, bd1, idesc, 1u);
-                umma_f16_2cta(tmem_d, ad1 + 2, bd1 + 2, idesc, 1u);
-                umma_f16_2cta(tmem_d, ad1 + 4, bd1 + 4, idesc, 1u);
-                umma_f16_2cta(tmem_d, ad1 + 6, bd1 + 6, idesc, 1u);
-                umma_commit_2cta(empty_bar(p.halo_nA + s1));
-                if (tap + 2 == n_tap) umma_commit_2cta(empty_bar(stage));
+                if (tap + tg >= n_tap) umma_commit_2cta(empty_bar(stage));
               } else {
                 umma_f16(tmem_d, ad0, bd0, idesc, first);
                 umma_f16(tmem_d, ad0 + 2, bd0 + 2, idesc, 1u);
                 umma_f16(tmem_d, ad0 + 4, bd0 + 4, idesc, 1u);
                 umma_f16(tmem_d, ad0 + 6, bd0 + 6, idesc, 1u);
+                if (tg > 1) {
+                  const uint64_t bd1 = bd0 + bstep;
+                  umma_f16(tmem_d, ad1, bd1, idesc, 1u);
+                  umma_f16(tmem_d, ad1 + 2, bd1 + 2, idesc, 1u);
+                  umma_f16(tmem_d, ad1 + 4, bd1 + 4, idesc, 1u);
+                  umma_f16(tmem_d, ad1 + 6, bd1 + 6, idesc, 1u);
+                }
+                if (tg > 2) {
+                  const uint64_t bd2 = bd0 + 2u * bstep;
+                  umma_f16(tmem_d, ad2, bd2, idesc, 1u);
+                  umma_f16(tmem_d, ad2 + 2, bd2 + 2, idesc, 1u);
+                  umma_f16(tmem_d, ad2 + 4, bd2 + 4, idesc, 1u);
+                  umma_f16(tmem_d, ad2 + 6, bd2 + 6, idesc, 1u);
+                }
                 umma_commit(empty_bar(p.halo_nA + hb_stage));
-                umma_f16(tmem_d, ad1, bd1, idesc, 1u);
-                umma_f16(tmem_d, ad1 + 2, bd1 + 2, idesc, 1u);
-                umma_f16(tmem_d, ad1 + 4, bd1 + 4, idesc, 1u);
-                umma_f16(tmem_d, ad1 + 6, bd1 + 6, idesc, 1u);
-                umma_commit(empty_bar(p.halo_nA + s1));
-                if (tap + 2 == n_tap) umma_commit(empty_bar(stage));
-              }
-            }
-            __syncwarp();
-            hb_stage = s1 + 1;
-            hb_phase = ph1;
-            if (hb_stage == p.halo_nB) { hb_stage = 0; hb_phase ^= 1u; }
-          }
-          for (; ok && tap < n_tap; ++tap) {
-            ok = mbar_wait(full_bar(p.halo_nA + hb_stage), hb_phase);
-            if (!ok) break;
-            tc_fence_after();
-            const uint64_t adesc = desc_hi | (uint64_t)(((sa + (uint32_t)p.tap_row[tap] * 128u) & 0x3ffffu) >> 4);
-            const uint64_t bdesc = desc_hi | (uint64_t)(((bring + (uint32_t)hb_stage * (uint32_t)p.b_bytes) & 0x3ffffu) >> 4);
-            if (elect_one()) {
-              const uint32_t first = (kb | tap) != 0 ? 1u : 0u;
-              if (k2) {
-                umma_f16_2cta(tmem_d, adesc, bdesc, idesc, first);
-                umma_f16_2cta(tmem_d, adesc + 2, bdesc + 2, idesc, 1u);
-                umma_f16_2cta(tmem_d, adesc + 4, bdesc + 4, idesc, 1u);
-                umma_f16_2cta(tmem_d, adesc + 6, bdesc + 6, idesc, 1u);
-                umma_commit_2cta(empty_bar(p.halo_nA + hb_stage));
-                if (tap == n_tap - 1) umma_commit_2cta(empty_bar(stage));
-              } else {
-                umma_f16(tmem_d, adesc, bdesc, idesc, first);
-                umma_f16(tmem_d, adesc + 2, bdesc + 2, idesc, 1u);
-                umma_f16(tmem_d, adesc + 4, bdesc + 4, idesc, 1u);
-                umma_f16(tmem_d, adesc + 6, bdesc + 6, idesc, 1u);
-                umma_commit(empty_bar(p.halo_nA + hb_stage));
-                if (tap == n_tap - 1) umma_commit(empty_bar(stage));
+                if (tap + tg >= n_tap) umma_commit(empty_bar(stage));
               }
             }
             __syncwarp();
@@ -1136,12 +1123,22 @@ static void plan_halo(UmmaParams& p, int n_tap) {
   const int rows = dh1 - dh0 + 1, hw = kTileM + (dw1 - dw0);
   const int box = rows * hw * 128;
   const int stage = (box + 1023) & ~1023;
+  // taps per weight stage: a whole tap row (3 of 3x3, 2 of the 2x2 phases) when three such stages fit next to two halo
+  // blocks -- tiles of <= 128 columns -- else one (SDB_CONV_HALO_TG=1 forces that: A/B)
+  static int tg_env = -1;
+  if (tg_env < 0) { const char* e = getenv("SDB_CONV_HALO_TG"); tg_env = e ? atoi(e) : 0; }
+  const int tg_row = n_tap == 9 ? 3 : (n_tap == 4 ? 2 : 1);
+  for (int pass = 0; pass < 2; ++pass) {
+  const int tg = pass == 0 ? (tg_env > 0 ? (tg_env < tg_row ? tg_env : tg_row) : tg_row) : 1;
+  if (pass == 1 && tg_row == 1) break;
+  if (n_tap % tg != 0) continue;
   for (int nA = 3; nA >= 2; --nA) {
     const int rem = kSmemBudget - p.nbuf * p.stg_bytes - nA * stage;
-    int nB = rem > 0 ? rem / p.b_bytes : 0;
+    int nB = rem > 0 ? rem / (tg * p.b_bytes) : 0;
     if (nB > kMaxStages - nA) nB = kMaxStages - nA;
-    if (nB < (nA == 3 ? 4 : 3)) continue;
+    if (nB < (tg > 1 ? 3 : (nA == 3 ? 4 : 3))) continue;
     p.halo = 1;
+    p.halo_tg = tg;
     p.halo_w = hw;
     p.halo_nA = nA;
     p.halo_nB = nB;
@@ -1151,8 +1148,9 @@ static void plan_halo(UmmaParams& p, int n_tap) {
     p.halo_dh0 = dh0;
     for (int t = 0; t < n_tap; ++t) p.tap_row[t] = (short)((p.tap_dh[t] - dh0) * hw + (p.tap_dw[t] - dw0));
     p.num_stages = nA + nB;
-    p.ring_bytes = nA * stage + nB * p.b_bytes;
+    p.ring_bytes = nA * stage + nB * tg * p.b_bytes;
     return;
+  }
   }
 }
 
@@ -1209,9 +1207,6 @@ static int launch_umma_epi(const UmmaParams& p, int grid, int smem, cudaStream_t
 
 static int launch_umma(UmmaParams& p, cudaStream_t st) {
   const int smem = kSmemBudget + kBiasBytes + 1024 /* alignment */ + 512 /* barriers */;
-  static int issue_group = -1;     // SDB_MMA_GROUP=1|2: A/B measurements
-  if (issue_group < 0) { const char* e = getenv("SDB_MMA_GROUP"); issue_group = e && atoi(e) > 0 ? atoi(e) : 2; }
-  p.issue_group = (p.halo && p.halo_nB >= 3 && p.BN <= 128) ? issue_group : 1;   // wide tiles: the ring depth matters more
   if (p.num_stages < 2) {
     sdb_set_error("umma: tile %dx%d (BK %d) leaves no room for a 2-stage operand ring", kTileM, p.BN, p.BK);
     return SDB_EUNSUPPORTED;
@@ -1486,10 +1481,18 @@ extern "C" int sdb_conv3x3(const SdbConvArgs* a, void* stream) {
   if (p.halo) { box[1] = (uint32_t)p.halo_w; box[2] = (uint32_t)(p.halo_box_bytes / (p.halo_w * 128)); }
   int rc = sdb_make_tensor_map(&p.tmA[0], a->x, 2, 4, dims, strides, box, p.swz);
   if (rc) return rc;
-  uint64_t wd[2] = {(uint64_t)n_tap * a->Cin, (uint64_t)a->Cout};
-  uint64_t ws[2] = {0, (uint64_t)n_tap * a->Cin * 2};
-  uint32_t wb[2] = {(uint32_t)p.BK, (uint32_t)(p.pair ? p.BN / 2 : p.BN)};
-  rc = sdb_make_tensor_map(&p.tmB, wph, 2, 2, wd, ws, wb, p.swz);
+  if (p.halo) {
+    // [Cin][Cout][tap]: a box of halo_tg taps lands as that many consecutive K-major weight tiles
+    uint64_t wd[3] = {(uint64_t)a->Cin, (uint64_t)a->Cout, (uint64_t)n_tap};
+    uint64_t ws[3] = {0, (uint64_t)n_tap * a->Cin * 2, (uint64_t)a->Cin * 2};
+    uint32_t wb[3] = {(uint32_t)p.BK, (uint32_t)(p.pair ? p.BN / 2 : p.BN), (uint32_t)p.halo_tg};
+    rc = sdb_make_tensor_map(&p.tmB, wph, 2, 3, wd, ws, wb, p.swz);
+  } else {
+    uint64_t wd[2] = {(uint64_t)n_tap * a->Cin, (uint64_t)a->Cout};
+    uint64_t ws[2] = {0, (uint64_t)n_tap * a->Cin * 2};
+    uint32_t wb[2] = {(uint32_t)p.BK, (uint32_t)(p.pair ? p.BN / 2 : p.BN)};
+    rc = sdb_make_tensor_map(&p.tmB, wph, 2, 2, wd, ws, wb, p.swz);
+  }
   if (rc) return rc;
   if (p.staged) {
     // the output box of a phase lands on every second pixel of every second row: strides doubled, base shifted
