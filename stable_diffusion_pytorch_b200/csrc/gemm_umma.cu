@@ -530,36 +530,45 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
         h0 = ((m_tile / p.tiles_w) % p.tiles_h) * p.TH;
         i0 = (m_tile / (p.tiles_w * p.tiles_h)) * p.TN;
       }
+      if (p.mode == 1) {
+        // conv: this warp fetches the activation tiles (and posts the stage's byte count), warp 3 the weight tiles --
+        // one producer thread's wait / post / two-TMA round trip per stage was as long as the stage's four MMAs
+        const int n_tap = p.num_kb / p.kb_per_tap;
+        for (int tap = 0; tap < n_tap && ok; ++tap) {
+          const int wt = w0 + p.tap_dw[tap], ht = h0 + p.tap_dh[tap];
+          for (int c0 = 0; c0 < p.kb_per_tap * p.BK; c0 += p.BK) {
+            ok = mbar_wait(empty_bar(stage), phase ^ 1u);
+            if (!ok) break;
+            const uint32_t sa = ring_base + (uint32_t)stage * p.stage_bytes;
+            if (elect_one()) {
+              if (k2) {
+                if (pair_rank == 0) mbar_arrive_expect_tx(full_bar(stage), tx);
+                tma_load_4d_2cta(sa, &p.tmA[0], sdb_mapa(full_bar(stage), 0u), c0, wt, ht, i0);
+              } else {
+                mbar_arrive_expect_tx(full_bar(stage), tx);
+                tma_load_4d(sa, &p.tmA[0], full_bar(stage), c0, wt, ht, i0);
+              }
+            }
+            __syncwarp();
+            if (++stage == p.num_stages) { stage = 0; phase ^= 1u; }
+          }
+        }
+        GEMM_TRACE(0, j, 1);
+        continue;
+      }
       for (int kb = 0; kb < p.num_kb; ++kb) {
         ok = mbar_wait(empty_bar(stage), phase ^ 1u);
         if (!ok) break;
         const uint32_t sa = ring_base + (uint32_t)stage * p.stage_bytes;
         const uint32_t sb = sa + p.a_bytes;
-        if (k2) {
-          if (elect_one()) {
-            const uint32_t lead_full = sdb_mapa(full_bar(stage), 0u);
-            if (pair_rank == 0) mbar_arrive_expect_tx(full_bar(stage), tx);
-            const int tap = kb / p.kb_per_tap;
-            const int c0 = (kb - tap * p.kb_per_tap) * p.BK;
-            tma_load_4d_2cta(sa, &p.tmA[p.tap_map[tap]], lead_full, c0, w0 + p.tap_dw[tap], h0 + p.tap_dh[tap], i0);
-            tma_load_2d_2cta(sb, &p.tmB, lead_full, tap * p.Cin + c0, n0 + (int)pair_rank * (p.BN >> 1));
-          }
-        } else if (elect_one()) {
+        if (elect_one()) {
           mbar_arrive_expect_tx(full_bar(stage), tx);
-          if (p.mode == 0) {
-            if (kb < p.kb1) {
-              tma_load_2d(sa, &p.tmA[0], full_bar(stage), kb * p.BK, m_tile * kTileM);
-              if (!p.resB) tma_load_2d(sb, &p.tmB, full_bar(stage), kb * p.BK, n0);
-            } else {
-              tma_load_2d(sa, &p.tmA[1], full_bar(stage), (kb - p.kb1) * p.BK, m_tile * kTileM);
-              if (!p.resB) tma_load_2d(sb, &p.tmB, full_bar(stage), p.K1 + (kb - p.kb1) * p.BK, n0);
-            }
+          if (kb < p.kb1) {
+            tma_load_2d(sa, &p.tmA[0], full_bar(stage), kb * p.BK, m_tile * kTileM);
+            if (!p.resB) tma_load_2d(sb, &p.tmB, full_bar(stage), kb * p.BK, n0);
           } else {
-            const int tap = kb / p.kb_per_tap;
-            const int c0 = (kb - tap * p.kb_per_tap) * p.BK;
-            tma_load_4d(sa, &p.tmA[p.tap_map[tap]], full_bar(stage), c0, w0 + p.tap_dw[tap],
-                        h0 + p.tap_dh[tap], i0);
-            tma_load_2d(sb, &p.tmB, full_bar(stage), tap * p.Cin + c0, n0);
+            tma_load_2d(sa, &p.tmA[1], full_bar(stage), (kb - p.kb1) * p.BK, m_tile * kTileM);
+            if (!p.resB) tma_load_2d(sb, &p.tmB, full_bar(stage), p.K1 + (kb - p.kb1) * p.BK, n0);
           }
         }
         __syncwarp();
@@ -829,7 +838,30 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
       __syncwarp();
     }
   } else if (warp == 3) {
-    // ===================== halo-block producer (halo mode only) =====================
+    // ===================== second producer: conv weight tiles / halo blocks =====================
+    if (p.mode == 1 && !p.halo) {
+      // the weight tile of every (tap, channel block) stage; the byte count was posted by warp 0
+      int stage = 0;
+      uint32_t phase = 0;
+      bool ok = true;
+      const int n_tap = p.num_kb / p.kb_per_tap;
+      for (TileWalk tw(p); tw.valid() && ok; tw.next()) {
+        const int nrow = tw.n * p.BN + (k2 ? (int)pair_rank * (p.BN >> 1) : 0);
+        for (int tap = 0; tap < n_tap && ok; ++tap) {
+          for (int c0 = 0; c0 < p.kb_per_tap * p.BK; c0 += p.BK) {
+            ok = mbar_wait(empty_bar(stage), phase ^ 1u);
+            if (!ok) break;
+            const uint32_t sb = ring_base + (uint32_t)stage * p.stage_bytes + (uint32_t)p.a_bytes;
+            if (elect_one()) {
+              if (k2) tma_load_2d_2cta(sb, &p.tmB, sdb_mapa(full_bar(stage), 0u), tap * p.Cin + c0, nrow);
+              else tma_load_2d(sb, &p.tmB, full_bar(stage), tap * p.Cin + c0, nrow);
+            }
+            __syncwarp();
+            if (++stage == p.num_stages) { stage = 0; phase ^= 1u; }
+          }
+        }
+      }
+    }
     if (p.halo) {
       int stage = 0;
       uint32_t phase = 0;
