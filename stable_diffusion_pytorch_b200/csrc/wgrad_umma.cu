@@ -91,13 +91,28 @@ __global__ void __launch_bounds__(kWgThreads, 1) wgrad_umma_kernel(const __grid_
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot_ptr;
 
-  if (warp == 0) {
-    // ===================== TMA producer =====================
+  if (warp == 0 || warp == 2 || warp == 3) {
+    // ===================== TMA producers =====================
+    // A stage is 2 + nsub * atoms_b boxes (up to 11).  One thread issuing them all, with the sub-tile -> (tap, channel)
+    // divisions in the loop, took about as long as the stage's MMAs; so warp 0 posts the byte count and fetches the dY
+    // atoms, warps 2 and 3 share the X atoms (even and odd sub-tiles), each with its coordinates precomputed.
     const uint32_t tx = (uint32_t)(2 + nsub * p.atoms_b) * (uint32_t)kWgAtomBytes;
+    const int s_first = warp == 0 ? -1 : warp - 2;      // warp 0: no X atoms
+    int xc[4], xdh[4], xdw[4], xs[4], nx = 0;          // (512 TMEM columns / NW >= 64: at most 8 sub-tiles)
+    for (int sidx = s_first; s_first >= 0 && sidx < nsub && nx < 4; sidx += 2) {
+      const int sub = sub0 + sidx;
+      const int tap = sub / p.subs_per_tap;
+      xs[nx] = sidx;
+      xc[nx] = (sub - tap * p.subs_per_tap) * p.NW;
+      xdh[nx] = p.taps == 9 ? tap / 3 - 1 : 0;
+      xdw[nx] = p.taps == 9 ? tap - (tap / 3) * 3 - 1 : 0;
+      ++nx;
+    }
     bool ok = true;
     int stage = 0;
     uint32_t phase = 0;
-    for (int i = 0; i < nkb && ok; ++i) {
+    int ig = p.linear ? 0 : kb0 / p.tiles_h, hb = p.linear ? 0 : kb0 - ig * p.tiles_h;   // (image group, row block) of kb
+    for (int i = 0; i < nkb && ok && (warp == 0 || nx > 0); ++i) {
       ok = mbar_wait(empty_bar(stage), phase ^ 1u);
       if (!ok) break;
       const int kb = kb0 + i;
@@ -105,25 +120,22 @@ __global__ void __launch_bounds__(kWgThreads, 1) wgrad_umma_kernel(const __grid_
       if (p.linear) {
         w0 = kb * 64;
       } else {
-        const int ig = kb / p.tiles_h;
-        h0 = (kb - ig * p.tiles_h) * p.TH;
+        h0 = hb * p.TH;
         i0 = ig * p.TN;
+        if (++hb == p.tiles_h) { hb = 0; ++ig; }
       }
       const uint32_t sa = base + (uint32_t)stage * (uint32_t)p.stage_bytes;
       const uint32_t sb = sa + 2u * kWgAtomBytes;
       if (elect_one()) {
-        mbar_arrive_expect_tx(full_bar(stage), tx);
-        tma_load_4d(sa, &p.tmY, full_bar(stage), nt * 128, w0, h0, i0);
-        tma_load_4d(sa + kWgAtomBytes, &p.tmY, full_bar(stage), nt * 128 + 64, w0, h0, i0);
-        for (int s = 0; s < nsub; ++s) {
-          const int sub = sub0 + s;
-          const int tap = sub / p.subs_per_tap;
-          const int c0 = (sub - tap * p.subs_per_tap) * p.NW;
-          int dh = 0, dw = 0;
-          if (p.taps == 9) { dh = tap / 3 - 1; dw = tap - (tap / 3) * 3 - 1; }
-          for (int a = 0; a < p.atoms_b; ++a)
-            tma_load_4d(sb + (uint32_t)(s * p.atoms_b + a) * kWgAtomBytes, &p.tmX, full_bar(stage), c0 + a * 64,
-                        w0 + dw, h0 + dh, i0);
+        if (warp == 0) {
+          mbar_arrive_expect_tx(full_bar(stage), tx);
+          tma_load_4d(sa, &p.tmY, full_bar(stage), nt * 128, w0, h0, i0);
+          tma_load_4d(sa + kWgAtomBytes, &p.tmY, full_bar(stage), nt * 128 + 64, w0, h0, i0);
+        } else {
+          for (int x = 0; x < nx; ++x)
+            for (int a = 0; a < p.atoms_b; ++a)
+              tma_load_4d(sb + (uint32_t)(xs[x] * p.atoms_b + a) * kWgAtomBytes, &p.tmX, full_bar(stage), xc[x] + a * 64,
+                          w0 + xdw[x], h0 + xdh[x], i0);
         }
       }
       __syncwarp();
