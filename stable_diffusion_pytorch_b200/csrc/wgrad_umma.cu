@@ -175,6 +175,7 @@ __global__ void __launch_bounds__(kWgThreads, 1) wgrad_umma_kernel(const __grid_
     if (mbar_wait(tfull_bar, 0)) {
       tc_fence_after();
       const int n = nt * 128 + q * 32 + lane;
+      const bool vec4 = (p.ld_n & 3) == 0 && (p.Cin & 3) == 0 && (reinterpret_cast<uintptr_t>(p.out) & 15) == 0;
       for (int s = 0; s < nsub; ++s) {
         const int sub = sub0 + s;
         const int tap = sub / p.subs_per_tap;
@@ -185,8 +186,16 @@ __global__ void __launch_bounds__(kWgThreads, 1) wgrad_umma_kernel(const __grid_
           tmem_ld_32x16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)(s * p.NW + cc), v);
           tmem_ld_wait();
           if (n < p.Cout) {
+            if (vec4) {       // one 16-byte reduction per four columns (a quarter of the L2 atomic requests)
 #pragma unroll
-            for (int j = 0; j < 16; ++j) atomicAdd(orow + cc + j, __uint_as_float(v[j]));
+              for (int j = 0; j < 16; j += 4)
+                atomicAdd(reinterpret_cast<float4*>(orow + cc + j),
+                          make_float4(__uint_as_float(v[j]), __uint_as_float(v[j + 1]), __uint_as_float(v[j + 2]),
+                                      __uint_as_float(v[j + 3])));
+            } else {
+#pragma unroll
+              for (int j = 0; j < 16; ++j) atomicAdd(orow + cc + j, __uint_as_float(v[j]));
+            }
           }
         }
       }
