@@ -131,7 +131,7 @@ gn_finalize_kernel(const float* __restrict__ scratch, int chunks, int C, int gro
 constexpr int kGnMaxGroupsSums = 128;   // groups the sums-fed variant keeps in shared memory
 
 template <typename T, typename OutT>
-__global__ void __launch_bounds__(kGnThreads)
+__global__ void __launch_bounds__(kGnThreads, 4)
 gn_apply_kernel(const T* __restrict__ x1, int C1, const T* __restrict__ x2, int C2,
                 const float* __restrict__ stats, const float* __restrict__ gamma,
                 const float* __restrict__ beta, int act, OutT* __restrict__ out, long long hw,
