@@ -58,7 +58,6 @@ struct UmmaParams {
   short tap_row[12];  // first halo-block row of the tap's view (padded: the issue loop reads two ahead)
   int ring_bytes;     // operand ring(s) in shared memory
   int halo_tg;        // halo mode: taps per weight-ring stage (1, 2 or 3; divides the tap count)
-  int tail_slices;    // conv, classic ring: live K = 16 slices of a tap's last channel block (4 = all)
   // conv geometry (GEMM-M space = input-resolution pixels)
   int kb_per_tap, Cin;
   int TW, TH, TN, tiles_w, tiles_h;
@@ -678,35 +677,20 @@ umma_gemm_kernel(const __grid_constant__ UmmaParams p) {
           if (++stage == p.halo_nA) { stage = 0; phase ^= 1u; }
         }
       }
-      int tail_cnt = p.kb_per_tap;     // conv: counts down to the last channel block of a tap
       for (int kb = 0; !p.halo && kb < p.num_kb; ++kb) {
         ok = mbar_wait(full_bar(stage), phase);
         if (!ok) break;
         tc_fence_after();
         const uint64_t adesc = desc_hi | (uint64_t)a_lo;
         const uint64_t bdesc = desc_hi | (uint64_t)(p.resB ? b_lo : a_lo + ((uint32_t)p.a_bytes >> 4));
-        // the last 64-channel block of a 160- / 480-channel operand is half TMA zero fill: its dead K = 16 slices are
-        // not issued (tail_slices = 4 when the channel count is a multiple of 64, and for GEMMs)
-        bool part = false;
-        if (p.tail_slices < 4 && --tail_cnt == 0) { part = true; tail_cnt = p.kb_per_tap; }
         if (elect_one()) {
           // advance 16 bf16 = 32 B along K inside the swizzle atom: +2 in the (addr >> 4) field
-          if (k2 && part) {
-            umma_f16_2cta(tmem_d, adesc, bdesc, idesc, kb != 0 ? 1u : 0u);
-            if (p.tail_slices > 1) umma_f16_2cta(tmem_d, adesc + 2, bdesc + 2, idesc, 1u);
-            if (p.tail_slices > 2) umma_f16_2cta(tmem_d, adesc + 4, bdesc + 4, idesc, 1u);
-            umma_commit_2cta(empty_bar(stage));
-          } else if (k2) {
+          if (k2) {
             umma_f16_2cta(tmem_d, adesc, bdesc, idesc, kb != 0 ? 1u : 0u);
             umma_f16_2cta(tmem_d, adesc + 2, bdesc + 2, idesc, 1u);
             umma_f16_2cta(tmem_d, adesc + 4, bdesc + 4, idesc, 1u);
             umma_f16_2cta(tmem_d, adesc + 6, bdesc + 6, idesc, 1u);
             umma_commit_2cta(empty_bar(stage));     // frees the slot in both CTAs
-          } else if (part) {
-            umma_f16(tmem_d, adesc, bdesc, idesc, kb != 0 ? 1u : 0u);
-            if (p.tail_slices > 1) umma_f16(tmem_d, adesc + 2, bdesc + 2, idesc, 1u);
-            if (p.tail_slices > 2) umma_f16(tmem_d, adesc + 4, bdesc + 4, idesc, 1u);
-            umma_commit(empty_bar(stage));
           } else {
             umma_f16(tmem_d, adesc, bdesc, idesc, kb != 0 ? 1u : 0u);
             umma_f16(tmem_d, adesc + 2, bdesc + 2, idesc, 1u);
@@ -1331,7 +1315,6 @@ extern "C" int sdb_gemm(const SdbGemmArgs* a, void* stream) {
   UmmaParams p;
   memset(&p, 0, sizeof(p));
   p.mode = 0;
-  p.tail_slices = 4;
   pick_bk(a->K1, K2, &p.BK, &p.swz);
   // short-K GEMMs are bound by the output stream, not the tensor pipe: tiles of <= 128 output columns keep
   // two staging buffers and the resident weight tile inside shared memory
@@ -1501,9 +1484,6 @@ extern "C" int sdb_conv3x3(const SdbConvArgs* a, void* stream) {
     }
   }
   plan_halo(p, n_tap);
-  static int tail_skip = -1;       // SDB_CONV_TAIL_SKIP=0: A/B
-  if (tail_skip < 0) { const char* e = getenv("SDB_CONV_TAIL_SKIP"); tail_skip = e ? atoi(e) : 1; }
-  p.tail_slices = (tail_skip && !p.halo && p.BK == 64 && a->Cin % 64 != 0) ? ((a->Cin % 64) + 15) / 16 : 4;
   p.M = 0;
   p.N = a->Cout;
   p.bias = a->bias;
