@@ -68,7 +68,7 @@ static int attention_p32_impl(const void* q, int64_t ldq, const void* k, int64_t
     const char* t = getenv("SDB_FA_CTX_TILES");
     if (t && atoi(t) > 0) ctx_tiles = atoi(t);
   }
-  if (m <= kCuMaxNS && ctx_umma && !no_ctx && !lse) {
+  if (m <= kCuMaxNS && ctx_umma && !no_ctx) {      // (no short-context kernel keeps the lse: *lse_written stays 0)
     CuParams c;
     memset(&c, 0, sizeof(c));
     const int NS = (m + 15) / 16 * 16;
