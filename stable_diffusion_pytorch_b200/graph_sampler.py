@@ -119,7 +119,48 @@ class GraphedLatentStep:
     def step_host(self, x_host: Tensor, ctx_host: Tensor, out_host: Tensor):
         """End-to-end single step with HOST (pinned) buffers: H2D latent + context, one latent-step,
         D2H of the updated latent.  Used by bench.py's e2e leg."""
-        self.x.copy_(x_host, non_blocking=True)
-        (self.c_in[self.B:] if self.cfg else self.c_in).copy_(ctx_host, non_blocking=True)
+        # The PCIe copies run on a side stream through device staging buffers, so the H2D of this call overlaps the
+        # kernels of the previous one and the D2H of its result overlaps the next one's; the hand-overs to the buffers the
+        # captured graph reads and writes are device-to-device copies on the main stream.  Every call still moves its own
+        # inputs from, and its own result to, host memory.
+        c_dst = self.c_in[self.B:] if self.cfg else self.c_in
+        main = torch.cuda.current_stream(self.device)
+        if getattr(self, "_io", None) is None:
+            self._io = {
+                "stream": torch.cuda.Stream(device=self.device),
+                "x": torch.empty_like(self.x), "c": torch.empty_like(c_dst), "o": torch.empty_like(self.x),
+                "in_free": torch.cuda.Event(), "in_ready": torch.cuda.Event(),
+                "out_ready": torch.cuda.Event(), "out_free": torch.cuda.Event(),
+            }
+            self._io["in_free"].record(main)
+            self._io["out_free"].record(main)
+        io = self._io
+        cs = io["stream"]
+        cs.wait_event(io["in_free"])                     # the previous call has taken its inputs out of the staging
+        with torch.cuda.stream(cs):
+            io["x"].copy_(x_host, non_blocking=True)
+            io["c"].copy_(ctx_host, non_blocking=True)
+            io["in_ready"].record(cs)
+        main.wait_event(io["in_ready"])
+        self.x.copy_(io["x"])
+        c_dst.copy_(io["c"])
+        io["in_free"].record(main)
         self.step()
-        out_host.copy_(self.x, non_blocking=True)
+        main.wait_event(io["out_free"])                  # the previous result has left the output staging
+        io["o"].copy_(self.x)
+        io["out_ready"].record(main)
+        cs.wait_event(io["out_ready"])
+        with torch.cuda.stream(cs):
+            out_host.copy_(io["o"], non_blocking=True)
+            io["out_free"].record(cs)
+
+    def join_host(self):
+        """Orders the current stream behind every copy ``step_host`` has enqueued (no host wait): an event recorded
+        afterwards covers the last result's trip to host memory."""
+        if getattr(self, "_io", None) is not None:
+            torch.cuda.current_stream(self.device).wait_stream(self._io["stream"])
+
+    def sync_host(self):
+        """Wait until the results of all ``step_host`` calls have landed in their host buffers."""
+        self.join_host()
+        torch.cuda.current_stream(self.device).synchronize()

@@ -150,3 +150,30 @@ def test_latent_diffusion_sample_ddim_and_graph_cache_vs_oracle():
     torch.manual_seed(cases.SAMPLE_NOISE_SEED)
     again = ld.sample(x.to(DEV), ctx.to(DEV), guidance_scale=g, time_steps=steps, sampler="ddpm")
     assert torch.equal(again, outs[True]) and len(ld._graphs) == 2
+
+
+def test_step_host_pipelined_copies_match_device_resident_steps():
+    """``step_host`` (the bench's end-to-end call: host buffers in, host result out, PCIe copies on a side stream through
+    staging buffers) must return, for every call, exactly what a device-resident step on the same inputs returns --
+    also when calls are enqueued back to back without a host wait in between."""
+    cfg, seed, B, H, W = cases.TINY, 5, 2, 16, 16
+    m, _ = build_unet(cfg, seed)
+    gs = graphed(m, B, H, W, 50, "ddim", 7.5)
+    _, ctx0, uncond = cases.sample_inputs(cfg, B, H, W, seed)
+    gs.reset(torch.zeros(B, cfg.latent_channels, H, W), ctx0, uncond)
+    gs.capture()
+    g = torch.Generator().manual_seed(3)
+    xs = [torch.randn(B, cfg.latent_channels, H, W, generator=g).to(torch.bfloat16).pin_memory() for _ in range(4)]
+    cs = [torch.randn(B, 77, cfg.context_dim, generator=g).to(torch.bfloat16).pin_memory() for _ in range(4)]
+    outs = [torch.empty_like(xs[0]).pin_memory() for _ in range(4)]
+    want = []
+    for x, c in zip(xs, cs):                       # device-resident reference: same slot (0) every time
+        gs.reset(x, c)
+        gs.step()
+        want.append(gs.x.clone())
+    for i in range(4):                             # back to back, no host synchronisation
+        gs.slot.zero_(); gs.t.fill_(gs.steps[0])
+        gs.step_host(xs[i], cs[i], outs[i])
+    gs.sync_host()
+    for i in range(4):
+        assert torch.equal(outs[i], want[i].cpu()), f"call {i}"
