@@ -582,6 +582,10 @@ def run_b200(args):
                    "batch_per_gpu": B, "latent": [4, S, S], "sampler": args.sampler, "guidance_scale": 7.5,
                    "parallelism": f"latent-batch sharded x{world}, no collective in the step",
                    "cuda_graph": not args.no_graph,
+                   "cfg_prefix_shared": os.environ.get("SDB_CFG_SHARE", "1") != "0",
+                   "cfg_note": "the two CFG copies of a latent differ only in their context: the layers ahead of the first "
+                               "cross-attention (conv_in, ResBlock 1, GroupNorm / proj_in / self-attention of transformer 1) are "
+                               "evaluated once per latent and copied -- same outputs; SDB_CFG_SHARE=0 evaluates both copies",
                    "l2": "no flush: per-step activation working set (~3 GB) is far larger than the 126 MB L2"},
         "e2e": {"value": e2e, "unit": "latent-steps/s", "ms_per_step": ms_e2e / args.steps,
                 "h2d_bytes_per_step": x_host.numel() * 2 + ctx_host.numel() * 2,

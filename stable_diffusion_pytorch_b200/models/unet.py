@@ -12,6 +12,7 @@ forward() plan (all kernels in libsdb200, activations NHWC bf16):
 from __future__ import annotations
 
 from dataclasses import dataclass, field
+import os
 from typing import Dict, List, Optional
 
 import torch
@@ -20,10 +21,12 @@ from torch import nn
 from .. import _pack, ops
 from .._lib import ACT_SILU
 from ..modules.resnet2d import ResBlock
-from ..modules.timestep_embedding import sinusoidal_freq, sinusoidal_time_proj
+from ..modules.timestep_embedding import TimestepEmbedSequential, sinusoidal_freq, sinusoidal_time_proj
 from ..modules.transformer import SpatialTransformer
 from .utils import (build_bottleneck, build_conv_in, build_final_output, build_input_blocks,
                     build_output_blocks)
+
+_CFG_SHARE = os.environ.get("SDB_CFG_SHARE", "1") != "0"   # A/B switch of the CFG prefix sharing in UNetModel.forward
 
 Tensor = torch.Tensor
 
@@ -144,7 +147,9 @@ class UNetModel(nn.Module):
     def forward(self, x: Tensor, timesteps: Tensor, context_emb: Optional[Tensor] = None, x_repeat: int = 1):
         """``x_repeat`` (extension, default 1): the effective batch is ``x`` repeated that many times
         along dim 0 -- the ``torch.cat([x] * 2)`` of classifier-free guidance without the copy;
-        ``timesteps`` / ``context_emb`` carry the full repeated batch."""
+        ``timesteps`` / ``context_emb`` carry the full repeated batch, and ``timesteps`` repeats like ``x``
+        (row i + k * B equals row i, as ``torch.cat([time_step] * 2)`` of latent_diffusion.py:54 does): the layers ahead
+        of the first cross-attention are evaluated once per distinct latent."""
         if context_emb is not None:
             assert context_emb.shape[-1] == self.context_dim, (
                 f"context dim from passed in context({context_emb.shape}) should be equal to "
@@ -171,11 +176,20 @@ class UNetModel(nn.Module):
             kv_of = lambda st_mod: views[id(st_mod)]  # noqa: E731
         # 3. block chain
         # (inside the scope the conv / GEMM epilogues leave per-channel sums for the GroupNorm that reads them next)
+        # classifier-free guidance (x_repeat > 1): the copies of a latent differ only in their context, so everything
+        # ahead of the first cross-attention -- conv_in, the first ResBlock, the first transformer's GroupNorm, proj_in
+        # and self-attention (one of ten 4096 x 4096 attentions at config 2) -- is evaluated once per distinct latent.
+        # Same arithmetic per sample; SDB_CFG_SHARE=0 evaluates every copy (A/B).  Inference only.
+        share = (x_repeat > 1 and _CFG_SHARE and not torch.is_grad_enabled() and context_emb is not None
+                 and len(self.input_blocks) > 0 and isinstance(self.input_blocks[0], TimestepEmbedSequential))
         with ops.gn_sums_scope(x.device):
-            h = ops.conv3x3_in(x, p["wci"], p["bci"], _pack.compute_dtype(), repeat=x_repeat)
-            skips = [h]
-            for module in self.input_blocks:
-                h = module.forward_nhwc(h, temb_of, None, kv_of)
+            h = ops.conv3x3_in(x, p["wci"], p["bci"], _pack.compute_dtype(), repeat=1 if share else x_repeat)
+            skips = [h.repeat(x_repeat, 1, 1, 1) if share else h]
+            for i, module in enumerate(self.input_blocks):
+                if share and i == 0:
+                    h = module.forward_nhwc(h, temb_of, None, kv_of, expand=x_repeat)
+                else:
+                    h = module.forward_nhwc(h, temb_of, None, kv_of)
                 skips.append(h)
             h = self.middle_block.forward_nhwc(h, temb_of, None, kv_of)
             for module in self.output_blocks:

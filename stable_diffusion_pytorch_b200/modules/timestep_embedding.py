@@ -57,16 +57,26 @@ class TimestepEmbedSequential(nn.Sequential, TimestepBlock):
         return x
 
     def forward_nhwc(self, x: Tensor, temb_of=None, ctx: Optional[Tensor] = None, kv_of=None,
-                     x2: Optional[Tensor] = None) -> Tensor:
+                     x2: Optional[Tensor] = None, expand: int = 1) -> Tensor:
         """Channels-last chain.  ``temb_of(resblock)`` -> projected time embedding [B, Cout] or None;
         ``kv_of(spatial_transformer)`` -> per-layer precomputed context (K, V) or None; ``x2`` is the
-        UNet skip tensor virtually concatenated in front of the first ResBlock."""
+        UNet skip tensor virtually concatenated in front of the first ResBlock.
+        ``expand`` > 1 (classifier-free guidance, UNetModel.forward): ``x`` holds every distinct latent ONCE although
+        the batch is that latent repeated ``expand`` times; the layers run on the distinct latents until the first
+        cross-attention needs the per-copy context (``SpatialTransformer.forward_nhwc``); the result has the full batch."""
         for module in self:
+            if expand > 1 and not isinstance(module, (ResBlock, SpatialTransformer)):
+                x = x.repeat(expand, 1, 1, 1)                # nothing left to share: materialise the copies
+                expand = 1
             if isinstance(module, ResBlock):
-                x = module.forward_nhwc(x, None if temb_of is None else temb_of(module), x2)
+                temb = None if temb_of is None else temb_of(module)
+                if expand > 1 and temb is not None:
+                    temb = temb[:x.shape[0]]                 # (the time steps are repeated like the latents)
+                x = module.forward_nhwc(x, temb, x2)
                 x2 = None
             elif isinstance(module, SpatialTransformer):
-                x = module.forward_nhwc(x, ctx, None if kv_of is None else kv_of(module))
+                x = module.forward_nhwc(x, ctx, None if kv_of is None else kv_of(module), expand=expand)
+                expand = 1
             elif isinstance(module, TimestepEmbedSequential):
                 x = module.forward_nhwc(x, temb_of, ctx, kv_of)
             elif hasattr(module, "forward_nhwc"):
@@ -76,5 +86,7 @@ class TimestepEmbedSequential(nn.Sequential, TimestepBlock):
                 x = module.forward_tokens(x.view(B, H * W, C)).view(B, H, W, C)
             else:
                 raise TypeError(f"no channels-last path for {type(module).__name__}")
+        if expand > 1:
+            x = x.repeat(expand, 1, 1, 1)
         assert x2 is None, "skip tensor was not consumed by a ResBlock"
         return x

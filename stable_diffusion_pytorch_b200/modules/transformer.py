@@ -224,10 +224,13 @@ class BasicTransformerBlock(nn.Module):
                 self._cache.get(f"b{i}", [ln.bias], lambda: _pack.f32(ln.bias)))
 
     def forward_tokens(self, x: Tensor, ctx: Optional[Tensor] = None,
-                       kv: Optional[Tuple[Tensor, Tensor]] = None) -> Tensor:
+                       kv: Optional[Tuple[Tensor, Tensor]] = None, expand: int = 1) -> Tensor:
         B, n, C = x.shape
         # every residual add AND the LayerNorm after it ride in the epilogue of the GEMM that ends the sub-layer
         x = self.self_attn.forward_tokens(x, None, None, residual=x, ln=self._ln(1))      # LN1(x + SA(x))
+        if expand > 1:                                       # the cross-attention is the first per-copy layer
+            x = x.repeat(expand, 1, 1)
+            B = B * expand
         if ctx is None and kv is None:
             x = self.cross_attn.forward_tokens(x, None, None, residual=x, ln=self._ln(2))  # reference: ctx None => self-attn
         else:
@@ -271,8 +274,11 @@ class SpatialTransformer(nn.Module):
         self.proj_out = _pack.zero_module(nn.Conv2d(in_channels, in_channels, kernel_size=1, padding=0))
         self._cache = _pack.PackCache()
 
-    def forward_nhwc(self, x: Tensor, ctx: Optional[Tensor] = None, kvs=None) -> Tensor:
-        """x NHWC bf16; ctx [B, m, Cc] bf16; kvs = optional per-layer precomputed (K, V)."""
+    def forward_nhwc(self, x: Tensor, ctx: Optional[Tensor] = None, kvs=None, expand: int = 1) -> Tensor:
+        """x NHWC bf16; ctx [B, m, Cc] bf16; kvs = optional per-layer precomputed (K, V).
+        ``expand`` > 1: ``x`` holds B / expand distinct latents of a batch that repeats them ``expand`` times (classifier-free
+        guidance: ``torch.cat([x] * 2)``, latent_diffusion.py:53); GroupNorm, proj_in and the first block's self-attention
+        -- everything ahead of the first cross-attention -- are evaluated once per distinct latent and copied."""
         B, H, W, C = x.shape
         assert C == self.in_channels, f"input channels {C} should be equal to in_channels {self.in_channels}"
         c = self._cache
@@ -285,7 +291,12 @@ class SpatialTransformer(nn.Module):
         h = ops.group_norm(x, g, b, self.groups, ACT_NONE)
         t = ops.gemm(h.view(B * H * W, C), wi, bi).view(B, H * W, C)
         for i, blk in enumerate(self.transformer_blocks):
-            t = blk.forward_tokens(t, ctx, None if kvs is None else kvs[i])
+            t = blk.forward_tokens(t, ctx, None if kvs is None else kvs[i], expand=expand if i == 0 else 1)
+        if expand > 1:
+            if len(self.transformer_blocks) == 0:
+                t = t.repeat(expand, 1, 1)
+            x = x.repeat(expand, 1, 1, 1)                    # the residual of proj_out, per copy
+            B = B * expand
         o = ops.gemm(t.view(B * H * W, C), wo, bo, residual=x.view(B * H * W, C), sums_rows=H * W)
         return ops.carry_sums(o, o.view(B, H, W, C))      # the next ResBlock's GroupNorm reads it
 

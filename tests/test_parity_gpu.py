@@ -225,6 +225,32 @@ def test_epilogue_channel_sums_route_vs_goldens(golden, monkeypatch):
     assert ops.sums_counters["tagged"] > before["tagged"] and ops.sums_counters["consumed"] > before["consumed"]
 
 
+def test_cfg_prefix_sharing_equals_evaluating_both_copies(monkeypatch):
+    """Classifier-free guidance feeds the UNet every latent twice (latent_diffusion.py:53 `torch.cat([x] * 2)`); the two
+    copies differ only in their context, so UNetModel.forward(x_repeat=2) evaluates the layers ahead of the first
+    cross-attention once per latent.  Must equal evaluating both copies (and the materialised `cat`) to fp rounding of
+    the GroupNorm partial-sum order, on the default UNet at config-2 geometry and on a small one."""
+    from stable_diffusion_pytorch_b200.models import unet as unet_mod
+    for cfg, seed, B, H, W in ((cases.DEFAULT, 13, 2, 64, 64), (cases.TINY, 7, 3, 16, 24)):
+        m, _ = build_unet(cfg, seed)
+        x, t, ctx = cases.unet_inputs(cfg, B, H, W, seed)
+        g = torch.Generator().manual_seed(seed)
+        ctx2 = torch.cat([torch.randn(ctx.shape, generator=g), ctx]).to(DEV, torch.bfloat16)     # [uncond | cond]
+        xb, t2 = x.to(DEV, torch.bfloat16), torch.cat([t, t]).to(DEV)
+        with torch.no_grad():
+            monkeypatch.setattr(unet_mod, "_CFG_SHARE", True)
+            shared = m(xb, t2, ctx2, x_repeat=2)
+            monkeypatch.setattr(unet_mod, "_CFG_SHARE", False)
+            both = m(xb, t2, ctx2, x_repeat=2)
+            cat = m(torch.cat([xb, xb]), t2, ctx2)
+        assert tuple(shared.shape) == (2 * B, cfg.latent_channels, H, W)
+        assert torch.equal(both, cat)
+        e = rel_l2(shared.float(), both.float())
+        print(f"cfg prefix sharing, {H}x{W}: rel-L2 vs both copies {e:.2e}")
+        assert e < 2e-3
+        assert float((shared[:B] - shared[B:]).abs().max()) > 0      # the halves do see different contexts
+
+
 # ---------------------------------------------------------------- ragged shapes / edge cases
 @pytest.mark.parametrize("B,H,W,ctx_len", [
     (1, 8, 8, 77),       # smallest latent the reference runs at (64 px / 8)
