@@ -450,6 +450,25 @@ gn_coop_kernel(const GnCoopParams p) {
       if (c < p.C1) { base = p.x1 + (long long)b * p.hw * p.C1 + c; pitch = p.C1; }
       else { base = p.x2 + (long long)b * p.hw * p.C2 + (c - p.C1); pitch = p.C2; }
       long long px = p0 + r;
+      // eight 16-byte loads in flight per thread: with two 256-thread CTAs per SM the statistics pass is bound by the
+      // bytes in flight (4 loads: 30 KB per SM against the ~66 KB that the HBM rate x latency asks for)
+      for (; px + 7LL * R < p1; px += 8LL * R) {
+        uint4 q[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) q[i] = __ldg(reinterpret_cast<const uint4*>(base + (px + (long long)i * R) * pitch));
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const uint32_t w[4] = {q[i].x, q[i].y, q[i].z, q[i].w};
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float lo = __uint_as_float(w[j] << 16), hi = __uint_as_float(w[j] & 0xffff0000u);
+            s[2 * j] += lo;
+            s[2 * j + 1] += hi;
+            ss[2 * j] = fmaf(lo, lo, ss[2 * j]);
+            ss[2 * j + 1] = fmaf(hi, hi, ss[2 * j + 1]);
+          }
+        }
+      }
       for (; px + 3LL * R < p1; px += 4LL * R) {
         float v0[8], v1[8], v2[8], v3[8];
         Vec8<__nv_bfloat16>::load(base + px * pitch, v0);
